@@ -1,0 +1,262 @@
+// tcgen05 / TMEM / TMA GEMM core for the online learners (sm_100a only).
+//
+// Two operand arrangements, both fp32 in global memory and consumed by the tensor core as tf32
+// with fp32 accumulation in TMEM:
+//
+//   gemm_tn   : C[M,N] (+)= A[M,K] * B[N,K]^T      (both operands K-major; "scores" shape:
+//               X W^T for MultiClassPA / NN forward, X C^T for k-means distances)
+//   gemm_outer: C[M,N] (+)= A[K,M]^T * B[K,N]      (both operands MN-major; "outer-product" shape:
+//               Z^T Z Gram for ridge regression, T^T X for MultiClassPA / k-means / NN updates;
+//               K is the mini-batch axis so records are consumed exactly as they sit in the
+//               staged ring slot, no transpose pass)
+//
+// Replaces the per-record Breeze `Double` arithmetic behind `node.receiveTuple`
+// (reference call site: src/main/scala/omldm/operators/spoke/FlinkSpoke.scala:101); the
+// reference has no GEMM of its own.
+//
+// Structure: one CTA = one 128 x BN output tile x one K split.  Warp 0 = TMA producer,
+// warp 1 = TMEM allocator + single-thread tcgen05.mma issuer, warps 2..5 = epilogue
+// (tcgen05.ld -> registers -> st / red.add.v4 to global).  4-stage smem ring, mbarrier
+// full/empty pairs, tcgen05.commit releases stages and publishes the accumulator.
+#include "ptx.cuh"
+#include "host_common.h"
+
+namespace omldm {
+
+constexpr int BM = 128;
+constexpr int BK = 32;  // tf32 elements per stage along K (= one 128-byte swizzle row)
+constexpr int STAGES = 4;
+constexpr int GEMM_THREADS = 192;
+
+enum : int { GEMM_ACCUMULATE = 1, GEMM_UPPER_ONLY = 2 };
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int A_BYTES = BM * BK * 4;
+  static constexpr int B_BYTES = BN * BK * 4;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, bool MN_MAJOR>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 float* __restrict__ C, int ldc, int M, int N, int K, int k_per_split, int flags) {
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  if ((flags & GEMM_UPPER_ONLY) && m0 > n0 + BN - 1) return;  // tile strictly below the diagonal
+  const int k_begin = blockIdx.z * k_per_split;
+  const int k_end = min(K, k_begin + k_per_split);
+  const int num_kb = (k_end - k_begin + BK - 1) / BK;
+  if (num_kb <= 0) return;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  using S = GemmSmem<BN>;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * S::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* accum_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(accum_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * S::STAGE_BYTES;
+        uint8_t* sb = sa + S::A_BYTES;
+        mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+        const int k0 = k_begin + kb * BK;
+        if constexpr (MN_MAJOR) {
+          tma_load_3d(sa, &tmA, &full_bar[stage], 0, k0, m0 / 32);
+          tma_load_3d(sb, &tmB, &full_bar[stage], 0, k0, n0 / 32);
+        } else {
+          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+        }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = make_idesc_tf32(BM, BN, MN_MAJOR, MN_MAJOR);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; ++kb) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sa = smem_u32(smem + stage * S::STAGE_BYTES);
+        const uint32_t sb = sa + S::A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < BK / 8; ++kk) {
+          uint64_t da, db;
+          if constexpr (MN_MAJOR) {
+            // K advance = 8 rows of 128 B; MN atoms (32 floats) are BK*128 B apart.
+            da = make_smem_desc_sw128(sa + kk * 1024, BK * 128, 1024);
+            db = make_smem_desc_sw128(sb + kk * 1024, BK * 128, 1024);
+          } else {
+            // K advance = 8 tf32 = 32 B inside the 128-B swizzle row; 8-row groups 1024 B apart.
+            da = make_smem_desc_sw128(sa + kk * 32, 16, 1024);
+            db = make_smem_desc_sw128(sb + kk * 32, 16, 1024);
+          }
+          umma_tf32(tmem_base, da, db, idesc, (kb | kk) != 0);
+        }
+        umma_commit(&empty_bar[stage]);                 // frees this smem stage when MMAs retire
+        if (kb == num_kb - 1) umma_commit(accum_bar);   // accumulator complete
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue (warps 2..5)
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    mbar_wait(accum_bar, 0);
+    tc_fence_after();
+    const int row = m0 + q * 32 + static_cast<int>(lane_id());
+    const bool accumulate = (flags & GEMM_ACCUMULATE) != 0;
+    const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      float v[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
+      tmem_ld_wait();
+      if (row < M) {
+        const int col0 = n0 + c * 32;
+        float* dst = C + static_cast<size_t>(row) * ldc + col0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          if (vec_ok && col0 + j + 3 < N) {
+            if (accumulate) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+            else *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              if (col0 + j + t < N) {
+                if (accumulate) atomicAdd(dst + j + t, v[j + t]);
+                else dst[j + t] = v[j + t];
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+static int encode_kmajor(CUtensorMap* tm, const float* base, int rows, int k, int ld, int box_rows) {
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(k), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims,
+                          strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+static int encode_mnmajor(CUtensorMap* tm, const float* base, int k_rows, int ld, int box_chunks) {
+  // view [k_rows, ld] row-major as {32 floats, k_rows, ld/32 chunks}; one box = box_chunks slabs
+  // of (BK rows x 128 B), which is exactly the MN-major SWIZZLE_128B canonical layout.
+  cuuint64_t dims[3] = {32, static_cast<cuuint64_t>(k_rows), static_cast<cuuint64_t>(ld / 32)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 4, 128};
+  cuuint32_t box[3] = {32, static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_chunks)};
+  cuuint32_t estr[3] = {1, 1, 1};
+  return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims,
+                          strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+template <int BN, bool MN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, float* C, int ldc, int M,
+                       int N, int K, int ksplit, int flags, cudaStream_t stream) {
+  static bool attr_set[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto kern = umma_gemm_kernel<BN, MN>;
+  constexpr int smem = GemmSmem<BN>::TOTAL;
+  if (!attr_set[dev & 15]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm)", e);
+    attr_set[dev & 15] = true;
+  }
+  if (ksplit < 1) ksplit = 1;
+  int k_per_split = ((K + ksplit - 1) / ksplit + BK - 1) / BK * BK;
+  dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, (K + k_per_split - 1) / k_per_split);
+  kern<<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, C, ldc, M, N, K, k_per_split, flags);
+  return check_launch("umma_gemm_kernel");
+}
+
+template <bool MN>
+static int dispatch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, int bn, float* C, int ldc,
+                       int M, int N, int K, int ksplit, int flags, cudaStream_t stream) {
+  switch (bn) {
+    case 32: return launch_gemm<32, MN>(tmA, tmB, C, ldc, M, N, K, ksplit, flags, stream);
+    case 64: return launch_gemm<64, MN>(tmA, tmB, C, ldc, M, N, K, ksplit, flags, stream);
+    case 128: return launch_gemm<128, MN>(tmA, tmB, C, ldc, M, N, K, ksplit, flags, stream);
+    default: return launch_gemm<256, MN>(tmA, tmB, C, ldc, M, N, K, ksplit, flags, stream);
+  }
+}
+static int pick_bn(int N) { return N <= 32 ? 32 : N <= 64 ? 64 : N <= 128 ? 128 : 256; }
+
+}  // namespace omldm
+
+using namespace omldm;
+
+extern "C" int omldm_gemm_tn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                             int M, int N, int K, int ksplit, int flags, void* stream) {
+  if ((lda & 3) || (ldb & 3)) return set_error_msg("gemm_tn: lda/ldb must be multiples of 4 floats");
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15))
+    return set_error_msg("gemm_tn: operands must be 16-byte aligned");
+  if (ksplit > 1 && !(flags & GEMM_ACCUMULATE))
+    return set_error_msg("gemm_tn: split-K requires the accumulate flag");
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB;
+  if (encode_kmajor(&tmA, A, M, K, lda, BM)) return -1;
+  if (encode_kmajor(&tmB, B, N, K, ldb, bn)) return -1;
+  return dispatch_bn<false>(tmA, tmB, bn, C, ldc, M, N, K, ksplit, flags,
+                            static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                                int M, int N, int K, int ksplit, int flags, void* stream) {
+  if ((lda & 31) || (ldb & 31))
+    return set_error_msg("gemm_outer: lda/ldb must be multiples of 32 floats (padded record rows)");
+  if ((reinterpret_cast<uintptr_t>(A) & 127) || (reinterpret_cast<uintptr_t>(B) & 127))
+    return set_error_msg("gemm_outer: operands must be 128-byte aligned");
+  if (M > lda || N > ldb) return set_error_msg("gemm_outer: M/N exceed the row pitch");
+  if (ksplit > 1 && !(flags & GEMM_ACCUMULATE))
+    return set_error_msg("gemm_outer: split-K requires the accumulate flag");
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB;
+  if (encode_mnmajor(&tmA, A, K, lda, BM / 32)) return -1;
+  if (encode_mnmajor(&tmB, B, K, ldb, bn / 32)) return -1;
+  return dispatch_bn<true>(tmA, tmB, bn, C, ldc, M, N, K, ksplit, flags,
+                           static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,99 @@
+"""ctypes loader for the in-tree native libraries.
+
+`libomldm_kernels.so` exposes an `extern "C"` ABI (declared in `include/omldm_kernels.h`) that
+takes raw device pointers and a `cudaStream_t`; Python hands it `tensor.data_ptr()` and the
+current torch stream.  There is deliberately no silent fallback on a GPU machine: if CUDA is
+available and the library cannot be loaded, every op raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+
+import torch
+
+_LIBDIR = Path(__file__).resolve().parents[1] / "lib"
+_kernels = None
+_host = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _try_build() -> None:
+    if os.environ.get("OMLDM_NO_AUTOBUILD"):
+        return
+    try:
+        from . import build
+
+        build.build_all()
+    except Exception as e:  # pragma: no cover - reported by the caller
+        raise NativeError(f"building the native libraries failed: {e}") from e
+
+
+def kernels() -> ctypes.CDLL:
+    """The CUDA kernel library (requires a CUDA runtime to be loadable)."""
+    global _kernels
+    if _kernels is None:
+        path = _LIBDIR / "libomldm_kernels.so"
+        if not path.exists():
+            _try_build()
+        if not path.exists():
+            raise NativeError(f"{path} is missing; run `python -m omldm_b200.ops.build`")
+        try:
+            _kernels = ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
+        except OSError as e:
+            raise NativeError(f"cannot load {path}: {e}") from e
+        _kernels.omldm_last_error.restype = ctypes.c_char_p
+        _kernels.omldm_launch_count.restype = ctypes.c_longlong
+    return _kernels
+
+
+def host() -> ctypes.CDLL:
+    """The host runtime library (ring buffers, record parser); no CUDA dependency."""
+    global _host
+    if _host is None:
+        path = _LIBDIR / "libomldm_host.so"
+        if not path.exists():
+            _try_build()
+        if not path.exists():
+            raise NativeError(f"{path} is missing; run `python -m omldm_b200.ops.build`")
+        _host = ctypes.CDLL(str(path))
+    return _host
+
+
+def have_cuda() -> bool:
+    return torch.cuda.is_available()
+
+
+def use_native(*tensors: torch.Tensor) -> bool:
+    """True when the tensors live on a GPU (then the native path is mandatory)."""
+    return any(t is not None and t.is_cuda for t in tensors)
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = kernels().omldm_last_error().decode(errors="replace")
+        raise NativeError(f"{what} failed: {msg}")
+
+
+def stream_ptr() -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t: torch.Tensor | None) -> ctypes.c_void_p:
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def launch_count() -> int:
+    """Number of kernels this library has launched since the last reset (0 on CPU-only hosts)."""
+    if not have_cuda():
+        return 0
+    return int(kernels().omldm_launch_count())
+
+
+def reset_launch_count() -> None:
+    if have_cuda():
+        kernels().omldm_reset_launch_count()
