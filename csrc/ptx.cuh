@@ -154,14 +154,17 @@ __device__ __forceinline__ void tmem_ld_wait() {
 //   K-major : SBO = byte stride between 8-row groups (1024 for dense 128-B rows); LBO unused.
 //   MN-major: LBO = byte stride between 128-byte MN atoms (one TMA slab), SBO = byte stride
 //             between 8-row K groups (1024 for dense 128-B rows).
+//   MN-major fp32/tf32 operands must use the 32-byte-atom flavour (layout type 1,
+//   SWIZZLE_128B_BASE32B == TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): 4-row K groups, SBO = 512.
 __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes,
-                                                         uint32_t sbo_bytes) {
+                                                         uint32_t sbo_bytes,
+                                                         uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((saddr & 0x3FFFF) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= static_cast<uint64_t>(1) << 46;  // descriptor version (sm_100)
-  d |= static_cast<uint64_t>(2) << 61;  // SWIZZLE_128B
+  d |= static_cast<uint64_t>(layout_type) << 61;  // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B
   return d;
 }
 // Instruction descriptor for kind::tf32, fp32 accumulate, M x N tile.

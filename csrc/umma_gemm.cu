@@ -28,7 +28,7 @@ constexpr int BK = 32;  // tf32 elements per stage along K (= one 128-byte swizz
 constexpr int STAGES = 4;
 constexpr int GEMM_THREADS = 192;
 
-enum : int { GEMM_ACCUMULATE = 1, GEMM_UPPER_ONLY = 2 };
+enum : int { GEMM_ACCUMULATE = 1, GEMM_UPPER_ONLY = 2, GEMM_MN_SLAB2D = 4 };
 
 template <int BN>
 struct GemmSmem {
@@ -78,7 +78,29 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  if (warp == 0 && MN_MAJOR && (flags & GEMM_MN_SLAB2D)) {
+    // ------------------------------------------------------------ TMA producer, one 2-D box per
+    // 32-float slab (lane l loads slab l): A has BM/32 slabs, B has BN/32.
+    constexpr int A_SLABS = BM / 32, B_SLABS = BN / 32;
+    const int l = static_cast<int>(lane_id());
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; ++kb) {
+      if (l == 0) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+      }
+      __syncwarp();
+      uint8_t* sa = smem + stage * S::STAGE_BYTES;
+      uint8_t* sb = sa + S::A_BYTES;
+      const int k0 = k_begin + kb * BK;
+      if (l < A_SLABS) tma_load_2d(sa + l * (BK * 128), &tmA, &full_bar[stage], m0 + l * 32, k0);
+      else if (l < A_SLABS + B_SLABS)
+        tma_load_2d(sb + (l - A_SLABS) * (BK * 128), &tmB, &full_bar[stage], n0 + (l - A_SLABS) * 32, k0);
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
       int stage = 0;
@@ -115,8 +137,9 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint64_t da, db;
           if constexpr (MN_MAJOR) {
             // K advance = 8 rows of 128 B; MN atoms (32 floats) are BK*128 B apart.
-            da = make_smem_desc_sw128(sa + kk * 1024, BK * 128, 1024);
-            db = make_smem_desc_sw128(sb + kk * 1024, BK * 128, 1024);
+            // 32-byte-atom swizzle: K groups are 4 rows (512 B) apart.
+            da = make_smem_desc_sw128(sa + kk * 1024, BK * 128, 512, 1);
+            db = make_smem_desc_sw128(sb + kk * 1024, BK * 128, 512, 1);
           } else {
             // K advance = 8 tf32 = 32 B inside the 128-B swizzle row; 8-row groups 1024 B apart.
             da = make_smem_desc_sw128(sa + kk * 32, 16, 1024);
@@ -182,15 +205,23 @@ static int encode_kmajor(CUtensorMap* tm, const float* base, int rows, int k, in
   return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims,
                           strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B);
 }
+static int encode_mnmajor_2d(CUtensorMap* tm, const float* base, int k_rows, int ld) {
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(k_rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {32, static_cast<cuuint32_t>(BK)};
+  cuuint32_t estr[2] = {1, 1};
+  return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims,
+                          strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+}
 static int encode_mnmajor(CUtensorMap* tm, const float* base, int k_rows, int ld, int box_chunks) {
   // view [k_rows, ld] row-major as {32 floats, k_rows, ld/32 chunks}; one box = box_chunks slabs
-  // of (BK rows x 128 B), which is exactly the MN-major SWIZZLE_128B canonical layout.
+  // of (BK rows x 128 B), which is exactly the MN-major SWIZZLE_128B_BASE32B canonical layout.
   cuuint64_t dims[3] = {32, static_cast<cuuint64_t>(k_rows), static_cast<cuuint64_t>(ld / 32)};
   cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 4, 128};
   cuuint32_t box[3] = {32, static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_chunks)};
   cuuint32_t estr[3] = {1, 1, 1};
   return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims,
-                          strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B);
+                          strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
 }
 
 template <int BN, bool MN>
@@ -255,8 +286,13 @@ extern "C" int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb
     return set_error_msg("gemm_outer: split-K requires the accumulate flag");
   const int bn = pick_bn(N);
   CUtensorMap tmA, tmB;
-  if (encode_mnmajor(&tmA, A, K, lda, BM / 32)) return -1;
-  if (encode_mnmajor(&tmB, B, K, ldb, bn / 32)) return -1;
+  if (flags & GEMM_MN_SLAB2D) {
+    if (encode_mnmajor_2d(&tmA, A, K, lda)) return -1;
+    if (encode_mnmajor_2d(&tmB, B, K, ldb)) return -1;
+  } else {
+    if (encode_mnmajor(&tmA, A, K, lda, BM / 32)) return -1;
+    if (encode_mnmajor(&tmB, B, K, ldb, bn / 32)) return -1;
+  }
   return dispatch_bn<true>(tmA, tmB, bn, C, ldc, M, N, K, ksplit, flags,
                            static_cast<cudaStream_t>(stream));
 }

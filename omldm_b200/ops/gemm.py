@@ -16,6 +16,7 @@ from . import _lib
 
 ACCUMULATE = 1
 UPPER_ONLY = 2
+MN_SLAB2D = 4
 
 
 def _check2d(t: torch.Tensor, name: str) -> None:
@@ -76,6 +77,9 @@ def gemm_outer(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None
         out[:M, :N].add_(r) if accumulate_eff else out[:M, :N].copy_(r)
         return out
     flags = (ACCUMULATE if (accumulate_eff or ksplit > 1) else 0) | (UPPER_ONLY if upper_only else 0)
+    import os
+    if os.environ.get('OMLDM_MN_LOAD', '3d') == '2d':
+        flags |= MN_SLAB2D
     if ksplit > 1 and not accumulate_eff:
         out.zero_()
     rc = _lib.kernels().omldm_gemm_outer(
