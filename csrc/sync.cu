@@ -1,0 +1,547 @@
+// Fused worker<->hub synchronisation kernels over NVLink peer memory (sm_100a).
+//
+// The reference moves every model between workers ("spokes") and parameter-server shards
+// ("hubs") as serialized messages: spoke->hub through a Flink keyBy shuffle
+// (network/FlinkNetwork.scala:260-261,279-281) and hub->spoke through a Kafka topic used as a
+// feedback edge (Job.scala:77-87,136-142; FlinkNetwork.scala:262-271,282-291).  Here every GPU
+// is one worker and one hub shard; buffers live in symmetric (peer-mapped) memory and ONE kernel
+// per protocol step does reduce-scatter + averaging + all-gather (+ safe-zone check) with
+// in-kernel peer loads/stores or NVLS multimem instructions.  No NCCL on this path.
+//
+// Cross-GPU ordering: data is written with plain/relaxed.sys stores, then
+// __threadfence_system(), then a flag is published with st.release.sys; consumers poll with
+// ld.acquire.sys.  All spin loops are bounded and record a timeout in the status word instead
+// of hanging the GPU.
+#include "ptx.cuh"
+#include "host_common.h"
+#include "omldm_kernels.h"
+#include <cstring>
+
+namespace omldm {
+
+struct Comm {
+  float* const* bufs;
+  float* const* hubs;
+  uint32_t* const* pads;
+  uint32_t* local;
+  float* mc_buf;
+  int rank, world, emulate;
+};
+
+constexpr int LOCAL_WORDS = 64;  // private scratch words per (emulated) rank
+// local scratch word indices
+enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4 };
+
+__device__ __forceinline__ int my_rank(const Comm& c) { return c.emulate > 1 ? static_cast<int>(blockIdx.y) : c.rank; }
+__device__ __forceinline__ uint32_t* my_local(const Comm& c) { return c.local + my_rank(c) * LOCAL_WORDS; }
+
+constexpr uint32_t SPIN_LIMIT = 1u << 26;
+
+__device__ __forceinline__ void flag_timeout(const Comm& c, int me, uint32_t code) {
+  atomicOr(reinterpret_cast<unsigned int*>(c.pads[me] + OMLDM_PAD_STATUS), code);
+}
+
+// thread t < world publishes `seq` into slot base+me of peer t's pad
+__device__ __forceinline__ void signal_all(const Comm& c, int me, int base, uint32_t seq) {
+  if (threadIdx.x < c.world) st_release_sys(c.pads[threadIdx.x] + base + me, seq);
+}
+// every thread t < world waits for slot base+t of the own pad to reach seq; block-wide result
+__device__ __forceinline__ void wait_all(const Comm& c, int me, int base, uint32_t seq) {
+  if (threadIdx.x < c.world) {
+    const uint32_t* p = c.pads[me] + base + threadIdx.x;
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(p) - seq) < 0) {
+      if (++spins > 64) __nanosleep(spins > 4096 ? 256 : 32);
+      if (spins > SPIN_LIMIT) { flag_timeout(c, me, 1u); break; }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 f4_add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float4 f4_scale(float4 a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
+
+__device__ __forceinline__ float4 mc_ld_reduce(const float* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void mc_st(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ float4 atom_add_sys_v4(float* a, float4 v) {
+  float4 r;
+  asm volatile("atom.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4], {%5,%6,%7,%8};"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------
+// Phase: owner-side reduce of this rank's shard over all peers and write-back to all peers.
+// n4 = number of float4 elements.  Shards are contiguous: shard r = [r*per, min(n4,(r+1)*per)).
+__device__ __forceinline__ void reduce_and_broadcast_shard(const Comm& c, int me, size_t n4, float scale) {
+  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t lo = per * me, hi = lo + per < n4 ? lo + per : n4;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  if (c.mc_buf != nullptr && c.emulate <= 1) {
+    for (size_t i = lo + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
+      float4 acc = mc_ld_reduce(c.mc_buf + 4 * i);  // switch-side sum over all ranks
+      mc_st(c.mc_buf + 4 * i, f4_scale(acc, scale));  // switch multicast to all ranks
+    }
+    return;
+  }
+  for (size_t i = lo + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
+    float4 v[16];
+#pragma unroll
+    for (int p = 0; p < 16; ++p)
+      if (p < c.world) v[p] = ld_peer_v4(reinterpret_cast<const float4*>(c.bufs[p]) + i);
+    float4 acc = v[0];
+#pragma unroll
+    for (int p = 1; p < 16; ++p)
+      if (p < c.world) acc = f4_add(acc, v[p]);
+    acc = f4_scale(acc, scale);
+#pragma unroll
+    for (int p = 0; p < 16; ++p)
+      if (p < c.world) st_peer_v4(reinterpret_cast<float4*>(c.bufs[p]) + i, acc);
+  }
+}
+
+// grid-wide "all blocks of this rank finished": returns true in exactly one (the last) block
+__device__ __forceinline__ bool grid_done(uint32_t* counter) {
+  __shared__ bool s_last;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(counter, 1u);
+    s_last = (prev == gridDim.x - 1);
+    if (s_last) *counter = 0;  // self-reset for the next launch
+  }
+  __syncthreads();
+  return s_last;
+}
+
+// grid-wide sum of squares of (buf - e); every block adds its partial to *acc (float bits)
+__device__ __forceinline__ void partial_sqdist(const float* buf, const float* e, size_t n, float* acc) {
+  float s = 0.f;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += stride) {
+    const float d = buf[i] - (e ? e[i] : 0.f);
+    s = fmaf(d, d, s);
+  }
+  __shared__ float sh[32];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < (blockDim.x >> 5); ++i) t += sh[i];
+    atomicAdd(acc, t);
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void local_tail(float* buf, float* e, size_t n, int mode) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t n4 = n / 4;
+  float4* b4 = reinterpret_cast<float4*>(buf);
+  float4* e4 = reinterpret_cast<float4*>(e);
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    // buf was written by peers: read it through the coherent path
+    const float4 b = ld_peer_v4(b4 + i);
+    if (mode == 0) {
+      if (e) e4[i] = b;
+    } else {
+      e4[i] = f4_add(e4[i], b);
+      b4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Synchronous / GM kernel.  gm_threshold < 0: plain synchronous allreduce.
+// gm_threshold >= 0: each rank first votes ||buf - e||^2 > threshold; the vote travels with the
+// entry barrier and the allreduce only happens if any rank voted "violated".
+__global__ void __launch_bounds__(256)
+sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode,
+                      uint32_t epoch, float gm_threshold) {
+  const int me = my_rank(c);
+  uint32_t* loc = my_local(c);
+  float* buf = c.bufs[me];
+  float* e = e_base ? e_base + e_stride * (c.emulate > 1 ? me : 0) : nullptr;
+  const uint32_t seq_entry = 2 * epoch + 1, seq_exit = 2 * epoch + 2;
+
+  if (gm_threshold >= 0.f) {
+    partial_sqdist(buf, e, n, reinterpret_cast<float*>(loc + L_NORM));
+    if (grid_done(loc + L_DONE2)) {
+      const float nrm2 = __ldcg(reinterpret_cast<float*>(loc + L_NORM));
+      loc[L_NORM] = 0;
+      const uint32_t vote = 2 * epoch + (nrm2 > gm_threshold ? 1u : 0u);
+      if (threadIdx.x < c.world) {
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[threadIdx.x] + OMLDM_PAD_VOTE + me), "r"(vote) : "memory");
+      }
+      __threadfence_system();
+      __syncthreads();
+      signal_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+    }
+  } else if (blockIdx.x == 0) {
+    signal_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+  }
+  wait_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+
+  if (gm_threshold >= 0.f) {
+    __shared__ int s_any;
+    if (threadIdx.x == 0) s_any = 0;
+    __syncthreads();
+    if (threadIdx.x < c.world) {
+      const uint32_t v = ld_acquire_sys(c.pads[me] + OMLDM_PAD_VOTE + threadIdx.x);
+      if (v == 2 * epoch + 1) atomicOr(&s_any, 1);
+    }
+    __syncthreads();
+    if (!s_any) return;  // every rank sees the same votes, so every rank returns here together
+  }
+
+  reduce_and_broadcast_shard(c, me, n / 4, scale);
+  if (grid_done(loc + L_DONE)) signal_all(c, me, OMLDM_PAD_EXIT, seq_exit);
+  wait_all(c, me, OMLDM_PAD_EXIT, seq_exit);
+  local_tail(buf, e, n, mode);
+}
+
+// ------------------------------------------------------------------------------------------
+// Asynchronous / SSP: one worker pushes scale*(buf - e) into the owning hub shards with
+// returning vector atomics and installs the fresh hub value locally.  No rendezvous.
+__global__ void __launch_bounds__(256)
+sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int ssp, uint32_t clock,
+                  int staleness) {
+  const int me = my_rank(c);
+  uint32_t* loc = my_local(c);
+  float4* b4 = reinterpret_cast<float4*>(c.bufs[me]);
+  float4* e4 = reinterpret_cast<float4*>(e_base + e_stride * (c.emulate > 1 ? me : 0));
+  const size_t n4 = n / 4;
+  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    const int owner = static_cast<int>(i / per);
+    const float4 w = b4[i], e = e4[i];
+    const float4 d = make_float4(scale * (w.x - e.x), scale * (w.y - e.y), scale * (w.z - e.z), scale * (w.w - e.w));
+    const float4 old = atom_add_sys_v4(c.hubs[owner] + 4 * i, d);
+    const float4 nv = f4_add(old, d);
+    b4[i] = nv;
+    e4[i] = nv;
+  }
+  if (!ssp) return;
+  if (grid_done(loc + L_DONE3)) {
+    signal_all(c, me, OMLDM_PAD_CLOCK, clock);
+    // stale-synchronous wait: nobody may be more than `staleness` clocks behind me
+    if (threadIdx.x < c.world) {
+      const uint32_t* p = c.pads[me] + OMLDM_PAD_CLOCK + threadIdx.x;
+      uint32_t spins = 0;
+      while (static_cast<int32_t>(ld_acquire_sys(p) + static_cast<uint32_t>(staleness) - clock) < 0) {
+        if (++spins > 64) __nanosleep(spins > 4096 ? 256 : 32);
+        if (spins > SPIN_LIMIT) { flag_timeout(c, me, 2u); break; }
+      }
+    }
+  }
+}
+
+// EASGD: x_i -= alpha (x_i - x~);  x~ += alpha (x_i - x~), x~ sharded over the hubs.
+__global__ void __launch_bounds__(256) sync_easgd_kernel(Comm c, size_t n, float alpha) {
+  const int me = my_rank(c);
+  float4* b4 = reinterpret_cast<float4*>(c.bufs[me]);
+  const size_t n4 = n / 4;
+  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    const int owner = static_cast<int>(i / per);
+    float* h = c.hubs[owner] + 4 * i;
+    const float4 x = b4[i];
+    const float4 t = ld_peer_v4(reinterpret_cast<const float4*>(h));
+    const float4 d = make_float4(alpha * (x.x - t.x), alpha * (x.y - t.y), alpha * (x.z - t.z), alpha * (x.w - t.w));
+    b4[i] = make_float4(x.x - d.x, x.y - d.y, x.z - d.z, x.w - d.w);
+    red_add_sys_v4(h, d);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// FGM (functional geometric monitoring), one launch per mini-batch and rank.
+//   safe function  phi(D) = ||D|| - sqrt(T),  D = buf - e  (convex; phi(mean D) <= mean phi(D_i))
+//   round          psi0 = k*phi(0); quantum theta = -psi/(2k); local counter c_i = floor((phi_i - zeta_i)/theta)
+//   sub-round end  when the hub's global counter exceeds k it sums the published phi_i into psi;
+//                  psi >= eps_psi * k * phi(0) ends the round (allreduce + reset), otherwise a new
+//                  sub-round starts with the smaller quantum.
+// Hub = rank 0's pad.  FGM words: [0] counter(s32) [1] subround id [2] theta bits [3] round id.
+// state_local (float[8], private): [0] round id [1] subround seen [2] zeta [3] counts sent [4] rounds [5] subrounds
+__global__ void __launch_bounds__(256)
+sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, float threshold, float eps_psi,
+                uint32_t step, float* state_base) {
+  const int me = my_rank(c);
+  const int k = c.world;
+  uint32_t* loc = my_local(c);
+  float* buf = c.bufs[me];
+  float* e = e_base + e_stride * (c.emulate > 1 ? me : 0);
+  float* st = state_base + 8 * (c.emulate > 1 ? me : 0);
+  uint32_t* hub = c.pads[0] + OMLDM_PAD_FGM;
+  const float phi0 = -sqrtf(threshold);
+
+  partial_sqdist(buf, e, n, reinterpret_cast<float*>(loc + L_NORM));
+  if (grid_done(loc + L_DONE2)) {
+    if (threadIdx.x == 0) {
+      const float nrm2 = __ldcg(reinterpret_cast<float*>(loc + L_NORM));
+      loc[L_NORM] = 0;
+      const float phi = sqrtf(nrm2) + phi0;
+      uint32_t round = static_cast<uint32_t>(st[0]);
+      // publish phi to the hub (push-based polling)
+      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + me), "r"(__float_as_uint(phi)) : "memory");
+      const uint32_t sub = ld_acquire_sys(hub + 1);
+      float theta = __uint_as_float(ld_relaxed_sys(hub + 2));
+      if (theta <= 0.f) theta = -phi0 / 2.f;  // first sub-round of the very first round
+      if (static_cast<uint32_t>(st[1]) != sub) {  // new sub-round: re-anchor
+        st[1] = static_cast<float>(sub);
+        st[2] = phi;
+        st[3] = 0.f;
+      }
+      const int ci = max(static_cast<int>(st[3]), static_cast<int>(floorf((phi - st[2]) / theta)));
+      const int inc = ci - static_cast<int>(st[3]);
+      if (inc > 0) {
+        atom_add_relaxed_sys_s32(reinterpret_cast<int32_t*>(hub), inc);
+        st[3] = static_cast<float>(ci);
+      }
+      if (me == 0) {
+        // hub logic
+        const int counter = static_cast<int>(ld_relaxed_sys(hub));
+        const uint32_t hub_round = ld_relaxed_sys(hub + 3);
+        if (counter > k && hub_round == round) {
+          float psi = 0.f;
+          for (int i = 0; i < k; ++i) psi += __uint_as_float(ld_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + i));
+          if (psi >= eps_psi * k * phi0) {
+            for (int p = 0; p < k; ++p) st_release_sys(c.pads[p] + OMLDM_PAD_FGM + 3, round + 1);  // round end
+          } else {
+            asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub + 2), "r"(__float_as_uint(-psi / (2.f * k))) : "memory");
+            asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub), "r"(0u) : "memory");
+            st_release_sys(hub + 1, sub + 1);
+            st[5] += 1.f;
+          }
+        }
+      }
+      const uint32_t seen_round = ld_acquire_sys(c.pads[me] + OMLDM_PAD_FGM + 3);
+      const uint32_t decision = 2 * step + ((seen_round != round) ? 1u : 0u);
+      __threadfence();
+      atomicExch(loc + L_DECISION, decision);
+    }
+  }
+  // every block learns the decision of this step
+  __shared__ uint32_t s_dec;
+  if (threadIdx.x == 0) {
+    uint32_t v, spins = 0;
+    while (((v = atomicAdd(loc + L_DECISION, 0u)) >> 1) != step) {
+      if (++spins > 64) __nanosleep(64);
+      if (spins > SPIN_LIMIT) { flag_timeout(c, me, 4u); v = 2 * step; break; }
+    }
+    s_dec = v & 1u;
+  }
+  __syncthreads();
+  if (!s_dec) return;
+
+  // ---------------- round end: synchronous allreduce keyed by the round number
+  const uint32_t round = static_cast<uint32_t>(st[0]);
+  const uint32_t seq_entry = 2 * round + 1, seq_exit = 2 * round + 2;
+  if (blockIdx.x == 0) signal_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+  wait_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+  reduce_and_broadcast_shard(c, me, n / 4, scale);
+  if (grid_done(loc + L_DONE)) {
+    if (threadIdx.x == 0) {
+      if (me == 0) {  // hub resets the monitoring state for the new round
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub), "r"(0u) : "memory");
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub + 2), "r"(__float_as_uint(-phi0 / 2.f)) : "memory");
+        for (int i = 0; i < k; ++i)
+          asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + i), "r"(__float_as_uint(phi0)) : "memory");
+        const uint32_t sub = ld_relaxed_sys(hub + 1);
+        st_release_sys(hub + 1, sub + 1);
+      }
+    }
+    __syncthreads();
+    __threadfence_system();
+    signal_all(c, me, OMLDM_PAD_EXIT, seq_exit);
+  }
+  wait_all(c, me, OMLDM_PAD_EXIT, seq_exit);
+  local_tail(buf, e, n, 0);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st[0] = static_cast<float>(round + 1);
+    st[1] = -1.f;  // force re-anchoring at the next step
+    st[3] = 0.f;
+    st[4] += 1.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void device_barrier_kernel(Comm c, uint32_t epoch) {
+  const int me = my_rank(c);
+  signal_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
+  wait_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
+  signal_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
+  wait_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
+}
+
+// Each rank scatters its 4 query scalars into every peer's pad, barrier, then sums locally.
+__global__ void query_reduce_kernel(Comm c, const float* vals_base, float* out_base, uint32_t epoch) {
+  const int me = my_rank(c);
+  const float* vals = vals_base + 4 * (c.emulate > 1 ? me : 0);
+  float* out = out_base + 4 * (c.emulate > 1 ? me : 0);
+  if (threadIdx.x < c.world * 4) {
+    const int p = threadIdx.x / 4, j = threadIdx.x % 4;
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[p] + OMLDM_PAD_QUERY + 4 * me + j), "r"(__float_as_uint(vals[j])) : "memory");
+  }
+  __threadfence_system();
+  __syncthreads();
+  signal_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
+  wait_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
+  if (threadIdx.x < 4) {
+    float s = 0.f;
+    for (int p = 0; p < c.world; ++p) s += __uint_as_float(ld_acquire_sys(c.pads[me] + OMLDM_PAD_QUERY + 4 * p + threadIdx.x));
+    out[threadIdx.x] = s;
+  }
+  __syncthreads();
+  signal_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
+  wait_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
+}
+
+static Comm to_comm(const omldm_comm* h) {
+  Comm c;
+  c.bufs = h->bufs; c.hubs = h->hubs; c.pads = h->pads; c.local = h->local; c.mc_buf = h->mc_buf;
+  c.rank = h->rank; c.world = h->world; c.emulate = h->emulate;
+  return c;
+}
+static int clamp_blocks(int blocks, size_t n, int emulate) {
+  int maxb = emulate > 1 ? (148 / emulate) : 148;
+  if (maxb < 1) maxb = 1;
+  int need = static_cast<int>((n / 4 + 255) / 256);
+  if (need < 1) need = 1;
+  if (blocks <= 0) blocks = need < 64 ? need : 64;
+  if (blocks > maxb) blocks = maxb;
+  return blocks;
+}
+// kernels whose blocks wait on one another must be co-resident: cooperative launch
+template <typename... Args>
+static int launch_coop(void (*kern)(Args...), dim3 grid, dim3 block, cudaStream_t st, const char* name, Args... args) {
+  void* params[] = {(void*)&args...};
+  cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kern), grid, block, params, 0, st);
+  if (e != cudaSuccess) return set_error(name, e);
+  count_launch(1);
+  return 0;
+}
+
+}  // namespace omldm
+
+using namespace omldm;
+
+static int check_world(const omldm_comm* h, size_t n) {
+  if (h->world < 1 || h->world > 16) return set_error_msg("comm: world must be in [1,16]");
+  if (n % 4) return set_error_msg("comm: element count must be a multiple of 4 (pad the model vector)");
+  return 0;
+}
+
+extern "C" int omldm_sync_allreduce(const omldm_comm* h, float* e_local, size_t n, float scale, int mode,
+                                    uint32_t epoch, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n / h->world, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_allreduce_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_allreduce_kernel",
+                     c, e_local, n, n, scale, mode, epoch, -1.0f);
+}
+
+extern "C" int omldm_sync_gm(const omldm_comm* h, float* e_local, size_t n, float scale, float threshold,
+                             uint32_t epoch, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  if (!e_local) return set_error_msg("sync_gm: the estimate vector e is required");
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n / h->world, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_allreduce_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_gm_kernel",
+                     c, e_local, n, n, scale, 0, epoch, threshold);
+}
+
+extern "C" int omldm_sync_async(const omldm_comm* h, float* e_local, size_t n, float scale, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  sync_async_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(c, e_local, n, n, scale, 0, 0u, 0);
+  return check_launch("sync_async_kernel");
+}
+
+extern "C" int omldm_sync_ssp(const omldm_comm* h, float* e_local, size_t n, float scale, uint32_t clock,
+                              int staleness, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_async_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_ssp_kernel",
+                     c, e_local, n, n, scale, 1, clock, staleness);
+}
+
+extern "C" int omldm_sync_easgd(const omldm_comm* h, size_t n, float alpha, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  sync_easgd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(c, n, alpha);
+  return check_launch("sync_easgd_kernel");
+}
+
+extern "C" int omldm_sync_fgm(const omldm_comm* h, float* e_local, size_t n, float scale, float threshold,
+                              float eps_psi, uint32_t step, float* state_local, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  if (!e_local || !state_local) return set_error_msg("sync_fgm: e and the FGM state are required");
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n / h->world, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_fgm_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_fgm_kernel",
+                     c, e_local, n, n, scale, threshold, eps_psi, step, state_local);
+}
+
+extern "C" int omldm_device_barrier(const omldm_comm* h, uint32_t epoch, void* stream) {
+  Comm c = to_comm(h);
+  dim3 grid(1, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(device_barrier_kernel, grid, dim3(32), static_cast<cudaStream_t>(stream), "device_barrier_kernel", c, epoch);
+}
+
+extern "C" int omldm_query_reduce(const omldm_comm* h, const float* vals4, float* out4, uint32_t epoch, void* stream) {
+  Comm c = to_comm(h);
+  dim3 grid(1, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(query_reduce_kernel, grid, dim3(64), static_cast<cudaStream_t>(stream), "query_reduce_kernel",
+                     c, vals4, out4, epoch);
+}
+
+extern "C" int omldm_ipc_export(void* dev_ptr, void* handle64_host) {
+  cudaIpcMemHandle_t hnd;
+  cudaError_t e = cudaIpcGetMemHandle(&hnd, dev_ptr);
+  if (e != cudaSuccess) return set_error("cudaIpcGetMemHandle", e);
+  static_assert(sizeof(hnd) == 64, "ipc handle size");
+  memcpy(handle64_host, &hnd, 64);
+  return 0;
+}
+extern "C" int omldm_ipc_import(const void* handle64_host, void** dev_ptr_out) {
+  cudaIpcMemHandle_t hnd;
+  memcpy(&hnd, handle64_host, 64);
+  cudaError_t e = cudaIpcOpenMemHandle(dev_ptr_out, hnd, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return set_error("cudaIpcOpenMemHandle", e);
+  return 0;
+}
+extern "C" int omldm_ipc_close(void* dev_ptr) {
+  cudaError_t e = cudaIpcCloseMemHandle(dev_ptr);
+  if (e != cudaSuccess) return set_error("cudaIpcCloseMemHandle", e);
+  return 0;
+}
+extern "C" int omldm_enable_peer_access(int peer_device) {
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }
+  if (e != cudaSuccess) return set_error("cudaDeviceEnablePeerAccess", e);
+  return 0;
+}

@@ -1,0 +1,168 @@
+/* C ABI of libomldm_kernels.so - the sm_100a kernel library of omldm_b200.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void*; all entry points are asynchronous on it;
+ *   - return value 0 = launched, non-zero = rejected; `omldm_last_error()` has the reason;
+ *   - "staged record row" (Z row, pitch `ld` floats, multiple of 32, 128-byte aligned base):
+ *         [ x_0 .. x_{d-1} | 1.0 bias/valid (0.0 = empty row) | target | zero pad ]
+ *
+ * Each declaration cites the reference call site whose work it replaces (paths relative to
+ * src/main/scala/omldm/ of ArisKonidaris/OMLDM); the reference itself has no native code.
+ */
+#ifndef OMLDM_KERNELS_H_
+#define OMLDM_KERNELS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ library */
+const char* omldm_last_error(void);
+long long omldm_launch_count(void);       /* kernels launched by this library so far */
+void omldm_reset_launch_count(void);
+int omldm_abi_version(void);
+
+/* ------------------------------------------------------------------ tcgen05 GEMMs (umma_gemm.cu)
+ * flags: 1 = accumulate into C (red.add), 2 = skip tiles strictly below the diagonal,
+ *        4 = load MN-major slabs with per-slab 2-D TMA boxes.
+ * Learner maths behind node.receiveTuple, operators/spoke/FlinkSpoke.scala:101. */
+int omldm_gemm_tn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                  int M, int N, int K, int ksplit, int flags, void* stream);
+int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                     int M, int N, int K, int ksplit, int flags, void* stream);
+
+/* ------------------------------------------------------------------ linear learners (linear_learners.cu)
+ * PA / RegressorPA / SVM named in utils/parsers/requestStream/PipelineMap.scala:68. */
+typedef struct omldm_linear_desc {
+  float* w;        /* d + 1 weights, w[d] = intercept */
+  double* stats;   /* [loss_sum, aux_sum (mistakes | squared error), fitted, svm_step] */
+  int d;
+  int kind;        /* 0 PA classifier, 1 PA regressor, 2 SVM (Pegasos) */
+  int variant;     /* PA family: 0 PA, 1 PA-I, 2 PA-II */
+  float C;
+  float eps;       /* regressor insensitivity */
+  float lambda;    /* SVM regularisation */
+} omldm_linear_desc;
+
+/* exact per-record order; one warp per pipeline; descs_dev is a device array */
+int omldm_linear_exact(const float* Z, int ld, int B, const omldm_linear_desc* descs_dev,
+                       int n_pipelines, int max_d, void* stream);
+/* mini-batch update; `scratch` must hold omldm_linear_minibatch_scratch_floats(d) floats and be
+ * zero before the first call (the kernel re-zeroes it on exit) */
+size_t omldm_linear_minibatch_scratch_floats(int d);
+int omldm_linear_minibatch(const float* Z, int ld, int B, const omldm_linear_desc* desc_host,
+                           float* scratch, int mean_update, void* stream);
+/* forecast path, operators/spoke/FlinkSpoke.scala:105 */
+int omldm_linear_predict(const float* Z, int ld, int B, const float* w, int d, float* out,
+                         void* stream);
+
+/* ------------------------------------------------------------------ ingest (ingest.cu)
+ * 2-in-10 holdout with evict-then-train, operators/spoke/FlinkSpoke.scala:92-107.
+ * `count0` = number of training records seen before this batch; holdout ring = `cap` rows. */
+int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, int cap, long long count0,
+                       void* stream);
+/* sparse (CSR batch) -> dense staged rows + squared row norms (SparseVector, utils/CommonUtils.scala:23) */
+int omldm_densify(const int* indptr, const int* indices, const float* values, int B, int d,
+                  const float* targets, float* Z, int ld, float* sqnorm, void* stream);
+/* raw ring slot [B, d+1] (features..., target) -> staged rows */
+int omldm_stage_rows(const float* raw, int raw_ld, int B, int d, float* Z, int ld, void* stream);
+
+/* ------------------------------------------------------------------ preprocessors (preprocess.cu)
+ * PolynomialFeatures / StandardScaler / MinMaxScaler, PipelineMap.scala:67. */
+int omldm_poly_features(const float* Zin, int ldin, int d_in, const short* factors, int degree,
+                        int d_out, float* Zout, int ldout, int B, void* stream);
+/* state: double[1 + 2*d] = [count, mean[d], M2[d]]; scratch: double[3 + 4*d], zero before first call */
+int omldm_standard_scaler(float* Z, int ld, int d, int B, double* state, double* scratch, int fit,
+                          void* stream);
+/* state: float[2*d] = [min[d], max[d]] */
+int omldm_minmax_scaler(float* Z, int ld, int d, int B, float* state, int fit, void* stream);
+
+/* ------------------------------------------------------------------ k-means / multiclass PA (cluster.cu)
+ * K-means and MultiClassPA, PipelineMap.scala:68. */
+/* scores S[B,K] = X C^T (from omldm_gemm_tn); writes one-hot assignment T[B,ldt], stats += {inertia, n} */
+int omldm_kmeans_assign(const float* Z, int ld, int d, int B, const float* S, int lds,
+                        const float* cnorm, int K, float* T, int ldt, int* assign, double* stats,
+                        void* stream);
+/* centroids = sums / counts (count column = d), also refreshes ||c||^2 */
+int omldm_kmeans_finalize(const float* sums, int lds, int K, int d, float* centroids, int ldc,
+                          float* cnorm, void* stream);
+/* exact (MacQueen, per record) k-means on one CTA */
+int omldm_kmeans_exact(const float* Z, int ld, int d, int B, float* sums, int lds, int K,
+                       double* stats, void* stream);
+/* scores S[B,C] -> update coefficients T[B,ldt] (+tau at y, -tau at runner-up), stats += {loss, mistakes, n} */
+int omldm_mcpa_coef(const float* Z, int ld, int d, int B, const float* S, int lds, int C,
+                    const float* sqnorm, int variant, float Creg, float* T, int ldt, double* stats,
+                    void* stream);
+int omldm_row_sqnorm(const float* Z, int ld, int d_plus_bias, int B, float* out, void* stream);
+/* y[i] (+)= alpha * x[i]  /  generic helpers used by learners and protocols */
+int omldm_axpy(float* y, const float* x, float alpha, size_t n, void* stream);
+int omldm_scale_rows(float* T, int ldt, int B, int C, const float* scale_dev, void* stream);
+
+/* ------------------------------------------------------------------ fused protocol kernels (sync.cu)
+ * worker<->hub synchronisation, network/FlinkNetwork.scala:242-293 (send / broadcast) and the
+ * Kafka feedback loop Job.scala:77-87,136-142.  Peer pointer tables live in device memory. */
+typedef struct omldm_comm {
+  float* const* bufs;        /* k symmetric model/delta buffers (peer-mapped)            */
+  float* const* hubs;        /* k symmetric hub-shard buffers (async / SSP / EASGD)      */
+  uint32_t* const* pads;     /* k symmetric signal pads (uint32 words)                   */
+  uint32_t* local;           /* private scratch words of this rank (>= 64 uint32)        */
+  float* mc_buf;             /* NVLS multicast alias of bufs (NULL = use P2P)            */
+  int rank;
+  int world;
+  int emulate;               /* >1: one launch plays `emulate` ranks (single-GPU tests)  */
+} omldm_comm;
+
+/* signal-pad word layout (per rank), uint32 indices */
+enum {
+  OMLDM_PAD_ENTRY = 0,     /* [0,16)   entry-barrier arrivals, one word per peer    */
+  OMLDM_PAD_EXIT = 16,     /* [16,32)  exit-barrier arrivals                        */
+  OMLDM_PAD_CLOCK = 32,    /* [32,48)  SSP clocks                                   */
+  OMLDM_PAD_VOTE = 48,     /* [48,64)  GM / FGM round votes                         */
+  OMLDM_PAD_PHI = 64,      /* [64,80)  FGM phi values (float bits), hub = rank 0    */
+  OMLDM_PAD_FGM = 80,      /* [80,96)  FGM hub state: counter, subround, theta, psi */
+  OMLDM_PAD_STATUS = 96,   /* [96,100) status bits: 1 barrier, 2 SSP, 4 FGM timeouts  */
+  OMLDM_PAD_QUERY = 128,   /* [128,192) query scalars, 4 per peer                   */
+  OMLDM_PAD_WORDS = 256
+};
+
+/* Synchronous: every shard owner reduces all peers' buffers and writes the result back to all
+ * peers. mode 0: buf <- scale * sum(buf_i); e <- buf (if e != NULL).
+ * mode 1 (additive statistics): buf holds a delta; e += scale * sum(buf_i); buf <- 0. */
+int omldm_sync_allreduce(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
+                         uint32_t epoch, int blocks, void* stream);
+/* Asynchronous push/pull of one worker: hub += scale*(buf - e); buf = e = hub. No barrier. */
+int omldm_sync_async(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int blocks,
+                     void* stream);
+/* SSP: async push/pull, then clock++ and wait until min(clock) >= clock - staleness. */
+int omldm_sync_ssp(const omldm_comm* comm_host, float* e_local, size_t n, float scale, uint32_t clock,
+                   int staleness, int blocks, void* stream);
+/* EASGD elastic step against the hub shards. */
+int omldm_sync_easgd(const omldm_comm* comm_host, size_t n, float alpha, int blocks, void* stream);
+/* GM: ||buf - e||^2 > threshold on any rank (vote carried by the entry barrier) => allreduce. */
+int omldm_sync_gm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, float threshold,
+                  uint32_t epoch, int blocks, void* stream);
+/* FGM monitor step: phi = ||buf - e|| - sqrt(threshold), counter increments to the hub,
+ * sub-round / round bookkeeping, and the round-end allreduce, all inside one kernel.
+ * `state_local` : float[8] private FGM state of this rank (zero-initialised); `step` counts from 1. */
+int omldm_sync_fgm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, float threshold,
+                   float eps_psi, uint32_t step, float* state_local, int blocks, void* stream);
+/* device barrier over the signal pads (termination probe, utils/statistics/StatisticsOperator.scala:135-142) */
+int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stream);
+/* query reduce: out4 = sum over ranks of vals4 (utils/ResponseConstructor.scala:43-52) */
+int omldm_query_reduce(const omldm_comm* comm_host, const float* vals4, float* out4, uint32_t epoch,
+                       void* stream);
+
+/* CUDA IPC plumbing for the symmetric arena when torch's symmetric memory is unavailable */
+int omldm_ipc_export(void* dev_ptr, void* handle64_host);
+int omldm_ipc_import(const void* handle64_host, void** dev_ptr_out);
+int omldm_ipc_close(void* dev_ptr);
+int omldm_enable_peer_access(int peer_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OMLDM_KERNELS_H_ */
