@@ -1,0 +1,241 @@
+#!/usr/bin/env python
+"""Headline benchmark: records/sec of distributed online learning on N B200s of one node.
+
+Default config = BASELINE.json config 2 (online ridge regression, 1000-dim synthetic stream,
+Synchronous protocol); `--config` selects the other BASELINE configs:
+  orr     ORR 1k-d, Synchronous                          (cfg 2, default)
+  pa      PA binary classifier 28-d, Asynchronous         (cfg 1)
+  fgm     RegressorPA + PolynomialFeatures + StandardScaler, FGM (cfg 3)
+  kmeans  K-means K=256 on 128-d, SSP                     (cfg 4)
+  mcpa    MultiClassPA 100k-d sparse->dense, Synchronous  (cfg 5)
+
+One step = every GPU ingests one mini-batch, updates every pipeline and runs the protocol's fused
+synchronisation kernel (weak scaling: per-GPU batch is fixed).  Prints ONE JSON line on rank 0.
+
+  value  : device-timed (CUDA events, max over ranks) aggregate records/s, inputs resident on the
+           device and rotated over a set larger than L2
+  e2e    : same metric through Engine.train_batch_host: pinned host ring slot -> async H2D -> train
+           -> loss copied back to pinned host memory every step
+
+`--impl nccl` runs the in-repo PyTorch + NCCL (+cuBLAS) baseline; `--impl reference` reports that
+the reference (a Flink/Kafka/Scala job) cannot run here.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+CONFIGS = {
+    "orr": dict(model="ORR", d=1000, batch=16384, protocol="Synchronous", kind=1, n_aux=0,
+                hyper={"lambda": 1.0, "solveEvery": 16}, tc={}, pre=[],
+                name="ORR 1k-dim synthetic stream, synchronous protocol"),
+    "pa": dict(model="PA", d=28, batch=65536, protocol="Asynchronous", kind=0, n_aux=0,
+               hyper={"C": 0.01, "trainingMode": "minibatch"}, tc={}, pre=[],
+               name="PA binary classifier, 28-dim dense synthetic stream, async protocol"),
+    "fgm": dict(model="RegressorPA", d=28, batch=16384, protocol="FGM", kind=1, n_aux=0,
+                hyper={"C": 0.01, "epsilon": 0.1, "trainingMode": "minibatch"}, tc={"threshold": 0.05},
+                pre=[{"name": "PolynomialFeatures", "hyperParameters": {"degree": 2}}, {"name": "StandardScaler"}],
+                name="PA regressor + polynomial features + standard scaler, FGM protocol"),
+    "kmeans": dict(model="K-means", d=128, batch=16384, protocol="SSP", kind=2, n_aux=256,
+                   hyper={"k": 256}, tc={"staleness": 3}, pre=[],
+                   name="Online k-means k=256 on 128-dim synthetic stream, SSP protocol"),
+    "mcpa": dict(model="MultiClassPA", d=100000, batch=256, protocol="Synchronous", kind=3, n_aux=10,
+                 hyper={"nClasses": 10, "C": 0.1}, tc={}, pre=[],
+                 name="Multiclass PA 100k-dim sparse-to-dense stream, hub sharded over all GPUs"),
+}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.proc = None
+        self.lines = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "fused", "nccl", "reference"])
+    ap.add_argument("--config", default="orr", choices=sorted(CONFIGS))
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "reference is a Scala/Flink/Kafka Maven job with 3 out-of-tree SNAPSHOT dependencies; "
+                          "no JVM/Maven/Kafka in this image and it is not pip-installable (no setup.py/pyproject)"}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from omldm_b200.engine import Engine
+    from omldm_b200.ops import _lib
+    from omldm_b200.ops import functional as F
+    from omldm_b200.stream import ring as R
+    from omldm_b200.utils.config import JobParameters
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device", "metric": "records/sec"}))
+        return
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = CONFIGS[args.config]
+    B = args.batch or cfg["batch"]
+    d = cfg["d"]
+    impl = "nccl" if args.impl == "nccl" else "fused"
+    if impl == "nccl":
+        F.set_impl("torch")
+        torch.backends.cuda.matmul.allow_tf32 = True     # same math class as the tcgen05 tf32 path
+
+    params = JobParameters(parallelism=world, jobName="bench_" + args.config)
+    eng = Engine(params, rank, world, dev, impl=impl)
+    tc = dict(cfg["tc"], protocol=cfg["protocol"], nFeatures=d)
+    eng.handle_request({"id": 1, "request": "Create", "learner": {"name": cfg["model"], "hyperParameters": cfg["hyper"]},
+                        "preProcessors": cfg["pre"], "trainingConfiguration": tc})
+
+    # ---- inputs: a set of distinct batches larger than L2 (126 MB), resident on the device
+    ld = F.pad32(d + 2)
+    n_rot = max(2, min(8, int(320e6 // (B * ld * 4)) + 1))
+    host_pool = [R.generate_batch(cfg["kind"], d, B, seed=1234 + rank, batch_index=i, n_aux=cfg["n_aux"], pin=True)
+                 for i in range(n_rot)]
+    dev_pool = [h.to(dev) for h in host_pool]
+
+    def step_device(i: int) -> None:
+        eng.train_batch(dev_pool[i % n_rot], d)
+
+    def sync_all() -> None:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step_device(i)
+    sync_all()
+    sampler = ClockSampler(local) if rank == 0 else None
+    _lib.reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step_device(args.warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    launches = _lib.launch_count()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    sync_all()
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    value = world * B * args.steps / (ms_total / 1e3)
+
+    # ---- end to end: pinned ring slot -> H2D -> train -> loss D2H, every step
+    e2e = None
+    if not args.no_e2e:
+        topic = R.Topic(d, B, n_slots=n_rot)
+        topic.start_synthetic(cfg["kind"], seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_REPLAY, n_threads=2)
+        pending = []   # (slot, event recorded after the slot's H2D copy)
+
+        def step_e2e():
+            got = topic.get(10000)
+            slot, Zh, _ = got
+            loss = eng.train_batch_host(Zh, d)
+            pending.append((slot, eng.last_copy_event))
+            while len(pending) > 1:          # give a slot back once its H2D copy has completed
+                s0, ev = pending.pop(0)
+                if ev is not None:
+                    ev.synchronize()
+                topic.release(s0)
+            return loss
+        for _ in range(max(3, args.warmup)):
+            step_e2e()
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            loss_host = step_e2e()
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * B * args.steps / float(dt.item()), "unit": "records/s",
+               "h2d_bytes_per_step": B * ld * 4, "d2h_bytes_per_step": 32,
+               "last_loss_sum": float(loss_host[0])}
+        topic.stop()
+    clocks = sampler.stop() if sampler else None
+    status = eng.comm_status()
+
+    if rank == 0:
+        p = eng.pipelines[1]
+        out = {
+            "metric": "records/sec", "value": value, "unit": "records/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "tf32 (fp32 storage, fp32 accumulate)",
+            "data": "synthetic", "impl": "ours" if impl == "fused" else "nccl-baseline",
+            "config": {"model": cfg["name"], "learner": cfg["model"], "protocol": p.protocol,
+                       "global_batch": B * world, "per_gpu_batch": B, "features": d, "seq_len": None,
+                       "parallelism": f"dp{world} workers + {world} hub shards",
+                       "l2": f"inputs rotate over {n_rot} distinct batches = {n_rot * B * ld * 4 / 1e6:.0f} MB > 126 MB L2",
+                       "sync_every": p.driver.sync_every, "model_bytes": p.comm.n * 4},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "comm_status": status,
+        }
+        print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -56,16 +56,17 @@ __global__ void kmeans_assign_kernel(const float* __restrict__ Z, int ld, int d,
   }
 }
 
-__global__ void kmeans_finalize_kernel(const float* __restrict__ sums, int lds, int K, int d,
-                                       float* __restrict__ centroids, int ldc, float* __restrict__ cnorm) {
+__global__ void kmeans_finalize_kernel(const float* __restrict__ sums, const float* __restrict__ sums2, int lds,
+                                       int K, int d, float* __restrict__ centroids, int ldc,
+                                       float* __restrict__ cnorm) {
   const int j = blockIdx.x;
   if (j >= K) return;
-  const float cnt = sums[static_cast<size_t>(j) * lds + d];
+  const float cnt = sums[static_cast<size_t>(j) * lds + d] + (sums2 ? sums2[static_cast<size_t>(j) * lds + d] : 0.f);
   const float inv = cnt > 0.f ? 1.f / cnt : 0.f;
   float acc = 0.f;
   for (int c = threadIdx.x; c < ldc; c += blockDim.x) {
     float v = 0.f;
-    if (c < d) v = sums[static_cast<size_t>(j) * lds + c] * inv;
+    if (c < d) v = (sums[static_cast<size_t>(j) * lds + c] + (sums2 ? sums2[static_cast<size_t>(j) * lds + c] : 0.f)) * inv;
     centroids[static_cast<size_t>(j) * ldc + c] = v;
     acc = fmaf(v, v, acc);
   }
@@ -222,8 +223,9 @@ __global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, 
 }
 
 // T[r, :] *= scale[0] (device scalar), e.g. 1 / n_active for averaged mini-batch updates.
-__global__ void scale_rows_kernel(float* __restrict__ T, int ldt, int B, int C, const float* __restrict__ scale) {
-  const float s = *scale;
+__global__ void scale_rows_kernel(float* __restrict__ T, int ldt, int B, int C, const float* __restrict__ scale,
+                                  int reciprocal) {
+  const float s = reciprocal ? 1.f / fmaxf(*scale, 1.f) : *scale;
   const size_t total = static_cast<size_t>(B) * C;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -232,9 +234,63 @@ __global__ void scale_rows_kernel(float* __restrict__ T, int ldt, int B, int C, 
   }
 }
 
+// sum over valid rows of (Z_r . wt)^2, wt has n entries (n <= ld)
+__global__ void sq_residual_kernel(const float* __restrict__ Z, int ld, int B, int d, const float* __restrict__ wt,
+                                   int n, double* __restrict__ stats) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  __shared__ double s_l[8];
+  __shared__ int s_n[8];
+  double acc = 0.0;
+  int nv = 0;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = warp; r < B; r += nwarps) {
+    const float* zr = Z + static_cast<size_t>(r) * ld;
+    if (zr[d] == 0.f) continue;
+    float dot = 0.f;
+    for (int c = lane; c < n; c += 32) dot = fmaf(zr[c], wt[c], dot);
+    dot = warp_sum(dot);
+    acc += static_cast<double>(dot) * dot;
+    nv += 1;
+  }
+  const int w = threadIdx.x >> 5;
+  if (lane == 0) { s_l[w] = acc; s_n[w] = nv; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double l = 0; int c = 0;
+    for (int i = 0; i < (blockDim.x >> 5); ++i) { l += s_l[i]; c += s_n[i]; }
+    if (c) { atomicAdd(&stats[0], l); atomicAdd(&stats[2], static_cast<double>(c)); }
+  }
+}
+
+__global__ void mirror_upper_kernel(float* __restrict__ A, int ld, int n) {
+  __shared__ float tile[32][33];
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bj < bi) return;  // read upper tiles only
+  const int i = bi * 32 + threadIdx.y, j = bj * 32 + threadIdx.x;
+  tile[threadIdx.y][threadIdx.x] = (i < n && j < n) ? A[static_cast<size_t>(i) * ld + j] : 0.f;
+  __syncthreads();
+  const int oi = bj * 32 + threadIdx.y, oj = bi * 32 + threadIdx.x;  // transposed position
+  if (oi < n && oj < n && oi > oj) A[static_cast<size_t>(oi) * ld + oj] = tile[threadIdx.x][threadIdx.y];
+}
+
 }  // namespace omldm
 
 using namespace omldm;
+
+extern "C" int omldm_sq_residual(const float* Z, int ld, int B, int d, const float* wt, int n, double* stats,
+                                 void* stream) {
+  if (B <= 0) return 0;
+  int blocks = (B + 7) / 8;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  sq_residual_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, wt, n, stats);
+  return check_launch("sq_residual_kernel");
+}
+
+extern "C" int omldm_mirror_upper(float* A, int ld, int n, void* stream) {
+  dim3 grid((n + 31) / 32, (n + 31) / 32), block(32, 32);
+  mirror_upper_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(A, ld, n);
+  return check_launch("mirror_upper_kernel");
+}
 
 extern "C" int omldm_kmeans_assign(const float* Z, int ld, int d, int B, const float* S, int lds,
                                    const float* cnorm, int K, float* T, int ldt, int* assign, double* stats,
@@ -245,9 +301,9 @@ extern "C" int omldm_kmeans_assign(const float* Z, int ld, int d, int B, const f
   return check_launch("kmeans_assign_kernel");
 }
 
-extern "C" int omldm_kmeans_finalize(const float* sums, int lds, int K, int d, float* centroids, int ldc,
-                                     float* cnorm, void* stream) {
-  kmeans_finalize_kernel<<<K, 128, 0, static_cast<cudaStream_t>(stream)>>>(sums, lds, K, d, centroids, ldc, cnorm);
+extern "C" int omldm_kmeans_finalize(const float* sums, const float* sums2, int lds, int K, int d, float* centroids,
+                                     int ldc, float* cnorm, void* stream) {
+  kmeans_finalize_kernel<<<K, 128, 0, static_cast<cudaStream_t>(stream)>>>(sums, sums2, lds, K, d, centroids, ldc, cnorm);
   return check_launch("kmeans_finalize_kernel");
 }
 
@@ -282,11 +338,11 @@ extern "C" int omldm_axpy(float* y, const float* x, float alpha, size_t n, void*
   return check_launch("axpy_kernel");
 }
 
-extern "C" int omldm_scale_rows(float* T, int ldt, int B, int C, const float* scale_dev, void* stream) {
+extern "C" int omldm_scale_rows(float* T, int ldt, int B, int C, const float* scale_dev, int reciprocal, void* stream) {
   if (B <= 0) return 0;
   size_t total = static_cast<size_t>(B) * C;
   int blocks = static_cast<int>((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  scale_rows_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(T, ldt, B, C, scale_dev);
+  scale_rows_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(T, ldt, B, C, scale_dev, reciprocal);
   return check_launch("scale_rows_kernel");
 }

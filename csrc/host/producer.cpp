@@ -1,0 +1,150 @@
+// Synthetic stream generators and producer threads: the stand-in for the Kafka source subtasks
+// that feed `trainingData` (Job.scala:42-50).  Records are written directly in the staged row
+// layout so a ring slot can be copied to the GPU as is.
+#include "omldm_host.h"
+
+#include <atomic>
+#include <cmath>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+namespace {
+
+struct Rng {  // xoshiro256** - fast and good enough for synthetic features
+  uint64_t s[4];
+  explicit Rng(uint64_t seed) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull;
+    for (int i = 0; i < 4; ++i) {
+      z += 0x9E3779B97F4A7C15ull;
+      uint64_t x = z;
+      x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+      x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+      s[i] = x ^ (x >> 31);
+    }
+  }
+  static inline uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
+  inline uint64_t next() {
+    const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
+    s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45);
+    return r;
+  }
+  inline float uniform() { return (next() >> 40) * (1.0f / 16777216.0f); }
+  // approx N(0,1): sum of 4 uniforms, variance-corrected (cheap; tails do not matter here)
+  inline float normal() {
+    const uint64_t a = next();
+    const float u = ((a & 0xFFFF) + ((a >> 16) & 0xFFFF) + ((a >> 32) & 0xFFFF) + (a >> 48)) * (1.0f / 65536.0f);
+    return (u - 2.0f) * 1.7320508f;
+  }
+};
+
+// hidden model shared by all batches of a stream: derived from the seed only
+struct Truth {
+  std::vector<float> w;  // kind 0/1: d weights; kind 2: n_aux centres x d; kind 3: n_aux planes x d
+  float bias;
+  Truth(int kind, int d, int n_aux, uint64_t seed) {
+    Rng g(seed ^ 0xABCDEF1234ull);
+    const int rows = (kind >= 2) ? (n_aux > 0 ? n_aux : 1) : 1;
+    w.resize(static_cast<size_t>(rows) * d);
+    const float scale = kind == 2 ? 4.0f : 1.0f / std::sqrt(static_cast<float>(d));
+    for (auto& v : w) v = g.normal() * scale;
+    bias = kind == 1 ? 0.5f : 0.0f;
+  }
+};
+
+void fill_batch(float* dst, const Truth& tr, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
+                uint64_t batch_index) {
+  Rng g(seed * 0x100000001B3ull + batch_index * 0x9E3779B97F4A7C15ull + 1);
+  for (int r = 0; r < batch; ++r) {
+    float* row = dst + static_cast<size_t>(r) * ld;
+    float y = 0.f;
+    if (kind == 2) {
+      const int c = static_cast<int>(g.next() % static_cast<uint64_t>(n_aux > 0 ? n_aux : 1));
+      const float* ctr = tr.w.data() + static_cast<size_t>(c) * d;
+      for (int j = 0; j < d; ++j) row[j] = ctr[j] + g.normal();
+      y = static_cast<float>(c);
+    } else {
+      for (int j = 0; j < d; ++j) row[j] = g.normal();
+      if (kind == 3) {
+        int best = 0;
+        float bs = -1e30f;
+        for (int c = 0; c < n_aux; ++c) {
+          const float* p = tr.w.data() + static_cast<size_t>(c) * d;
+          float s = 0.f;
+          for (int j = 0; j < d; ++j) s += p[j] * row[j];
+          if (s > bs) { bs = s; best = c; }
+        }
+        y = static_cast<float>(best);
+      } else {
+        float s = tr.bias;
+        for (int j = 0; j < d; ++j) s += tr.w[j] * row[j];
+        y = kind == 0 ? (s >= 0.f ? 1.f : -1.f) : s + 0.01f * g.normal();
+      }
+    }
+    row[d] = 1.0f;
+    row[d + 1] = y;
+    for (int j = d + 2; j < ld; ++j) row[j] = 0.f;
+  }
+}
+
+}  // namespace
+
+struct omldm_producer {
+  omldm_ring* ring;
+  int kind, d, ld, batch, n_aux, mode, n_threads;
+  uint64_t seed;
+  int64_t max_batches;
+  std::atomic<int64_t> next_batch{0};
+  std::atomic<bool> stop{false};
+  std::atomic<int> live{0};
+  std::vector<std::thread> threads;
+  std::vector<char> filled;  // replay mode: slot already holds data
+  Truth truth;
+  omldm_producer(int kind_, int d_, int n_aux_, uint64_t seed_) : truth(kind_, d_, n_aux_, seed_) {}
+};
+
+static void producer_loop(omldm_producer* p) {
+  while (!p->stop.load()) {
+    if (p->max_batches >= 0 && p->next_batch.load() >= p->max_batches) break;
+    const int slot = omldm_ring_acquire_write(p->ring, 50);
+    if (slot < 0) continue;
+    const int64_t b = p->next_batch.fetch_add(1);
+    if (p->max_batches >= 0 && b >= p->max_batches) {
+      omldm_ring_commit_write(p->ring, slot, 0);   // empty marker batch, the reader skips it
+      break;
+    }
+    float* dst = static_cast<float*>(omldm_ring_slot_ptr(p->ring, slot));
+    if (p->mode == 0 || !p->filled[slot]) {
+      fill_batch(dst, p->truth, p->kind, p->d, p->ld, p->batch, p->n_aux, p->seed, static_cast<uint64_t>(b));
+      p->filled[slot] = 1;
+    }
+    omldm_ring_commit_write(p->ring, slot, p->batch);
+  }
+  if (p->live.fetch_sub(1) == 1) omldm_ring_close(p->ring);
+}
+
+extern "C" omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
+                                                uint64_t seed, int mode, int64_t max_batches, int n_threads) {
+  if (!r || d <= 0 || ld < d + 2 || batch <= 0) return nullptr;
+  auto* p = new omldm_producer(kind, d, n_aux, seed);
+  p->ring = r; p->kind = kind; p->d = d; p->ld = ld; p->batch = batch; p->n_aux = n_aux; p->mode = mode;
+  p->seed = seed; p->max_batches = max_batches;
+  p->n_threads = n_threads < 1 ? 1 : n_threads;
+  p->filled.assign(1 << 16, 0);
+  p->live.store(p->n_threads);
+  for (int i = 0; i < p->n_threads; ++i) p->threads.emplace_back(producer_loop, p);
+  return p;
+}
+
+extern "C" void omldm_producer_stop(omldm_producer* p) {
+  if (!p) return;
+  p->stop.store(true);
+  for (auto& t : p->threads) t.join();
+  delete p;
+}
+
+extern "C" void omldm_generate_batch(float* dst, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
+                                     uint64_t batch_index) {
+  Truth tr(kind, d, n_aux, seed);
+  fill_batch(dst, tr, kind, d, ld, batch, n_aux, seed, batch_index);
+}

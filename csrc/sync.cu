@@ -178,10 +178,12 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
   const uint32_t seq_entry = 2 * epoch + 1, seq_exit = 2 * epoch + 2;
 
   if (gm_threshold >= 0.f) {
-    partial_sqdist(buf, e, n, reinterpret_cast<float*>(loc + L_NORM));
+    // delta-mode buffers are monitored by their own norm (the delta IS buf)
+    partial_sqdist(buf, mode == 0 ? e : nullptr, n, reinterpret_cast<float*>(loc + L_NORM));
     if (grid_done(loc + L_DONE2)) {
       const float nrm2 = __ldcg(reinterpret_cast<float*>(loc + L_NORM));
-      loc[L_NORM] = 0;
+      __syncthreads();                    // everyone has read the norm before it is reset
+      if (threadIdx.x == 0) loc[L_NORM] = 0;
       const uint32_t vote = 2 * epoch + (nrm2 > gm_threshold ? 1u : 0u);
       if (threadIdx.x < c.world) {
         asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[threadIdx.x] + OMLDM_PAD_VOTE + me), "r"(vote) : "memory");
@@ -217,8 +219,8 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
 // Asynchronous / SSP: one worker pushes scale*(buf - e) into the owning hub shards with
 // returning vector atomics and installs the fresh hub value locally.  No rendezvous.
 __global__ void __launch_bounds__(256)
-sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int ssp, uint32_t clock,
-                  int staleness) {
+sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode, int ssp,
+                  uint32_t clock, int staleness) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
   float4* b4 = reinterpret_cast<float4*>(c.bufs[me]);
@@ -229,10 +231,13 @@ sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale,
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
     const int owner = static_cast<int>(i / per);
     const float4 w = b4[i], e = e4[i];
-    const float4 d = make_float4(scale * (w.x - e.x), scale * (w.y - e.y), scale * (w.z - e.z), scale * (w.w - e.w));
+    // mode 0: buf is the model, push scale*(buf - e).  mode 1: buf is an additive delta, push it.
+    const float4 d = mode == 0
+        ? make_float4(scale * (w.x - e.x), scale * (w.y - e.y), scale * (w.z - e.z), scale * (w.w - e.w))
+        : f4_scale(w, scale);
     const float4 old = atom_add_sys_v4(c.hubs[owner] + 4 * i, d);
     const float4 nv = f4_add(old, d);
-    b4[i] = nv;
+    b4[i] = mode == 0 ? nv : make_float4(0.f, 0.f, 0.f, 0.f);
     e4[i] = nv;
   }
   if (!ssp) return;
@@ -278,8 +283,8 @@ __global__ void __launch_bounds__(256) sync_easgd_kernel(Comm c, size_t n, float
 // Hub = rank 0's pad.  FGM words: [0] counter(s32) [1] subround id [2] theta bits [3] round id.
 // state_local (float[8], private): [0] round id [1] subround seen [2] zeta [3] counts sent [4] rounds [5] subrounds
 __global__ void __launch_bounds__(256)
-sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, float threshold, float eps_psi,
-                uint32_t step, float* state_base) {
+sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode, float threshold,
+                float eps_psi, uint32_t step, float* state_base) {
   const int me = my_rank(c);
   const int k = c.world;
   uint32_t* loc = my_local(c);
@@ -289,7 +294,7 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, f
   uint32_t* hub = c.pads[0] + OMLDM_PAD_FGM;
   const float phi0 = -sqrtf(threshold);
 
-  partial_sqdist(buf, e, n, reinterpret_cast<float*>(loc + L_NORM));
+  partial_sqdist(buf, mode == 0 ? e : nullptr, n, reinterpret_cast<float*>(loc + L_NORM));
   if (grid_done(loc + L_DONE2)) {
     if (threadIdx.x == 0) {
       const float nrm2 = __ldcg(reinterpret_cast<float*>(loc + L_NORM));
@@ -370,7 +375,7 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, f
     signal_all(c, me, OMLDM_PAD_EXIT, seq_exit);
   }
   wait_all(c, me, OMLDM_PAD_EXIT, seq_exit);
-  local_tail(buf, e, n, 0);
+  local_tail(buf, e, n, mode);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st[0] = static_cast<float>(round + 1);
     st[1] = -1.f;  // force re-anchoring at the next step
@@ -456,7 +461,7 @@ extern "C" int omldm_sync_allreduce(const omldm_comm* h, float* e_local, size_t 
                      c, e_local, n, n, scale, mode, epoch, -1.0f);
 }
 
-extern "C" int omldm_sync_gm(const omldm_comm* h, float* e_local, size_t n, float scale, float threshold,
+extern "C" int omldm_sync_gm(const omldm_comm* h, float* e_local, size_t n, float scale, int mode, float threshold,
                              uint32_t epoch, int blocks, void* stream) {
   if (check_world(h, n)) return -1;
   if (!e_local) return set_error_msg("sync_gm: the estimate vector e is required");
@@ -464,26 +469,27 @@ extern "C" int omldm_sync_gm(const omldm_comm* h, float* e_local, size_t n, floa
   blocks = clamp_blocks(blocks, n / h->world, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_allreduce_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_gm_kernel",
-                     c, e_local, n, n, scale, 0, epoch, threshold);
+                     c, e_local, n, n, scale, mode, epoch, threshold);
 }
 
-extern "C" int omldm_sync_async(const omldm_comm* h, float* e_local, size_t n, float scale, int blocks, void* stream) {
+extern "C" int omldm_sync_async(const omldm_comm* h, float* e_local, size_t n, float scale, int mode, int blocks,
+                                void* stream) {
   if (check_world(h, n)) return -1;
   Comm c = to_comm(h);
   blocks = clamp_blocks(blocks, n, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
-  sync_async_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(c, e_local, n, n, scale, 0, 0u, 0);
+  sync_async_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(c, e_local, n, n, scale, mode, 0, 0u, 0);
   return check_launch("sync_async_kernel");
 }
 
-extern "C" int omldm_sync_ssp(const omldm_comm* h, float* e_local, size_t n, float scale, uint32_t clock,
+extern "C" int omldm_sync_ssp(const omldm_comm* h, float* e_local, size_t n, float scale, int mode, uint32_t clock,
                               int staleness, int blocks, void* stream) {
   if (check_world(h, n)) return -1;
   Comm c = to_comm(h);
   blocks = clamp_blocks(blocks, n, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_async_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_ssp_kernel",
-                     c, e_local, n, n, scale, 1, clock, staleness);
+                     c, e_local, n, n, scale, mode, 1, clock, staleness);
 }
 
 extern "C" int omldm_sync_easgd(const omldm_comm* h, size_t n, float alpha, int blocks, void* stream) {
@@ -495,7 +501,7 @@ extern "C" int omldm_sync_easgd(const omldm_comm* h, size_t n, float alpha, int 
   return check_launch("sync_easgd_kernel");
 }
 
-extern "C" int omldm_sync_fgm(const omldm_comm* h, float* e_local, size_t n, float scale, float threshold,
+extern "C" int omldm_sync_fgm(const omldm_comm* h, float* e_local, size_t n, float scale, int mode, float threshold,
                               float eps_psi, uint32_t step, float* state_local, int blocks, void* stream) {
   if (check_world(h, n)) return -1;
   if (!e_local || !state_local) return set_error_msg("sync_fgm: e and the FGM state are required");
@@ -503,7 +509,7 @@ extern "C" int omldm_sync_fgm(const omldm_comm* h, float* e_local, size_t n, flo
   blocks = clamp_blocks(blocks, n / h->world, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_fgm_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_fgm_kernel",
-                     c, e_local, n, n, scale, threshold, eps_psi, step, state_local);
+                     c, e_local, n, n, scale, mode, threshold, eps_psi, step, state_local);
 }
 
 extern "C" int omldm_device_barrier(const omldm_comm* h, uint32_t epoch, void* stream) {
@@ -543,5 +549,20 @@ extern "C" int omldm_enable_peer_access(int peer_device) {
   cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
   if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }
   if (e != cudaSuccess) return set_error("cudaDeviceEnablePeerAccess", e);
+  return 0;
+}
+
+// Arena memory for the symmetric buffers: a dedicated cudaMalloc so that the IPC handle maps the
+// whole region at offset 0 in every peer.
+extern "C" int omldm_dev_malloc(size_t bytes, void** out) {
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e != cudaSuccess) return set_error("cudaMalloc(arena)", e);
+  e = cudaMemset(*out, 0, bytes);
+  if (e != cudaSuccess) return set_error("cudaMemset(arena)", e);
+  return 0;
+}
+extern "C" int omldm_dev_free(void* p) {
+  cudaError_t e = cudaFree(p);
+  if (e != cudaSuccess) return set_error("cudaFree(arena)", e);
   return 0;
 }

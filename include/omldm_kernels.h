@@ -87,9 +87,9 @@ int omldm_minmax_scaler(float* Z, int ld, int d, int B, float* state, int fit, v
 int omldm_kmeans_assign(const float* Z, int ld, int d, int B, const float* S, int lds,
                         const float* cnorm, int K, float* T, int ldt, int* assign, double* stats,
                         void* stream);
-/* centroids = sums / counts (count column = d), also refreshes ||c||^2 */
-int omldm_kmeans_finalize(const float* sums, int lds, int K, int d, float* centroids, int ldc,
-                          float* cnorm, void* stream);
+/* centroids = (sums + sums2) / counts (count column = d; sums2 may be NULL), refreshes ||c||^2 */
+int omldm_kmeans_finalize(const float* sums, const float* sums2, int lds, int K, int d, float* centroids,
+                          int ldc, float* cnorm, void* stream);
 /* exact (MacQueen, per record) k-means on one CTA */
 int omldm_kmeans_exact(const float* Z, int ld, int d, int B, float* sums, int lds, int K,
                        double* stats, void* stream);
@@ -100,7 +100,12 @@ int omldm_mcpa_coef(const float* Z, int ld, int d, int B, const float* S, int ld
 int omldm_row_sqnorm(const float* Z, int ld, int d_plus_bias, int B, float* out, void* stream);
 /* y[i] (+)= alpha * x[i]  /  generic helpers used by learners and protocols */
 int omldm_axpy(float* y, const float* x, float alpha, size_t n, void* stream);
-int omldm_scale_rows(float* T, int ldt, int B, int C, const float* scale_dev, void* stream);
+/* T[:, :C] *= (reciprocal ? 1/max(*scale_dev,1) : *scale_dev) */
+int omldm_scale_rows(float* T, int ldt, int B, int C, const float* scale_dev, int reciprocal, void* stream);
+/* stats[0] += sum_r (Z_r . wt)^2 over valid rows, stats[2] += #valid: squared residuals with wt = [w, b, -1] */
+int omldm_sq_residual(const float* Z, int ld, int B, int d, const float* wt, int n, double* stats, void* stream);
+/* symmetric completion: A[j][i] = A[i][j] for j > i (upper -> lower) */
+int omldm_mirror_upper(float* A, int ld, int n, void* stream);
 
 /* ------------------------------------------------------------------ fused protocol kernels (sync.cu)
  * worker<->hub synchronisation, network/FlinkNetwork.scala:242-293 (send / broadcast) and the
@@ -134,29 +139,33 @@ enum {
  * mode 1 (additive statistics): buf holds a delta; e += scale * sum(buf_i); buf <- 0. */
 int omldm_sync_allreduce(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
                          uint32_t epoch, int blocks, void* stream);
-/* Asynchronous push/pull of one worker: hub += scale*(buf - e); buf = e = hub. No barrier. */
-int omldm_sync_async(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int blocks,
-                     void* stream);
+/* Asynchronous push/pull of one worker. mode 0: hub += scale*(buf - e); buf = e = hub.
+ * mode 1 (additive delta): hub += scale*buf; e = hub; buf = 0.  No barrier. */
+int omldm_sync_async(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
+                     int blocks, void* stream);
 /* SSP: async push/pull, then clock++ and wait until min(clock) >= clock - staleness. */
-int omldm_sync_ssp(const omldm_comm* comm_host, float* e_local, size_t n, float scale, uint32_t clock,
-                   int staleness, int blocks, void* stream);
+int omldm_sync_ssp(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
+                   uint32_t clock, int staleness, int blocks, void* stream);
 /* EASGD elastic step against the hub shards. */
 int omldm_sync_easgd(const omldm_comm* comm_host, size_t n, float alpha, int blocks, void* stream);
 /* GM: ||buf - e||^2 > threshold on any rank (vote carried by the entry barrier) => allreduce. */
-int omldm_sync_gm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, float threshold,
-                  uint32_t epoch, int blocks, void* stream);
+int omldm_sync_gm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
+                  float threshold, uint32_t epoch, int blocks, void* stream);
 /* FGM monitor step: phi = ||buf - e|| - sqrt(threshold), counter increments to the hub,
  * sub-round / round bookkeeping, and the round-end allreduce, all inside one kernel.
  * `state_local` : float[8] private FGM state of this rank (zero-initialised); `step` counts from 1. */
-int omldm_sync_fgm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, float threshold,
-                   float eps_psi, uint32_t step, float* state_local, int blocks, void* stream);
+int omldm_sync_fgm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
+                   float threshold, float eps_psi, uint32_t step, float* state_local, int blocks,
+                   void* stream);
 /* device barrier over the signal pads (termination probe, utils/statistics/StatisticsOperator.scala:135-142) */
 int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stream);
 /* query reduce: out4 = sum over ranks of vals4 (utils/ResponseConstructor.scala:43-52) */
 int omldm_query_reduce(const omldm_comm* comm_host, const float* vals4, float* out4, uint32_t epoch,
                        void* stream);
 
-/* CUDA IPC plumbing for the symmetric arena when torch's symmetric memory is unavailable */
+/* CUDA IPC plumbing for the symmetric arena (one dedicated, zero-filled cudaMalloc per region) */
+int omldm_dev_malloc(size_t bytes, void** out);
+int omldm_dev_free(void* p);
 int omldm_ipc_export(void* dev_ptr, void* handle64_host);
 int omldm_ipc_import(const void* handle64_host, void** dev_ptr_out);
 int omldm_ipc_close(void* dev_ptr);

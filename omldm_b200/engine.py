@@ -1,0 +1,297 @@
+"""GPU engine: one process per GPU = one worker ("spoke") and one hub shard.
+
+This is the B200-native counterpart of the whole Flink job (Job.scala:35-168,
+job/FlinkLearning.scala:33-150).  The public surface a reference user needs is unchanged -
+JSON `Create/Update/Query/Delete` requests in, `QueryResponse` / `Prediction` /
+`JobStatistics` JSON out - but the data plane is batch oriented: staged record rows come from a
+pinned host ring (stand-in for the Kafka trainingData / forecastingData topics), go to the GPU
+with one async copy, and every pipeline consumes them with hand-written kernels; replicas are
+reconciled by the fused protocol kernels over NVLink (parallel/fused.py, csrc/sync.cu).
+
+SPMD contract: every rank calls `handle_request` with the same requests in the same order and
+`train_batch` the same number of times between protocol barriers (the launcher / CLI guarantees
+this; requests are broadcast exactly like PipelineMap.scala:54-57 does).
+"""
+from __future__ import annotations
+
+import json
+import time
+from typing import Any, Dict, List, Optional, Union
+
+import torch
+
+from .api.bucketing import bucket_response
+from .api.pojos import (DataInstance, JobStatistics, Prediction, QueryResponse, Request, Statistics)
+from .api.registry import PipelineMap
+from .models.pipeline import GpuPipeline
+from .ops import functional as F
+from .ops import _lib
+from .parallel.fused import device_barrier, query_reduce
+from .stream.parsers import parse_request
+from .utils.config import JobParameters
+
+
+class Engine:
+    def __init__(self, params: Optional[JobParameters] = None, rank: int = 0, world: int = 1,
+                 device: Optional[Union[str, torch.device]] = None, impl: str = "fused", group=None):
+        self.params = params or JobParameters(parallelism=world)
+        self.rank, self.world, self.impl, self.group = rank, world, impl, group
+        if device is None:
+            device = f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "cpu"
+        self.device = torch.device(device)
+        self.pipeline_map = PipelineMap(world, self.params.distributedKMeans)
+        self.pipelines: Dict[int, GpuPipeline] = {}
+        self.pending_requests: List[Request] = []
+        self.holdout: Optional[torch.Tensor] = None   # [cap, ld] staged rows
+        self.count = 0                                # training records seen by this worker
+        self.d: Optional[int] = None
+        self.responses: List[str] = []
+        self.predictions: List[str] = []
+        self.performance: List[str] = []
+        self.t_first: Optional[float] = None
+        self.t_last: Optional[float] = None
+        self._copy_stream = None
+        self._stage: List[Optional[torch.Tensor]] = [None, None]
+        self._stage_evt: List[Any] = [None, None]
+        self._stage_i = 0
+        self._loss_host = None
+        self.last_copy_event = None
+        self.holdout_enabled = True
+
+    # ============================================================================ control plane
+    def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
+        r = parse_request(req)
+        if r is None:
+            return []
+        out: List[str] = []
+        for cm in self.pipeline_map.flat_map(r)[:1]:   # every worker gets the same message; we are one worker
+            out += self._process_control(cm.request)
+        return out
+
+    def _process_control(self, r: Request) -> List[str]:
+        kind = r.request
+        if kind == "Create":
+            self.pipelines[r.id] = GpuPipeline(
+                r, self.device, self.rank, self.world, impl=self.impl, group=self.group,
+                distributed_kmeans=self.params.distributedKMeans, max_msg_params=self.params.maxMsgParams)
+            d = (r.trainingConfiguration or {}).get("nFeatures") or (r.learner.hyperParameters or {}).get("nFeatures")
+            if d is not None:
+                self._build(self.pipelines[r.id], int(d))
+            elif self.d is not None:
+                self._build(self.pipelines[r.id], self.d)
+            return []
+        if kind == "Update":
+            return []                                   # accepted, routed, no-op (FlinkSpoke.scala:158)
+        if kind == "Delete":
+            p = self.pipelines.pop(r.id, None)
+            if p is not None:
+                p.close()
+            return []
+        if kind == "Query":
+            return self.query(r.id, r.requestId)
+        return []
+
+    def _build(self, p: GpuPipeline, d: int) -> None:
+        if not p.built and not (p.protocol == "SingleLearner" and self.rank != 0):
+            p.build(d)
+
+    def query(self, pipeline_id: int, response_id: int) -> List[str]:
+        p = self.pipelines.get(pipeline_id)
+        if p is None:
+            return []
+        single = p.protocol == "SingleLearner"
+        if single and self.rank != 0:
+            return []
+        ring = self._holdout_rows()
+        resp = p.local_response(response_id, ring)
+        if self.world > 1 and not single and p.built:
+            vals = torch.tensor([float(resp.dataFitted or 0), float(resp.loss or 0.0),
+                                 float(resp.cumulativeLoss or 0.0), float(resp.score or 0.0)],
+                                dtype=torch.float32, device=self.device)
+            tot = query_reduce(p.comm, vals, self.impl, self.group).tolist()
+            resp.dataFitted = int(round(tot[0]))                      # SUM (ResponseConstructor.scala:43)
+            resp.loss, resp.cumulativeLoss, resp.score = (tot[1] / self.world, tot[2] / self.world,
+                                                          tot[3] / self.world)     # MEAN (:44-52)
+        if self.rank != 0:
+            return []
+        frags = [str(f) for f in bucket_response(resp)]
+        self.responses += frags
+        return frags
+
+    # ============================================================================ data plane
+    def _ensure_holdout(self, ld: int) -> None:
+        if self.holdout is None:
+            self.holdout = torch.zeros(self.params.testSetSize, ld, device=self.device)
+
+    def _holdout_rows(self) -> torch.Tensor:
+        if self.holdout is None:
+            return torch.zeros(0, 1, device=self.device)
+        n = min(F.holdouts_before(self.count), self.holdout.shape[0])
+        return self.holdout[:n]
+
+    def train_batch(self, Z: torch.Tensor, d: Optional[int] = None, **kw) -> None:
+        """Train every pipeline on one batch of staged rows [B, ld] already on `self.device`.
+        The batch is consumed (the holdout swap and in-place scalers modify it)."""
+        if d is None:
+            d = self.d
+        if d is None:
+            raise ValueError("feature dimension not known; pass d on the first batch")
+        self.d = d
+        now = time.monotonic()
+        if self.t_first is None:
+            self.t_first = now
+        B, ld = Z.shape
+        if self.holdout_enabled and self.params.testSetSize > 0:
+            self._ensure_holdout(ld)
+            F.holdout_swap(Z, self.holdout, d, self.count)   # 2-in-10 holdout, evict-then-train
+        self.count += B
+        n_pipes = len(self.pipelines)
+        for p in self.pipelines.values():
+            if p.protocol == "SingleLearner":
+                Zs = self._forward_to_rank0(Z)
+                if self.rank == 0:
+                    self._build(p, d)
+                    p.train(Zs, protect_input=True, **kw)
+                continue
+            self._build(p, d)
+            p.train(Z, protect_input=n_pipes > 1, **kw)
+        self.t_last = time.monotonic()
+
+    def _forward_to_rank0(self, Z: torch.Tensor) -> torch.Tensor:
+        """SingleLearner: workers forward raw records to the one learner at hub 0."""
+        if self.world == 1:
+            return Z
+        import torch.distributed as dist
+        if self.rank == 0:
+            parts = [torch.empty_like(Z) for _ in range(self.world)]
+            dist.gather(Z, parts, dst=0, group=self.group)
+            return torch.cat(parts, 0)
+        dist.gather(Z, None, dst=0, group=self.group)
+        return Z
+
+    # ---- end-to-end path: pinned host slot -> device -> train -> loss back to the host -------------
+    def train_batch_host(self, Z_host: torch.Tensor, d: int, **kw) -> torch.Tensor:
+        """One e2e step from a pinned host slot.  Returns a pinned fp64[4] tensor that will hold
+        (loss_sum, aux, fitted, extra) of the first pipeline once the current stream has drained."""
+        if self.device.type != "cuda":
+            self.train_batch(Z_host.clone(), d, **kw)
+            return self._read_stats_host()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        i = self._stage_i
+        self._stage_i ^= 1
+        cur = torch.cuda.current_stream(self.device)
+        if self._stage[i] is None or self._stage[i].shape != Z_host.shape:
+            self._stage[i] = torch.empty(Z_host.shape, dtype=torch.float32, device=self.device)
+        self._copy_stream.wait_stream(cur)      # the compute that last used this buffer is ordered before
+        with torch.cuda.stream(self._copy_stream):
+            self._stage[i].copy_(Z_host, non_blocking=True)
+            self.last_copy_event = torch.cuda.Event()
+            self.last_copy_event.record(self._copy_stream)
+        cur.wait_stream(self._copy_stream)
+        self.train_batch(self._stage[i], d, **kw)
+        return self._read_stats_host()
+
+    def _read_stats_host(self) -> torch.Tensor:
+        if self._loss_host is None:
+            self._loss_host = torch.zeros(4, dtype=torch.float64)
+            if self.device.type == "cuda":
+                self._loss_host = self._loss_host.pin_memory()
+        for p in self.pipelines.values():
+            if p.built:
+                self._loss_host.copy_(p.learner.stats, non_blocking=True)
+                break
+        return self._loss_host
+
+    def forecast_batch(self, Z: torch.Tensor, instances: Optional[List[DataInstance]] = None) -> List[str]:
+        """Every pipeline predicts every forecasting record with its local replica
+        (FlinkSpoke.scala:105, FlinkNetwork.scala:250)."""
+        out: List[str] = []
+        for pid, p in self.pipelines.items():
+            if not p.built:
+                continue
+            preds = p.forecast(Z).tolist()
+            for i, v in enumerate(preds):
+                di = instances[i] if instances else None
+                out.append(str(Prediction(pid, di, float(v))))
+        self.predictions += out
+        return out
+
+    # ============================================================================ termination / stats
+    def statistics(self) -> List[Statistics]:
+        out = []
+        ring = self._holdout_rows()
+        for pid, p in self.pipelines.items():
+            if not p.built:
+                continue
+            c = p.learner.counters()
+            k = p.driver.counters
+            out.append(Statistics(pipeline=pid, protocol=k.protocol, models=k.models, bytes=k.bytes, blocks=k.blocks,
+                                  fitted=c["fitted"], score=p.score(ring),
+                                  learningCurve=[x[0] for x in p.curve], lcx=[x[1] for x in p.curve]))
+        return out
+
+    def terminate(self) -> Optional[JobStatistics]:
+        """Termination probe: device barrier, final holdout evaluation, JobStatistics on rank 0
+        (StatisticsOperator.scala:93-142)."""
+        for p in self.pipelines.values():
+            if p.built and p.protocol != "SingleLearner":
+                p.driver.flush()
+                device_barrier(p.comm)
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        stats = self.statistics()
+        dur_ms = 1000.0 * ((self.t_last or 0.0) - (self.t_first or 0.0))
+        if self.world > 1:
+            import torch.distributed as dist
+            gathered: List[Any] = [None] * self.world
+            dist.all_gather_object(gathered, [s.to_dict() for s in stats], group=self.group)
+            if self.rank != 0:
+                return None
+            merged: Dict[int, Statistics] = {}
+            for per_rank in gathered:
+                for sd in per_rank:
+                    m = merged.setdefault(sd["pipeline"], Statistics(sd["pipeline"], sd["protocol"]))
+                    m.fitted += sd["fitted"]
+                    m.score += sd["score"] / self.world
+                    m.models, m.bytes, m.blocks = max(m.models, sd["models"]), m.bytes + sd["bytes"], \
+                        max(m.blocks, sd["blocks"])
+                    if not m.learningCurve:
+                        m.learningCurve, m.lcx = sd["learningCurve"], sd["lcx"]
+            stats = list(merged.values())
+        js = JobStatistics(self.params.jobName, self.world, dur_ms, stats)
+        if dur_ms > 0:
+            js.extra["recordsPerSec"] = sum(s.fitted for s in stats) / (dur_ms / 1000.0)
+            js.extra["syncBytesPerSec"] = sum(s.bytes for s in stats) / (dur_ms / 1000.0)
+        self.performance.append(str(js))
+        return js
+
+    def comm_status(self) -> int:
+        st = 0
+        for p in self.pipelines.values():
+            if p.built and p.comm.device.type == "cuda":
+                st |= p.comm.status()
+        return st
+
+    # ============================================================================ checkpoint
+    def state_dict(self) -> dict:
+        return {"rank": self.rank, "world": self.world, "count": self.count, "d": self.d,
+                "registry": self.pipeline_map.state_dict(),
+                "holdout": None if self.holdout is None else self.holdout.cpu().clone(),
+                "pipelines": {pid: p.state_dict() for pid, p in self.pipelines.items()}}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self.count, self.d = sd["count"], sd["d"]
+        self.pipeline_map.load_state_dict(sd["registry"])
+        if sd["holdout"] is not None:
+            self.holdout = sd["holdout"].to(self.device)
+        for pid, ps in sd["pipelines"].items():
+            req = Request.from_dict(ps["request"])
+            if pid not in self.pipelines:
+                self._process_control(req)
+            self.pipelines[pid].load_state_dict(ps)
+
+    def close(self) -> None:
+        for p in self.pipelines.values():
+            p.close()
+        self.pipelines = {}

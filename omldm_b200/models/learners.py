@@ -1,0 +1,279 @@
+"""Device learners: the eight learners of PipelineMap.scala:68 on staged record rows.
+
+Every learner keeps its synchronisable state in ONE flat fp32 vector that lives in the
+symmetric arena (`PipelineComm.buf`), so the protocol kernels can move it without packing:
+
+  merge "mean": buf = the model itself (PA / RegressorPA / SVM / MultiClassPA / NN), e = last
+                global estimate.
+  merge "sum" : buf = additive delta since the last sync (ORR Gram matrix, k-means sums/counts),
+                e = global statistics; derived quantities (ORR weights, centroids) are refreshed
+                after every sync.
+
+The maths mirrors `omldm_b200/oracle/learners.py` (fp64 oracle); kernels are in csrc/.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Dict, Optional
+
+import numpy as np
+import torch
+
+from ..ops import functional as F
+from ..oracle import learners as O
+from ..oracle.learners import _h, parse_variant
+
+
+def pad4(n: int) -> int:
+    return (n + 3) // 4 * 4
+
+
+class GpuLearner:
+    name = ""
+    task = "regression"
+    merge_mode = "mean"
+
+    def __init__(self, hyper: Optional[dict], device):
+        self.hyper = dict(hyper or {})
+        self.device = torch.device(device)
+        self.d: Optional[int] = None
+        self.mode = str(_h(hyper, ["trainingMode", "mode"], "minibatch"))
+        self.stats = torch.zeros(4, dtype=torch.float64, device=self.device)  # loss, aux, fitted, extra
+        self.buf: Optional[torch.Tensor] = None
+        self.e: Optional[torch.Tensor] = None
+
+    # ---- sizing / binding -------------------------------------------------------------
+    def n_flat(self, d: int) -> int:
+        raise NotImplementedError
+
+    def needs_e(self) -> bool:
+        return True
+
+    def bind(self, d: int, buf: torch.Tensor, e: Optional[torch.Tensor]) -> None:
+        """`buf` is the symmetric flat vector (zero-filled), `e` a private vector of equal size."""
+        self.d, self.buf, self.e = d, buf, e
+        self.ld = F.pad32(d + 2)
+        self._init()
+
+    def _init(self) -> None: ...
+
+    # ---- training / inference -----------------------------------------------------------
+    def fit_batch(self, Z: torch.Tensor) -> None:
+        raise NotImplementedError
+
+    def predict(self, Z: torch.Tensor) -> torch.Tensor:
+        raise NotImplementedError
+
+    def after_sync(self) -> None:
+        """Refresh derived state once the protocol installed a new global model."""
+
+    def score(self, Z: torch.Tensor) -> float:
+        """accuracy / RMSE / mean inertia on staged holdout rows (empty rows are ignored)."""
+        if Z.shape[0] == 0:
+            return 0.0
+        valid = Z[:, self.d] != 0
+        if not bool(valid.any()):
+            return 0.0
+        p = self.predict(Z)[valid]
+        y = Z[valid, self.d + 1]
+        if self.task == "classification":
+            return float((self._labels(p) == self._labels_true(y)).float().mean().item())
+        return float(torch.sqrt(((p - y) ** 2).mean()).item())
+
+    def _labels(self, p):
+        return torch.where(p > 0, 1.0, -1.0)
+
+    def _labels_true(self, y):
+        return torch.where(y > 0, 1.0, -1.0)
+
+    # ---- bookkeeping ----------------------------------------------------------------------
+    def counters(self) -> Dict[str, float]:
+        s = self.stats.tolist()
+        return {"loss_sum": s[0], "aux": s[1], "fitted": int(s[2]), "extra": s[3]}
+
+    def to_oracle(self) -> O.OracleLearner:
+        raise NotImplementedError
+
+    def from_oracle(self, o: O.OracleLearner) -> None:
+        raise NotImplementedError
+
+    def to_parameters(self) -> Dict[str, Any]:
+        return self.to_oracle().to_parameters()
+
+    def data_structure(self) -> Optional[Dict[str, Any]]:
+        return None
+
+    def state_dict(self) -> dict:
+        return {"d": self.d, "buf": None if self.buf is None else self.buf.detach().cpu().clone(),
+                "e": None if self.e is None else self.e.detach().cpu().clone(), "stats": self.stats.cpu().clone()}
+
+    def load_state_dict(self, sd: dict) -> None:
+        if sd["buf"] is not None:
+            self.buf.copy_(sd["buf"].to(self.device))
+        if sd["e"] is not None and self.e is not None:
+            self.e.copy_(sd["e"].to(self.device))
+        self.stats.copy_(sd["stats"].to(self.device))
+        self.after_sync()
+
+
+# ====================================================================================== linear
+class GpuLinear(GpuLearner):
+    """PA classifier / PA regressor / Pegasos SVM (csrc/linear_learners.cu)."""
+    kind = F.KIND_PA
+
+    def __init__(self, hyper, device):
+        super().__init__(hyper, device)
+        self.C = float(_h(hyper, ["C", "c"], 0.01))
+        self.variant = parse_variant(hyper)
+        self.eps = float(_h(hyper, ["epsilon", "eps"], 0.1))
+        self.lam = float(_h(hyper, ["lambda", "lam", "regularization"], 0.01))
+        self.mean_update = str(_h(hyper, ["miniBatchUpdate"], "mean")) == "mean"
+
+    def n_flat(self, d):
+        return pad4(d + 1)
+
+    def _init(self):
+        self.w = self.buf[: self.d + 1]
+        self.scratch = F.linear_minibatch_scratch(self.d, self.device)
+        self._desc = None
+
+    def fit_batch(self, Z):
+        if self.mode == "exact":
+            if self._desc is None and Z.is_cuda:
+                self._desc = F.make_linear_descs([(self.w, self.stats, self.d, self.kind, self.variant, self.C,
+                                                   self.eps, self.lam)], self.device)
+            F.linear_exact(Z, self.d, self.w, self.stats, self.kind, self.variant, self.C, self.eps, self.lam,
+                           desc_dev=self._desc if F.native(Z) else None)
+        else:
+            F.linear_minibatch(Z, self.d, self.w, self.stats, self.scratch, self.kind, self.variant, self.C,
+                               self.eps, self.lam, self.mean_update)
+
+    def predict(self, Z):
+        return F.linear_predict(Z, self.d, self.w)
+
+    def _oracle_cls(self):
+        return O.PAClassifier
+
+    def to_oracle(self):
+        o = self._oracle_cls()(self.hyper)
+        o.ensure_init(self.d)
+        o.w = self.w.detach().double().cpu().numpy().copy()
+        c = self.counters()
+        o.fitted, o.cum_loss = c["fitted"], c["loss_sum"]
+        if hasattr(o, "t"):
+            o.t = int(c["extra"])
+        return o
+
+    def from_oracle(self, o):
+        self.w.copy_(torch.from_numpy(np.asarray(o.w, dtype=np.float32)).to(self.device))
+
+
+class GpuPA(GpuLinear):
+    name, task, kind = "PA", "classification", F.KIND_PA
+
+
+class GpuRegressorPA(GpuLinear):
+    name, task, kind = "RegressorPA", "regression", F.KIND_PA_REG
+
+    def _oracle_cls(self):
+        return O.PARegressor
+
+
+class GpuSVM(GpuLinear):
+    name, task, kind = "SVM", "classification", F.KIND_SVM
+
+    def _oracle_cls(self):
+        return O.SVM
+
+
+# ====================================================================================== ORR
+class GpuORR(GpuLearner):
+    """Online ridge regression on the augmented Gram matrix G = sum [x,1,y]^T [x,1,y].
+
+    One tcgen05 GEMM per mini-batch (csrc/umma_gemm.cu, MN-major operands straight from the staged
+    rows, upper-triangular tiles only, split-K with red.add epilogue).  A - lambda I, b and y^T y
+    are all blocks of G, so replicas merge by addition.
+    """
+    name, task, merge_mode = "ORR", "regression", "sum"
+
+    def __init__(self, hyper, device):
+        super().__init__(hyper, device)
+        self.lam = float(_h(hyper, ["lambda", "lam", "regularization"], 1.0))
+        self.solve_every = int(_h(hyper, ["solveEvery"], 16))
+        self._since = 0
+        self.solves = 0
+
+    def n_flat(self, d):
+        ld = F.pad32(d + 2)
+        return ld * ld
+
+    def _init(self):
+        ld = self.ld
+        self.dG = self.buf.view(ld, ld)
+        self.G = self.e.view(ld, ld)
+        self.wt = torch.zeros(self.d + 2, device=self.device)   # [w, b, -1]
+        self.wt[self.d + 1] = -1.0
+        self._work = torch.empty(ld, ld, device=self.device)
+        n = self.d + 2
+        tiles = sum(1 for mi in range((n + 127) // 128) for nj in range((n + 255) // 256)
+                    if not (128 * mi > 256 * nj + 255))
+        self.ksplit = max(1, 148 // max(tiles, 1))
+        if self.device.type == "cuda":
+            # create the cuSOLVER handle / workspaces now, not inside somebody's timed region
+            eye = torch.eye(self.d + 1, device=self.device)
+            L, _ = torch.linalg.cholesky_ex(eye)
+            torch.cholesky_solve(eye[:, :1], L)
+
+    def fit_batch(self, Z):
+        F.sq_residual(Z, self.d, self.wt, self.stats)    # prequential squared error with current w
+        n = self.d + 2
+        ks = max(1, min(self.ksplit, Z.shape[0] // 64))
+        F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+        self._since += 1
+        if self._since >= self.solve_every:
+            self.solve()
+
+    def after_sync(self):
+        pass   # the solve cadence is driven by `solveEvery`, and always runs before a query
+
+    def solve(self):
+        """w = (G_A + lambda I)^-1 G_b by Cholesky on the mirrored upper triangle."""
+        d1 = self.d + 1
+        torch.add(self.G, self.dG, out=self._work)
+        F.mirror_upper(self._work, self.d + 2)
+        A = self._work[:d1, :d1].clone()
+        A.diagonal().add_(self.lam)
+        b = self._work[:d1, d1].clone()
+        L, info = torch.linalg.cholesky_ex(A)
+        if int(info.item()) != 0:
+            w = torch.linalg.solve(A.double(), b.double()).float()
+        else:
+            w = torch.cholesky_solve(b[:, None], L)[:, 0]
+        self.wt[:d1] = w
+        self._since = 0
+        self.solves += 1
+
+    def predict(self, Z):
+        return Z[:, : self.d + 1] @ self.wt[: self.d + 1]
+
+    def to_oracle(self):
+        self.solve()
+        o = O.ORR(self.hyper)
+        o.ensure_init(self.d)
+        n = self.d + 2
+        o.G = self._work[:n, :n].detach().double().cpu().numpy().copy()
+        o.w = self.wt[: self.d + 1].detach().double().cpu().numpy().copy()
+        c = self.counters()
+        o.fitted, o.cum_loss = c["fitted"], c["loss_sum"]
+        return o
+
+    def from_oracle(self, o):
+        n = self.d + 2
+        self.G.zero_()
+        self.dG.zero_()
+        self.G[:n, :n] = torch.from_numpy(o.G.astype(np.float32)).to(self.device)
+        self.solve()
+
+    def load_state_dict(self, sd):
+        super().load_state_dict(sd)
+        self.solve()

@@ -1,0 +1,352 @@
+"""Device learners, part 2: k-means, multiclass PA, neural network, Hoeffding tree (see learners.py)."""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import numpy as np
+import torch
+
+from ..ops import functional as F
+from ..oracle import learners as O
+from ..oracle.learners import _h, parse_variant
+from .learners import GpuLearner, GpuORR, GpuPA, GpuRegressorPA, GpuSVM, pad4
+
+
+class GpuKMeans(GpuLearner):
+    """Online k-means on additive statistics; distances X C^T and updates T^T Z on tcgen05.
+
+    Distributed k-means (BASELINE.json config 4) is a capability the reference does not have: it
+    forces K-means to a single central learner (FlinkSpoke.scala:207-209).
+    """
+    name, task, merge_mode = "K-means", "clustering", "sum"
+
+    def __init__(self, hyper, device):
+        super().__init__(hyper, device)
+        self.k = int(_h(hyper, ["k", "K", "nClusters", "clusters"], 8))
+        self._boot = False
+
+    def n_flat(self, d):
+        return self.k * F.pad32(d + 2)
+
+    def _init(self):
+        K, ld = self.k, self.ld
+        self.dS = self.buf.view(K, ld)
+        self.S = self.e.view(K, ld)
+        self.centroids = torch.zeros(K, ld, device=self.device)
+        self.cnorm = torch.full((K,), float("inf"), device=self.device)
+        self._T = None
+        self._Sc = None
+
+    def _bufs(self, B):
+        if self._T is None or self._T.shape[0] < B:
+            self._T = torch.empty(B, F.pad32(self.k), device=self.device)
+            self._Sc = torch.empty(B, pad4(self.k), device=self.device)
+        return self._T[:B], self._Sc[:B]
+
+    def refresh(self):
+        F.kmeans_finalize(self.dS, self.S, self.k, self.d, self.centroids, self.cnorm)
+
+    def after_sync(self):
+        self.refresh()
+
+    def fit_batch(self, Z):
+        B = Z.shape[0]
+        start = 0
+        if not self._boot:
+            # bootstrap: the first records claim the empty centroids in exact (MacQueen) order
+            nb = min(B, max(2 * self.k, 64))
+            F.kmeans_exact(Z[:nb], self.d, self.dS, self.k, self.stats)
+            self.refresh()
+            self._boot = True
+            start = nb
+            if start >= B:
+                return
+        Zb = Z[start:]
+        if self.mode == "exact":
+            F.kmeans_exact(Zb, self.d, self.dS, self.k, self.stats)   # against local statistics only
+            self.refresh()
+            return
+        T, Sc = self._bufs(Zb.shape[0])
+        F.gemm_tn(Zb[:, : self.d], self.centroids[:, : self.d], Sc[:, : self.k])
+        F.kmeans_assign(Zb, self.d, Sc, self.cnorm, self.k, T, self.stats)
+        F.gemm_outer(T, Zb, self.dS, accumulate=True, m=self.k, n=self.d + 1,
+                     ksplit=max(1, min(32, Zb.shape[0] // 256)))
+        self.refresh()
+
+    def predict(self, Z):
+        T, Sc = self._bufs(Z.shape[0])
+        F.gemm_tn(Z[:, : self.d], self.centroids[:, : self.d], Sc[:, : self.k])
+        return (self.cnorm[None, :] - 2 * Sc[:, : self.k]).argmin(1).float()
+
+    def score(self, Z):
+        if Z.shape[0] == 0 or not self._boot:
+            return 0.0
+        valid = Z[:, self.d] != 0
+        if not bool(valid.any()):
+            return 0.0
+        T, Sc = self._bufs(Z.shape[0])
+        F.gemm_tn(Z[:, : self.d], self.centroids[:, : self.d], Sc[:, : self.k])
+        dist = (Z[:, : self.d] ** 2).sum(1) + (self.cnorm[None, :] - 2 * Sc[:, : self.k]).min(1).values
+        return float(dist[valid].clamp_min(0).mean().item())
+
+    def to_oracle(self):
+        o = O.KMeans(self.hyper)
+        o.ensure_init(self.d)
+        tot = (self.S + self.dS)[:, : self.d + 1].detach().double().cpu().numpy()
+        o.S = tot.copy()
+        c = self.counters()
+        o.fitted, o.cum_loss = c["fitted"], c["loss_sum"]
+        return o
+
+    def from_oracle(self, o):
+        self.S.zero_(); self.dS.zero_()
+        self.S[:, : self.d + 1] = torch.from_numpy(o.S.astype(np.float32)).to(self.device)
+        self._boot = bool((o.S[:, -1] > 0).any())
+        self.refresh()
+
+    def load_state_dict(self, sd):
+        super().load_state_dict(sd)
+        self._boot = bool(((self.S + self.dS)[:, self.d] > 0).any().item())
+
+
+class GpuMultiClassPA(GpuLearner):
+    """Multiclass PA: scores X W^T and the update T^T X both on tcgen05 (csrc/umma_gemm.cu)."""
+    name, task, merge_mode = "MultiClassPA", "classification", "mean"
+
+    def __init__(self, hyper, device):
+        super().__init__(hyper, device)
+        self.C = float(_h(hyper, ["C", "c"], 0.01))
+        self.variant = parse_variant(hyper)
+        self.n_classes = int(_h(hyper, ["nClasses", "classes", "numClasses"], 10))
+        self.mean_update = str(_h(hyper, ["miniBatchUpdate"], "mean")) == "mean"
+        self.max_rows = int(_h(hyper, ["exactChunk"], 1))
+
+    def n_flat(self, d):
+        return self.n_classes * F.pad32(d + 2)
+
+    def _init(self):
+        self.W = self.buf.view(self.n_classes, self.ld)
+        self._T = None
+        self._act = torch.zeros(1, device=self.device)
+
+    def _bufs(self, B):
+        if self._T is None or self._T.shape[0] < B:
+            self._T = torch.empty(B, F.pad32(self.n_classes), device=self.device)
+            self._S = torch.empty(B, pad4(self.n_classes), device=self.device)
+        return self._T[:B], self._S[:B]
+
+    def _step(self, Z, sqnorm=None):
+        C, d = self.n_classes, self.d
+        T, S = self._bufs(Z.shape[0])
+        ks = max(1, min(16, (d + 1) // 4096))
+        F.gemm_tn(Z[:, : d + 1], self.W[:, : d + 1], S[:, :C], ksplit=ks)
+        if sqnorm is None:
+            sqnorm = F.row_sqnorm(Z, self.ld)   # pad columns are zero, target excluded below
+            sqnorm = sqnorm - Z[:, d + 1] ** 2
+        prev = self.stats[3].clone()
+        F.mcpa_coef(Z, d, S, C, sqnorm, self.variant, self.C, T, self.stats)
+        if self.mean_update:
+            self._act.copy_((self.stats[3] - prev).float().reshape(1))
+            F.scale_rows(T, C, self._act, reciprocal=True)
+        F.gemm_outer(T, Z, self.W, accumulate=True, m=C, n=d + 1, ksplit=max(1, min(8, Z.shape[0] // 256)))
+
+    def fit_batch(self, Z, sqnorm=None):
+        if self.mode == "exact":
+            for r in range(Z.shape[0]):   # per-record order; the GEMMs degenerate to GEMVs
+                self._step(Z[r:r + 1], None if sqnorm is None else sqnorm[r:r + 1])
+        else:
+            self._step(Z, sqnorm)
+
+    def predict(self, Z):
+        T, S = self._bufs(Z.shape[0])
+        F.gemm_tn(Z[:, : self.d + 1], self.W[:, : self.d + 1], S[:, : self.n_classes])
+        return S[:, : self.n_classes].argmax(1).float()
+
+    def _labels(self, p):
+        return p
+
+    def _labels_true(self, y):
+        return torch.round(y)
+
+    def to_oracle(self):
+        o = O.MultiClassPA(self.hyper)
+        o.ensure_init(self.d)
+        o.W = self.W[:, : self.d + 1].detach().double().cpu().numpy().copy()
+        c = self.counters()
+        o.fitted, o.cum_loss = c["fitted"], c["loss_sum"]
+        return o
+
+    def from_oracle(self, o):
+        self.W.zero_()
+        self.W[:, : self.d + 1] = torch.from_numpy(o.W.astype(np.float32)).to(self.device)
+
+
+class GpuNN(GpuLearner):
+    """Small MLP (ReLU) trained by mini-batch SGD; forward X W^T and weight gradients dH^T A run on
+    the tcgen05 GEMMs, the element-wise glue is torch."""
+    name, merge_mode = "NN", "mean"
+
+    def __init__(self, hyper, device):
+        super().__init__(hyper, device)
+        self.hidden = [int(h) for h in _h(hyper, ["hiddenLayers", "hidden", "layers"], [32])]
+        self.lr = float(_h(hyper, ["learningRate", "lr"], 0.01))
+        self.n_classes = int(_h(hyper, ["nClasses", "classes"], 0))
+        self.task = "classification" if self.n_classes > 1 else "regression"
+        self.seed = int(_h(hyper, ["seed"], 0))
+
+    def _sizes(self, d):
+        return [d] + self.hidden + [self.n_classes if self.n_classes > 1 else 1]
+
+    def n_flat(self, d):
+        s = self._sizes(d)
+        return sum(s[i + 1] * F.pad32(s[i] + 1) for i in range(len(s) - 1))
+
+    def _init(self):
+        s = self._sizes(self.d)
+        ref = O.NN(self.hyper)
+        ref.ensure_init(self.d)       # same seed -> same initial weights as the oracle, on every rank
+        self.layers = []
+        o = 0
+        for i in range(len(s) - 1):
+            ldw = F.pad32(s[i] + 1)
+            W = self.buf[o:o + s[i + 1] * ldw].view(s[i + 1], ldw)
+            W.zero_()
+            W[:, : s[i] + 1] = torch.from_numpy(ref.layers[i].astype(np.float32)).to(self.device)
+            self.layers.append(W)
+            o += s[i + 1] * ldw
+        self.sizes = s
+        if self.e is not None:
+            self.e.copy_(self.buf)
+
+    def _forward(self, Z):
+        """Returns activations with a trailing ones column (pitch pad32)."""
+        B = Z.shape[0]
+        acts = [Z]
+        a, fan_in = Z, self.d
+        for i, W in enumerate(self.layers):
+            out_dim = self.sizes[i + 1]
+            H = torch.zeros(B, F.pad32(out_dim + 1), device=self.device)
+            F.gemm_tn(a[:, : fan_in + 1], W[:, : fan_in + 1], H[:, :out_dim])
+            if i < len(self.layers) - 1:
+                H[:, :out_dim].clamp_(min=0)
+                H[:, out_dim] = 1.0
+            acts.append(H)
+            a, fan_in = H, out_dim
+        return acts
+
+    def fit_batch(self, Z):
+        d = self.d
+        valid = (Z[:, d] != 0).float()
+        nv = valid.sum().clamp_min(1.0)
+        acts = self._forward(Z)
+        out_dim = self.sizes[-1]
+        out = acts[-1][:, :out_dim]
+        y = Z[:, d + 1]
+        if self.n_classes > 1:
+            p = torch.softmax(out, 1)
+            yi = torch.round(y).long().clamp(0, out_dim - 1)
+            ll = -torch.log(p.gather(1, yi[:, None]).squeeze(1).clamp_min(1e-30))
+            g = p.clone()
+            g[torch.arange(Z.shape[0], device=self.device), yi] -= 1.0
+            loss = (ll * valid).sum()
+        else:
+            err = out[:, 0] - y
+            g = (2.0 * err)[:, None]
+            loss = (err * err * valid).sum()
+        g = g * (valid / nv)[:, None]
+        self.stats[0] += loss.double()
+        self.stats[2] += valid.sum().double()
+        for i in range(len(self.layers) - 1, -1, -1):
+            fan_in, od = self.sizes[i], self.sizes[i + 1]
+            G = torch.zeros(Z.shape[0], F.pad32(od), device=self.device)
+            G[:, :od] = g
+            W = self.layers[i]
+            g_prev = None
+            if i > 0:
+                g_prev = (G[:, :od] @ W[:, :fan_in]) * (acts[i][:, :fan_in] > 0)
+            gW = torch.zeros(od, W.shape[1], device=self.device)
+            F.gemm_outer(G, acts[i], gW, accumulate=True, m=od, n=fan_in + 1)
+            W.sub_(gW, alpha=self.lr)
+            g = g_prev
+
+    def predict(self, Z):
+        out = self._forward(Z)[-1][:, : self.sizes[-1]]
+        return out.argmax(1).float() if self.n_classes > 1 else out[:, 0]
+
+    def _labels(self, p):
+        return p if self.n_classes > 1 else super()._labels(p)
+
+    def _labels_true(self, y):
+        return torch.round(y) if self.n_classes > 1 else super()._labels_true(y)
+
+    def to_oracle(self):
+        o = O.NN(self.hyper)
+        o.ensure_init(self.d)
+        for i, W in enumerate(self.layers):
+            o.layers[i] = W[:, : self.sizes[i] + 1].detach().double().cpu().numpy().copy()
+        c = self.counters()
+        o.fitted, o.cum_loss = c["fitted"], c["loss_sum"]
+        return o
+
+    def from_oracle(self, o):
+        for i, W in enumerate(self.layers):
+            W.zero_()
+            W[:, : self.sizes[i] + 1] = torch.from_numpy(o.layers[i].astype(np.float32)).to(self.device)
+
+
+class GpuHT(GpuLearner):
+    """Hoeffding tree.  The reference never distributes it (forced SingleLearner,
+    FlinkSpoke.scala:204-206); the irregular tree lives on the host (fp64 oracle implementation)
+    and is fed from the staged rows."""
+    name, task, merge_mode = "HT", "classification", "none"
+
+    def __init__(self, hyper, device):
+        super().__init__(hyper, device)
+        self.tree = O.HoeffdingTree(hyper)
+
+    def n_flat(self, d):
+        return 4
+
+    def needs_e(self):
+        return False
+
+    def _init(self):
+        self.tree.ensure_init(self.d)
+
+    def fit_batch(self, Z):
+        h = Z[:, : self.d + 2].detach().cpu().double().numpy()
+        for r in h:
+            if r[self.d] != 0:
+                self.tree.fit(r[: self.d], r[self.d + 1])
+        self.stats[0] = self.tree.cum_loss
+        self.stats[2] = self.tree.fitted
+
+    def predict(self, Z):
+        h = Z[:, : self.d].detach().cpu().double().numpy()
+        return torch.tensor([self.tree.predict(r) for r in h], device=self.device, dtype=torch.float32)
+
+    def _labels(self, p):
+        return p
+
+    def _labels_true(self, y):
+        c = torch.round(y)
+        return torch.where(c < 0, torch.zeros_like(c), c) if self.tree.n_classes == 2 else c
+
+    def to_oracle(self):
+        return self.tree
+
+    def from_oracle(self, o):
+        self.tree = o
+
+    def data_structure(self):
+        return self.tree.data_structure()
+
+
+GPU_LEARNERS = {c.name: c for c in (GpuPA, GpuRegressorPA, GpuSVM, GpuORR, GpuKMeans, GpuMultiClassPA, GpuNN, GpuHT)}
+
+
+def make_gpu_learner(name: str, hyper: Optional[dict], device) -> GpuLearner:
+    if name not in GPU_LEARNERS:
+        raise KeyError(f"unknown learner {name!r}")
+    return GPU_LEARNERS[name](hyper, device)

@@ -1,0 +1,160 @@
+"""Device ML pipeline: ordered preprocessors + one learner + its protocol driver.
+
+A pipeline is what one `Create` request builds (Request.getPreProcessors + getLearner,
+PipelineMap.scala:23-30); every worker holds one replica per pipeline
+(operators/spoke/SpokeLogic.scala:28-29) and the protocol driver reconciles the replicas.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from ..api.pojos import LearnerPOJO, PreprocessorPOJO, QueryResponse, Request
+from ..parallel.comm import PipelineComm
+from ..parallel.fused import SyncDriver, make_driver
+from ..parallel.host_protocols import cfg
+from .learners import GpuLearner
+from .learners2 import make_gpu_learner
+from .preprocessors import GpuPreprocessor, make_gpu_preprocessor
+
+
+def effective_protocol(request: Request, world: int, distributed_kmeans: bool) -> str:
+    """Protocol rewrites of FlinkSpoke.scala:202-216 / FlinkHub.scala:185-190."""
+    tc = request.trainingConfiguration or {}
+    proto = tc.get("protocol")
+    from ..parallel.fused import DRIVERS
+    if proto not in DRIVERS:
+        proto = "Asynchronous"                       # MLNodeGenerator.scala:34-43 fallback
+    name = request.learner.name
+    if name == "HT" or (name == "K-means" and not distributed_kmeans):
+        return "SingleLearner"
+    if world == 1:
+        return "CentralizedTraining"
+    return proto
+
+
+class GpuPipeline:
+    def __init__(self, request: Request, device, rank: int, world: int, *, impl: str = "fused", group=None,
+                 distributed_kmeans: bool = True, max_msg_params: int = 2000, emulate: int = 1):
+        self.request = request
+        self.device = torch.device(device)
+        self.rank, self.world, self.impl, self.group, self.emulate = rank, world, impl, group, emulate
+        self.max_msg_params = max_msg_params
+        self.protocol = effective_protocol(request, world, distributed_kmeans)
+        self.preprocessors: List[GpuPreprocessor] = [
+            make_gpu_preprocessor(p.name, p.hyperParameters, self.device) for p in (request.preProcessors or [])]
+        hyper = dict(request.learner.hyperParameters or {})
+        tc = request.trainingConfiguration or {}
+        if "trainingMode" in tc and "trainingMode" not in hyper:
+            hyper["trainingMode"] = tc["trainingMode"]
+        self.learner: GpuLearner = make_gpu_learner(request.learner.name, hyper, self.device)
+        self.comm: Optional[PipelineComm] = None
+        self.driver: Optional[SyncDriver] = None
+        self.d_in: Optional[int] = None
+        self.batches = 0
+        self.curve: List[tuple] = []
+        self._win_loss = 0.0
+        self._win_n = 0
+        self._inplace = any(p.name != "PolynomialFeatures" for p in self.preprocessors[:1])
+
+    @property
+    def built(self) -> bool:
+        return self.comm is not None
+
+    def build(self, d_in: int) -> None:
+        """Allocate the symmetric region and bind everything.  COLLECTIVE when world > 1: every rank
+        must build its pipelines in the same order."""
+        self.d_in = d_in
+        d = d_in
+        for p in self.preprocessors:
+            p.bind(d)
+            d = p.out_dim(d)
+        lrn = self.learner
+        n = lrn.n_flat(d)
+        single = self.protocol == "SingleLearner"
+        world = 1 if single else self.world
+        self.comm = PipelineComm(n, self.device, self.rank if not single else 0, world, self.group,
+                                 emulate=1, with_hub=True)
+        e = torch.zeros(self.comm.n, device=self.device) if lrn.needs_e() else None
+        lrn.bind(d, self.comm.buf, e)
+        self.driver = make_driver(self.protocol, self.comm, e, lrn.merge_mode,
+                                  self.request.trainingConfiguration, self.impl, self.group, self.max_msg_params)
+        init = self.request.learner.parameters
+        if init and init.get("a") is not None:       # warm start from a serialized model
+            o = lrn.to_oracle()
+            o.from_parameters(init)
+            lrn.from_oracle(o)
+            if e is not None and lrn.merge_mode == "mean":
+                e.copy_(self.comm.buf)
+
+    # ------------------------------------------------------------------ data path
+    def preprocess(self, Z: torch.Tensor, fit: bool, protect_input: bool) -> torch.Tensor:
+        if self.preprocessors and self._inplace and protect_input:
+            Z = Z.clone()
+        for p in self.preprocessors:
+            Z = p.apply(Z, fit)
+        return Z
+
+    def train(self, Z: torch.Tensor, protect_input: bool = False, **kw) -> None:
+        if not self.built:
+            from ..ops.functional import pad32
+            self.build(self._infer_dim(Z))
+        Zp = self.preprocess(Z, True, protect_input)
+        self.learner.fit_batch(Zp, **kw)
+        self.batches += 1
+        if self.driver.after_batch():
+            self.learner.after_sync()
+
+    def _infer_dim(self, Z: torch.Tensor) -> int:
+        d = cfg(self.request.trainingConfiguration, ["nFeatures", "dim"], None)
+        if d is None:
+            d = (self.request.learner.hyperParameters or {}).get("nFeatures")
+        if d is None:
+            raise ValueError("feature dimension unknown: pass nFeatures or use Engine.train_batch(Z, d)")
+        return int(d)
+
+    def forecast(self, Z: torch.Tensor) -> torch.Tensor:
+        return self.learner.predict(self.preprocess(Z, False, True))
+
+    def score(self, ring: torch.Tensor) -> float:
+        if not self.built or ring.shape[0] == 0:
+            return 0.0
+        return self.learner.score(self.preprocess(ring, False, True))
+
+    # ------------------------------------------------------------------ control path
+    def local_response(self, response_id: int, ring: torch.Tensor) -> QueryResponse:
+        lrn = self.learner
+        pps = [PreprocessorPOJO(p.name, dict(p.hyper), p.to_parameters() if self.built else None, None)
+               for p in self.preprocessors]
+        if not self.built:
+            return QueryResponse(response_id, None, self.request.id, pps,
+                                 LearnerPOJO(lrn.name, dict(lrn.hyper), None, None), self.protocol, 0, 0.0, 0.0, 0.0)
+        c = lrn.counters()
+        win_n = c["fitted"] - self._win_n
+        loss = (c["loss_sum"] - self._win_loss) / win_n if win_n > 0 else 0.0
+        self._win_loss, self._win_n = c["loss_sum"], c["fitted"]
+        pojo = LearnerPOJO(lrn.name, dict(lrn.hyper), lrn.to_parameters(), lrn.data_structure())
+        return QueryResponse(response_id, None, self.request.id, pps, pojo, self.protocol, c["fitted"], loss,
+                             c["loss_sum"], self.score(ring))
+
+    def state_dict(self) -> dict:
+        return {"request": self.request.to_dict(), "d_in": self.d_in, "batches": self.batches,
+                "learner": self.learner.state_dict() if self.built else None,
+                "pre": [p.state_dict() for p in self.preprocessors] if self.built else None,
+                "epoch": self.comm.epoch if self.built else 0, "clock": self.comm.clock if self.built else 0}
+
+    def load_state_dict(self, sd: dict) -> None:
+        if sd["learner"] is None:
+            return
+        if not self.built:
+            self.build(sd["d_in"])
+        self.learner.load_state_dict(sd["learner"])
+        for p, s in zip(self.preprocessors, sd["pre"]):
+            p.load_state_dict(s)
+        self.batches = sd["batches"]
+
+    def close(self) -> None:
+        if self.comm is not None:
+            self.comm.close()
+            self.comm = None

@@ -1,0 +1,474 @@
+"""Python surface of the sm_100a kernels (csrc/*.cu), one function per kernel.
+
+Every op has two implementations with identical semantics:
+
+* native - the hand-written CUDA kernel through the C ABI (mandatory for CUDA tensors unless the
+  torch implementation is selected explicitly);
+* torch  - plain PyTorch ops.  It is (a) what runs on CPU tensors so host-side logic is testable
+  without a GPU, and (b) with `use_impl("torch")` on CUDA tensors, the PyTorch(+cuBLAS) baseline
+  the native path is measured against (BASELINE.md "what the build measures itself against").
+
+Staged record rows ("Z rows", pitch ld, multiple of 32 floats):
+    [ x_0..x_{d-1} | 1.0 bias/valid (0 = empty row) | target | zero pad ]
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from .gemm import gemm_outer, gemm_tn  # noqa: F401  (re-exported)
+
+_IMPL = "auto"
+
+
+@contextlib.contextmanager
+def use_impl(name: str):
+    """Force the implementation: "native", "torch" or "auto" (native on CUDA tensors)."""
+    global _IMPL
+    old, _IMPL = _IMPL, name
+    try:
+        yield
+    finally:
+        _IMPL = old
+
+
+def set_impl(name: str) -> None:
+    global _IMPL
+    _IMPL = name
+
+
+def native(*tensors: torch.Tensor) -> bool:
+    if _IMPL == "torch":
+        return False
+    on_gpu = any(t is not None and t.is_cuda for t in tensors)
+    if _IMPL == "native" and not on_gpu:
+        raise _lib.NativeError("native implementation requested for CPU tensors")
+    return on_gpu
+
+
+def pad32(n: int) -> int:
+    return (n + 31) // 32 * 32
+
+
+def _k():
+    return _lib.kernels()
+
+
+_i = ctypes.c_int
+_f = ctypes.c_float
+_p = _lib.ptr
+
+
+class LinearDesc(ctypes.Structure):
+    _fields_ = [("w", ctypes.c_void_p), ("stats", ctypes.c_void_p), ("d", ctypes.c_int),
+                ("kind", ctypes.c_int), ("variant", ctypes.c_int), ("C", ctypes.c_float),
+                ("eps", ctypes.c_float), ("lam", ctypes.c_float)]
+
+
+class CommStruct(ctypes.Structure):
+    _fields_ = [("bufs", ctypes.c_void_p), ("hubs", ctypes.c_void_p), ("pads", ctypes.c_void_p),
+                ("local", ctypes.c_void_p), ("mc_buf", ctypes.c_void_p), ("rank", ctypes.c_int),
+                ("world", ctypes.c_int), ("emulate", ctypes.c_int)]
+
+
+KIND_PA, KIND_PA_REG, KIND_SVM = 0, 1, 2
+
+
+# ------------------------------------------------------------------------------ ingest
+def holdouts_before(c: int) -> int:
+    r = c % 10
+    return 2 * (c // 10) + (r - 8 if r > 8 else 0)
+
+
+def holdout_swap(Z: torch.Tensor, ring: torch.Tensor, d: int, count0: int) -> None:
+    """In-place 2-in-10 holdout with evict-then-train (FlinkSpoke.scala:92-107)."""
+    B, ld = Z.shape
+    cap = ring.shape[0]
+    if native(Z, ring):
+        _lib.check(_k().omldm_holdout_swap(_p(Z), _i(ld), _i(B), _i(d), _p(ring), _i(cap),
+                                           ctypes.c_longlong(count0), _lib.stream_ptr()), "holdout_swap")
+        return
+    h0, h1 = holdouts_before(count0), holdouts_before(count0 + B)
+    for h in range(h0, h1):
+        c = (h // 2) * 10 + 8 + (h & 1)
+        i, slot = c - count0, h % cap
+        new = Z[i].clone()
+        Z[i] = ring[slot] if h >= cap else 0.0
+        ring[slot] = new
+
+
+def stage_rows(raw: torch.Tensor, d: int, ld: Optional[int] = None) -> torch.Tensor:
+    """[B, d+1] (features..., target) -> staged rows [B, ld]."""
+    B = raw.shape[0]
+    ld = ld or pad32(d + 2)
+    Z = torch.empty(B, ld, device=raw.device, dtype=torch.float32)
+    if native(raw):
+        _lib.check(_k().omldm_stage_rows(_p(raw), _i(raw.stride(0)), _i(B), _i(d), _p(Z), _i(ld),
+                                         _lib.stream_ptr()), "stage_rows")
+        return Z
+    Z.zero_()
+    Z[:, :d] = raw[:, :d]
+    Z[:, d] = 1.0
+    Z[:, d + 1] = raw[:, d]
+    return Z
+
+
+def densify(indptr: torch.Tensor, indices: torch.Tensor, values: torch.Tensor, targets: Optional[torch.Tensor],
+            d: int, ld: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """CSR batch -> staged dense rows and squared row norms (bias included)."""
+    B = indptr.numel() - 1
+    ld = ld or pad32(d + 2)
+    Z = torch.empty(B, ld, device=values.device, dtype=torch.float32)
+    sq = torch.empty(B, device=values.device, dtype=torch.float32)
+    if native(values):
+        _lib.check(_k().omldm_densify(_p(indptr), _p(indices), _p(values), _i(B), _i(d), _p(targets), _p(Z),
+                                      _i(ld), _p(sq), _lib.stream_ptr()), "densify")
+        return Z, sq
+    Z.zero_()
+    rows = torch.repeat_interleave(torch.arange(B, device=values.device), (indptr[1:] - indptr[:-1]).long())
+    ok = (indices >= 0) & (indices < d)
+    Z.index_put_((rows[ok], indices[ok].long()), values[ok], accumulate=True)
+    sq.zero_()
+    sq.index_add_(0, rows[ok], values[ok] ** 2)
+    sq += 1.0
+    Z[:, d] = 1.0
+    if targets is not None:
+        Z[:, d + 1] = targets
+    return Z, sq
+
+
+# ------------------------------------------------------------------------------ preprocessors
+def poly_features(Zin: torch.Tensor, d_in: int, factors: torch.Tensor, d_out: int) -> torch.Tensor:
+    B = Zin.shape[0]
+    degree = factors.shape[1]
+    ldout = pad32(d_out + 2)
+    Zout = torch.empty(B, ldout, device=Zin.device, dtype=torch.float32)
+    if native(Zin):
+        _lib.check(_k().omldm_poly_features(_p(Zin), _i(Zin.stride(0)), _i(d_in), _p(factors), _i(degree),
+                                            _i(d_out), _p(Zout), _i(ldout), _i(B), _lib.stream_ptr()),
+                   "poly_features")
+        return Zout
+    xe = torch.cat([Zin[:, :d_in], torch.ones(B, 1, device=Zin.device)], 1)
+    idx = factors.long().clone()
+    idx[idx < 0] = d_in
+    feats = xe[:, idx.reshape(-1)].reshape(B, d_out, degree).prod(-1)
+    valid = Zin[:, d_in:d_in + 1]
+    Zout.zero_()
+    Zout[:, :d_out] = feats * (valid != 0)
+    Zout[:, d_out] = Zin[:, d_in]
+    Zout[:, d_out + 1] = Zin[:, d_in + 1]
+    return Zout
+
+
+def standard_scaler(Z: torch.Tensor, d: int, state: torch.Tensor, scratch: torch.Tensor, fit: bool = True) -> None:
+    """state: float64 [1 + 2d] = [count, mean, M2]; scratch: float64 [3 + 4d] zeros."""
+    B = Z.shape[0]
+    if native(Z):
+        _lib.check(_k().omldm_standard_scaler(_p(Z), _i(Z.stride(0)), _i(d), _i(B), _p(state), _p(scratch),
+                                              _i(1 if fit else 0), _lib.stream_ptr()), "standard_scaler")
+        return
+    valid = Z[:, d] != 0
+    X = Z[valid, :d].double()
+    n, mean, m2 = state[0].clone(), state[1:1 + d].clone(), state[1 + d:1 + 2 * d].clone()
+    if fit and X.shape[0] > 0:
+        nb = float(X.shape[0])
+        mb = X.mean(0)
+        m2b = ((X - mb) ** 2).sum(0)
+        tot = n + nb
+        delta = mb - mean
+        m2 = m2 + m2b + delta ** 2 * n * nb / tot
+        mean = mean + delta * nb / tot
+        n = tot
+        state[0], state[1:1 + d], state[1 + d:1 + 2 * d] = n, mean, m2
+    var = m2 / (n - 1.0) if float(n) > 1 else torch.zeros_like(m2)
+    inv = torch.where(var > 1e-24, 1.0 / torch.sqrt(var.clamp_min(1e-300)), torch.ones_like(var))
+    Z[valid, :d] = ((Z[valid, :d] - mean.float()) * inv.float())
+
+
+def minmax_scaler(Z: torch.Tensor, d: int, state: torch.Tensor, fit: bool = True) -> None:
+    """state: float32 [2d] = [min, max] (initialise to +inf / -inf)."""
+    B = Z.shape[0]
+    if native(Z):
+        _lib.check(_k().omldm_minmax_scaler(_p(Z), _i(Z.stride(0)), _i(d), _i(B), _p(state), _i(1 if fit else 0),
+                                            _lib.stream_ptr()), "minmax_scaler")
+        return
+    valid = Z[:, d] != 0
+    X = Z[valid, :d]
+    if fit and X.shape[0] > 0:
+        state[:d] = torch.minimum(state[:d], X.min(0).values)
+        state[d:] = torch.maximum(state[d:], X.max(0).values)
+    rng = state[d:] - state[:d]
+    inv = torch.where(rng > 1e-30, 1.0 / rng.clamp_min(1e-30), torch.zeros_like(rng))
+    Z[valid, :d] = (X - state[:d]) * inv
+
+
+# ------------------------------------------------------------------------------ linear learners
+def _linear_coef(kind, variant, C, eps, f, y, n2):
+    if kind == KIND_PA_REG:
+        err = f - y
+        loss = (err.abs() - eps).clamp_min(0)
+        aux = err * err
+        sign = torch.where(err > 0, -1.0, 1.0)
+    else:
+        yy = torch.where(y > 0, 1.0, -1.0)
+        loss = (1 - yy * f).clamp_min(0)
+        aux = (yy * f <= 0).float()
+        sign = yy
+    if variant == 0:
+        tau = loss / n2
+    elif variant == 1:
+        tau = torch.minimum(torch.full_like(loss, C), loss / n2)
+    else:
+        tau = loss / (n2 + 1.0 / (2.0 * C))
+    tau = torch.where((loss > 0) & (n2 > 0), tau, torch.zeros_like(tau))
+    return sign * tau, loss, aux
+
+
+def linear_exact(Z: torch.Tensor, d: int, w: torch.Tensor, stats: torch.Tensor, kind: int, variant: int,
+                 C: float, eps: float, lam: float, desc_dev: Optional[torch.Tensor] = None,
+                 n_pipelines: int = 1) -> None:
+    """Record-by-record update of one (or, with desc_dev, many) linear pipelines.
+
+    w: float32 [d+1]; stats: float64 [4] = [loss, aux, fitted, svm_step].
+    """
+    B, ld = Z.shape
+    if native(Z):
+        if desc_dev is None:
+            desc = LinearDesc(w.data_ptr(), stats.data_ptr(), d, kind, variant, C, eps, lam)
+            desc_dev = torch.frombuffer(bytearray(bytes(desc)), dtype=torch.uint8).to(Z.device)
+        _lib.check(_k().omldm_linear_exact(_p(Z), _i(ld), _i(B), _p(desc_dev), _i(n_pipelines), _i(d),
+                                           _lib.stream_ptr()), "linear_exact")
+        return
+    wz = w[:d + 1].double().clone()
+    loss_sum = aux_sum = 0.0
+    fitted = 0
+    t = int(stats[3].item())
+    Zc = Z[:, :d + 2].double()
+    for r in range(B):
+        if Zc[r, d] == 0:
+            continue
+        x, y = Zc[r, :d + 1], Zc[r, d + 1]
+        f = torch.dot(wz, x)
+        n2 = torch.dot(x, x)
+        if kind == KIND_SVM:
+            yy = 1.0 if y > 0 else -1.0
+            loss = max(0.0, 1.0 - yy * float(f))
+            aux = 1.0 if yy * float(f) <= 0 else 0.0
+            t += 1
+            eta = 1.0 / (lam * t)
+            wz = (1 - eta * lam) * wz + ((eta * yy) * x if yy * float(f) < 1 else 0)
+        else:
+            c, l, a = _linear_coef(kind, variant, C, eps, f, y, n2)
+            loss, aux = float(l), float(a)
+            wz = wz + c * x
+        loss_sum += loss
+        aux_sum += aux
+        fitted += 1
+    w[:d + 1] = wz.float()
+    stats[0] += loss_sum
+    stats[1] += aux_sum
+    stats[2] += fitted
+    stats[3] = t
+
+
+def make_linear_descs(entries, device) -> torch.Tensor:
+    """Pack (w, stats, d, kind, variant, C, eps, lam) tuples into a device descriptor array."""
+    raw = bytearray()
+    for (w, stats, d, kind, variant, C, eps, lam) in entries:
+        raw += bytes(LinearDesc(w.data_ptr(), stats.data_ptr(), d, kind, variant, C, eps, lam))
+    return torch.frombuffer(raw, dtype=torch.uint8).to(device)
+
+
+def linear_minibatch_scratch(d: int, device) -> torch.Tensor:
+    return torch.zeros(d + 3, device=device, dtype=torch.float32)
+
+
+def linear_minibatch(Z: torch.Tensor, d: int, w: torch.Tensor, stats: torch.Tensor, scratch: torch.Tensor,
+                     kind: int, variant: int, C: float, eps: float, lam: float, mean_update: bool = True) -> None:
+    B, ld = Z.shape
+    if native(Z):
+        desc = LinearDesc(w.data_ptr(), stats.data_ptr(), d, kind, variant, C, eps, lam)
+        _lib.check(_k().omldm_linear_minibatch(_p(Z), _i(ld), _i(B), ctypes.byref(desc), _p(scratch),
+                                               _i(1 if mean_update else 0), _lib.stream_ptr()), "linear_minibatch")
+        return
+    valid = Z[:, d] != 0
+    X = Z[valid, :d + 1]
+    y = Z[valid, d + 1]
+    if X.shape[0] == 0:
+        return
+    f = X @ w[:d + 1]
+    n2 = (X * X).sum(1)
+    if kind == KIND_SVM:
+        yy = torch.where(y > 0, 1.0, -1.0)
+        loss = (1 - yy * f).clamp_min(0)
+        aux = (yy * f <= 0).float()
+        t = float(stats[3].item()) + 1.0
+        eta = 1.0 / (lam * t)
+        viol = yy * f < 1
+        w[:d + 1] = (1 - eta * lam) * w[:d + 1] + (eta / max(1, B)) * (X[viol].t() @ yy[viol])
+        stats[3] += 1
+    else:
+        c, loss, aux = _linear_coef(kind, variant, C, eps, f, y, n2)
+        act = int((c != 0).sum().item())
+        if act:
+            delta = X.t() @ c
+            w[:d + 1] += delta / act if mean_update else delta
+    stats[0] += loss.double().sum()
+    stats[1] += aux.double().sum()
+    stats[2] += X.shape[0]
+
+
+def linear_predict(Z: torch.Tensor, d: int, w: torch.Tensor) -> torch.Tensor:
+    B = Z.shape[0]
+    out = torch.empty(B, device=Z.device, dtype=torch.float32)
+    if native(Z):
+        _lib.check(_k().omldm_linear_predict(_p(Z), _i(Z.stride(0)), _i(B), _p(w), _i(d), _p(out),
+                                             _lib.stream_ptr()), "linear_predict")
+        return out
+    return Z[:, :d] @ w[:d] + w[d]
+
+
+# ------------------------------------------------------------------------------ ORR helpers
+def sq_residual(Z: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor) -> None:
+    """stats[0] += sum over valid rows of (Z_r . wt)^2; stats[2] += #valid.  wt = [w, b, -1]."""
+    B = Z.shape[0]
+    n = wt.numel()
+    if native(Z):
+        _lib.check(_k().omldm_sq_residual(_p(Z), _i(Z.stride(0)), _i(B), _i(d), _p(wt), _i(n), _p(stats),
+                                          _lib.stream_ptr()), "sq_residual")
+        return
+    valid = Z[:, d] != 0
+    r = Z[valid, :n] @ wt
+    stats[0] += (r.double() ** 2).sum()
+    stats[2] += int(valid.sum().item())
+
+
+def mirror_upper(A: torch.Tensor, n: int) -> None:
+    if native(A):
+        _lib.check(_k().omldm_mirror_upper(_p(A), _i(A.stride(0)), _i(n), _lib.stream_ptr()), "mirror_upper")
+        return
+    iu = torch.triu(A[:n, :n], 1)
+    A[:n, :n] = torch.triu(A[:n, :n]) + iu.t()
+
+
+# ------------------------------------------------------------------------------ k-means
+def kmeans_assign(Z, d, S, cnorm, K, T, stats, assign=None) -> None:
+    B = Z.shape[0]
+    if native(Z):
+        _lib.check(_k().omldm_kmeans_assign(_p(Z), _i(Z.stride(0)), _i(d), _i(B), _p(S), _i(S.stride(0)), _p(cnorm),
+                                            _i(K), _p(T), _i(T.stride(0)), _p(assign), _p(stats), _lib.stream_ptr()),
+                   "kmeans_assign")
+        return
+    valid = Z[:, d] != 0
+    v = cnorm[None, :K] - 2 * S[:, :K]
+    best, bj = v.min(1)
+    nrm = (Z[:, :d] ** 2).sum(1)
+    T.zero_()
+    rows = torch.nonzero(valid).squeeze(1)
+    T[rows, bj[rows]] = 1.0
+    stats[0] += (nrm + best).clamp_min(0)[valid].double().sum()
+    stats[2] += int(valid.sum().item())
+    if assign is not None:
+        assign.copy_(torch.where(valid, bj, torch.full_like(bj, -1)).int())
+
+
+def kmeans_finalize(sums, sums2, K, d, centroids, cnorm) -> None:
+    if native(sums):
+        _lib.check(_k().omldm_kmeans_finalize(_p(sums), _p(sums2), _i(sums.stride(0)), _i(K), _i(d), _p(centroids),
+                                              _i(centroids.stride(0)), _p(cnorm), _lib.stream_ptr()), "kmeans_finalize")
+        return
+    tot = sums[:K] + (sums2[:K] if sums2 is not None else 0)
+    cnt = tot[:, d]
+    inv = torch.where(cnt > 0, 1.0 / cnt.clamp_min(1e-30), torch.zeros_like(cnt))
+    centroids.zero_()
+    centroids[:K, :d] = tot[:, :d] * inv[:, None]
+    cn = (centroids[:K, :d] ** 2).sum(1)
+    cnorm[:K] = torch.where(cnt > 0, cn, torch.full_like(cn, float("inf")))
+
+
+def kmeans_exact(Z, d, sums, K, stats) -> None:
+    B = Z.shape[0]
+    if native(Z):
+        _lib.check(_k().omldm_kmeans_exact(_p(Z), _i(Z.stride(0)), _i(d), _i(B), _p(sums), _i(sums.stride(0)), _i(K),
+                                           _p(stats), _lib.stream_ptr()), "kmeans_exact")
+        return
+    for r in range(B):
+        if Z[r, d] == 0:
+            continue
+        x = Z[r, :d]
+        cnt = sums[:K, d]
+        empty = torch.nonzero(cnt <= 0)
+        if empty.numel():
+            j, loss = int(empty[0]), 0.0
+        else:
+            dist = ((sums[:K, :d] / cnt[:, None] - x) ** 2).sum(1)
+            j = int(dist.argmin())
+            loss = float(dist[j])
+        sums[j, :d] += x
+        sums[j, d] += 1
+        stats[0] += loss
+        stats[2] += 1
+
+
+# ------------------------------------------------------------------------------ multiclass PA
+def row_sqnorm(Z: torch.Tensor, n: int) -> torch.Tensor:
+    B = Z.shape[0]
+    out = torch.empty(B, device=Z.device, dtype=torch.float32)
+    if native(Z):
+        _lib.check(_k().omldm_row_sqnorm(_p(Z), _i(Z.stride(0)), _i(n), _i(B), _p(out), _lib.stream_ptr()), "row_sqnorm")
+        return out
+    return (Z[:, :n] ** 2).sum(1)
+
+
+def mcpa_coef(Z, d, S, C, sqnorm, variant, Creg, T, stats) -> None:
+    """stats: float64 [4] += [loss, mistakes, fitted, active]."""
+    B = Z.shape[0]
+    if native(Z):
+        _lib.check(_k().omldm_mcpa_coef(_p(Z), _i(Z.stride(0)), _i(d), _i(B), _p(S), _i(S.stride(0)), _i(C), _p(sqnorm),
+                                        _i(variant), _f(Creg), _p(T), _i(T.stride(0)), _p(stats), _lib.stream_ptr()),
+                   "mcpa_coef")
+        return
+    valid = Z[:, d] != 0
+    y = (Z[:, d + 1] + 0.5).long().clamp(0, C - 1)
+    Sc = S[:, :C].clone()
+    sy = Sc.gather(1, y[:, None]).squeeze(1)
+    Sc.scatter_(1, y[:, None], float("-inf"))
+    best, rj = Sc.max(1)
+    loss = (1 - (sy - best)).clamp_min(0)
+    n2 = 2 * sqnorm
+    if variant == 0:
+        tau = loss / n2
+    elif variant == 1:
+        tau = torch.minimum(torch.full_like(loss, Creg), loss / n2)
+    else:
+        tau = loss / (n2 + 1.0 / (2.0 * Creg))
+    tau = torch.where((loss > 0) & (n2 > 0) & valid, tau, torch.zeros_like(tau))
+    T.zero_()
+    ar = torch.arange(B, device=Z.device)
+    T[ar, y] = tau
+    T[ar, rj] = -tau
+    stats[0] += loss[valid].double().sum()
+    stats[1] += (best >= sy)[valid].double().sum()
+    stats[2] += int(valid.sum().item())
+    stats[3] += int((tau > 0).sum().item())
+
+
+def scale_rows(T: torch.Tensor, C: int, scale_dev: torch.Tensor, reciprocal: bool = False) -> None:
+    B = T.shape[0]
+    if native(T):
+        _lib.check(_k().omldm_scale_rows(_p(T), _i(T.stride(0)), _i(B), _i(C), _p(scale_dev), _i(1 if reciprocal else 0),
+                                         _lib.stream_ptr()), "scale_rows")
+        return
+    s = 1.0 / scale_dev.clamp_min(1.0) if reciprocal else scale_dev
+    T[:, :C] *= s
+
+
+def axpy(y: torch.Tensor, x: torch.Tensor, alpha: float) -> None:
+    if native(y):
+        _lib.check(_k().omldm_axpy(_p(y), _p(x), _f(alpha), ctypes.c_size_t(y.numel()), _lib.stream_ptr()), "axpy")
+        return
+    y.add_(x, alpha=alpha)

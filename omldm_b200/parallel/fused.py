@@ -1,0 +1,332 @@
+"""Device-side protocol drivers: one fused kernel launch per synchronisation step.
+
+Each driver is the GPU counterpart of a worker/PS class pair of `host_protocols.py`
+(utils/generators/MLNodeGenerator.scala:25-36,54-65).  `impl="fused"` launches the hand-written
+kernels of csrc/sync.cu on the symmetric arena; `impl="nccl"` is the torch.distributed baseline
+(all_reduce etc.) the fused path is measured against - "a path that only calls NCCL is the
+baseline, not the product".
+
+Buffer conventions (see csrc/sync.cu):
+  mode 0 (merge "mean"): comm.buf IS the model w; e = last global estimate.
+  mode 1 (merge "sum") : comm.buf is the additive delta since the last sync; e = global statistics.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from typing import Optional
+
+import torch
+
+from ..ops import _lib
+from ..ops.functional import native
+from .comm import PipelineComm
+from .host_protocols import cfg
+
+_i, _f, _u = ctypes.c_int, ctypes.c_float, ctypes.c_uint32
+_sz = ctypes.c_size_t
+
+
+class ProtocolCounters:
+    """models / bytes / blocks shipped, as in FlinkHub.scala:118-127."""
+
+    def __init__(self, protocol: str, max_msg_params: int = 2000):
+        self.protocol = protocol
+        self.models = self.bytes = self.blocks = self.syncs = 0
+        self.max_msg_params = max_msg_params
+
+    def ship(self, n_params: int, k: int) -> None:
+        self.syncs += 1
+        self.models += 2 * k                      # k pushes + k installs
+        self.bytes += 2 * k * 4 * n_params
+        self.blocks += 2 * k * max(1, math.ceil(n_params / self.max_msg_params))
+
+
+class SyncDriver:
+    protocol = "CentralizedTraining"
+
+    def __init__(self, comm: PipelineComm, e: Optional[torch.Tensor], merge_mode: str, tc: Optional[dict],
+                 impl: str = "fused", group=None, max_msg_params: int = 2000):
+        self.comm, self.e, self.tc = comm, e, tc or {}
+        self.mode = 1 if merge_mode == "sum" else 0
+        self.k = comm.k
+        self.scale = 1.0 if self.mode == 1 else 1.0 / self.k
+        self.impl = impl if comm.device.type == "cuda" else "nccl"
+        self.group = group
+        self.sync_every = int(cfg(tc, ["syncEvery", "syncPeriod"], 1))
+        self.blocks = int(cfg(tc, ["syncBlocks"], 0))
+        self.counters = ProtocolCounters(self.protocol, max_msg_params)
+        self._batches = 0
+        self.synced_last_step = False
+
+    # ------------------------------------------------------------------ helpers
+    def _dist(self):
+        import torch.distributed as dist
+        return dist if (dist.is_available() and dist.is_initialized() and self.comm.world > 1) else None
+
+    def _eptr(self):
+        return _lib.ptr(self.e)
+
+    def after_batch(self) -> bool:
+        """Called after every learner mini-batch; returns True if the model may have changed."""
+        self._batches += 1
+        self.synced_last_step = False
+        if self._batches % self.sync_every:
+            return False
+        self.synced_last_step = bool(self.step())
+        return self.synced_last_step
+
+    def step(self) -> bool:
+        return False
+
+    def flush(self) -> None:
+        """End of stream: make sure no rank is left waiting inside a collective."""
+
+    def _nccl_allreduce(self) -> None:
+        d = self._dist()
+        buf = self.comm.buf
+        if d is not None:
+            d.all_reduce(buf, group=self.group)
+        if self.mode == 0:
+            if self.scale != 1.0:
+                buf.mul_(self.scale)
+            if self.e is not None:
+                self.e.copy_(buf)
+        else:
+            self.e.add_(buf)
+            buf.zero_()
+
+    def _fused_allreduce(self) -> None:
+        c = self.comm
+        _lib.check(_lib.kernels().omldm_sync_allreduce(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
+                                                       _i(self.mode), _u(c.next_epoch()), _i(self.blocks),
+                                                       _lib.stream_ptr()), "sync_allreduce")
+
+
+class LocalDriver(SyncDriver):
+    """CentralizedTraining: a lone learner (parallelism 1, FlinkSpoke.scala:213-216)."""
+
+    def step(self) -> bool:
+        if self.mode == 1:   # fold the delta into the global statistics locally
+            self.e.add_(self.comm.buf)
+            self.comm.buf.zero_()
+            return True
+        return False
+
+
+class SynchronousDriver(SyncDriver):
+    protocol = "Synchronous"
+
+    def step(self) -> bool:
+        self._fused_allreduce() if self.impl == "fused" else self._nccl_allreduce()
+        self.counters.ship(self.comm.n, self.k)
+        return True
+
+
+class AsynchronousDriver(SyncDriver):
+    protocol = "Asynchronous"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        if self.e is None:
+            raise ValueError("asynchronous protocols need the estimate vector e")
+        # hub shards start at the initial global state (identical on every rank)
+        if self.comm.with_hub and self.comm.hub is not None:
+            for h in self.comm.hubs:
+                h.copy_(self.e if self.mode == 1 else self.comm.buf)
+
+    def _fused(self, ssp: bool = False, staleness: int = 0) -> None:
+        c = self.comm
+        k = _lib.kernels()
+        if ssp:
+            c.clock += 1
+            _lib.check(k.omldm_sync_ssp(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale), _i(self.mode),
+                                        _u(c.clock), _i(staleness), _i(self.blocks), _lib.stream_ptr()), "sync_ssp")
+        else:
+            _lib.check(k.omldm_sync_async(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale), _i(self.mode),
+                                          _i(self.blocks), _lib.stream_ptr()), "sync_async")
+
+    def step(self) -> bool:
+        if self.impl == "fused":
+            self._fused()
+        else:   # closest NCCL equivalent: everybody folds everybody's delta in lock-step
+            self._nccl_delta_allreduce()
+        self.counters.ship(self.comm.n, 1)
+        return True
+
+    def _nccl_delta_allreduce(self) -> None:
+        d = self._dist()
+        buf = self.comm.buf
+        if self.mode == 0:
+            delta = (buf - self.e) * self.scale
+            if d is not None:
+                d.all_reduce(delta, group=self.group)
+            self.e.add_(delta)
+            buf.copy_(self.e)
+        else:
+            if d is not None:
+                d.all_reduce(buf, group=self.group)
+            self.e.add_(buf)
+            buf.zero_()
+
+
+class SSPDriver(AsynchronousDriver):
+    protocol = "SSP"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.staleness = int(cfg(self.tc, ["staleness", "s", "stalenessBound"], 3))
+
+    def step(self) -> bool:
+        if self.impl == "fused":
+            self._fused(ssp=True, staleness=self.staleness)
+        else:
+            self._nccl_delta_allreduce()
+        self.counters.ship(self.comm.n, 1)
+        return True
+
+
+class EASGDDriver(SyncDriver):
+    protocol = "EASGD"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.alpha = float(cfg(self.tc, ["alpha", "elasticity", "rho"], 0.1))
+        self.sync_every = int(cfg(self.tc, ["tau", "commPeriod", "syncEvery"], 1))
+        if self.mode == 1:
+            raise ValueError("EASGD needs an averaged model (merge mode 'mean')")
+        for h in self.comm.hubs:
+            if h is not None:
+                h.copy_(self.comm.buf)
+
+    def step(self) -> bool:
+        c = self.comm
+        if self.impl == "fused":
+            _lib.check(_lib.kernels().omldm_sync_easgd(c.struct_ptr(), _sz(c.n), _f(self.alpha), _i(self.blocks),
+                                                       _lib.stream_ptr()), "sync_easgd")
+        else:
+            d = self._dist()
+            # centre variable replicated in hub[]: x~ += alpha * sum_i (x_i - x~); x_i -= alpha (x_i - x~)
+            diff = (c.buf - c.hub) * self.alpha
+            c.buf.sub_(diff)
+            if d is not None:
+                d.all_reduce(diff, group=self.group)
+            c.hub.add_(diff)
+        self.counters.ship(c.n, 1)
+        return True
+
+
+class GMDriver(SyncDriver):
+    protocol = "GM"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.threshold = float(cfg(self.tc, ["threshold", "T", "gmThreshold"], 0.5))
+        self.rounds = 0
+        if self.e is None:
+            raise ValueError("GM needs the estimate vector e")
+
+    def step(self) -> bool:
+        c = self.comm
+        if self.impl == "fused":
+            _lib.check(_lib.kernels().omldm_sync_gm(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
+                                                    _i(self.mode), _f(self.threshold), _u(c.next_epoch()),
+                                                    _i(self.blocks), _lib.stream_ptr()), "sync_gm")
+            return True   # whether a round happened is only known on the device
+        d = self._dist()
+        diff = c.buf - self.e if self.mode == 0 else c.buf
+        flag = ((diff * diff).sum() > self.threshold).float().reshape(1)
+        if d is not None:
+            d.all_reduce(flag, op=d.ReduceOp.MAX, group=self.group)
+        if float(flag.item()) > 0:
+            self._nccl_allreduce()
+            self.rounds += 1
+            self.counters.ship(c.n, self.k)
+            return True
+        return False
+
+
+class FGMDriver(SyncDriver):
+    protocol = "FGM"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.threshold = float(cfg(self.tc, ["threshold", "T", "fgmThreshold"], 0.5))
+        self.eps_psi = float(cfg(self.tc, ["epsPsi", "eps_psi"], 0.01))
+        if self.e is None:
+            raise ValueError("FGM needs the estimate vector e")
+        n_state = 8 * max(self.comm.emulate, 1)
+        self.state = torch.zeros(n_state, dtype=torch.float32, device=self.comm.device)
+        self.state[1::8] = -1.0   # force re-anchoring on the first step
+        self.rounds = 0
+        if self.impl == "fused":
+            # hub (rank 0) starts the first round: theta = sqrt(T)/2, every phi = phi(0)
+            phi0 = -math.sqrt(self.threshold)
+            from .comm import PAD_FGM, PAD_PHI
+            pad0 = self.comm.pads[0]
+            fl = pad0.view(torch.float32)
+            fl[PAD_FGM + 2] = -phi0 / 2.0
+            fl[PAD_PHI:PAD_PHI + 16] = phi0
+
+    def step(self) -> bool:
+        c = self.comm
+        if self.impl == "fused":
+            c.step += 1
+            _lib.check(_lib.kernels().omldm_sync_fgm(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
+                                                     _i(self.mode), _f(self.threshold), _f(self.eps_psi), _u(c.step),
+                                                     _lib.ptr(self.state), _i(self.blocks), _lib.stream_ptr()),
+                       "sync_fgm")
+            return True
+        d = self._dist()
+        diff = c.buf - self.e if self.mode == 0 else c.buf
+        phi0 = -math.sqrt(self.threshold)
+        psi = (torch.sqrt((diff * diff).sum()) + phi0).reshape(1)
+        if d is not None:
+            d.all_reduce(psi, group=self.group)
+        if float(psi.item()) >= self.eps_psi * self.k * phi0:
+            self._nccl_allreduce()
+            self.rounds += 1
+            self.counters.ship(c.n, self.k)
+            return True
+        return False
+
+    def device_rounds(self) -> int:
+        return int(self.state[4].item()) if self.impl == "fused" else self.rounds
+
+
+DRIVERS = {"CentralizedTraining": LocalDriver, "SingleLearner": LocalDriver, "Synchronous": SynchronousDriver,
+           "Asynchronous": AsynchronousDriver, "SSP": SSPDriver, "EASGD": EASGDDriver, "GM": GMDriver,
+           "FGM": FGMDriver}
+
+
+def make_driver(protocol: str, comm: PipelineComm, e, merge_mode: str, tc, impl: str = "fused", group=None,
+                max_msg_params: int = 2000) -> SyncDriver:
+    cls = DRIVERS.get(protocol, AsynchronousDriver)
+    if comm.k == 1:
+        cls = LocalDriver
+    if cls is EASGDDriver and merge_mode == "sum":
+        cls = AsynchronousDriver   # elastic averaging is meaningless for additive statistics
+    drv = cls(comm, e, merge_mode, tc, impl, group, max_msg_params)
+    drv.counters.protocol = protocol if comm.k > 1 else "CentralizedTraining"
+    return drv
+
+
+def device_barrier(comm: PipelineComm) -> None:
+    """Termination probe rendezvous (StatisticsOperator.scala:135-142) on the signal pads."""
+    if comm.device.type == "cuda" and comm.k > 1:
+        _lib.check(_lib.kernels().omldm_device_barrier(comm.struct_ptr(), _u(comm.next_epoch()), _lib.stream_ptr()),
+                   "device_barrier")
+
+
+def query_reduce(comm: PipelineComm, vals4: torch.Tensor, impl: str = "fused", group=None) -> torch.Tensor:
+    """Sum of (fitted, loss, cumLoss, score) over ranks (ResponseConstructor.scala:43-52)."""
+    out = torch.empty_like(vals4)
+    if comm.device.type == "cuda" and comm.k > 1 and impl == "fused":
+        _lib.check(_lib.kernels().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals4), _lib.ptr(out),
+                                                     _u(comm.next_epoch()), _lib.stream_ptr()), "query_reduce")
+        return out
+    out.copy_(vals4)
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and comm.world > 1:
+        dist.all_reduce(out, group=group)
+    return out

@@ -1,0 +1,153 @@
+"""Pinned host ring buffers ("topics") and synthetic stream producers (csrc/host/*.cpp).
+
+A `Topic` replaces one Kafka topic of the reference (trainingData / forecastingData, Job.scala:42-67):
+fixed-size slots of pinned host memory, each holding one mini-batch of staged record rows, filled by
+native producer threads and drained by the worker, which copies a slot to its GPU with a single
+async H2D transfer.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from ..ops import _lib
+from ..ops.functional import pad32
+
+KIND_BINARY, KIND_REGRESSION, KIND_CLUSTERS, KIND_MULTICLASS = 0, 1, 2, 3
+MODE_GENERATE, MODE_REPLAY = 0, 1
+
+_configured = False
+
+
+def _h():
+    global _configured
+    h = _lib.host()
+    if not _configured:
+        vp, i, i64, u64, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_size_t
+        h.omldm_ring_create.restype = vp
+        h.omldm_ring_create.argtypes = [vp, i, sz]
+        h.omldm_ring_destroy.argtypes = [vp]
+        h.omldm_ring_acquire_write.argtypes = [vp, i]
+        h.omldm_ring_commit_write.argtypes = [vp, i, i64]
+        h.omldm_ring_acquire_read.argtypes = [vp, i, ctypes.POINTER(i64)]
+        h.omldm_ring_release_read.argtypes = [vp, i]
+        h.omldm_ring_close.argtypes = [vp]
+        h.omldm_ring_produced.restype = i64
+        h.omldm_ring_produced.argtypes = [vp]
+        h.omldm_ring_consumed.restype = i64
+        h.omldm_ring_consumed.argtypes = [vp]
+        h.omldm_ring_slot_ptr.restype = vp
+        h.omldm_ring_slot_ptr.argtypes = [vp, i]
+        h.omldm_producer_start.restype = vp
+        h.omldm_producer_start.argtypes = [vp, i, i, i, i, i, u64, i, i64, i]
+        h.omldm_producer_stop.argtypes = [vp]
+        h.omldm_generate_batch.argtypes = [vp, i, i, i, i, i, u64, u64]
+        h.omldm_parse_json_records.restype = i
+        h.omldm_parse_json_records.argtypes = [ctypes.c_char_p, sz, i, vp, i, i, ctypes.POINTER(i),
+                                               ctypes.POINTER(sz)]
+        _configured = True
+    return h
+
+
+class Topic:
+    """Ring of `n_slots` batches of `batch` staged rows with `d` features."""
+
+    def __init__(self, d: int, batch: int, n_slots: int = 8, pin: Optional[bool] = None):
+        self.d, self.batch, self.n_slots = d, batch, n_slots
+        self.ld = pad32(d + 2)
+        self.storage = torch.zeros(n_slots, batch, self.ld, dtype=torch.float32)
+        if pin is None:
+            pin = torch.cuda.is_available()
+        if pin:
+            self.storage = self.storage.pin_memory()
+        self.slot_bytes = batch * self.ld * 4
+        self._ring = _h().omldm_ring_create(self.storage.data_ptr(), n_slots, self.slot_bytes)
+        if not self._ring:
+            raise RuntimeError("ring creation failed")
+        self._producer = None
+
+    # ---- producer side -------------------------------------------------------------------------
+    def start_synthetic(self, kind: int, seed: int = 0, n_aux: int = 0, mode: int = MODE_GENERATE,
+                        max_batches: int = -1, n_threads: int = 1) -> None:
+        self._producer = _h().omldm_producer_start(self._ring, kind, self.d, self.ld, self.batch, n_aux, seed, mode,
+                                                   max_batches, n_threads)
+        if not self._producer:
+            raise RuntimeError("producer start failed")
+
+    def put(self, rows: torch.Tensor, timeout_ms: int = -1) -> bool:
+        """Publish one batch of staged rows from Python (e.g. parsed JSON records)."""
+        s = _h().omldm_ring_acquire_write(self._ring, timeout_ms)
+        if s < 0:
+            return False
+        n = rows.shape[0]
+        self.storage[s, :n].copy_(rows)
+        if n < self.batch:
+            self.storage[s, n:].zero_()
+        _h().omldm_ring_commit_write(self._ring, s, n)
+        return True
+
+    def close(self) -> None:
+        _h().omldm_ring_close(self._ring)
+
+    # ---- consumer side -------------------------------------------------------------------------
+    def get(self, timeout_ms: int = -1) -> Optional[Tuple[int, torch.Tensor, int]]:
+        """(slot, pinned batch view, n_records) or None at end of stream / timeout."""
+        n = ctypes.c_int64(0)
+        while True:
+            s = _h().omldm_ring_acquire_read(self._ring, timeout_ms, ctypes.byref(n))
+            if s < 0:
+                return None
+            if n.value == 0:        # empty end-marker batch
+                _h().omldm_ring_release_read(self._ring, s)
+                continue
+            return s, self.storage[s], int(n.value)
+
+    def release(self, slot: int) -> None:
+        _h().omldm_ring_release_read(self._ring, slot)
+
+    @property
+    def produced(self) -> int:
+        return int(_h().omldm_ring_produced(self._ring))
+
+    @property
+    def consumed(self) -> int:
+        return int(_h().omldm_ring_consumed(self._ring))
+
+    def stop(self) -> None:
+        if self._producer:
+            _h().omldm_ring_close(self._ring)
+            _h().omldm_producer_stop(self._producer)
+            self._producer = None
+
+    def __del__(self):
+        try:
+            self.stop()
+            if self._ring:
+                _h().omldm_ring_destroy(self._ring)
+                self._ring = None
+        except Exception:
+            pass
+
+
+def generate_batch(kind: int, d: int, batch: int, seed: int = 0, batch_index: int = 0, n_aux: int = 0,
+                   pin: bool = False) -> torch.Tensor:
+    """One synthetic staged batch [batch, pad32(d+2)] on the host."""
+    ld = pad32(d + 2)
+    out = torch.empty(batch, ld, dtype=torch.float32)
+    if pin and torch.cuda.is_available():
+        out = out.pin_memory()
+    _h().omldm_generate_batch(out.data_ptr(), kind, d, ld, batch, n_aux, seed, batch_index)
+    return out
+
+
+def parse_json_records(text: bytes, d: int, max_rows: int) -> Tuple[torch.Tensor, int, int]:
+    """(staged rows [n, ld], n_forecast, bytes consumed); rows with valid flag 2.0 are forecasts."""
+    ld = pad32(d + 2)
+    out = torch.zeros(max_rows, ld, dtype=torch.float32)
+    nf = ctypes.c_int(0)
+    used = ctypes.c_size_t(0)
+    n = _h().omldm_parse_json_records(text, len(text), d, out.data_ptr(), ld, max_rows, ctypes.byref(nf),
+                                      ctypes.byref(used))
+    return out[:n], int(nf.value), int(used.value)
