@@ -163,6 +163,8 @@ def main() -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
+    for i in range(3 * n_rot):     # untimed set-up: every batch buffer gets its CUDA graph captured
+        step_device(i)
     for i in range(args.warmup):
         step_device(i)
     sync_all()
@@ -200,7 +202,7 @@ def main() -> None:
                     ev.synchronize()
                 topic.release(s0)
             return loss
-        for _ in range(max(3, args.warmup)):
+        for _ in range(max(8, args.warmup)):   # includes graph capture for the two staging buffers
             step_e2e()
         sync_all()
         t0 = time.perf_counter()

@@ -234,24 +234,38 @@ __global__ void scale_rows_kernel(float* __restrict__ T, int ldt, int B, int C, 
   }
 }
 
-// sum over valid rows of (Z_r . wt)^2, wt has n entries (n <= ld)
-__global__ void sq_residual_kernel(const float* __restrict__ Z, int ld, int B, int d, const float* __restrict__ wt,
-                                   int n, double* __restrict__ stats) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  __shared__ double s_l[8];
-  __shared__ int s_n[8];
+// sum over valid rows of (Z_r . wt)^2, wt has n entries (n <= ld).  One warp per row, float4
+// loads, two rows in flight per warp; wt is staged in shared memory once per CTA.
+__global__ void __launch_bounds__(256)
+sq_residual_kernel(const float* __restrict__ Z, int ld, int B, int d, const float* __restrict__ wt, int n,
+                   double* __restrict__ stats) {
+  extern __shared__ float s_w[];   // ld floats, zero beyond n
+  for (int c = threadIdx.x; c < ld; c += blockDim.x) s_w[c] = c < n ? wt[c] : 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int n4 = (n + 3) >> 2;
+  const float4* w4 = reinterpret_cast<const float4*>(s_w);
   double acc = 0.0;
   int nv = 0;
-  const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  for (int r = warp; r < B; r += nwarps) {
-    const float* zr = Z + static_cast<size_t>(r) * ld;
-    if (zr[d] == 0.f) continue;
-    float dot = 0.f;
-    for (int c = lane; c < n; c += 32) dot = fmaf(zr[c], wt[c], dot);
-    dot = warp_sum(dot);
-    acc += static_cast<double>(dot) * dot;
-    nv += 1;
+  for (int r = warp; r < B; r += 2 * nwarps) {
+    const int r2 = r + nwarps;
+    const float4* z0 = reinterpret_cast<const float4*>(Z + static_cast<size_t>(r) * ld);
+    const float4* z1 = reinterpret_cast<const float4*>(Z + static_cast<size_t>(r2 < B ? r2 : r) * ld);
+    float d0 = 0.f, d1 = 0.f;
+    for (int c = lane; c < n4; c += 32) {
+      const float4 a = ld_nc_v4(z0 + c), b = ld_nc_v4(z1 + c), w = w4[c];
+      d0 += a.x * w.x + a.y * w.y + a.z * w.z + a.w * w.w;
+      d1 += b.x * w.x + b.y * w.y + b.z * w.z + b.w * w.w;
+    }
+    d0 = warp_sum(d0);
+    d1 = warp_sum(d1);
+    if (Z[static_cast<size_t>(r) * ld + d] != 0.f) { acc += static_cast<double>(d0) * d0; nv += 1; }
+    if (r2 < B && Z[static_cast<size_t>(r2) * ld + d] != 0.f) { acc += static_cast<double>(d1) * d1; nv += 1; }
   }
+  __shared__ double s_l[8];
+  __shared__ int s_n[8];
   const int w = threadIdx.x >> 5;
   if (lane == 0) { s_l[w] = acc; s_n[w] = nv; }
   __syncthreads();
@@ -280,9 +294,16 @@ using namespace omldm;
 extern "C" int omldm_sq_residual(const float* Z, int ld, int B, int d, const float* wt, int n, double* stats,
                                  void* stream) {
   if (B <= 0) return 0;
-  int blocks = (B + 7) / 8;
-  if (blocks > 148 * 8) blocks = 148 * 8;
-  sq_residual_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, wt, n, stats);
+  if ((ld & 3) || n > ld) return set_error_msg("sq_residual: ld must be a multiple of 4 and >= n");
+  if (ld * sizeof(float) > 200 * 1024) return set_error_msg("sq_residual: row pitch too large for the smem weight copy");
+  if (ld * sizeof(float) > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(sq_residual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(ld * sizeof(float)));
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(sq_residual)", e);
+  }
+  int blocks = (B + 15) / 16;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  sq_residual_kernel<<<blocks, 256, ld * sizeof(float), static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, wt, n, stats);
   return check_launch("sq_residual_kernel");
 }
 

@@ -56,5 +56,6 @@ int tensormap_encode(CUtensorMap* tm, CUtensorMapDataType dtype, uint32_t rank, 
 
 extern "C" const char* omldm_last_error() { return omldm::g_err; }
 extern "C" long long omldm_launch_count() { return omldm::g_launches.load(); }
+extern "C" void omldm_add_launch_count(long long n) { omldm::g_launches.fetch_add(n); }
 extern "C" void omldm_reset_launch_count() { omldm::g_launches.store(0); }
 extern "C" int omldm_abi_version() { return 1; }

@@ -17,29 +17,55 @@ __host__ __device__ inline long long holdouts_before(long long c) {
   return 2 * (c / 10) + (r > 8 ? r - 8 : 0);
 }
 
-__global__ void holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restrict__ ring,
-                                    int cap, long long count0) {
-  const int warps_per_block = blockDim.x >> 5;
-  const int slot = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
+// One CTA per ring slot.  The holdouts of this batch that map to the slot form a chain
+// h, h+cap, h+2cap, ... (batch rows i_0 < i_1 < ... < i_m).  Sequential semantics: every new
+// holdout evicts the previous occupant, which is trained on in its place.  In place that is a
+// shift by one along the chain: ring <- row i_m, row i_j <- row i_{j-1}, row i_0 <- old ring
+// content (or an empty row while the ring is still filling).  Each thread owns a fixed set of
+// columns, walks the chain from the tail and so never needs a barrier.
+__global__ void __launch_bounds__(256)
+holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restrict__ ring, int cap,
+                    long long count0_arg, const long long* __restrict__ count_dev) {
+  const long long count0 = count_dev ? *count_dev : count0_arg;
+  const int slot = blockIdx.x;
   if (slot >= cap) return;
   const long long h0 = holdouts_before(count0), h1 = holdouts_before(count0 + B);
-  long long h = h0 + ((slot - (h0 % cap)) % cap + cap) % cap;
-  for (; h < h1; h += cap) {
+  const long long hf = h0 + ((slot - (h0 % cap)) % cap + cap) % cap;   // first chain element
+  if (hf >= h1) return;
+  const int m = static_cast<int>((h1 - 1 - hf) / cap);                // chain has m + 1 elements
+  auto row_of = [&](int j) -> float* {
+    const long long h = hf + static_cast<long long>(j) * cap;
     const long long c = (h / 2) * 10 + 8 + (h & 1);
-    const int i = static_cast<int>(c - count0);
-    float* row = Z + static_cast<size_t>(i) * ld;
-    float* rs = ring + static_cast<size_t>(slot) * ld;
-    const bool evict = h >= cap;
-    for (int col = lane; col < ld; col += 32) {
-      const float nv = row[col];
-      const float ov = evict ? rs[col] : 0.f;
-      rs[col] = nv;
-      row[col] = ov;
+    return Z + static_cast<size_t>(c - count0) * ld;
+  };
+  const bool evict = hf >= cap;
+  float* rs = ring + static_cast<size_t>(slot) * ld;
+  const int ld4 = ld >> 2;   // ld is a multiple of 32
+  constexpr int MAXC = 16;
+  for (int c4 = threadIdx.x; c4 < ld4; c4 += blockDim.x) {
+    float4* r4 = reinterpret_cast<float4*>(rs) + c4;
+    const float4 old = evict ? *r4 : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (m < MAXC) {
+      // short chain: issue every load first (independent, pipelined), then the shifted stores
+      float4 v[MAXC];
+#pragma unroll
+      for (int j = 0; j < MAXC; ++j)
+        if (j <= m) v[j] = reinterpret_cast<const float4*>(row_of(j))[c4];
+#pragma unroll
+      for (int j = 0; j < MAXC; ++j) {
+        if (j == m) *r4 = v[j];
+        else if (j < m) reinterpret_cast<float4*>(row_of(j + 1))[c4] = v[j];
+      }
+    } else {
+      *r4 = reinterpret_cast<float4*>(row_of(m))[c4];
+      for (int j = m; j >= 1; --j)
+        reinterpret_cast<float4*>(row_of(j))[c4] = reinterpret_cast<float4*>(row_of(j - 1))[c4];
     }
-    __syncwarp();
+    reinterpret_cast<float4*>(row_of(0))[c4] = old;
   }
 }
+
+__global__ void advance_count_kernel(long long* c, long long delta) { *c += delta; }
 
 __global__ void densify_kernel(const int* __restrict__ indptr, const int* __restrict__ indices,
                                const float* __restrict__ values, int d, const float* __restrict__ targets,
@@ -94,10 +120,24 @@ extern "C" int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, i
                                   void* stream) {
   if (B <= 0 || cap <= 0) return 0;
   if (holdouts_before(count0 + B) == holdouts_before(count0)) return 0;
-  const int wpb = 8;
-  holdout_swap_kernel<<<(cap + wpb - 1) / wpb, wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-      Z, ld, B, d, ring, cap, count0);
+  if (ld & 3) return set_error_msg("holdout_swap: ld must be a multiple of 4");
+  holdout_swap_kernel<<<cap, 256, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, ring, cap, count0, nullptr);
   return check_launch("holdout_swap_kernel");
+}
+
+// Graph-replayable variant: the running record count lives in device memory and is advanced by
+// `omldm_advance_count` (a separate node, so every block of the swap kernel reads the old value).
+extern "C" int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* ring, int cap,
+                                      const long long* count_dev, void* stream) {
+  if (B <= 0 || cap <= 0) return 0;
+  if (ld & 3) return set_error_msg("holdout_swap: ld must be a multiple of 4");
+  holdout_swap_kernel<<<cap, 256, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, ring, cap, 0, count_dev);
+  return check_launch("holdout_swap_kernel");
+}
+
+extern "C" int omldm_advance_count(long long* count_dev, long long delta, void* stream) {
+  advance_count_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(count_dev, delta);
+  return check_launch("advance_count_kernel");
 }
 
 extern "C" int omldm_densify(const int* indptr, const int* indices, const float* values, int B, int d,

@@ -30,7 +30,13 @@ struct Comm {
 
 constexpr int LOCAL_WORDS = 64;  // private scratch words per (emulated) rank
 // local scratch word indices
-enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4 };
+enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4, L_EPOCH = 5, L_CLOCK = 6, L_STEP = 7 };
+
+// A sequence number passed as 0 means "device managed": the kernel uses (stored value + 1) and the
+// block that finishes last stores it back, so the identical launch can be replayed from a CUDA graph.
+__device__ __forceinline__ uint32_t resolve_seq(uint32_t given, const uint32_t* slot) {
+  return given ? given : *reinterpret_cast<const volatile uint32_t*>(slot) + 1u;
+}
 
 __device__ __forceinline__ int my_rank(const Comm& c) { return c.emulate > 1 ? static_cast<int>(blockIdx.y) : c.rank; }
 __device__ __forceinline__ uint32_t* my_local(const Comm& c) { return c.local + my_rank(c) * LOCAL_WORDS; }
@@ -170,9 +176,10 @@ __device__ __forceinline__ void local_tail(float* buf, float* e, size_t n, int m
 // entry barrier and the allreduce only happens if any rank voted "violated".
 __global__ void __launch_bounds__(256)
 sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode,
-                      uint32_t epoch, float gm_threshold) {
+                      uint32_t epoch_arg, float gm_threshold) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
+  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_EPOCH);
   float* buf = c.bufs[me];
   float* e = e_base ? e_base + e_stride * (c.emulate > 1 ? me : 0) : nullptr;
   const uint32_t seq_entry = 2 * epoch + 1, seq_exit = 2 * epoch + 2;
@@ -183,7 +190,7 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
     if (grid_done(loc + L_DONE2)) {
       const float nrm2 = __ldcg(reinterpret_cast<float*>(loc + L_NORM));
       __syncthreads();                    // everyone has read the norm before it is reset
-      if (threadIdx.x == 0) loc[L_NORM] = 0;
+      if (threadIdx.x == 0) { loc[L_NORM] = 0; loc[L_EPOCH] = epoch; }
       const uint32_t vote = 2 * epoch + (nrm2 > gm_threshold ? 1u : 0u);
       if (threadIdx.x < c.world) {
         asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[threadIdx.x] + OMLDM_PAD_VOTE + me), "r"(vote) : "memory");
@@ -210,7 +217,10 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
   }
 
   reduce_and_broadcast_shard(c, me, n / 4, scale);
-  if (grid_done(loc + L_DONE)) signal_all(c, me, OMLDM_PAD_EXIT, seq_exit);
+  if (grid_done(loc + L_DONE)) {
+    if (threadIdx.x == 0) loc[L_EPOCH] = epoch;
+    signal_all(c, me, OMLDM_PAD_EXIT, seq_exit);
+  }
   wait_all(c, me, OMLDM_PAD_EXIT, seq_exit);
   local_tail(buf, e, n, mode);
 }
@@ -220,9 +230,10 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
 // returning vector atomics and installs the fresh hub value locally.  No rendezvous.
 __global__ void __launch_bounds__(256)
 sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode, int ssp,
-                  uint32_t clock, int staleness) {
+                  uint32_t clock_arg, int staleness) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
+  const uint32_t clock = ssp ? resolve_seq(clock_arg, loc + L_CLOCK) : 0u;
   float4* b4 = reinterpret_cast<float4*>(c.bufs[me]);
   float4* e4 = reinterpret_cast<float4*>(e_base + e_stride * (c.emulate > 1 ? me : 0));
   const size_t n4 = n / 4;
@@ -242,6 +253,7 @@ sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale,
   }
   if (!ssp) return;
   if (grid_done(loc + L_DONE3)) {
+    if (threadIdx.x == 0) loc[L_CLOCK] = clock;
     signal_all(c, me, OMLDM_PAD_CLOCK, clock);
     // stale-synchronous wait: nobody may be more than `staleness` clocks behind me
     if (threadIdx.x < c.world) {
@@ -284,10 +296,11 @@ __global__ void __launch_bounds__(256) sync_easgd_kernel(Comm c, size_t n, float
 // state_local (float[8], private): [0] round id [1] subround seen [2] zeta [3] counts sent [4] rounds [5] subrounds
 __global__ void __launch_bounds__(256)
 sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode, float threshold,
-                float eps_psi, uint32_t step, float* state_base) {
+                float eps_psi, uint32_t step_arg, float* state_base) {
   const int me = my_rank(c);
   const int k = c.world;
   uint32_t* loc = my_local(c);
+  const uint32_t step = resolve_seq(step_arg, loc + L_STEP);
   float* buf = c.bufs[me];
   float* e = e_base + e_stride * (c.emulate > 1 ? me : 0);
   float* st = state_base + 8 * (c.emulate > 1 ? me : 0);
@@ -299,14 +312,19 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
     if (threadIdx.x == 0) {
       const float nrm2 = __ldcg(reinterpret_cast<float*>(loc + L_NORM));
       loc[L_NORM] = 0;
+      loc[L_STEP] = step;
       const float phi = sqrtf(nrm2) + phi0;
       uint32_t round = static_cast<uint32_t>(st[0]);
+      // Round-end flag is sampled BEFORE this step's hub logic: a round declared by the hub during
+      // step s is acted on by every rank (hub included) in its step s+1, so ranks that advance in
+      // lock-step all take the same branch.
+      const uint32_t seen_round = ld_acquire_sys(c.pads[me] + OMLDM_PAD_FGM + 3);
       // publish phi to the hub (push-based polling)
       asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + me), "r"(__float_as_uint(phi)) : "memory");
       const uint32_t sub = ld_acquire_sys(hub + 1);
       float theta = __uint_as_float(ld_relaxed_sys(hub + 2));
       if (theta <= 0.f) theta = -phi0 / 2.f;  // first sub-round of the very first round
-      if (static_cast<uint32_t>(st[1]) != sub) {  // new sub-round: re-anchor
+      if (static_cast<int>(st[1]) != static_cast<int>(sub)) {  // new sub-round (or first step): re-anchor
         st[1] = static_cast<float>(sub);
         st[2] = phi;
         st[3] = 0.f;
@@ -321,7 +339,7 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
         // hub logic
         const int counter = static_cast<int>(ld_relaxed_sys(hub));
         const uint32_t hub_round = ld_relaxed_sys(hub + 3);
-        if (counter > k && hub_round == round) {
+        if (counter > k && hub_round == round && seen_round == round) {
           float psi = 0.f;
           for (int i = 0; i < k; ++i) psi += __uint_as_float(ld_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + i));
           if (psi >= eps_psi * k * phi0) {
@@ -334,7 +352,6 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
           }
         }
       }
-      const uint32_t seen_round = ld_acquire_sys(c.pads[me] + OMLDM_PAD_FGM + 3);
       const uint32_t decision = 2 * step + ((seen_round != round) ? 1u : 0u);
       __threadfence();
       atomicExch(loc + L_DECISION, decision);
@@ -385,8 +402,12 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void device_barrier_kernel(Comm c, uint32_t epoch) {
+__global__ void device_barrier_kernel(Comm c, uint32_t epoch_arg) {
   const int me = my_rank(c);
+  uint32_t* loc = my_local(c);
+  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_EPOCH);
+  __syncthreads();
+  if (threadIdx.x == 0) loc[L_EPOCH] = epoch;
   signal_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
   wait_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
   signal_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
@@ -394,8 +415,12 @@ __global__ void device_barrier_kernel(Comm c, uint32_t epoch) {
 }
 
 // Each rank scatters its 4 query scalars into every peer's pad, barrier, then sums locally.
-__global__ void query_reduce_kernel(Comm c, const float* vals_base, float* out_base, uint32_t epoch) {
+__global__ void query_reduce_kernel(Comm c, const float* vals_base, float* out_base, uint32_t epoch_arg) {
   const int me = my_rank(c);
+  uint32_t* loc = my_local(c);
+  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_EPOCH);
+  __syncthreads();
+  if (threadIdx.x == 0) loc[L_EPOCH] = epoch;
   const float* vals = vals_base + 4 * (c.emulate > 1 ? me : 0);
   float* out = out_base + 4 * (c.emulate > 1 ? me : 0);
   if (threadIdx.x < c.world * 4) {
@@ -434,6 +459,12 @@ static int clamp_blocks(int blocks, size_t n, int emulate) {
 // kernels whose blocks wait on one another must be co-resident: cooperative launch
 template <typename... Args>
 static int launch_coop(void (*kern)(Args...), dim3 grid, dim3 block, cudaStream_t st, const char* name, Args... args) {
+  if (grid.y == 1) {
+    // one rank per launch: the grid is far below one wave, every block is resident, and a plain
+    // launch can be captured into a CUDA graph
+    kern<<<grid, block, 0, st>>>(args...);
+    return check_launch(name);
+  }
   void* params[] = {(void*)&args...};
   cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kern), grid, block, params, 0, st);
   if (e != cudaSuccess) return set_error(name, e);

@@ -24,6 +24,7 @@ extern "C" {
 const char* omldm_last_error(void);
 long long omldm_launch_count(void);       /* kernels launched by this library so far */
 void omldm_reset_launch_count(void);
+void omldm_add_launch_count(long long n); /* kernels run by replaying a captured graph */
 int omldm_abi_version(void);
 
 /* ------------------------------------------------------------------ tcgen05 GEMMs (umma_gemm.cu)
@@ -65,6 +66,11 @@ int omldm_linear_predict(const float* Z, int ld, int B, const float* w, int d, f
  * `count0` = number of training records seen before this batch; holdout ring = `cap` rows. */
 int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, int cap, long long count0,
                        void* stream);
+/* CUDA-graph friendly variant: the record count is read from device memory; advance it with
+ * omldm_advance_count after the swap (separate launch, so all blocks saw the old value) */
+int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* ring, int cap,
+                           const long long* count_dev, void* stream);
+int omldm_advance_count(long long* count_dev, long long delta, void* stream);
 /* sparse (CSR batch) -> dense staged rows + squared row norms (SparseVector, utils/CommonUtils.scala:23) */
 int omldm_densify(const int* indptr, const int* indices, const float* values, int B, int d,
                   const float* targets, float* Z, int ld, float* sqnorm, void* stream);
@@ -121,6 +127,9 @@ typedef struct omldm_comm {
   int emulate;               /* >1: one launch plays `emulate` ranks (single-GPU tests)  */
 } omldm_comm;
 
+/* Sequence numbers (`epoch`, `clock`, `step`) passed as 0 are device managed: the kernel keeps the
+ * counter in `local` and advances it itself, which makes the launch replayable from a CUDA graph.
+ * Do not mix explicit and device-managed numbering on one omldm_comm. */
 /* signal-pad word layout (per rank), uint32 indices */
 enum {
   OMLDM_PAD_ENTRY = 0,     /* [0,16)   entry-barrier arrivals, one word per peer    */

@@ -57,6 +57,13 @@ class Engine:
         self._loss_host = None
         self.last_copy_event = None
         self.holdout_enabled = True
+        # CUDA graphs of the steady-state step, one per batch buffer
+        self.use_graphs = str(self.params.extra.get("graphs", "true")).lower() in ("1", "true", "yes")
+        self.graph_after = 2
+        self._graphs: Dict[Any, Any] = {}
+        self._graph_launches: Dict[Any, int] = {}
+        self._seen: Dict[Any, int] = {}
+        self._count_dev: Optional[torch.Tensor] = None
 
     # ============================================================================ control plane
     def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
@@ -70,6 +77,10 @@ class Engine:
 
     def _process_control(self, r: Request) -> List[str]:
         kind = r.request
+        if kind in ("Create", "Delete"):
+            self._graphs.clear()      # captured steps reference the old set of pipelines
+            self._graph_launches.clear()
+            self._seen.clear()
         if kind == "Create":
             self.pipelines[r.id] = GpuPipeline(
                 r, self.device, self.rank, self.world, impl=self.impl, group=self.group,
@@ -131,7 +142,12 @@ class Engine:
 
     def train_batch(self, Z: torch.Tensor, d: Optional[int] = None, **kw) -> None:
         """Train every pipeline on one batch of staged rows [B, ld] already on `self.device`.
-        The batch is consumed (the holdout swap and in-place scalers modify it)."""
+        The batch is consumed (the holdout swap and in-place scalers modify it).
+
+        Launch-bound steady state: once a batch BUFFER (address + shape) has been seen
+        `graph_after` times and every pipeline is graph safe, the device work of the step is captured
+        into a CUDA graph and replayed; step-varying scalars (record count, protocol epochs) live in
+        device memory so the captured launches stay valid."""
         if d is None:
             d = self.d
         if d is None:
@@ -141,21 +157,63 @@ class Engine:
         if self.t_first is None:
             self.t_first = now
         B, ld = Z.shape
+        for p in self.pipelines.values():
+            if p.protocol != "SingleLearner" or self.rank == 0:
+                self._build(p, d)
+        key = (Z.data_ptr(), B, ld)
+        g = None
+        if self.use_graphs and not kw and self._graphable(Z):
+            g = self._graphs.get(key)
+            if g is None and self._seen.get(key, 0) >= self.graph_after:
+                g = self._capture(key, Z, d)
+        if g is not None:
+            g.replay()
+            _lib.add_launch_count(self._graph_launches[key])
+        else:
+            self._seen[key] = self._seen.get(key, 0) + 1
+            self._device_step(Z, d, **kw)
+        self.count += B
+        for p in self.pipelines.values():
+            if p.built and (p.protocol != "SingleLearner" or self.rank == 0):
+                p.host_tick()
+        self.t_last = time.monotonic()
+
+    def _graphable(self, Z: torch.Tensor) -> bool:
+        if not (Z.is_cuda and F.native(Z)) or not self.pipelines:
+            return False
+        return all(p.graph_safe() for p in self.pipelines.values())
+
+    def _capture(self, key, Z: torch.Tensor, d: int):
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        before = _lib.launch_count()
+        with torch.cuda.graph(g):
+            self._device_step(Z, d)
+        self._graph_launches[key] = _lib.launch_count() - before
+        _lib.add_launch_count(-self._graph_launches[key])   # capture does not execute anything
+        self._graphs[key] = g
+        return g
+
+    def _device_step(self, Z: torch.Tensor, d: int, **kw) -> None:
+        """All device work of one training step, in stream order."""
+        B, ld = Z.shape
         if self.holdout_enabled and self.params.testSetSize > 0:
             self._ensure_holdout(ld)
-            F.holdout_swap(Z, self.holdout, d, self.count)   # 2-in-10 holdout, evict-then-train
-        self.count += B
+            if Z.is_cuda and F.native(Z):
+                if self._count_dev is None:
+                    self._count_dev = torch.tensor([self.count], dtype=torch.int64, device=self.device)
+                F.holdout_swap_dev(Z, self.holdout, d, self._count_dev)   # 2-in-10 holdout, evict-then-train
+            else:
+                F.holdout_swap(Z, self.holdout, d, self.count)
         n_pipes = len(self.pipelines)
         for p in self.pipelines.values():
+            due = p.built and (p.driver._batches % p.driver.sync_every == p.driver.sync_every - 1)
             if p.protocol == "SingleLearner":
                 Zs = self._forward_to_rank0(Z)
                 if self.rank == 0:
-                    self._build(p, d)
-                    p.train(Zs, protect_input=True, **kw)
+                    p.device_train(Zs, True, due, **kw)
                 continue
-            self._build(p, d)
-            p.train(Z, protect_input=n_pipes > 1, **kw)
-        self.t_last = time.monotonic()
+            p.device_train(Z, n_pipes > 1, due, **kw)
 
     def _forward_to_rank0(self, Z: torch.Tensor) -> torch.Tensor:
         """SingleLearner: workers forward raw records to the one learner at hub 0."""
@@ -282,6 +340,8 @@ class Engine:
 
     def load_state_dict(self, sd: dict) -> None:
         self.count, self.d = sd["count"], sd["d"]
+        self._count_dev = None
+        self._graphs, self._seen = {}, {}
         self.pipeline_map.load_state_dict(sd["registry"])
         if sd["holdout"] is not None:
             self.holdout = sd["holdout"].to(self.device)

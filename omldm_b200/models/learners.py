@@ -65,7 +65,14 @@ class GpuLearner:
         raise NotImplementedError
 
     def after_sync(self) -> None:
-        """Refresh derived state once the protocol installed a new global model."""
+        """Refresh derived state once the protocol installed a new global model (device work only)."""
+
+    def host_tick(self) -> None:
+        """Host-side cadence work after a step (may synchronise); never part of a CUDA graph."""
+
+    def graph_ready(self) -> bool:
+        """True once `fit_batch` enqueues the same device work every step (graph-capturable)."""
+        return True
 
     def score(self, Z: torch.Tensor) -> float:
         """accuracy / RMSE / mean inertia on staged holdout rows (empty rows are ignored)."""
@@ -202,6 +209,10 @@ class GpuORR(GpuLearner):
         self.solve_every = int(_h(hyper, ["solveEvery"], 16))
         self._since = 0
         self.solves = 0
+        self._side = None
+        self._pending = None
+        self._install_at = 0
+        self._w_next = None
 
     def n_flat(self, d):
         ld = F.pad32(d + 2)
@@ -220,36 +231,81 @@ class GpuORR(GpuLearner):
         self.ksplit = max(1, 148 // max(tiles, 1))
         if self.device.type == "cuda":
             # create the cuSOLVER handle / workspaces now, not inside somebody's timed region
+            self._side = torch.cuda.Stream(device=self.device)
+            self._w_next = torch.zeros(self.d + 1, device=self.device)
             eye = torch.eye(self.d + 1, device=self.device)
-            L, _ = torch.linalg.cholesky_ex(eye)
-            torch.cholesky_solve(eye[:, :1], L)
+            for st in (torch.cuda.current_stream(self.device), self._side):
+                with torch.cuda.stream(st):
+                    L, _ = torch.linalg.cholesky_ex(eye, check_errors=False)
+                    torch.cholesky_solve(eye[:, :1], L)
+            torch.cuda.synchronize(self.device)
 
     def fit_batch(self, Z):
         F.sq_residual(Z, self.d, self.wt, self.stats)    # prequential squared error with current w
         n = self.d + 2
         ks = max(1, min(self.ksplit, Z.shape[0] // 64))
         F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+
+    def host_tick(self):
         self._since += 1
+        if self._pending is not None and self._since >= self._install_at:
+            self._install()
         if self._since >= self.solve_every:
-            self.solve()
+            if self.device.type == "cuda":
+                self.solve_async()
+            else:
+                self.solve()
 
     def after_sync(self):
         pass   # the solve cadence is driven by `solveEvery`, and always runs before a query
 
-    def solve(self):
-        """w = (G_A + lambda I)^-1 G_b by Cholesky on the mirrored upper triangle."""
-        d1 = self.d + 1
+    def _snapshot(self) -> None:
+        """_work <- G + dG; must run on the stream that orders the Gram / sync kernels."""
         torch.add(self.G, self.dG, out=self._work)
+
+    def _solve_into(self, out: torch.Tensor) -> None:
+        """out <- (G_A + lambda I)^-1 G_b by Cholesky on the mirrored upper triangle of _work."""
+        d1 = self.d + 1
         F.mirror_upper(self._work, self.d + 2)
         A = self._work[:d1, :d1].clone()
         A.diagonal().add_(self.lam)
         b = self._work[:d1, d1].clone()
-        L, info = torch.linalg.cholesky_ex(A)
-        if int(info.item()) != 0:
-            w = torch.linalg.solve(A.double(), b.double()).float()
-        else:
-            w = torch.cholesky_solve(b[:, None], L)[:, 0]
-        self.wt[:d1] = w
+        L, _ = torch.linalg.cholesky_ex(A, check_errors=False)
+        out.copy_(torch.cholesky_solve(b[:, None], L)[:, 0])
+
+    def solve_async(self):
+        """Refresh w on a side stream so the ~0.6 ms latency-bound factorisation overlaps the next
+        mini-batches; the result is installed a few steps later (`_install_at`)."""
+        if self._pending is not None:
+            self._install()
+        main = torch.cuda.current_stream(self.device)
+        self._snapshot()                      # consistent copy, ordered with the Gram / sync kernels
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            self._solve_into(self._w_next)
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+        self._pending = ev
+        self._since = 0
+        self._install_at = min(8, max(1, self.solve_every - 1))
+        self.solves += 1
+
+    def _install(self):
+        torch.cuda.current_stream(self.device).wait_event(self._pending)
+        self.wt[: self.d + 1].copy_(self._w_next)
+        self._pending = None
+
+    def solve(self):
+        """Synchronous refresh (queries, checkpoints, CPU)."""
+        if self._pending is not None:
+            self._install()
+        d1 = self.d + 1
+        self._snapshot()
+        self._solve_into(self.wt[:d1])
+        if not bool(torch.isfinite(self.wt).all()):      # ill-conditioned in fp32: redo in fp64
+            A = self._work[:d1, :d1].double()
+            A.diagonal().add_(self.lam)
+            self.wt[:d1] = torch.linalg.solve(A, self._work[:d1, d1].double()).float()
         self._since = 0
         self.solves += 1
 

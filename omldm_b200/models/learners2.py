@@ -47,6 +47,9 @@ class GpuKMeans(GpuLearner):
     def refresh(self):
         F.kmeans_finalize(self.dS, self.S, self.k, self.d, self.centroids, self.cnorm)
 
+    def graph_ready(self):
+        return self._boot and self.mode != "exact"
+
     def after_sync(self):
         self.refresh()
 
@@ -150,6 +153,9 @@ class GpuMultiClassPA(GpuLearner):
             self._act.copy_((self.stats[3] - prev).float().reshape(1))
             F.scale_rows(T, C, self._act, reciprocal=True)
         F.gemm_outer(T, Z, self.W, accumulate=True, m=C, n=d + 1, ksplit=max(1, min(8, Z.shape[0] // 256)))
+
+    def graph_ready(self):
+        return self.mode != "exact"
 
     def fit_batch(self, Z, sqnorm=None):
         if self.mode == "exact":
@@ -313,6 +319,9 @@ class GpuHT(GpuLearner):
 
     def _init(self):
         self.tree.ensure_init(self.d)
+
+    def graph_ready(self):
+        return False
 
     def fit_batch(self, Z):
         h = Z[:, : self.d + 2].detach().cpu().double().numpy()

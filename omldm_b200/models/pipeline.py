@@ -98,13 +98,27 @@ class GpuPipeline:
 
     def train(self, Z: torch.Tensor, protect_input: bool = False, **kw) -> None:
         if not self.built:
-            from ..ops.functional import pad32
             self.build(self._infer_dim(Z))
+        due = self.driver._batches % self.driver.sync_every == self.driver.sync_every - 1
+        self.device_train(Z, protect_input, due, **kw)
+        self.host_tick()
+
+    def device_train(self, Z: torch.Tensor, protect_input: bool, sync_due: bool, **kw) -> None:
+        """Device work of one step (graph-capturable when `graph_safe()`)."""
         Zp = self.preprocess(Z, True, protect_input)
         self.learner.fit_batch(Zp, **kw)
-        self.batches += 1
-        if self.driver.after_batch():
+        if sync_due and self.driver.step():
             self.learner.after_sync()
+
+    def host_tick(self) -> None:
+        """Host bookkeeping of one step; runs after the device work was enqueued (or replayed)."""
+        self.batches += 1
+        self.driver.host_tick()
+        self.learner.host_tick()
+
+    def graph_safe(self) -> bool:
+        return (self.built and self.protocol != "SingleLearner" and self.driver.graph_safe
+                and self.driver.sync_every == 1 and self.learner.graph_ready())
 
     def _infer_dim(self, Z: torch.Tensor) -> int:
         d = cfg(self.request.trainingConfiguration, ["nFeatures", "dim"], None)

@@ -94,6 +94,12 @@ def launch_count() -> int:
     return int(kernels().omldm_launch_count())
 
 
+def add_launch_count(n: int) -> None:
+    """Account for kernels launched by replaying a captured CUDA graph (n per replay)."""
+    if have_cuda() and n:
+        kernels().omldm_add_launch_count(ctypes.c_longlong(n))
+
+
 def reset_launch_count() -> None:
     if have_cuda():
         kernels().omldm_reset_launch_count()

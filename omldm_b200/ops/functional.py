@@ -93,12 +93,36 @@ def holdout_swap(Z: torch.Tensor, ring: torch.Tensor, d: int, count0: int) -> No
                                            ctypes.c_longlong(count0), _lib.stream_ptr()), "holdout_swap")
         return
     h0, h1 = holdouts_before(count0), holdouts_before(count0 + B)
-    for h in range(h0, h1):
-        c = (h // 2) * 10 + 8 + (h & 1)
-        i, slot = c - count0, h % cap
-        new = Z[i].clone()
-        Z[i] = ring[slot] if h >= cap else 0.0
-        ring[slot] = new
+    if h1 == h0:
+        return
+    # vectorised shift along each slot's chain (same result as the sequential rule); the index
+    # maps depend only on (count0, B, cap), so they are built on the host without device syncs
+    import numpy as np
+    h = np.arange(h0, h1)
+    rows = (h // 2) * 10 + 8 + (h & 1) - count0             # batch row of holdout h
+    prev = h - cap                                           # the holdout it evicts
+    in_batch = np.nonzero(prev >= h0)[0]
+    from_ring = np.nonzero((prev < h0) & (h >= cap))[0]
+    last = np.nonzero(h >= h1 - cap)[0]                      # final occupant of each touched slot
+    dev = Z.device
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    old_rows = Z[t(rows)]
+    new_vals = torch.zeros_like(old_rows)
+    if len(in_batch):
+        new_vals[t(in_batch)] = old_rows[t(prev[in_batch] - h0)]
+    if len(from_ring):
+        new_vals[t(from_ring)] = ring[t(h[from_ring] % cap)]
+    Z[t(rows)] = new_vals
+    ring[t(h[last] % cap)] = old_rows[t(last)]
+
+
+def holdout_swap_dev(Z: torch.Tensor, ring: torch.Tensor, d: int, count_dev: torch.Tensor) -> None:
+    """Graph-replayable holdout: the record count is an int64 device scalar, advanced here."""
+    B, ld = Z.shape
+    cap = ring.shape[0]
+    _lib.check(_k().omldm_holdout_swap_dev(_p(Z), _i(ld), _i(B), _i(d), _p(ring), _i(cap), _p(count_dev),
+                                           _lib.stream_ptr()), "holdout_swap_dev")
+    _lib.check(_k().omldm_advance_count(_p(count_dev), ctypes.c_longlong(B), _lib.stream_ptr()), "advance_count")
 
 
 def stage_rows(raw: torch.Tensor, d: int, ld: Optional[int] = None) -> torch.Tensor:

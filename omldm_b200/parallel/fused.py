@@ -45,6 +45,12 @@ class ProtocolCounters:
 class SyncDriver:
     protocol = "CentralizedTraining"
 
+    @property
+    def graph_safe(self) -> bool:
+        """True if `step()` enqueues device work only (no host reads), so it can be graph-captured."""
+        return self.impl == "fused" or self.protocol in ("CentralizedTraining", "SingleLearner", "Synchronous",
+                                                         "Asynchronous", "SSP", "EASGD")
+
     def __init__(self, comm: PipelineComm, e: Optional[torch.Tensor], merge_mode: str, tc: Optional[dict],
                  impl: str = "fused", group=None, max_msg_params: int = 2000):
         self.comm, self.e, self.tc = comm, e, tc or {}
@@ -69,12 +75,20 @@ class SyncDriver:
 
     def after_batch(self) -> bool:
         """Called after every learner mini-batch; returns True if the model may have changed."""
+        due = self.host_tick()
+        self.synced_last_step = bool(self.step()) if due else False
+        return self.synced_last_step
+
+    def host_tick(self) -> bool:
+        """Host bookkeeping of one mini-batch; True if a protocol step is due now."""
         self._batches += 1
-        self.synced_last_step = False
         if self._batches % self.sync_every:
             return False
-        self.synced_last_step = bool(self.step())
-        return self.synced_last_step
+        self.account()
+        return True
+
+    def account(self) -> None:
+        """models / bytes / blocks shipped by one protocol step (FlinkHub.scala:118-127)."""
 
     def step(self) -> bool:
         return False
@@ -99,7 +113,7 @@ class SyncDriver:
     def _fused_allreduce(self) -> None:
         c = self.comm
         _lib.check(_lib.kernels().omldm_sync_allreduce(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
-                                                       _i(self.mode), _u(c.next_epoch()), _i(self.blocks),
+                                                       _i(self.mode), _u(0), _i(self.blocks),
                                                        _lib.stream_ptr()), "sync_allreduce")
 
 
@@ -107,19 +121,19 @@ class LocalDriver(SyncDriver):
     """CentralizedTraining: a lone learner (parallelism 1, FlinkSpoke.scala:213-216)."""
 
     def step(self) -> bool:
-        if self.mode == 1:   # fold the delta into the global statistics locally
-            self.e.add_(self.comm.buf)
-            self.comm.buf.zero_()
-            return True
+        # nothing to reconcile: additive learners always read (e + buf), so the delta may simply keep
+        # accumulating in buf - no fold pass per mini-batch
         return False
 
 
 class SynchronousDriver(SyncDriver):
     protocol = "Synchronous"
 
+    def account(self):
+        self.counters.ship(self.comm.n, self.k)
+
     def step(self) -> bool:
         self._fused_allreduce() if self.impl == "fused" else self._nccl_allreduce()
-        self.counters.ship(self.comm.n, self.k)
         return True
 
 
@@ -139,19 +153,20 @@ class AsynchronousDriver(SyncDriver):
         c = self.comm
         k = _lib.kernels()
         if ssp:
-            c.clock += 1
             _lib.check(k.omldm_sync_ssp(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale), _i(self.mode),
-                                        _u(c.clock), _i(staleness), _i(self.blocks), _lib.stream_ptr()), "sync_ssp")
+                                        _u(0), _i(staleness), _i(self.blocks), _lib.stream_ptr()), "sync_ssp")
         else:
             _lib.check(k.omldm_sync_async(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale), _i(self.mode),
                                           _i(self.blocks), _lib.stream_ptr()), "sync_async")
+
+    def account(self):
+        self.counters.ship(self.comm.n, 1)
 
     def step(self) -> bool:
         if self.impl == "fused":
             self._fused()
         else:   # closest NCCL equivalent: everybody folds everybody's delta in lock-step
             self._nccl_delta_allreduce()
-        self.counters.ship(self.comm.n, 1)
         return True
 
     def _nccl_delta_allreduce(self) -> None:
@@ -182,7 +197,6 @@ class SSPDriver(AsynchronousDriver):
             self._fused(ssp=True, staleness=self.staleness)
         else:
             self._nccl_delta_allreduce()
-        self.counters.ship(self.comm.n, 1)
         return True
 
 
@@ -212,8 +226,10 @@ class EASGDDriver(SyncDriver):
             if d is not None:
                 d.all_reduce(diff, group=self.group)
             c.hub.add_(diff)
-        self.counters.ship(c.n, 1)
         return True
+
+    def account(self):
+        self.counters.ship(self.comm.n, 1)
 
 
 class GMDriver(SyncDriver):
@@ -230,7 +246,7 @@ class GMDriver(SyncDriver):
         c = self.comm
         if self.impl == "fused":
             _lib.check(_lib.kernels().omldm_sync_gm(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
-                                                    _i(self.mode), _f(self.threshold), _u(c.next_epoch()),
+                                                    _i(self.mode), _f(self.threshold), _u(0),
                                                     _i(self.blocks), _lib.stream_ptr()), "sync_gm")
             return True   # whether a round happened is only known on the device
         d = self._dist()
@@ -271,9 +287,8 @@ class FGMDriver(SyncDriver):
     def step(self) -> bool:
         c = self.comm
         if self.impl == "fused":
-            c.step += 1
             _lib.check(_lib.kernels().omldm_sync_fgm(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
-                                                     _i(self.mode), _f(self.threshold), _f(self.eps_psi), _u(c.step),
+                                                     _i(self.mode), _f(self.threshold), _f(self.eps_psi), _u(0),
                                                      _lib.ptr(self.state), _i(self.blocks), _lib.stream_ptr()),
                        "sync_fgm")
             return True
@@ -314,7 +329,7 @@ def make_driver(protocol: str, comm: PipelineComm, e, merge_mode: str, tc, impl:
 def device_barrier(comm: PipelineComm) -> None:
     """Termination probe rendezvous (StatisticsOperator.scala:135-142) on the signal pads."""
     if comm.device.type == "cuda" and comm.k > 1:
-        _lib.check(_lib.kernels().omldm_device_barrier(comm.struct_ptr(), _u(comm.next_epoch()), _lib.stream_ptr()),
+        _lib.check(_lib.kernels().omldm_device_barrier(comm.struct_ptr(), _u(0), _lib.stream_ptr()),
                    "device_barrier")
 
 
@@ -323,7 +338,7 @@ def query_reduce(comm: PipelineComm, vals4: torch.Tensor, impl: str = "fused", g
     out = torch.empty_like(vals4)
     if comm.device.type == "cuda" and comm.k > 1 and impl == "fused":
         _lib.check(_lib.kernels().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals4), _lib.ptr(out),
-                                                     _u(comm.next_epoch()), _lib.stream_ptr()), "query_reduce")
+                                                     _u(0), _lib.stream_ptr()), "query_reduce")
         return out
     out.copy_(vals4)
     import torch.distributed as dist
