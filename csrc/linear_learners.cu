@@ -273,3 +273,52 @@ extern "C" int omldm_linear_predict(const float* Z, int ld, int B, const float* 
   linear_predict_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, w, d, out);
   return check_launch("linear_predict_kernel");
 }
+
+// ------------------------------------------------------------------------------------------
+// Mini-batch update without any allocation: the accumulator the kernel needs lives in a
+// file-scope device array instead of caller-provided scratch.  Meant for callers that cannot
+// obtain device memory at call time - e.g. an ingest loop whose latency budget cannot absorb the
+// device-wide synchronisation cudaMalloc/cudaFree imply, or an embedding process that handed all
+// of its HBM to other components at start-up and forbids driver allocations afterwards.
+//
+// The array below is part of the loaded module: every GPU that loads this library holds its
+// OMLDM_STATIC_SCRATCH_FLOATS * 4 bytes until the process exits.
+static __device__ __align__(256) float g_static_scratch[OMLDM_STATIC_SCRATCH_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+// Device address of g_static_scratch per device.  In host code the symbol name is only a
+// stand-in, not an address a kernel can use, so it is resolved once per device with
+// cudaGetSymbolAddress (with that device current) and cached.
+float* g_static_scratch_ptr[kMaxDevices] = {};
+}  // namespace
+
+extern "C" int omldm_linear_minibatch_static(const float* Z, int ld, int B, const omldm_linear_desc* desc_host,
+                                             int mean_update, void* stream) {
+  if (B <= 0) return 0;
+  const int dw = desc_host->d + 1;
+  if (desc_host->d < 1 || dw + 2 > OMLDM_STATIC_SCRATCH_FLOATS)
+    return set_error_msg("linear_minibatch_static: d exceeds OMLDM_STATIC_SCRATCH_MAX_D (the built-in scratch "
+                         "array is fixed-size); use omldm_linear_minibatch with caller-provided scratch");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_error("cudaGetDevice", e);
+  if (dev < 0 || dev >= kMaxDevices) return set_error_msg("linear_minibatch_static: device ordinal out of range");
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    // one-time set-up for this device (the current one): resolve the symbol's device address
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch);
+    if (e != cudaSuccess) return set_error("cudaGetSymbolAddress(g_static_scratch)", e);
+    g_static_scratch_ptr[dev] = p;
+  }
+  float* scratch = g_static_scratch_ptr[dev];
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array is shared by every call and keeps whatever the last call left behind; the
+  // accumulators, the active count and the block counter must start at zero.
+  e = cudaMemsetAsync(scratch, 0, sizeof(float) * (dw + 2), st);
+  if (e != cudaSuccess) return set_error("cudaMemsetAsync(g_static_scratch)", e);
+  int blocks = (B + MB_WARPS - 1) / MB_WARPS;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  linear_minibatch_kernel<<<blocks, MB_WARPS * 32, dw * 4, st>>>(Z, ld, B, *desc_host, scratch, mean_update);
+  return check_launch("linear_minibatch_kernel(static scratch)");
+}

@@ -57,6 +57,24 @@ int omldm_linear_exact(const float* Z, int ld, int B, const omldm_linear_desc* d
 size_t omldm_linear_minibatch_scratch_floats(int d);
 int omldm_linear_minibatch(const float* Z, int ld, int B, const omldm_linear_desc* desc_host,
                            float* scratch, int mean_update, void* stream);
+/* Same update as omldm_linear_minibatch, but it allocates nothing and takes no scratch pointer:
+ * the accumulator sits in a fixed-size array inside the library's device image.  This entry point
+ * has no counterpart in the reference.  It exists for callers that cannot allocate device memory
+ * when they call in - a latency-critical ingest loop that must not hit the device-wide
+ * synchronisation of cudaMalloc/cudaFree, or a host process that gave away all of its HBM at
+ * start-up and does not permit driver allocations afterwards.
+ *   - limit: d <= OMLDM_STATIC_SCRATCH_MAX_D, larger models are rejected with an error (use the
+ *     entry point above); every GPU that loads the library holds the
+ *     OMLDM_STATIC_SCRATCH_FLOATS * 4 bytes until the process exits;
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress);
+ *     make that first call before starting any stream capture on that device;
+ *   - all calls on a device share the one array: the call clears what it needs on `stream` first,
+ *     and two calls that overlap on the GPU (different streams, no ordering) race on it;
+ *   - calls no cudaMalloc / cudaFree / allocating library routine. */
+#define OMLDM_STATIC_SCRATCH_FLOATS 4096
+#define OMLDM_STATIC_SCRATCH_MAX_D (OMLDM_STATIC_SCRATCH_FLOATS - 3)
+int omldm_linear_minibatch_static(const float* Z, int ld, int B, const omldm_linear_desc* desc_host,
+                                  int mean_update, void* stream);
 /* forecast path, operators/spoke/FlinkSpoke.scala:105 */
 int omldm_linear_predict(const float* Z, int ld, int B, const float* w, int d, float* out,
                          void* stream);
