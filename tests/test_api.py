@@ -1,0 +1,119 @@
+"""JSON control API: codecs, validation, registry, bucketing (FlinkNetwork.scala:48-240), merging."""
+import json
+
+from omldm_b200.api.bucketing import MAX_PARAM_BUCKET_SIZE, bucket_response, reassemble, split
+from omldm_b200.api.pojos import (DataInstance, JobStatistics, LearnerPOJO, Prediction, QueryResponse, Request,
+                                  Statistics)
+from omldm_b200.api.registry import PipelineMap
+from omldm_b200.api.response_merger import ResponseConstructor
+from omldm_b200.messages import HubMessage, NodeId, NodeType, RemoteCallIdentifier, SpokeMessage
+from omldm_b200.stream.parsers import parse_data_instance, parse_request
+from omldm_b200.utils.partitioners import hub_key, hub_message_partition, identity_partitioner
+
+CREATE = {"id": 1, "request": "Create", "learner": {"name": "PA", "hyperParameters": {"C": 0.1}},
+          "preProcessors": [{"name": "StandardScaler"}], "trainingConfiguration": {"protocol": "FGM"}}
+
+
+def test_request_roundtrip_and_validation():
+    r = Request.from_json(json.dumps(CREATE))
+    assert r.is_valid() and r.learner.name == "PA" and r.preProcessors[0].name == "StandardScaler"
+    assert Request.from_dict(r.to_dict()).to_dict() == r.to_dict()
+    assert not Request.from_dict({"id": 1, "request": "Bogus"}).is_valid()
+    assert not Request.from_dict({"id": 1, "request": "Create"}).is_valid()          # no learner
+    assert not Request.from_dict({"id": 1, "request": "Query"}).is_valid()           # no requestId
+    assert parse_request({"id": -3, "request": "Delete"}) is None
+
+
+def test_data_instance_parser_drops_garbage_silently():
+    ok = parse_data_instance('{"numericalFeatures":[1,2],"discreteFeatures":[3],"target":1.0,"operation":"training"}')
+    assert ok.numericalFeatures == [1, 2] and ok.discreteFeatures == [3]
+    assert parse_data_instance("EOS") is None
+    assert parse_data_instance("{not json") is None
+    assert parse_data_instance('{"numericalFeatures":[1],"operation":"other"}') is None
+
+
+def test_pipeline_map_whitelist_and_routing():
+    pm = PipelineMap(4)
+    assert len(pm.flat_map(Request.from_dict(CREATE))) == 4                        # broadcast to every worker
+    assert pm.flat_map(Request.from_dict(CREATE)) == []                            # duplicate id
+    bad = dict(CREATE, id=2, learner={"name": "XGBoost"})
+    assert pm.flat_map(Request.from_dict(bad)) == []
+    badpp = dict(CREATE, id=3, preProcessors=[{"name": "PCA"}])
+    assert pm.flat_map(Request.from_dict(badpp)) == []
+    assert len(pm.flat_map(Request.from_dict({"id": 1, "request": "Query", "requestId": 9}))) == 4
+    assert len(pm.flat_map(Request.from_dict({"id": 1, "request": "Update"}))) == 4
+    ht = dict(CREATE, id=5, learner={"name": "HT"})
+    pm.flat_map(Request.from_dict(ht))
+    q = pm.flat_map(Request.from_dict({"id": 5, "request": "Query", "requestId": 1}))
+    assert len(q) == 1 and q[0].destination.node_id == 0                           # HT: worker 0 only
+    assert len(pm.flat_map(Request.from_dict({"id": 1, "request": "Delete"}))) == 4
+    assert pm.flat_map(Request.from_dict({"id": 1, "request": "Query", "requestId": 2})) == []
+    pm2 = PipelineMap(4)
+    pm2.load_state_dict(pm.state_dict())
+    assert set(pm2.nodes) == set(pm.nodes)
+
+
+def test_split_bucket_keys_and_scalars():
+    b = split({"a": list(range(25000)), "b": 0.5, "c": [7]})
+    assert sorted(b) == [0, 1, 2]
+    assert set(b[0]) == {"a[0-9999]", "b", "c"} and b[0]["c"] == 7 and b[0]["b"] == 0.5
+    assert list(b[1]) == ["a[10000-19999]"] and list(b[2]) == ["a[20000-24999]"]
+    assert len(b[2]["a[20000-24999]"]) == 5000
+    exact = split({"a": list(range(2 * MAX_PARAM_BUCKET_SIZE))})                  # reference bug fixed: no empty slice
+    assert list(exact[1]) == ["a[10000-19999]"] and len(exact[1]["a[10000-19999]"]) == 10000
+
+
+def test_bucket_response_layout_and_reassembly():
+    resp = QueryResponse(5, None, 1, [], LearnerPOJO("PA", {"C": 0.1}, {"a": list(range(35000)), "b": 0.5}, None),
+                         "Synchronous", 10, 0.1, 0.2, 0.3)
+    frags = bucket_response(resp)
+    assert len(frags) == 4 and [f.bucketIndex for f in frags] == [0, 1, 2, 3]
+    assert frags[0].dataFitted is None and frags[0].protocol is None               # bucket 0: learner maps only
+    assert frags[3].dataFitted == 10 and frags[3].protocol == "Synchronous"        # last parameter bucket: scalars
+    assert all(f.loss is None for f in frags[:3])
+    whole = reassemble(frags)
+    assert whole.learner.parameters["a"] == list(range(35000)) and whole.score == 0.3
+    small = QueryResponse(6, None, 1, [], LearnerPOJO("PA", None, {"a": list(range(15000))}, None), "x", 1, 0., 0., 0.)
+    assert len(bucket_response(small)) == 1                                        # <= 2 buckets: sent whole
+    probe = QueryResponse(-1, None, 1, None, LearnerPOJO("PA", None, {"a": list(range(50000))}, None))
+    assert bucket_response(probe) == [probe]
+
+
+def test_response_constructor_sum_and_mean():
+    rc = ResponseConstructor(3)
+    out = []
+    for i in range(3):
+        out += rc.flat_map(QueryResponse(7, None, 1, None, LearnerPOJO("PA"), "Asynchronous", 10 * (i + 1),
+                                         float(i), float(2 * i), 0.5 + 0.1 * i))
+    assert len(out) == 1
+    m = out[0]
+    assert m.dataFitted == 60 and abs(m.loss - 1.0) < 1e-12 and abs(m.cumulativeLoss - 2.0) < 1e-12
+    assert abs(m.score - 0.6) < 1e-12 and m.protocol == "Asynchronous"
+    frag = QueryResponse(8, 0, 1, None, LearnerPOJO("PA"))                          # bucket fragment passes through
+    assert rc.flat_map(frag) == [frag]
+    rc.expect(9, 1)
+    assert len(rc.flat_map(QueryResponse(9, None, 1, None, LearnerPOJO("HT"), "SingleLearner", 5, 0., 0., 1.))) == 1
+
+
+def test_messages_sizes_fanout_partitioners():
+    hm = HubMessage(3, [RemoteCallIdentifier("update_model")] * 2, NodeId(NodeType.HUB, 0),
+                    [NodeId(NodeType.SPOKE, 0), NodeId(NodeType.SPOKE, 5)], [1.0, 2.0, 3.0], None)
+    cms = hm.fan_out()
+    assert [c.destination.node_id for c in cms] == [0, 5] and cms[0].data is cms[1].data
+    assert hm.get_size() > 4 and SpokeMessage().get_size() == 4
+    assert HubMessage().fan_out() == []                                             # termination message
+    assert hub_message_partition(HubMessage(), 36) == 0
+    assert hub_message_partition(hm, 36) == 3
+    single = HubMessage(3, [RemoteCallIdentifier("x")], None, [NodeId(NodeType.SPOKE, 40)])
+    assert hub_message_partition(single, 36) == 4
+    assert identity_partitioner(5, 8) == 5 and hub_key(3, 1) == "3_1"
+
+
+def test_statistics_and_prediction_json():
+    st = Statistics(1, "FGM")
+    st.update_stats(2, 100, 3); st.update_fitted(10); st.update_score(0.5); st.update_mean_buffer_size(1.5)
+    js = JobStatistics("job", 4, 12.5, [st])
+    d = json.loads(str(js))
+    assert d["parallelism"] == 4 and d["statistics"][0]["bytes"] == 100 and d["statistics"][0]["blocks"] == 3
+    p = Prediction(1, DataInstance([1.0, 2.0], operation="forecasting"), 0.25)
+    assert json.loads(str(p))["prediction"] == 0.25

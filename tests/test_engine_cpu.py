@@ -1,0 +1,130 @@
+"""GPU-engine code path on CPU tensors (torch implementation of every op) against the fp64 oracle,
+plus the native host library (rings, producers, JSON scanner)."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from omldm_b200.engine import Engine
+from omldm_b200.ops import functional as F
+from omldm_b200.oracle.learners import make_oracle_learner
+from omldm_b200.stream import ring as R
+from omldm_b200.utils.config import JobParameters
+
+
+def run(name, hyper, kind, d, B, steps, n_aux=0, pre=(), holdout=0):
+    eng = Engine(JobParameters(parallelism=1, testSetSize=holdout), device="cpu")
+    eng.handle_request({"id": 1, "request": "Create", "learner": {"name": name, "hyperParameters": hyper},
+                        "preProcessors": list(pre), "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": d}})
+    batches = [R.generate_batch(kind, d, B, seed=4, batch_index=i, n_aux=n_aux) for i in range(steps)]
+    for b in batches:
+        eng.train_batch(b.clone(), d)
+    resp = [json.loads(o) for o in eng.handle_request({"id": 1, "request": "Query", "requestId": 2})]
+    return eng, batches, resp
+
+
+def oracle(name, hyper, batches, d):
+    o = make_oracle_learner(name, hyper)
+    for b in batches:
+        o.fit_batch(b[:, :d].double().numpy(), b[:, d + 1].double().numpy())
+    return o
+
+
+@pytest.mark.parametrize("name,kind,hyper", [("PA", R.KIND_BINARY, {"C": 0.1}),
+                                             ("RegressorPA", R.KIND_REGRESSION, {"C": 0.5, "epsilon": 0.01}),
+                                             ("SVM", R.KIND_BINARY, {"lambda": 0.01})])
+def test_linear_minibatch_equals_oracle(name, kind, hyper):
+    d = 20
+    eng, batches, resp = run(name, dict(hyper, trainingMode="minibatch"), kind, d, 128, 10)
+    o = oracle(name, hyper, batches, d)
+    assert np.allclose(resp[0]["learner"]["parameters"]["a"], o.w[:-1], rtol=1e-3, atol=1e-4)
+    assert resp[0]["protocol"] == "CentralizedTraining" and resp[0]["dataFitted"] == 1280
+
+
+def test_linear_exact_equals_oracle_per_record():
+    d = 10
+    eng, batches, resp = run("PA", {"C": 0.1, "trainingMode": "exact"}, R.KIND_BINARY, d, 64, 3)
+    o = make_oracle_learner("PA", {"C": 0.1})
+    for b in batches:
+        for r in b:
+            o.fit(r[:d].double().numpy(), float(r[d + 1]))
+    assert np.allclose(resp[0]["learner"]["parameters"]["a"], o.w[:-1], rtol=1e-4, atol=1e-5)
+
+
+def test_orr_kmeans_mcpa_nn_against_oracle():
+    d = 16
+    eng, batches, resp = run("ORR", {"lambda": 1.0, "solveEvery": 1}, R.KIND_REGRESSION, d, 256, 4)
+    o = oracle("ORR", {"lambda": 1.0}, batches, d)
+    assert np.allclose(resp[0]["learner"]["parameters"]["weights"], o.w, rtol=1e-3, atol=1e-4)
+    eng, batches, resp = run("K-means", {"k": 6}, R.KIND_CLUSTERS, d, 512, 4, n_aux=6)
+    assert abs(sum(resp[0]["learner"]["parameters"]["counts"]) - 2048) < 1e-3
+    eng, batches, resp = run("MultiClassPA", {"nClasses": 4, "C": 1.0}, R.KIND_MULTICLASS, d, 256, 20, n_aux=4)
+    o = oracle("MultiClassPA", {"nClasses": 4, "C": 1.0}, batches, d)
+    W = np.array(resp[0]["learner"]["parameters"]["a"]).reshape(4, d)
+    assert np.allclose(W, o.W[:, :-1], rtol=5e-3, atol=5e-4)
+    eng, batches, resp = run("NN", {"hiddenLayers": [8], "learningRate": 0.05}, R.KIND_REGRESSION, d, 64, 10)
+    o = oracle("NN", {"hiddenLayers": [8], "learningRate": 0.05}, batches, d)
+    assert np.allclose(np.array(resp[0]["learner"]["parameters"]["layer0"]), o.layers[0].reshape(-1), rtol=1e-3, atol=1e-4)
+
+
+def test_holdout_rule_matches_reference_semantics_and_scores():
+    d = 8
+    eng, batches, resp = run("PA", {"C": 0.1}, R.KIND_BINARY, d, 500, 6, holdout=64)
+    # 3000 records: 600 holdouts, 64 kept, the rest (evicted) trained
+    assert resp[0]["dataFitted"] == 3000 - 64 and resp[0]["score"] > 0.8
+    assert eng._holdout_rows().shape[0] == 64
+
+
+def test_preprocessor_pipeline_and_warm_start():
+    d = 6
+    pre = [{"name": "PolynomialFeatures", "hyperParameters": {"degree": 2}}, {"name": "MinMaxScaler"}]
+    eng, batches, resp = run("RegressorPA", {"C": 0.5}, R.KIND_REGRESSION, d, 128, 5, pre=pre)
+    assert len(resp[0]["learner"]["parameters"]["a"]) == 27
+    assert [p["name"] for p in resp[0]["preprocessors"]] == ["PolynomialFeatures", "MinMaxScaler"]
+    params = resp[0]["learner"]["parameters"]
+    eng2 = Engine(JobParameters(parallelism=1), device="cpu")
+    eng2.handle_request({"id": 9, "request": "Create", "learner": {"name": "RegressorPA", "parameters": params},
+                         "preProcessors": pre, "trainingConfiguration": {"nFeatures": d}})
+    r2 = json.loads(eng2.handle_request({"id": 9, "request": "Query", "requestId": 1})[0])
+    assert np.allclose(r2["learner"]["parameters"]["a"], params["a"], atol=1e-6)
+
+
+def test_checkpoint_roundtrip_and_delete():
+    d = 12
+    eng, batches, resp = run("PA", {"C": 0.1}, R.KIND_BINARY, d, 128, 4, holdout=32)
+    sd = eng.state_dict()
+    eng2 = Engine(JobParameters(parallelism=1, testSetSize=32), device="cpu")
+    eng2.load_state_dict(sd)
+    r2 = json.loads(eng2.handle_request({"id": 1, "request": "Query", "requestId": 5})[0])
+    assert np.allclose(r2["learner"]["parameters"]["a"], resp[0]["learner"]["parameters"]["a"])
+    assert r2["dataFitted"] == resp[0]["dataFitted"]
+    eng2.handle_request({"id": 1, "request": "Delete"})
+    assert eng2.handle_request({"id": 1, "request": "Query", "requestId": 6}) == []
+    js = eng.terminate()
+    assert js.statistics[0].fitted == resp[0]["dataFitted"]
+
+
+def test_topic_ring_producer_and_json_scanner():
+    t = R.Topic(5, 64, n_slots=3, pin=False)
+    t.start_synthetic(R.KIND_BINARY, seed=2, max_batches=7, n_threads=2)
+    n, seen = 0, []
+    while True:
+        g = t.get(5000)
+        if g is None:
+            break
+        slot, Z, nr = g
+        assert bool((Z[:, 5] == 1).all()) and set(Z[:, 6].unique().tolist()) <= {-1.0, 1.0}
+        n += nr
+        t.release(slot)
+    assert n == 7 * 64 and t.consumed == n
+    t.stop()
+    t2 = R.Topic(3, 4, n_slots=2, pin=False)
+    rows, nf, used = R.parse_json_records(
+        b'{"numericalFeatures":[1.5,2,3],"target":1.0,"operation":"training"}\nEOS\n{"numericalFeatures":[1,2]}\n'
+        b'{"numericalFeatures":[4,5],"discreteFeatures":[6],"operation":"forecasting"}\n', 3, 10)
+    assert rows.shape[0] == 2 and nf == 1 and rows[0, :5].tolist() == [1.5, 2.0, 3.0, 1.0, 1.0]
+    assert rows[1, :4].tolist() == [4.0, 5.0, 6.0, 2.0]
+    assert t2.put(rows) and t2.get(100)[2] == 2
+    same = R.generate_batch(R.KIND_REGRESSION, 7, 16, seed=5, batch_index=3)
+    assert torch.equal(same, R.generate_batch(R.KIND_REGRESSION, 7, 16, seed=5, batch_index=3))
