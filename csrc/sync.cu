@@ -103,7 +103,29 @@ __device__ __forceinline__ void reduce_and_broadcast_shard(const Comm& c, int me
     }
     return;
   }
-  for (size_t i = lo + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
+  size_t i = lo + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  for (; i + stride < hi; i += 2 * stride) {   // two elements (2 x world peer loads) in flight per thread
+    float4 v0[16], v1[16];
+#pragma unroll
+    for (int p = 0; p < 16; ++p)
+      if (p < c.world) {
+        v0[p] = ld_peer_v4(reinterpret_cast<const float4*>(c.bufs[p]) + i);
+        v1[p] = ld_peer_v4(reinterpret_cast<const float4*>(c.bufs[p]) + i + stride);
+      }
+    float4 a0 = v0[0], a1 = v1[0];
+#pragma unroll
+    for (int p = 1; p < 16; ++p)
+      if (p < c.world) { a0 = f4_add(a0, v0[p]); a1 = f4_add(a1, v1[p]); }
+    a0 = f4_scale(a0, scale);
+    a1 = f4_scale(a1, scale);
+#pragma unroll
+    for (int p = 0; p < 16; ++p)
+      if (p < c.world) {
+        st_peer_v4(reinterpret_cast<float4*>(c.bufs[p]) + i, a0);
+        st_peer_v4(reinterpret_cast<float4*>(c.bufs[p]) + i + stride, a1);
+      }
+  }
+  for (; i < hi; i += stride) {
     float4 v[16];
 #pragma unroll
     for (int p = 0; p < 16; ++p)
@@ -158,8 +180,27 @@ __device__ __forceinline__ void local_tail(float* buf, float* e, size_t n, int m
   const size_t n4 = n / 4;
   float4* b4 = reinterpret_cast<float4*>(buf);
   float4* e4 = reinterpret_cast<float4*>(e);
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
-    // buf was written by peers: read it through the coherent path
+  constexpr int U = 4;   // independent loads in flight per thread
+  size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  for (; i + (U - 1) * stride < n4; i += U * stride) {
+    float4 b[U], ev[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) b[u] = ld_peer_v4(b4 + i + u * stride);   // written by peers: coherent path
+    if (mode != 0) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) ev[u] = e4[i + u * stride];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (mode == 0) {
+        if (e) e4[i + u * stride] = b[u];
+      } else {
+        e4[i + u * stride] = f4_add(ev[u], b[u]);
+        b4[i + u * stride] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+  for (; i < n4; i += stride) {
     const float4 b = ld_peer_v4(b4 + i);
     if (mode == 0) {
       if (e) e4[i] = b;
@@ -450,9 +491,9 @@ static Comm to_comm(const omldm_comm* h) {
 static int clamp_blocks(int blocks, size_t n, int emulate) {
   int maxb = emulate > 1 ? (148 / emulate) : 148;
   if (maxb < 1) maxb = 1;
-  int need = static_cast<int>((n / 4 + 255) / 256);
+  int need = static_cast<int>((n / 4 + 1023) / 1024);   // ~4 float4 per thread
   if (need < 1) need = 1;
-  if (blocks <= 0) blocks = need < 64 ? need : 64;
+  if (blocks <= 0) blocks = need < 128 ? need : 128;
   if (blocks > maxb) blocks = maxb;
   return blocks;
 }
@@ -486,7 +527,7 @@ extern "C" int omldm_sync_allreduce(const omldm_comm* h, float* e_local, size_t 
                                     uint32_t epoch, int blocks, void* stream) {
   if (check_world(h, n)) return -1;
   Comm c = to_comm(h);
-  blocks = clamp_blocks(blocks, n / h->world, h->emulate);
+  blocks = clamp_blocks(blocks, n, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_allreduce_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_allreduce_kernel",
                      c, e_local, n, n, scale, mode, epoch, -1.0f);
@@ -497,7 +538,7 @@ extern "C" int omldm_sync_gm(const omldm_comm* h, float* e_local, size_t n, floa
   if (check_world(h, n)) return -1;
   if (!e_local) return set_error_msg("sync_gm: the estimate vector e is required");
   Comm c = to_comm(h);
-  blocks = clamp_blocks(blocks, n / h->world, h->emulate);
+  blocks = clamp_blocks(blocks, n, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_allreduce_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_gm_kernel",
                      c, e_local, n, n, scale, mode, epoch, threshold);
@@ -537,7 +578,7 @@ extern "C" int omldm_sync_fgm(const omldm_comm* h, float* e_local, size_t n, flo
   if (check_world(h, n)) return -1;
   if (!e_local || !state_local) return set_error_msg("sync_fgm: e and the FGM state are required");
   Comm c = to_comm(h);
-  blocks = clamp_blocks(blocks, n / h->world, h->emulate);
+  blocks = clamp_blocks(blocks, n, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_fgm_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_fgm_kernel",
                      c, e_local, n, n, scale, mode, threshold, eps_psi, step, state_local);

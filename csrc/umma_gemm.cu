@@ -20,6 +20,7 @@
 // full/empty pairs, tcgen05.commit releases stages and publishes the accumulator.
 #include "ptx.cuh"
 #include "host_common.h"
+#include <cstring>
 
 namespace omldm {
 
@@ -28,7 +29,7 @@ constexpr int BK = 32;  // tf32 elements per stage along K (= one 128-byte swizz
 constexpr int STAGES = 4;
 constexpr int GEMM_THREADS = 192;
 
-enum : int { GEMM_ACCUMULATE = 1, GEMM_UPPER_ONLY = 2, GEMM_MN_SLAB2D = 4 };
+enum : int { GEMM_ACCUMULATE = 1, GEMM_UPPER_ONLY = 2, GEMM_MN_SLAB2D = 4, GEMM_TMA_EPILOGUE = 8, GEMM_NO_TMA_EPILOGUE = 16 };
 
 template <int BN>
 struct GemmSmem {
@@ -41,7 +42,8 @@ struct GemmSmem {
 template <int BN, bool MN_MAJOR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 float* __restrict__ C, int ldc, int M, int N, int K, int k_per_split, int flags) {
+                 const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, int ldc, int M, int N, int K,
+                 int k_per_split, int flags) {
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * BN;
   if ((flags & GEMM_UPPER_ONLY) && m0 > n0 + BN - 1) return;  // tile strictly below the diagonal
@@ -65,6 +67,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (flags & GEMM_TMA_EPILOGUE) tma_prefetch_desc(&tmC);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -160,6 +163,35 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tc_fence_after();
     const int row = m0 + q * 32 + static_cast<int>(lane_id());
     const bool accumulate = (flags & GEMM_ACCUMULATE) != 0;
+    if (flags & GEMM_TMA_EPILOGUE) {
+      // TMEM -> registers -> swizzled smem tile (32 rows x 128 B per warp and 32-column chunk) ->
+      // TMA store / TMA reduce-add: the TMA unit writes full 128-B lines and performs the fp32
+      // adds at L2 (the vector red.global is lowered to scalar REDGs on sm_100a).  The operand
+      // stages are free by now (accum_bar fired), each (warp, chunk) owns a private 4 KB slot.
+      const uint32_t r = lane_id();
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= N || m0 + q * 32 >= M) break;   // warp-uniform
+        float v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
+        tmem_ld_wait();
+        uint8_t* slot = smem + (q * (BN / 32) + c) * 4096;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(slot + r * 128 + ((j ^ (r & 7)) << 4)) =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        fence_proxy_async();
+        __syncwarp();
+        if (r == 0) {
+          if (accumulate) tma_reduce_add_2d(&tmC, slot, col0, m0 + q * 32);
+          else tma_store_2d(&tmC, slot, col0, m0 + q * 32);
+          tma_commit_group();
+        }
+      }
+      if (r == 0) tma_wait_group0();
+      __syncwarp();
+    } else {
     const bool vec_ok = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
@@ -185,6 +217,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+    }
     }
   }
 
@@ -224,9 +257,25 @@ static int encode_mnmajor(CUtensorMap* tm, const float* base, int k_rows, int ld
                           strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
 }
 
+static int encode_c(CUtensorMap* tm, float* C, int M, int N, int ldc) {
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(N), static_cast<cuuint64_t>(M)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ldc) * 4};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, C, dims, strides, box, estr,
+                          CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
 template <int BN, bool MN>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, float* C, int ldc, int M,
                        int N, int K, int ksplit, int flags, cudaStream_t stream) {
+  CUtensorMap tmC;
+  memset(&tmC, 0, sizeof(tmC));
+  // the TMA epilogue needs a 16-byte aligned C with a pitch that is a multiple of 4 floats
+  if (!(flags & GEMM_NO_TMA_EPILOGUE) && (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0) {
+    if (encode_c(&tmC, C, M, N, ldc)) return -1;
+    flags |= GEMM_TMA_EPILOGUE;
+  }
   static bool attr_set[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -240,7 +289,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, float* C,
   if (ksplit < 1) ksplit = 1;
   int k_per_split = ((K + ksplit - 1) / ksplit + BK - 1) / BK * BK;
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, (K + k_per_split - 1) / k_per_split);
-  kern<<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, C, ldc, M, N, K, k_per_split, flags);
+  kern<<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, tmC, C, ldc, M, N, K, k_per_split, flags);
   return check_launch("umma_gemm_kernel");
 }
 

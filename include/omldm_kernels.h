@@ -29,7 +29,8 @@ int omldm_abi_version(void);
 
 /* ------------------------------------------------------------------ tcgen05 GEMMs (umma_gemm.cu)
  * flags: 1 = accumulate into C (red.add), 2 = skip tiles strictly below the diagonal,
- *        4 = load MN-major slabs with per-slab 2-D TMA boxes.
+ *        4 = load MN-major slabs with per-slab 2-D TMA boxes, 16 = do not use the TMA store /
+ *        reduce-add epilogue (it is used automatically when C is 16-byte aligned, ldc % 4 == 0).
  * Learner maths behind node.receiveTuple, operators/spoke/FlinkSpoke.scala:101. */
 int omldm_gemm_tn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                   int M, int N, int K, int ksplit, int flags, void* stream);

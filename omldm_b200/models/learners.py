@@ -210,6 +210,8 @@ class GpuORR(GpuLearner):
         self._since = 0
         self.solves = 0
         self._side = None
+        self._fork = None
+        self.overlap = str(_h(hyper, ["overlapLoss"], "true")).lower() in ("1", "true", "yes")
         self._pending = None
         self._install_at = 0
         self._w_next = None
@@ -232,6 +234,7 @@ class GpuORR(GpuLearner):
         if self.device.type == "cuda":
             # create the cuSOLVER handle / workspaces now, not inside somebody's timed region
             self._side = torch.cuda.Stream(device=self.device)
+            self._fork = torch.cuda.Stream(device=self.device)
             self._w_next = torch.zeros(self.d + 1, device=self.device)
             eye = torch.eye(self.d + 1, device=self.device)
             for st in (torch.cuda.current_stream(self.device), self._side):
@@ -241,9 +244,19 @@ class GpuORR(GpuLearner):
             torch.cuda.synchronize(self.device)
 
     def fit_batch(self, Z):
-        F.sq_residual(Z, self.d, self.wt, self.stats)    # prequential squared error with current w
         n = self.d + 2
         ks = max(1, min(self.ksplit, Z.shape[0] // 64))
+        if Z.is_cuda and self.overlap:
+            # fork: the prequential-loss pass (HBM-bound) runs beside the Gram GEMM (tensor-bound);
+            # they touch disjoint outputs and both only read Z
+            main = torch.cuda.current_stream(self.device)
+            self._fork.wait_stream(main)
+            F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+            with torch.cuda.stream(self._fork):
+                F.sq_residual(Z, self.d, self.wt, self.stats)
+            main.wait_stream(self._fork)
+            return
+        F.sq_residual(Z, self.d, self.wt, self.stats)    # prequential squared error with current w
         F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
 
     def host_tick(self):

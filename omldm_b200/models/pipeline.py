@@ -148,6 +148,7 @@ class GpuPipeline:
         win_n = c["fitted"] - self._win_n
         loss = (c["loss_sum"] - self._win_loss) / win_n if win_n > 0 else 0.0
         self._win_loss, self._win_n = c["loss_sum"], c["fitted"]
+        self.curve.append((loss, c["fitted"]))     # learning curve = (windowed loss, #fitted), FlinkHub.scala:101-107
         pojo = LearnerPOJO(lrn.name, dict(lrn.hyper), lrn.to_parameters(), lrn.data_structure())
         return QueryResponse(response_id, None, self.request.id, pps, pojo, self.protocol, c["fitted"], loss,
                              c["loss_sum"], self.score(ring))

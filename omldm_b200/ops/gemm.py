@@ -17,6 +17,12 @@ from . import _lib
 ACCUMULATE = 1
 UPPER_ONLY = 2
 MN_SLAB2D = 4
+NO_TMA_EPILOGUE = 16
+
+
+import os as _os
+_ENV_FLAGS = (MN_SLAB2D if _os.environ.get('OMLDM_MN_LOAD', '3d') == '2d' else 0) | \
+    (NO_TMA_EPILOGUE if _os.environ.get('OMLDM_GEMM_EPILOGUE', 'tma') == 'red' else 0)
 
 
 def _check2d(t: torch.Tensor, name: str) -> None:
@@ -40,7 +46,7 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None, *
         r = a @ b.t()
         out.add_(r) if accumulate else out.copy_(r)
         return out
-    flags = ACCUMULATE if (accumulate or ksplit > 1) else 0
+    flags = (ACCUMULATE if (accumulate or ksplit > 1) else 0) | _ENV_FLAGS
     if ksplit > 1 and not accumulate:
         out.zero_()
     rc = _lib.kernels().omldm_gemm_tn(
@@ -77,9 +83,8 @@ def gemm_outer(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None
         out[:M, :N].add_(r) if accumulate_eff else out[:M, :N].copy_(r)
         return out
     flags = (ACCUMULATE if (accumulate_eff or ksplit > 1) else 0) | (UPPER_ONLY if upper_only else 0)
-    import os
-    if os.environ.get('OMLDM_MN_LOAD', '3d') == '2d':
-        flags |= MN_SLAB2D
+    if _ENV_FLAGS:
+        flags |= _ENV_FLAGS
     if ksplit > 1 and not accumulate_eff:
         out.zero_()
     rc = _lib.kernels().omldm_gemm_outer(
