@@ -46,7 +46,7 @@ CONFIGS = {
     "kmeans": dict(model="K-means", d=128, batch=16384, protocol="SSP", kind=2, n_aux=256,
                    hyper={"k": 256}, tc={"staleness": 3}, pre=[],
                    name="Online k-means k=256 on 128-dim synthetic stream, SSP protocol"),
-    "mcpa": dict(model="MultiClassPA", d=100000, batch=256, protocol="Synchronous", kind=3, n_aux=10,
+    "mcpa": dict(model="MultiClassPA", d=100000, batch=256, protocol="Synchronous", kind=4, n_aux=10, nnz=128,
                  hyper={"nClasses": 10, "C": 0.1}, tc={}, pre=[],
                  name="Multiclass PA 100k-dim sparse-to-dense stream, hub sharded over all GPUs"),
 }
@@ -153,12 +153,22 @@ def main() -> None:
     # ---- inputs: a set of distinct batches larger than L2 (126 MB), resident on the device
     ld = F.pad32(d + 2)
     n_rot = max(3, min(64, -(-160_000_000 // (B * ld * 4)) + 1))   # distinct batches: > 126 MB L2 in total
-    host_pool = [R.generate_batch(cfg["kind"], d, B, seed=1234 + rank, batch_index=i, n_aux=cfg["n_aux"], pin=True)
-                 for i in range(n_rot)]
+    sparse = cfg["kind"] == 4
+    nnz = cfg.get("nnz", 0)
+    if sparse:      # device-resident sparse slots; the dense rows are produced on the GPU every step
+        n_rot = 4
+        host_pool = [R.generate_sparse_batch(d, B, nnz, n_aux=cfg["n_aux"], seed=1234 + rank, batch_index=i, pin=True)
+                     for i in range(n_rot)]
+    else:
+        host_pool = [R.generate_batch(cfg["kind"], d, B, seed=1234 + rank, batch_index=i, n_aux=cfg["n_aux"], pin=True)
+                     for i in range(n_rot)]
     dev_pool = [h.to(dev) for h in host_pool]
 
     def step_device(i: int) -> None:
-        eng.train_batch(dev_pool[i % n_rot], d)
+        if sparse:
+            eng.train_sparse(dev_pool[i % n_rot], B, nnz, d)
+        else:
+            eng.train_batch(dev_pool[i % n_rot], d)
 
     def sync_all() -> None:
         if world > 1:
@@ -189,14 +199,18 @@ def main() -> None:
     # ---- end to end: pinned ring slot -> H2D -> train -> loss D2H, every step
     e2e = None
     if not args.no_e2e:
-        topic = R.Topic(d, B, n_slots=n_rot)
-        topic.start_synthetic(cfg["kind"], seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_REPLAY, n_threads=2)
+        if sparse:
+            topic = R.SparseTopic(d, B, nnz, n_slots=8)
+            topic.start_synthetic(seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_GENERATE, n_threads=2)
+        else:
+            topic = R.Topic(d, B, n_slots=n_rot)
+            topic.start_synthetic(cfg["kind"], seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_REPLAY, n_threads=2)
         pending = []   # (slot, event recorded after the slot's H2D copy)
 
         def step_e2e():
             got = topic.get(10000)
             slot, Zh, _ = got
-            loss = eng.train_batch_host(Zh, d)
+            loss = eng.train_sparse_host(Zh, B, nnz, d) if sparse else eng.train_batch_host(Zh, d)
             pending.append((slot, eng.last_copy_event))
             while len(pending) > 1:          # give a slot back once its H2D copy has completed
                 s0, ev = pending.pop(0)
@@ -215,7 +229,7 @@ def main() -> None:
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": world * B * args.steps / float(dt.item()), "unit": "records/s",
-               "h2d_bytes_per_step": B * ld * 4, "d2h_bytes_per_step": 32,
+               "h2d_bytes_per_step": (B * (2 * nnz + 1) * 4) if sparse else (B * ld * 4), "d2h_bytes_per_step": 32,
                "last_loss_sum": float(loss_host[0])}
         topic.stop()
     clocks = sampler.stop() if sampler else None
@@ -231,8 +245,11 @@ def main() -> None:
             "config": {"model": cfg["name"], "learner": cfg["model"], "protocol": p.protocol,
                        "global_batch": B * world, "per_gpu_batch": B, "features": d, "seq_len": None,
                        "parallelism": f"dp{world} workers + {world} hub shards",
-                       "l2": f"inputs rotate over {n_rot} distinct batches = {n_rot * B * ld * 4 / 1e6:.0f} MB > 126 MB L2",
-                       "sync_every": p.driver.sync_every, "model_bytes": p.comm.n * 4},
+                       "l2": (f"dense rows are rebuilt every step into 2 alternating {B * ld * 4 / 1e6:.0f} MB buffers "
+                              f"(sparse->dense on the GPU); working set per step > 126 MB L2") if sparse else
+                             f"inputs rotate over {n_rot} distinct batches = {n_rot * B * ld * 4 / 1e6:.0f} MB > 126 MB L2",
+                       "sync_every": p.driver.sync_every, "model_bytes": p.comm.n * 4,
+                       "sync_transport": "NVLS multimem" if getattr(p.comm, "multicast", False) else "P2P ld/st over NVLink"},
             "clocks": clocks, "numa_node": numa, "e2e": e2e, "gpu_launches": launches, "comm_status": status,
         }
         print(json.dumps(out))

@@ -44,7 +44,7 @@ struct Truth {
   float bias;
   Truth(int kind, int d, int n_aux, uint64_t seed) {
     Rng g(seed ^ 0xABCDEF1234ull);
-    const int rows = (kind >= 2) ? (n_aux > 0 ? n_aux : 1) : 1;
+    const int rows = (kind >= 2) ? (n_aux > 0 ? n_aux : 1) : 1;   // kind 3 / 4: one plane per class
     w.resize(static_cast<size_t>(rows) * d);
     const float scale = kind == 2 ? 4.0f : 1.0f / std::sqrt(static_cast<float>(d));
     for (auto& v : w) v = g.normal() * scale;
@@ -87,6 +87,33 @@ void fill_batch(float* dst, const Truth& tr, int kind, int d, int ld, int batch,
   }
 }
 
+// Sparse multiclass batch in fixed-width (ELL) form: slot = [int32 idx B*nnz | float val B*nnz | float y B].
+// The label is the argmax over n_aux hidden planes evaluated on the non-zeros only.
+void fill_sparse_batch(uint8_t* slot, const Truth& tr, int d, int nnz, int batch, int n_aux, uint64_t seed,
+                       uint64_t batch_index) {
+  Rng g(seed * 0x100000001B3ull + batch_index * 0x9E3779B97F4A7C15ull + 7);
+  int32_t* idx = reinterpret_cast<int32_t*>(slot);
+  float* val = reinterpret_cast<float*>(slot + sizeof(int32_t) * static_cast<size_t>(batch) * nnz);
+  float* tgt = val + static_cast<size_t>(batch) * nnz;
+  for (int r = 0; r < batch; ++r) {
+    float best = -1e30f;
+    int bc = 0;
+    int32_t* ri = idx + static_cast<size_t>(r) * nnz;
+    float* rv = val + static_cast<size_t>(r) * nnz;
+    for (int j = 0; j < nnz; ++j) {
+      ri[j] = static_cast<int32_t>(g.next() % static_cast<uint64_t>(d));
+      rv[j] = g.normal();
+    }
+    for (int c = 0; c < n_aux; ++c) {
+      const float* p = tr.w.data() + static_cast<size_t>(c) * d;
+      float s = 0.f;
+      for (int j = 0; j < nnz; ++j) s += p[ri[j]] * rv[j];
+      if (s > best) { best = s; bc = c; }
+    }
+    tgt[r] = static_cast<float>(bc);
+  }
+}
+
 }  // namespace
 
 struct omldm_producer {
@@ -115,7 +142,11 @@ static void producer_loop(omldm_producer* p) {
     }
     float* dst = static_cast<float*>(omldm_ring_slot_ptr(p->ring, slot));
     if (p->mode == 0 || !p->filled[slot]) {
-      fill_batch(dst, p->truth, p->kind, p->d, p->ld, p->batch, p->n_aux, p->seed, static_cast<uint64_t>(b));
+      if (p->kind == 4)   // sparse multiclass: `ld` carries the non-zeros per record
+        fill_sparse_batch(reinterpret_cast<uint8_t*>(dst), p->truth, p->d, p->ld, p->batch, p->n_aux, p->seed,
+                          static_cast<uint64_t>(b));
+      else
+        fill_batch(dst, p->truth, p->kind, p->d, p->ld, p->batch, p->n_aux, p->seed, static_cast<uint64_t>(b));
       p->filled[slot] = 1;
     }
     omldm_ring_commit_write(p->ring, slot, p->batch);
@@ -125,7 +156,7 @@ static void producer_loop(omldm_producer* p) {
 
 extern "C" omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
                                                 uint64_t seed, int mode, int64_t max_batches, int n_threads) {
-  if (!r || d <= 0 || ld < d + 2 || batch <= 0) return nullptr;
+  if (!r || d <= 0 || batch <= 0 || (kind != 4 && ld < d + 2) || (kind == 4 && ld <= 0)) return nullptr;
   auto* p = new omldm_producer(kind, d, n_aux, seed);
   p->ring = r; p->kind = kind; p->d = d; p->ld = ld; p->batch = batch; p->n_aux = n_aux; p->mode = mode;
   p->seed = seed; p->max_batches = max_batches;
@@ -141,6 +172,12 @@ extern "C" void omldm_producer_stop(omldm_producer* p) {
   p->stop.store(true);
   for (auto& t : p->threads) t.join();
   delete p;
+}
+
+extern "C" void omldm_generate_sparse_batch(void* slot, int d, int nnz, int batch, int n_aux, uint64_t seed,
+                                            uint64_t batch_index) {
+  Truth tr(4, d, n_aux, seed);
+  fill_sparse_batch(static_cast<uint8_t*>(slot), tr, d, nnz, batch, n_aux, seed, batch_index);
 }
 
 extern "C" void omldm_generate_batch(float* dst, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,

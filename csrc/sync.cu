@@ -41,7 +41,8 @@ __device__ __forceinline__ uint32_t resolve_seq(uint32_t given, const uint32_t* 
 __device__ __forceinline__ int my_rank(const Comm& c) { return c.emulate > 1 ? static_cast<int>(blockIdx.y) : c.rank; }
 __device__ __forceinline__ uint32_t* my_local(const Comm& c) { return c.local + my_rank(c) * LOCAL_WORDS; }
 
-constexpr uint32_t SPIN_LIMIT = 1u << 26;
+// ~1.3 us per poll once the back-off reaches 256 ns: 2^21 polls bound every wait to about 3 s
+constexpr uint32_t SPIN_LIMIT = 1u << 21;
 
 __device__ __forceinline__ void flag_timeout(const Comm& c, int me, uint32_t code) {
   atomicOr(reinterpret_cast<unsigned int*>(c.pads[me] + OMLDM_PAD_STATUS), code);

@@ -38,6 +38,11 @@ omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int
                                      uint64_t seed, int mode, int64_t max_batches, int n_threads);
 void omldm_producer_stop(omldm_producer* p);
 
+/* kind 4 = sparse multiclass stream (BASELINE.json config 5): pass the non-zeros per record as `ld`;
+ * a slot is [int32 idx batch*nnz | float val batch*nnz | float target batch] (fixed-width rows, so the
+ * CSR row pointer is implicit) and is densified on the GPU (omldm_densify). */
+void omldm_generate_sparse_batch(void* slot, int d, int nnz, int batch, int n_aux, uint64_t seed,
+                                 uint64_t batch_index);
 /* Fill one caller buffer with a synthetic staged batch (same generators, no ring). */
 void omldm_generate_batch(float* dst, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
                           uint64_t batch_index);

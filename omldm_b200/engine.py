@@ -64,6 +64,7 @@ class Engine:
         self._graph_launches: Dict[Any, int] = {}
         self._seen: Dict[Any, int] = {}
         self._count_dev: Optional[torch.Tensor] = None
+        self._sparse_key = None
 
     # ============================================================================ control plane
     def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
@@ -248,6 +249,46 @@ class Engine:
             self.last_copy_event.record(self._copy_stream)
         cur.wait_stream(self._copy_stream)
         self.train_batch(self._stage[i], d, **kw)
+        return self._read_stats_host()
+
+    # ---- sparse streams (BASELINE config 5: "100k-dim sparse-to-dense stream") ---------------------
+    def train_sparse(self, slot: torch.Tensor, batch: int, nnz: int, d: int) -> None:
+        """One step from a fixed-width sparse slot on the device ([int32 idx | float val | float y],
+        see stream.ring.SparseTopic): densify on the GPU (csrc/ingest.cu), then the normal step."""
+        from .stream.ring import SparseTopic
+        idx, val, tgt = SparseTopic.unpack(slot, batch, nnz)
+        key = (batch, nnz, d)
+        if self._sparse_key != key:
+            self._sparse_key = key
+            self._indptr = torch.arange(0, (batch + 1) * nnz, nnz, dtype=torch.int32, device=self.device)
+            self._dense = [torch.empty(batch, F.pad32(d + 2), device=self.device) for _ in range(2)]
+            self._sqn = torch.empty(batch, device=self.device)
+            self._dense_i = 0
+        Z = self._dense[self._dense_i]
+        self._dense_i ^= 1
+        F.densify(self._indptr, idx, val, tgt, d, out=Z, sq_out=self._sqn)
+        self.train_batch(Z, d)
+
+    def train_sparse_host(self, slot_host: torch.Tensor, batch: int, nnz: int, d: int) -> torch.Tensor:
+        """e2e sparse step: pinned host slot -> H2D (a few hundred KB instead of the dense batch) ->
+        densify -> train; returns the pinned stats tensor like `train_batch_host`."""
+        if self.device.type != "cuda":
+            self.train_sparse(slot_host.clone(), batch, nnz, d)
+            return self._read_stats_host()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        i = self._stage_i
+        self._stage_i ^= 1
+        cur = torch.cuda.current_stream(self.device)
+        if self._stage[i] is None or self._stage[i].shape != slot_host.shape or self._stage[i].dtype != slot_host.dtype:
+            self._stage[i] = torch.empty(slot_host.shape, dtype=slot_host.dtype, device=self.device)
+        self._copy_stream.wait_stream(cur)
+        with torch.cuda.stream(self._copy_stream):
+            self._stage[i].copy_(slot_host, non_blocking=True)
+            self.last_copy_event = torch.cuda.Event()
+            self.last_copy_event.record(self._copy_stream)
+        cur.wait_stream(self._copy_stream)
+        self.train_sparse(self._stage[i], batch, nnz, d)
         return self._read_stats_host()
 
     def _read_stats_host(self) -> torch.Tensor:

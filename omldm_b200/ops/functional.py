@@ -95,25 +95,38 @@ def holdout_swap(Z: torch.Tensor, ring: torch.Tensor, d: int, count0: int) -> No
     h0, h1 = holdouts_before(count0), holdouts_before(count0 + B)
     if h1 == h0:
         return
-    # vectorised shift along each slot's chain (same result as the sequential rule); the index
-    # maps depend only on (count0, B, cap), so they are built on the host without device syncs
+    # vectorised shift along each slot's chain (same result as the sequential rule).  The index maps
+    # depend only on (count0 mod 10, h0 mod cap, B, cap) once the ring is full, so they are built on
+    # the host once and cached on the device: the steady state issues no host<->device syncs.
     import numpy as np
-    h = np.arange(h0, h1)
-    rows = (h // 2) * 10 + 8 + (h & 1) - count0             # batch row of holdout h
-    prev = h - cap                                           # the holdout it evicts
-    in_batch = np.nonzero(prev >= h0)[0]
-    from_ring = np.nonzero((prev < h0) & (h >= cap))[0]
-    last = np.nonzero(h >= h1 - cap)[0]                      # final occupant of each touched slot
-    dev = Z.device
-    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    old_rows = Z[t(rows)]
+    steady = h0 >= cap
+    key = (count0 % 10, h0 % cap, B, cap, str(Z.device)) if steady else None
+    idx = _HOLDOUT_IDX.get(key) if key is not None else None
+    if idx is None:
+        h = np.arange(h0, h1)
+        rows = (h // 2) * 10 + 8 + (h & 1) - count0             # batch row of holdout h
+        prev = h - cap                                           # the holdout it evicts
+        in_batch = np.nonzero(prev >= h0)[0]
+        from_ring = np.nonzero((prev < h0) & (h >= cap))[0]
+        last = np.nonzero(h >= h1 - cap)[0]                      # final occupant of each touched slot
+        dev = Z.device
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        idx = (t(rows), t(in_batch), t(prev[in_batch] - h0), t(from_ring), t(h[from_ring] % cap),
+               t(h[last] % cap), t(last))
+        if key is not None:
+            _HOLDOUT_IDX[key] = idx
+    rows_t, inb, inb_src, fr, fr_slot, last_slot, last_i = idx
+    old_rows = Z[rows_t]
     new_vals = torch.zeros_like(old_rows)
-    if len(in_batch):
-        new_vals[t(in_batch)] = old_rows[t(prev[in_batch] - h0)]
-    if len(from_ring):
-        new_vals[t(from_ring)] = ring[t(h[from_ring] % cap)]
-    Z[t(rows)] = new_vals
-    ring[t(h[last] % cap)] = old_rows[t(last)]
+    if inb.numel():
+        new_vals[inb] = old_rows[inb_src]
+    if fr.numel():
+        new_vals[fr] = ring[fr_slot]
+    Z[rows_t] = new_vals
+    ring[last_slot] = old_rows[last_i]
+
+
+_HOLDOUT_IDX: dict = {}
 
 
 def holdout_swap_dev(Z: torch.Tensor, ring: torch.Tensor, d: int, count_dev: torch.Tensor) -> None:
@@ -142,12 +155,13 @@ def stage_rows(raw: torch.Tensor, d: int, ld: Optional[int] = None) -> torch.Ten
 
 
 def densify(indptr: torch.Tensor, indices: torch.Tensor, values: torch.Tensor, targets: Optional[torch.Tensor],
-            d: int, ld: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+            d: int, ld: Optional[int] = None, out: Optional[torch.Tensor] = None,
+            sq_out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """CSR batch -> staged dense rows and squared row norms (bias included)."""
     B = indptr.numel() - 1
     ld = ld or pad32(d + 2)
-    Z = torch.empty(B, ld, device=values.device, dtype=torch.float32)
-    sq = torch.empty(B, device=values.device, dtype=torch.float32)
+    Z = out if out is not None else torch.empty(B, ld, device=values.device, dtype=torch.float32)
+    sq = sq_out if sq_out is not None else torch.empty(B, device=values.device, dtype=torch.float32)
     if native(values):
         _lib.check(_k().omldm_densify(_p(indptr), _p(indices), _p(values), _i(B), _i(d), _p(targets), _p(Z),
                                       _i(ld), _p(sq), _lib.stream_ptr()), "densify")
@@ -365,10 +379,10 @@ def sq_residual(Z: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor) 
         _lib.check(_k().omldm_sq_residual(_p(Z), _i(Z.stride(0)), _i(B), _i(d), _p(wt), _i(n), _p(stats),
                                           _lib.stream_ptr()), "sq_residual")
         return
-    valid = Z[:, d] != 0
-    r = Z[valid, :n] @ wt
+    valid = (Z[:, d] != 0)
+    r = (Z[:, :n] @ wt) * valid                 # no boolean indexing: stays asynchronous on the GPU
     stats[0] += (r.double() ** 2).sum()
-    stats[2] += int(valid.sum().item())
+    stats[2] += valid.sum()
 
 
 def mirror_upper(A: torch.Tensor, n: int) -> None:

@@ -77,10 +77,12 @@ def gemm_outer(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None
         accumulate_eff = accumulate
     _check2d(out, "out")
     if not _lib.use_native(a, b, out):
-        r = a[:, :M].t() @ b[:, :N]
-        if upper_only:
-            pass  # the CPU path simply computes every tile
-        out[:M, :N].add_(r) if accumulate_eff else out[:M, :N].copy_(r)
+        # torch / cuBLAS implementation (CPU tests and the GPU baseline): every tile is computed
+        if accumulate_eff:
+            out[:M, :N].addmm_(a[:, :M].t(), b[:, :N])
+        else:
+            torch.mm(a[:, :M].t(), b[:, :N], out=out[:M, :N]) if out[:M, :N].is_contiguous() else \
+                out[:M, :N].copy_(a[:, :M].t() @ b[:, :N])
         return out
     flags = (ACCUMULATE if (accumulate_eff or ksplit > 1) else 0) | (UPPER_ONLY if upper_only else 0)
     if _ENV_FLAGS:

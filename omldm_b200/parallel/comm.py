@@ -63,6 +63,9 @@ class Region:
             self.locals = [torch.zeros(nbytes, dtype=torch.uint8) for _ in range(n)]
             self.bases = [t.data_ptr() for t in self.locals]
             return
+        if emulate <= 1 and world > 1 and os.environ.get("OMLDM_USE_SYMM_MEM", "0") == "1":
+            if self._try_symm_mem(nbytes, device, group):
+                return
         n_local = emulate if emulate > 1 else 1
         self.locals = []
         bases_local = []
@@ -91,6 +94,27 @@ class Region:
             self._imported.append(out.value)
             self.bases.append(out.value)
         dist.barrier(group=group)
+
+    def _try_symm_mem(self, nbytes: int, device, group) -> bool:
+        """torch symmetric memory: peer pointers plus an NVLS multicast alias (multimem path)."""
+        try:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm_mem
+            g = group if group is not None else dist.group.WORLD
+            t = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+            t.zero_()
+            hdl = symm_mem.rendezvous(t, g.group_name if hasattr(g, "group_name") else g)
+            self.locals = [t]
+            self.bases = [int(p) for p in hdl.buffer_ptrs]
+            self.mc_base = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            self._keep = [hdl]
+            torch.cuda.synchronize(device)
+            dist.barrier(group=group)
+            return True
+        except Exception as e:   # fall back to CUDA IPC
+            import warnings
+            warnings.warn(f"symmetric memory unavailable ({e}); using CUDA IPC")
+            return False
 
     def close(self) -> None:
         if self.device.type != "cuda":
@@ -137,7 +161,9 @@ class PipelineComm:
         self.tables = torch.tensor([ptr_bufs, ptr_hubs, ptr_pads], dtype=torch.int64).to(self.device)
         self.struct = CommStruct(
             self.tables[0].data_ptr(), self.tables[1].data_ptr(), self.tables[2].data_ptr(),
-            self.local.data_ptr(), 0, rank if emulate <= 1 else 0, self.k, emulate if emulate > 1 else 0)
+            self.local.data_ptr(), (self.region.mc_base + self._off_buf) if self.region.mc_base else 0,
+            rank if emulate <= 1 else 0, self.k, emulate if emulate > 1 else 0)
+        self.multicast = bool(self.region.mc_base)
 
     # local views of this rank (rank 0 in emulate mode)
     @property

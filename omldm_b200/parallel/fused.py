@@ -308,6 +308,25 @@ class FGMDriver(SyncDriver):
     def device_rounds(self) -> int:
         return int(self.state[4].item()) if self.impl == "fused" else self.rounds
 
+    def flush(self) -> None:
+        """End of stream.  A round the hub declared during the very last steps may have been seen by
+        some ranks only; those ranks would wait in the round-end barrier for peers that stopped
+        stepping.  Agree (host side) whether a round is pending anywhere and, if so, step once more
+        on every rank - the flag is in every pad, so everybody now takes the round-end branch."""
+        if self.impl != "fused" or self.comm.k <= 1:
+            return
+        from .comm import PAD_FGM
+        d = self._dist()
+        for _ in range(4):
+            torch.cuda.synchronize(self.comm.device)
+            pending = int(self.comm.pad[PAD_FGM + 3].item()) != int(self.state[0].item())
+            flag = torch.tensor([1.0 if pending else 0.0], device=self.comm.device)
+            if d is not None:
+                d.all_reduce(flag, op=d.ReduceOp.MAX, group=self.group)
+            if float(flag.item()) == 0.0:
+                return
+            self.step()
+
 
 DRIVERS = {"CentralizedTraining": LocalDriver, "SingleLearner": LocalDriver, "Synchronous": SynchronousDriver,
            "Asynchronous": AsynchronousDriver, "SSP": SSPDriver, "EASGD": EASGDDriver, "GM": GMDriver,

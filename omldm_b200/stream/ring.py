@@ -15,7 +15,7 @@ import torch
 from ..ops import _lib
 from ..ops.functional import pad32
 
-KIND_BINARY, KIND_REGRESSION, KIND_CLUSTERS, KIND_MULTICLASS = 0, 1, 2, 3
+KIND_BINARY, KIND_REGRESSION, KIND_CLUSTERS, KIND_MULTICLASS, KIND_SPARSE_MULTICLASS = 0, 1, 2, 3, 4
 MODE_GENERATE, MODE_REPLAY = 0, 1
 
 _configured = False
@@ -44,6 +44,7 @@ def _h():
         h.omldm_producer_start.argtypes = [vp, i, i, i, i, i, u64, i, i64, i]
         h.omldm_producer_stop.argtypes = [vp]
         h.omldm_generate_batch.argtypes = [vp, i, i, i, i, i, u64, u64]
+        h.omldm_generate_sparse_batch.argtypes = [vp, i, i, i, i, u64, u64]
         h.omldm_parse_json_records.restype = i
         h.omldm_parse_json_records.argtypes = [ctypes.c_char_p, sz, i, vp, i, i, ctypes.POINTER(i),
                                                ctypes.POINTER(sz)]
@@ -129,6 +130,45 @@ class Topic:
                 self._ring = None
         except Exception:
             pass
+
+
+class SparseTopic(Topic):
+    """Ring of sparse mini-batches in fixed-width form (the "sparse" half of BASELINE config 5's
+    sparse-to-dense stream).  A slot is one uint8 row: [int32 idx B*nnz | float val B*nnz | float y B]."""
+
+    def __init__(self, d: int, batch: int, nnz: int, n_slots: int = 8, pin: Optional[bool] = None):
+        self.d, self.batch, self.nnz, self.n_slots = d, batch, nnz, n_slots
+        self.ld = nnz
+        self.slot_bytes = batch * (2 * nnz + 1) * 4
+        self.storage = torch.zeros(n_slots, self.slot_bytes, dtype=torch.uint8)
+        if pin is None:
+            pin = torch.cuda.is_available()
+        if pin:
+            self.storage = self.storage.pin_memory()
+        self._ring = _h().omldm_ring_create(self.storage.data_ptr(), n_slots, self.slot_bytes)
+        self._producer = None
+
+    def start_synthetic(self, kind: int = KIND_SPARSE_MULTICLASS, seed: int = 0, n_aux: int = 10,
+                        mode: int = MODE_GENERATE, max_batches: int = -1, n_threads: int = 1) -> None:
+        super().start_synthetic(KIND_SPARSE_MULTICLASS, seed, n_aux, mode, max_batches, n_threads)
+
+    @staticmethod
+    def unpack(slot: torch.Tensor, batch: int, nnz: int):
+        """(indices int32 [B*nnz], values fp32 [B*nnz], targets fp32 [B]) views of a (device) slot."""
+        n = batch * nnz
+        idx = slot[: 4 * n].view(torch.int32)
+        val = slot[4 * n: 8 * n].view(torch.float32)
+        tgt = slot[8 * n: 8 * n + 4 * batch].view(torch.float32)
+        return idx, val, tgt
+
+
+def generate_sparse_batch(d: int, batch: int, nnz: int, n_aux: int = 10, seed: int = 0, batch_index: int = 0,
+                          pin: bool = False) -> torch.Tensor:
+    out = torch.empty(batch * (2 * nnz + 1) * 4, dtype=torch.uint8)
+    if pin and torch.cuda.is_available():
+        out = out.pin_memory()
+    _h().omldm_generate_sparse_batch(out.data_ptr(), d, nnz, batch, n_aux, seed, batch_index)
+    return out
 
 
 def generate_batch(kind: int, d: int, batch: int, seed: int = 0, batch_index: int = 0, n_aux: int = 0,
