@@ -107,6 +107,8 @@ def main() -> None:
     ap.add_argument("--config", default="orr", choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tc", action="append", default=[], help="extra trainingConfiguration key=value")
+    ap.add_argument("--hyper", action="append", default=[], help="extra learner hyper-parameter key=value")
     args = ap.parse_args()
 
     if args.impl == "reference":
@@ -147,6 +149,8 @@ def main() -> None:
     params = JobParameters(parallelism=world, jobName="bench_" + args.config)
     eng = Engine(params, rank, world, dev, impl=impl)
     tc = dict(cfg["tc"], protocol=cfg["protocol"], nFeatures=d)
+    tc.update(kv.split("=", 1) for kv in args.tc)
+    cfg = dict(cfg, hyper=dict(cfg["hyper"], **dict(kv.split("=", 1) for kv in args.hyper)))
     eng.handle_request({"id": 1, "request": "Create", "learner": {"name": cfg["model"], "hyperParameters": cfg["hyper"]},
                         "preProcessors": cfg["pre"], "trainingConfiguration": tc})
 
@@ -179,6 +183,7 @@ def main() -> None:
         step_device(i)
     for i in range(args.warmup):
         step_device(i)
+    eng.flush()
     sync_all()
     sampler = ClockSampler(local) if rank == 0 else None
     _lib.reset_launch_count()
@@ -186,6 +191,7 @@ def main() -> None:
     e0.record()
     for i in range(args.steps):
         step_device(args.warmup + i)
+    eng.flush()          # inside the timed region: the protocol's end-of-stream settlement is part of the work
     e1.record()
     torch.cuda.synchronize()
     launches = _lib.launch_count()
@@ -220,10 +226,12 @@ def main() -> None:
             return loss
         for _ in range(max(8, args.warmup)):   # includes graph capture for the two staging buffers
             step_e2e()
+        eng.flush()
         sync_all()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             loss_host = step_e2e()
+        eng.flush()
         torch.cuda.synchronize()
         dt = torch.tensor([time.perf_counter() - t0], device=dev)
         if world > 1:

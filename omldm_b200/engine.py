@@ -114,6 +114,8 @@ class Engine:
         single = p.protocol == "SingleLearner"
         if single and self.rank != 0:
             return []
+        if p.built and not single:
+            p.driver.flush()     # collective: pipelined / monitored protocols share their last delta first
         ring = self._holdout_rows()
         resp = p.local_response(response_id, ring)
         if self.world > 1 and not single and p.built:
@@ -161,7 +163,8 @@ class Engine:
         for p in self.pipelines.values():
             if p.protocol != "SingleLearner" or self.rank == 0:
                 self._build(p, d)
-        key = (Z.data_ptr(), B, ld)
+        key = (Z.data_ptr(), B, ld) + tuple(p.driver.graph_key() for p in self.pipelines.values()
+                                            if p.built and hasattr(p.driver, "graph_key"))
         g = None
         if self.use_graphs and not kw and self._graphable(Z):
             g = self._graphs.get(key)
@@ -198,6 +201,9 @@ class Engine:
     def _device_step(self, Z: torch.Tensor, d: int, **kw) -> None:
         """All device work of one training step, in stream order."""
         B, ld = Z.shape
+        for p in self.pipelines.values():
+            if p.built and hasattr(p.driver, "begin_step"):
+                p.driver.begin_step()          # fork: overlapped all-reduce of the previous step's delta
         if self.holdout_enabled and self.params.testSetSize > 0:
             self._ensure_holdout(ld)
             if Z.is_cuda and F.native(Z):
@@ -301,6 +307,15 @@ class Engine:
                 self._loss_host.copy_(p.learner.stats, non_blocking=True)
                 break
         return self._loss_host
+
+    def flush(self) -> None:
+        """Collective end-of-stream hook: let every protocol driver settle (share the last pipelined
+        delta, resolve an FGM round that only some ranks have entered).  Call it on every rank before
+        a host-side barrier, otherwise a rank may sit in a device-side rendezvous that its peers will
+        never join."""
+        for p in self.pipelines.values():
+            if p.built and p.protocol != "SingleLearner":
+                p.driver.flush()
 
     def forecast_batch(self, Z: torch.Tensor, instances: Optional[List[DataInstance]] = None) -> List[str]:
         """Every pipeline predicts every forecasting record with its local replica

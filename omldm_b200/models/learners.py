@@ -210,6 +210,8 @@ class GpuORR(GpuLearner):
         self._since = 0
         self.solves = 0
         self._side = None
+        self._deltas = None
+        self._drain = None
         self._fork = None
         self.overlap = str(_h(hyper, ["overlapLoss"], "true")).lower() in ("1", "true", "yes")
         self._pending = None
@@ -272,8 +274,24 @@ class GpuORR(GpuLearner):
     def after_sync(self):
         pass   # the solve cadence is driven by `solveEvery`, and always runs before a query
 
+    # ---- pipelined synchronisation (parallel/fused.py::PipelinedSynchronousDriver) -----------------
+    def use_delta_buffers(self, bufs, drain) -> None:
+        """Two symmetric delta buffers: updates go to the current one while the other is all-reduced."""
+        ld = self.ld
+        self._deltas = [b.view(ld, ld) for b in bufs]
+        self._drain = drain
+        self.dG = self._deltas[0]
+
+    def switch_delta(self, i: int) -> None:
+        self.dG = self._deltas[i]
+
     def _snapshot(self) -> None:
-        """_work <- G + dG; must run on the stream that orders the Gram / sync kernels."""
+        """_work <- G + (all deltas); must run on the stream that orders the Gram / sync kernels."""
+        if self._deltas is not None:
+            self._drain()                       # in-flight all-reduces update G and clear their delta
+            torch.add(self.G, self._deltas[0], out=self._work)
+            self._work.add_(self._deltas[1])
+            return
         torch.add(self.G, self.dG, out=self._work)
 
     def _solve_into(self, out: torch.Tensor) -> None:
@@ -343,6 +361,18 @@ class GpuORR(GpuLearner):
         self.G[:n, :n] = torch.from_numpy(o.G.astype(np.float32)).to(self.device)
         self.solve()
 
+    def state_dict(self):
+        if self._deltas is not None:            # fold both local deltas into the saved one; G stays global
+            self._drain()
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            sd = super().state_dict()
+            sd["buf"] = (self._deltas[0] + self._deltas[1]).reshape(-1).detach().cpu().clone()
+            return sd
+        return super().state_dict()
+
     def load_state_dict(self, sd):
         super().load_state_dict(sd)
+        if self._deltas is not None:
+            self._deltas[1].zero_()
         self.solve()

@@ -79,7 +79,11 @@ class GpuPipeline:
         e = torch.zeros(self.comm.n, device=self.device) if lrn.needs_e() else None
         lrn.bind(d, self.comm.buf, e)
         self.driver = make_driver(self.protocol, self.comm, e, lrn.merge_mode,
-                                  self.request.trainingConfiguration, self.impl, self.group, self.max_msg_params)
+                                  self.request.trainingConfiguration, self.impl, self.group, self.max_msg_params,
+                                  pipelined_ok=hasattr(lrn, "use_delta_buffers"))
+        if hasattr(self.driver, "on_switch"):
+            lrn.use_delta_buffers(self.driver.bufs, self.driver.drain)
+            self.driver.on_switch = lrn.switch_delta
         init = self.request.learner.parameters
         if init and init.get("a") is not None:       # warm start from a serialized model
             o = lrn.to_oracle()

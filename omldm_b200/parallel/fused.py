@@ -137,6 +137,77 @@ class SynchronousDriver(SyncDriver):
         return True
 
 
+class PipelinedSynchronousDriver(SyncDriver):
+    """Synchronous protocol for ADDITIVE statistics with the all-reduce hidden behind the next
+    mini-batch.  The learner accumulates step t into delta buffer t % 2 (the two symmetric buffers
+    of the region: `buf` and `hub`).  At the start of step t+1 the fused all-reduce of buffer t % 2
+    is forked onto a communication stream and runs beside the holdout / Gram kernels of step t+1,
+    which write the other buffer; the streams join at the end of the step, so the whole step is
+    still one capturable unit (one CUDA graph per batch buffer and parity).  Every contribution is
+    folded into the global statistics exactly once - the sum is order independent - it just becomes
+    visible to the peers one step later; `flush()` pushes the last delta at end of stream.  Not valid
+    for averaged models."""
+    protocol = "Synchronous"
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        if self.mode != 1:
+            raise ValueError("pipelined synchronisation needs additive statistics (merge mode 'sum')")
+        c = self.comm
+        self.stream = torch.cuda.Stream(device=c.device)
+        self.cur = 0                   # delta buffer the learner writes in the current step
+        self.bufs = [c.buf, c.hub]
+        from ..ops.functional import CommStruct
+        # second view of the region: the kernels' "buf" table points at the hub buffers
+        self._struct_b = CommStruct(c.tables[1].data_ptr(), c.tables[0].data_ptr(), c.tables[2].data_ptr(),
+                                    c.local.data_ptr(), 0, c.struct.rank, c.struct.world, c.struct.emulate)
+        self.on_switch = None          # learner callback: (index) -> use that delta buffer from now on
+        if self.blocks == 0:
+            self.blocks = 48           # leave the SMs to the tensor-core kernel it overlaps with
+        self._forked = False
+
+    def graph_key(self):
+        return self.cur
+
+    def _launch_sync(self, i: int) -> None:
+        c = self.comm
+        struct = ctypes.byref(c.struct) if i == 0 else ctypes.byref(self._struct_b)
+        _lib.check(_lib.kernels().omldm_sync_allreduce(struct, self._eptr(), _sz(c.n), _f(self.scale), _i(1),
+                                                       _u(0), _i(self.blocks), _lib.stream_ptr()), "sync_allreduce")
+
+    def begin_step(self) -> None:
+        """Fork: all-reduce the delta written in the previous step while this step computes."""
+        main = torch.cuda.current_stream(self.comm.device)
+        self.stream.wait_stream(main)
+        with torch.cuda.stream(self.stream):
+            self._launch_sync(self.cur ^ 1)
+        self._forked = True
+
+    def step(self) -> bool:
+        """Join the communication stream (end of the step's device work)."""
+        if self._forked:
+            torch.cuda.current_stream(self.comm.device).wait_stream(self.stream)
+            self._forked = False
+        return False                   # derived state is refreshed by the learner's own cadence
+
+    def host_tick(self) -> bool:
+        due = super().host_tick()
+        self.cur ^= 1
+        if self.on_switch is not None:
+            self.on_switch(self.cur)
+        return due
+
+    def drain(self) -> None:
+        """Nothing is in flight between steps (every step joins); kept for the learner's snapshot."""
+
+    def flush(self) -> None:
+        """End of stream: the delta of the last step has not been shared yet."""
+        self._launch_sync(self.cur ^ 1)
+
+    def account(self):
+        self.counters.ship(self.comm.n, self.k)
+
+
 class AsynchronousDriver(SyncDriver):
     protocol = "Asynchronous"
 
@@ -334,10 +405,15 @@ DRIVERS = {"CentralizedTraining": LocalDriver, "SingleLearner": LocalDriver, "Sy
 
 
 def make_driver(protocol: str, comm: PipelineComm, e, merge_mode: str, tc, impl: str = "fused", group=None,
-                max_msg_params: int = 2000) -> SyncDriver:
+                max_msg_params: int = 2000, pipelined_ok: bool = False) -> SyncDriver:
     cls = DRIVERS.get(protocol, AsynchronousDriver)
     if comm.k == 1:
         cls = LocalDriver
+    overlap = str(cfg(tc, ["overlapSync"], "false")).lower() in ("1", "true", "yes")   # opt-in: measured slower at 2 GPUs
+    if (cls is SynchronousDriver and merge_mode == "sum" and overlap and impl == "fused" and comm.k > 1
+            and comm.device.type == "cuda" and comm.emulate <= 1 and int(cfg(tc, ["syncEvery", "syncPeriod"], 1)) == 1
+            and pipelined_ok):
+        cls = PipelinedSynchronousDriver
     if cls is EASGDDriver and merge_mode == "sum":
         cls = AsynchronousDriver   # elastic averaging is meaningless for additive statistics
     drv = cls(comm, e, merge_mode, tc, impl, group, max_msg_params)

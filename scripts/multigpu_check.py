@@ -121,8 +121,14 @@ for name, hyper, kind, d in (("ORR", {"solveEvery": 1}, R.KIND_REGRESSION, 100),
         out = eng.handle_request({"id": 1, "request": "Query", "requestId": 1})
         res[impl] = json.loads(out[-1]) if out else None
         p = eng.pipelines[1]
-        res[impl + "_flat"] = (p.learner.e + p.comm.buf).clone() if p.learner.merge_mode == "sum" else p.comm.buf.clone()
+        if p.learner.merge_mode == "sum":
+            res[impl + "_flat"] = torch.from_numpy(p.learner.to_oracle().G).float().to(dev).reshape(-1)
+        else:
+            res[impl + "_flat"] = p.comm.buf.clone()
+        res[impl + "_driver"] = type(p.driver).__name__
         eng.close(); dist.barrier()
+    if rank == 0:
+        print("drivers:", res["fused_driver"], res["nccl_driver"], flush=True)
     check(f"engine {name}: fused replicas == nccl replicas",
           torch.allclose(res["fused_flat"], res["nccl_flat"], rtol=2e-2, atol=2e-2 * float(res["nccl_flat"].abs().max())))
     if rank == 0:
