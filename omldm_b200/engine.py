@@ -65,6 +65,8 @@ class Engine:
         self._seen: Dict[Any, int] = {}
         self._count_dev: Optional[torch.Tensor] = None
         self._sparse_key = None
+        self._multi_key = None
+        self._multi_desc = None
 
     # ============================================================================ control plane
     def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
@@ -170,12 +172,17 @@ class Engine:
             g = self._graphs.get(key)
             if g is None and self._seen.get(key, 0) >= self.graph_after:
                 g = self._capture(key, Z, d)
+        nvtx = self.device.type == "cuda"
+        if nvtx:
+            torch.cuda.nvtx.range_push("omldm.step.replay" if g is not None else "omldm.step.eager")
         if g is not None:
             g.replay()
             _lib.add_launch_count(self._graph_launches[key])
         else:
             self._seen[key] = self._seen.get(key, 0) + 1
             self._device_step(Z, d, **kw)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         self.count += B
         for p in self.pipelines.values():
             if p.built and (p.protocol != "SingleLearner" or self.rank == 0):
@@ -213,14 +220,39 @@ class Engine:
             else:
                 F.holdout_swap(Z, self.holdout, d, self.count)
         n_pipes = len(self.pipelines)
+        batched = self._batched_exact_fit(Z, d)
         for p in self.pipelines.values():
             due = p.built and (p.driver._batches % p.driver.sync_every == p.driver.sync_every - 1)
+            if p in batched:
+                p.device_train(Z, False, due, skip_fit=True)
+                continue
             if p.protocol == "SingleLearner":
                 Zs = self._forward_to_rank0(Z)
                 if self.rank == 0:
                     p.device_train(Zs, True, due, **kw)
                 continue
             p.device_train(Z, n_pipes > 1, due, **kw)
+
+    def _batched_exact_fit(self, Z: torch.Tensor, d: int):
+        """Multi-tenant fast path: all exact-mode linear pipelines without preprocessors advance in ONE
+        kernel launch, one warp per pipeline (tiny models are latency bound; the launch is shared)."""
+        from .models.learners import GpuLinear
+        if not (Z.is_cuda and F.native(Z)):
+            return ()
+        group = [p for p in self.pipelines.values()
+                 if p.built and p.protocol != "SingleLearner" and isinstance(p.learner, GpuLinear)
+                 and p.learner.mode == "exact" and not p.preprocessors]
+        if len(group) < 2:
+            return ()
+        key = tuple(id(p) for p in group)
+        if self._multi_key != key:
+            self._multi_key = key
+            self._multi_desc = F.make_linear_descs(
+                [(p.learner.w, p.learner.stats, p.learner.d, p.learner.kind, p.learner.variant, p.learner.C,
+                  p.learner.eps, p.learner.lam) for p in group], self.device)
+        with torch.cuda.nvtx.range("linear_exact_multi"):
+            F.linear_exact_multi(Z, d, self._multi_desc, len(group))
+        return group
 
     def _forward_to_rank0(self, Z: torch.Tensor) -> torch.Tensor:
         """SingleLearner: workers forward raw records to the one learner at hub 0."""

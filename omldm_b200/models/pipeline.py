@@ -107,10 +107,12 @@ class GpuPipeline:
         self.device_train(Z, protect_input, due, **kw)
         self.host_tick()
 
-    def device_train(self, Z: torch.Tensor, protect_input: bool, sync_due: bool, **kw) -> None:
-        """Device work of one step (graph-capturable when `graph_safe()`)."""
-        Zp = self.preprocess(Z, True, protect_input)
-        self.learner.fit_batch(Zp, **kw)
+    def device_train(self, Z: torch.Tensor, protect_input: bool, sync_due: bool, skip_fit: bool = False, **kw) -> None:
+        """Device work of one step (graph-capturable when `graph_safe()`).  `skip_fit`: the learner
+        update was already done by a batched multi-pipeline launch."""
+        if not skip_fit:
+            Zp = self.preprocess(Z, True, protect_input)
+            self.learner.fit_batch(Zp, **kw)
         if sync_due and self.driver.step():
             self.learner.after_sync()
 

@@ -80,7 +80,7 @@ def build_host(verbose: bool = False) -> Path:
     LIBDIR.mkdir(parents=True, exist_ok=True)
     OBJDIR.mkdir(parents=True, exist_ok=True)
     out = LIBDIR / "libomldm_host.so"
-    sources = sorted((CSRC / "host").glob("*.cpp"))
+    sources = sorted(s for s in (CSRC / "host").glob("*.cpp") if not s.name.endswith("_test.cpp"))
     headers = list((ROOT / "include").glob("*.h")) + list((CSRC / "host").glob("*.h"))
     if not sources:
         return out

@@ -313,6 +313,14 @@ def linear_exact(Z: torch.Tensor, d: int, w: torch.Tensor, stats: torch.Tensor, 
     stats[3] = t
 
 
+def linear_exact_multi(Z: torch.Tensor, max_d: int, desc_dev: torch.Tensor, n_pipelines: int) -> None:
+    """One launch advances `n_pipelines` linear pipelines (one warp each) over the same batch - the
+    multi-tenant case of FlinkSpoke.scala:97-105 where every pipeline sees every record."""
+    B, ld = Z.shape
+    _lib.check(_k().omldm_linear_exact(_p(Z), _i(ld), _i(B), _p(desc_dev), _i(n_pipelines), _i(max_d),
+                                       _lib.stream_ptr()), "linear_exact(multi)")
+
+
 def make_linear_descs(entries, device) -> torch.Tensor:
     """Pack (w, stats, d, kind, variant, C, eps, lam) tuples into a device descriptor array."""
     raw = bytearray()

@@ -123,3 +123,30 @@ def test_e2e_host_path_and_forecast():
     assert js.statistics[0].fitted > 0 and js.statistics[0].score > 0.8
     topic.stop()
     eng.close()
+
+
+def test_multi_pipeline_exact_batched_launch_matches_separate_pipelines():
+    """Many tiny pipelines share one kernel launch (one warp each) and still equal the oracle."""
+    d, B = 28, 256
+    specs = [("PA", {"C": 0.1}), ("PA", {"C": 1.0, "updateType": "PA-II"}), ("SVM", {"lambda": 0.01}),
+             ("RegressorPA", {"C": 0.5, "epsilon": 0.05})]
+    eng = Engine(JobParameters(parallelism=1, testSetSize=0), device="cuda")
+    for i, (name, hyper) in enumerate(specs):
+        eng.handle_request({"id": i + 1, "request": "Create",
+                            "learner": {"name": name, "hyperParameters": dict(hyper, trainingMode="exact")},
+                            "trainingConfiguration": {"protocol": "Asynchronous", "nFeatures": d}})
+    batches = [R.generate_batch(R.KIND_BINARY, d, B, seed=21, batch_index=i) for i in range(6)]
+    before = _lib.launch_count()
+    for b in batches:
+        eng.train_batch(b.cuda(), d)
+    torch.cuda.synchronize()
+    assert _lib.launch_count() - before <= len(batches) * 2      # one shared launch per batch (+ nothing per pipeline)
+    for i, (name, hyper) in enumerate(specs):
+        o = make_oracle_learner(name, hyper)
+        for b in batches:
+            for r in b:
+                o.fit(r[:d].double().numpy(), float(r[d + 1]))
+        resp = json.loads(eng.handle_request({"id": i + 1, "request": "Query", "requestId": 1})[0])
+        assert np.allclose(resp["learner"]["parameters"]["a"], o.w[:-1], rtol=2e-3, atol=2e-4), name
+        assert resp["dataFitted"] == B * len(batches)
+    eng.close()
