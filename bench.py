@@ -33,7 +33,7 @@ import time
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 CONFIGS = {
-    "orr": dict(model="ORR", d=1000, batch=16384, protocol="Synchronous", kind=1, n_aux=0,
+    "orr": dict(model="ORR", d=1000, batch=32768, protocol="Synchronous", kind=1, n_aux=0,
                 hyper={"lambda": 1.0, "solveEvery": 16}, tc={}, pre=[],
                 name="ORR 1k-dim synthetic stream, synchronous protocol"),
     "pa": dict(model="PA", d=28, batch=65536, protocol="Asynchronous", kind=0, n_aux=0,
