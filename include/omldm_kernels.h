@@ -132,6 +132,16 @@ int omldm_sq_residual(const float* Z, int ld, int B, int d, const float* wt, int
 /* symmetric completion: A[j][i] = A[i][j] for j > i (upper -> lower) */
 int omldm_mirror_upper(float* A, int ld, int n, void* stream);
 
+/* ------------------------------------------------------------------ Hoeffding tree statistics (tree.cu)
+ * HT, PipelineMap.scala:68 (never distributed by the reference: FlinkSpoke.scala:204-206).
+ * Tree arrays are indexed by node: feature (-1 = leaf), threshold, left, right, slot (leaf -> statistics
+ * slot).  cnt[slot][C], sum/sq[slot][C][d] are updated with atomics; stats += {mistakes, -, fitted}. */
+int omldm_ht_accumulate(const float* Z, int ld, int d, int B, const int* feature, const float* threshold,
+                        const int* left, const int* right, const int* slot, int C, float* cnt, float* sum,
+                        float* sq, int* leaf_out, double* stats, void* stream);
+int omldm_ht_route(const float* Z, int ld, int B, const int* feature, const float* threshold, const int* left,
+                   const int* right, int* leaf_out, void* stream);
+
 /* ------------------------------------------------------------------ fused protocol kernels (sync.cu)
  * worker<->hub synchronisation, network/FlinkNetwork.scala:242-293 (send / broadcast) and the
  * Kafka feedback loop Job.scala:77-87,136-142.  Peer pointer tables live in device memory. */

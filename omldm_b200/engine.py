@@ -171,7 +171,13 @@ class Engine:
         if self.use_graphs and not kw and self._graphable(Z):
             g = self._graphs.get(key)
             if g is None and self._seen.get(key, 0) >= self.graph_after:
-                g = self._capture(key, Z, d)
+                try:
+                    g = self._capture(key, Z, d)
+                except Exception as e:      # never lose a job over an optimisation: fall back to eager steps
+                    import warnings
+                    warnings.warn(f"CUDA graph capture failed ({e}); continuing with eager launches")
+                    self.use_graphs = False
+                    g = None
         nvtx = self.device.type == "cuda"
         if nvtx:
             torch.cuda.nvtx.range_push("omldm.step.replay" if g is not None else "omldm.step.eager")

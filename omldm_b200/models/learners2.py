@@ -303,13 +303,15 @@ class GpuNN(GpuLearner):
 
 class GpuHT(GpuLearner):
     """Hoeffding tree.  The reference never distributes it (forced SingleLearner,
-    FlinkSpoke.scala:204-206); the irregular tree lives on the host (fp64 oracle implementation)
-    and is fed from the staged rows."""
+    FlinkSpoke.scala:204-206).  Routing and the per-leaf sufficient statistics of the Gaussian
+    attribute observers run on the GPU (csrc/tree.cu); the small, irregular tree and the Hoeffding-bound
+    split test stay on the host and are evaluated per mini-batch for the leaves that passed their grace
+    period.  `trainingMode: "exact"` runs the fp64 per-record oracle on the host instead."""
     name, task, merge_mode = "HT", "classification", "none"
 
     def __init__(self, hyper, device):
         super().__init__(hyper, device)
-        self.tree = O.HoeffdingTree(hyper)
+        self.tree = O.HoeffdingTree(hyper)          # host mirror: structure + split logic
 
     def n_flat(self, d):
         return 4
@@ -317,39 +319,120 @@ class GpuHT(GpuLearner):
     def needs_e(self):
         return False
 
-    def _init(self):
-        self.tree.ensure_init(self.d)
-
     def graph_ready(self):
-        return False
+        return False                                 # split decisions need a host round trip per batch
 
+    def _init(self):
+        t = self.tree
+        t.ensure_init(self.d)
+        C, d = t.n_classes, self.d
+        cap = max(3, min(t.max_nodes, int(256e6 // (8 * C * d))))   # statistics stay below ~256 MB
+        cap -= (cap + 1) % 2                                         # odd: root + pairs of children
+        self.cap = t.max_nodes = cap
+        dev = self.device
+        self.feature = torch.full((cap,), -1, dtype=torch.int32, device=dev)
+        self.threshold = torch.zeros(cap, device=dev)
+        self.left = torch.full((cap,), -1, dtype=torch.int32, device=dev)
+        self.right = torch.full((cap,), -1, dtype=torch.int32, device=dev)
+        self.slot = torch.arange(cap, dtype=torch.int32, device=dev)  # statistics slot = node id
+        self.cnt = torch.zeros(cap, C, device=dev)
+        self.sum = torch.zeros(cap, C, d, device=dev)
+        self.sq = torch.zeros(cap, C, d, device=dev)
+        self.checked = {0: 0.0}
+
+    # ---- training ---------------------------------------------------------------------------------------
     def fit_batch(self, Z):
-        h = Z[:, : self.d + 2].detach().cpu().double().numpy()
-        for r in h:
-            if r[self.d] != 0:
-                self.tree.fit(r[: self.d], r[self.d + 1])
-        self.stats[0] = self.tree.cum_loss
-        self.stats[2] = self.tree.fitted
+        if self.mode == "exact":
+            h = Z[:, : self.d + 2].detach().cpu().double().numpy()
+            for r in h:
+                if r[self.d] != 0:
+                    self.tree.fit(r[: self.d], r[self.d + 1])
+            self.stats[0] = self.tree.cum_loss
+            self.stats[2] = self.tree.fitted
+            return
+        t = self.tree
+        F.ht_accumulate(Z, self.d, self.feature, self.threshold, self.left, self.right, self.slot, t.n_classes,
+                        self.cnt, self.sum, self.sq, self.stats)
+        self._maybe_split()
 
+    def _maybe_split(self):
+        t = self.tree
+        n_nodes = len(t.feature)
+        cnt_h = self.cnt[:n_nodes].detach().cpu().double().numpy()
+        for leaf in [i for i in range(n_nodes) if t.feature[i] < 0]:
+            tot = float(cnt_h[leaf].sum())
+            if tot - self.checked.get(leaf, 0.0) < t.grace or len(t.feature) + 2 > self.cap:
+                continue
+            self.checked[leaf] = tot
+            lf = O._Leaf(t.n_classes, self.d)
+            lf.counts = cnt_h[leaf].copy()
+            s = self.sum[leaf].detach().cpu().double().numpy()
+            q = self.sq[leaf].detach().cpu().double().numpy()
+            n = np.maximum(lf.counts[:, None], 0.0) * np.ones((1, self.d))
+            lf.n = n
+            lf.mean = np.divide(s, n, out=np.zeros_like(s), where=n > 0)
+            lf.m2 = np.maximum(q - n * lf.mean ** 2, 0.0)
+            t.leaves[leaf] = lf
+            before = len(t.feature)
+            t._try_split(leaf, lf)
+            if len(t.feature) > before:                # split happened: publish it to the device arrays
+                li, ri = t.left[leaf], t.right[leaf]
+                self.feature[leaf] = t.feature[leaf]
+                self.threshold[leaf] = float(t.threshold[leaf])
+                self.left[leaf], self.right[leaf] = li, ri
+                for ch in (li, ri):                    # children start from the parent's class prior
+                    self.cnt[ch] = torch.from_numpy(t.leaves[ch].counts.astype(np.float32)).to(self.device)
+                    self.checked[ch] = float(t.leaves[ch].counts.sum())
+        t.fitted = int(self.stats[2].item())
+        t.cum_loss = float(self.stats[0].item())
+
+    # ---- inference -------------------------------------------------------------------------------------------
     def predict(self, Z):
-        h = Z[:, : self.d].detach().cpu().double().numpy()
-        return torch.tensor([self.tree.predict(r) for r in h], device=self.device, dtype=torch.float32)
+        if self.mode == "exact":
+            h = Z[:, : self.d].detach().cpu().double().numpy()
+            return torch.tensor([self.tree.predict(r) for r in h], device=self.device, dtype=torch.float32)
+        leaf = F.ht_route(Z, self.feature, self.threshold, self.left, self.right)
+        return self.cnt[leaf].argmax(1).float()
 
     def _labels(self, p):
         return p
 
     def _labels_true(self, y):
-        c = torch.round(y)
-        return torch.where(c < 0, torch.zeros_like(c), c) if self.tree.n_classes == 2 else c
+        return F.ht_class(y, self.tree.n_classes).float()
 
     def to_oracle(self):
-        return self.tree
+        t = self.tree
+        if self.mode != "exact":
+            cnt_h = self.cnt[: len(t.feature)].detach().cpu().double().numpy()
+            for i in range(len(t.feature)):
+                if t.feature[i] < 0:
+                    lf = t.leaves.get(i) or O._Leaf(t.n_classes, self.d)
+                    lf.counts = cnt_h[i].copy()
+                    t.leaves[i] = lf
+        return t
 
     def from_oracle(self, o):
         self.tree = o
 
     def data_structure(self):
-        return self.tree.data_structure()
+        return self.to_oracle().data_structure()
+
+    def state_dict(self):
+        sd = super().state_dict()
+        sd["tree"] = self.to_oracle()
+        if self.mode != "exact":
+            sd["ht"] = {k: getattr(self, k).detach().cpu().clone() for k in
+                        ("feature", "threshold", "left", "right", "cnt", "sum", "sq")}
+            sd["checked"] = dict(self.checked)
+        return sd
+
+    def load_state_dict(self, sd):
+        self.stats.copy_(sd["stats"].to(self.device))
+        self.tree = sd["tree"]
+        if "ht" in sd:
+            for k, v in sd["ht"].items():
+                getattr(self, k).copy_(v.to(self.device))
+            self.checked = dict(sd["checked"])
 
 
 GPU_LEARNERS = {c.name: c for c in (GpuPA, GpuRegressorPA, GpuSVM, GpuORR, GpuKMeans, GpuMultiClassPA, GpuNN, GpuHT)}

@@ -518,3 +518,60 @@ def axpy(y: torch.Tensor, x: torch.Tensor, alpha: float) -> None:
         _lib.check(_k().omldm_axpy(_p(y), _p(x), _f(alpha), ctypes.c_size_t(y.numel()), _lib.stream_ptr()), "axpy")
         return
     y.add_(x, alpha=alpha)
+
+
+# ------------------------------------------------------------------------------ Hoeffding tree
+def _ht_route_torch(Z, feature, threshold, left, right):
+    node = torch.zeros(Z.shape[0], dtype=torch.long, device=Z.device)
+    ar = torch.arange(Z.shape[0], device=Z.device)
+    for _ in range(64):
+        f = feature[node].long()
+        inner = f >= 0
+        if not bool(inner.any()):
+            break
+        x = Z[ar, f.clamp_min(0)]
+        nxt = torch.where(x <= threshold[node], left[node].long(), right[node].long())
+        node = torch.where(inner, nxt, node)
+    return node
+
+
+def ht_class(y: torch.Tensor, C: int) -> torch.Tensor:
+    c = torch.round(y).long()
+    if C == 2:
+        c = torch.where(c < 0, torch.zeros_like(c), c)
+    return c.clamp(0, C - 1)
+
+
+def ht_accumulate(Z, d, feature, threshold, left, right, slot, C, cnt, sums, sq, stats, leaf_out=None) -> None:
+    """Route every record to its leaf and add it to the leaf's (count, sum, sum-of-squares) statistics."""
+    B = Z.shape[0]
+    if native(Z):
+        _lib.check(_k().omldm_ht_accumulate(_p(Z), _i(Z.stride(0)), _i(d), _i(B), _p(feature), _p(threshold), _p(left),
+                                            _p(right), _p(slot), _i(C), _p(cnt), _p(sums), _p(sq), _p(leaf_out),
+                                            _p(stats), _lib.stream_ptr()), "ht_accumulate")
+        return
+    valid = Z[:, d] != 0
+    node = _ht_route_torch(Z, feature, threshold, left, right)
+    s = slot[node].long()
+    c = ht_class(Z[:, d + 1], C)
+    best, pred = cnt[s].max(1)
+    pred = torch.where(best > 0, pred, torch.full_like(pred, -1))
+    stats[0] += ((pred != c) & valid).sum()
+    stats[2] += valid.sum()
+    idx = (s * C + c)[valid]
+    cnt.view(-1).index_add_(0, idx, torch.ones(idx.numel(), device=Z.device))
+    X = Z[valid, :d]
+    sums.view(-1, d).index_add_(0, idx, X)
+    sq.view(-1, d).index_add_(0, idx, X * X)
+    if leaf_out is not None:
+        leaf_out.copy_(torch.where(valid, node, torch.full_like(node, -1)).int())
+
+
+def ht_route(Z, feature, threshold, left, right) -> torch.Tensor:
+    B = Z.shape[0]
+    if native(Z):
+        out = torch.empty(B, dtype=torch.int32, device=Z.device)
+        _lib.check(_k().omldm_ht_route(_p(Z), _i(Z.stride(0)), _i(B), _p(feature), _p(threshold), _p(left), _p(right),
+                                       _p(out), _lib.stream_ptr()), "ht_route")
+        return out.long()
+    return _ht_route_torch(Z, feature, threshold, left, right)

@@ -128,3 +128,26 @@ def test_topic_ring_producer_and_json_scanner():
     assert t2.put(rows) and t2.get(100)[2] == 2
     same = R.generate_batch(R.KIND_REGRESSION, 7, 16, seed=5, batch_index=3)
     assert torch.equal(same, R.generate_batch(R.KIND_REGRESSION, 7, 16, seed=5, batch_index=3))
+
+
+def test_hoeffding_tree_device_statistics_path_learns():
+    """HT with leaf statistics accumulated by the (torch-implemented on CPU) tree kernels."""
+    d = 10
+    eng = Engine(JobParameters(parallelism=1, testSetSize=64), device="cpu")
+    eng.handle_request({"id": 1, "request": "Create",
+                        "learner": {"name": "HT", "hyperParameters": {"nClasses": 2, "gracePeriod": 200}},
+                        "trainingConfiguration": {"nFeatures": d}})
+    rng = np.random.default_rng(0)
+    for i in range(30):
+        X = rng.standard_normal((256, d)).astype(np.float32)
+        y = np.where((X[:, 2] > 0.3) ^ (X[:, 5] < -0.5), 1.0, -1.0)
+        eng.train_batch(F.stage_rows(torch.from_numpy(np.hstack([X, y[:, None]]).astype(np.float32)), d), d)
+    r = json.loads(eng.handle_request({"id": 1, "request": "Query", "requestId": 1})[0])
+    assert r["protocol"] == "SingleLearner" and r["score"] > 0.9
+    ds = r["learner"]["dataStructure"]
+    assert len(ds["feature"]) >= 5 and set(f for f in ds["feature"] if f >= 0) <= {2, 5}
+    sd = eng.state_dict()
+    eng2 = Engine(JobParameters(parallelism=1, testSetSize=64), device="cpu")
+    eng2.load_state_dict(sd)
+    r2 = json.loads(eng2.handle_request({"id": 1, "request": "Query", "requestId": 2})[0])
+    assert r2["learner"]["dataStructure"]["feature"] == ds["feature"]

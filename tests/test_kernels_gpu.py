@@ -200,3 +200,31 @@ def test_sq_residual_mirror_axpy():
     ref, nat = both(run)
     assert torch.allclose(ref[0], nat[0], rtol=1e-4)
     assert torch.equal(ref[1], nat[1]) and torch.equal(ref[2], nat[2])
+
+
+def test_hoeffding_tree_kernels():
+    d, C, B = 20, 3, 3000
+    Z = staged(R.KIND_MULTICLASS, d, B, seed=4, n_aux=C)
+    Z[11, d] = 0.0
+    cap = 7
+    feature = torch.tensor([3, 7, -1, -1, -1, -1, -1], dtype=torch.int32, device=DEV)
+    threshold = torch.tensor([0.1, -0.2, 0, 0, 0, 0, 0], device=DEV)
+    left = torch.tensor([1, 3, -1, -1, -1, -1, -1], dtype=torch.int32, device=DEV)
+    right = torch.tensor([2, 4, -1, -1, -1, -1, -1], dtype=torch.int32, device=DEV)
+    slot = torch.arange(cap, dtype=torch.int32, device=DEV)
+
+    def run():
+        cnt = torch.zeros(cap, C, device=DEV)
+        cnt[2, 1] = 5.0   # a prior, so the prequential prediction is defined for that leaf
+        sm = torch.zeros(cap, C, d, device=DEV)
+        sq = torch.zeros(cap, C, d, device=DEV)
+        st = torch.zeros(4, dtype=torch.float64, device=DEV)
+        leaf = torch.empty(B, dtype=torch.int32, device=DEV)
+        F.ht_accumulate(Z, d, feature, threshold, left, right, slot, C, cnt, sm, sq, st, leaf)
+        routed = F.ht_route(Z, feature, threshold, left, right)
+        return cnt, sm, sq, st[2:3], leaf, routed
+    ref, nat = both(run)
+    assert torch.equal(ref[0], nat[0]) and torch.equal(ref[4], nat[4]) and torch.equal(ref[5], nat[5])
+    assert torch.allclose(ref[1], nat[1], rtol=1e-4, atol=1e-3) and torch.allclose(ref[2], nat[2], rtol=1e-4, atol=1e-3)
+    assert ref[3].item() == nat[3].item() == B - 1
+    assert set(nat[5].unique().tolist()) == {2, 3, 4}
