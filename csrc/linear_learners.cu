@@ -16,38 +16,9 @@
 #include "ptx.cuh"
 #include "host_common.h"
 #include "omldm_kernels.h"
+#include "linear_math.cuh"
 
 namespace omldm {
-
-// kind: 0 = PA classifier, 1 = PA regressor, 2 = SVM (Pegasos)
-// variant (PA family): 0 = PA, 1 = PA-I, 2 = PA-II
-
-__device__ __forceinline__ float pa_tau(float loss, float nrm2, int variant, float C) {
-  if (loss <= 0.f || nrm2 <= 0.f) return 0.f;
-  if (variant == 0) return loss / nrm2;
-  if (variant == 1) return fminf(C, loss / nrm2);
-  return loss / (nrm2 + 1.f / (2.f * C));
-}
-
-// Returns the coefficient c such that w += c * x, and reports loss / aux metric.
-__device__ __forceinline__ float linear_coef(int kind, int variant, float C, float eps, float f,
-                                             float y_raw, float nrm2, float& loss, float& aux) {
-  if (kind == 0) {
-    const float y = y_raw > 0.f ? 1.f : -1.f;
-    loss = fmaxf(0.f, 1.f - y * f);
-    aux = (y * f <= 0.f) ? 1.f : 0.f;  // mistake indicator
-    return y * pa_tau(loss, nrm2, variant, C);
-  } else if (kind == 1) {
-    const float err = f - y_raw;
-    loss = fmaxf(0.f, fabsf(err) - eps);
-    aux = err * err;  // squared error
-    return (err > 0.f ? -1.f : 1.f) * pa_tau(loss, nrm2, variant, C);
-  }
-  const float y = y_raw > 0.f ? 1.f : -1.f;
-  loss = fmaxf(0.f, 1.f - y * f);
-  aux = (y * f <= 0.f) ? 1.f : 0.f;
-  return 0.f;  // SVM handled by the caller (needs the step counter)
-}
 
 template <int R>
 __global__ void __launch_bounds__(32)
@@ -254,7 +225,8 @@ extern "C" int omldm_linear_minibatch(const float* Z, int ld, int B, const omldm
   const int dw = desc_host->d + 1;
   if (dw * 4 > 200 * 1024) return set_error_msg("linear_minibatch: d too large for the smem accumulator");
   int blocks = (B + MB_WARPS - 1) / MB_WARPS;
-  if (blocks > 148 * 4) blocks = 148 * 4;
+  const int cap = 148 * 4;
+  if (blocks > cap) blocks = cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dw * 4 > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(linear_minibatch_kernel,

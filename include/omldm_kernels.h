@@ -106,6 +106,15 @@ int omldm_standard_scaler(float* Z, int ld, int d, int B, double* state, double*
 /* state: float[2*d] = [min[d], max[d]] */
 int omldm_minmax_scaler(float* Z, int ld, int d, int B, float* state, int fit, void* stream);
 
+/* ------------------------------------------------------------------ fused pipeline (fused_pipeline.cu)
+ * PolynomialFeatures -> StandardScaler(fit) -> mini-batch linear learner in two passes over the RAW rows,
+ * never materialising the expanded features (BASELINE config 3).  State / scratch layouts are those of
+ * omldm_standard_scaler (width d_out) and omldm_linear_minibatch; same result as running the three kernels. */
+int omldm_fused_poly_scaler_linear(const float* Z, int ld, int d_in, int B, const short* factors, int degree,
+                                   int d_out, double* scaler_state, double* scaler_scratch,
+                                   const omldm_linear_desc* desc_host, float* lin_scratch, int mean_update,
+                                   void* stream);
+
 /* ------------------------------------------------------------------ k-means / multiclass PA (cluster.cu)
  * K-means and MultiClassPA, PipelineMap.scala:68. */
 /* scores S[B,K] = X C^T (from omldm_gemm_tn); writes one-hot assignment T[B,ldt], stats += {inertia, n} */

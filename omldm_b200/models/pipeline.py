@@ -57,6 +57,7 @@ class GpuPipeline:
         self._win_loss = 0.0
         self._win_n = 0
         self._inplace = any(p.name != "PolynomialFeatures" for p in self.preprocessors[:1])
+        self._fused = None
 
     @property
     def built(self) -> bool:
@@ -110,11 +111,29 @@ class GpuPipeline:
     def device_train(self, Z: torch.Tensor, protect_input: bool, sync_due: bool, skip_fit: bool = False, **kw) -> None:
         """Device work of one step (graph-capturable when `graph_safe()`).  `skip_fit`: the learner
         update was already done by a batched multi-pipeline launch."""
-        if not skip_fit:
+        if not skip_fit and self._fusable():
+            # PolynomialFeatures -> StandardScaler -> mini-batch linear learner: two passes over the raw
+            # rows, the expanded features only ever exist in registers (csrc/fused_pipeline.cu)
+            from ..ops import functional as F
+            pf, sc, l = self.preprocessors[0], self.preprocessors[1], self.learner
+            F.fused_poly_scaler_linear(Z, pf.d_in, pf.factors, pf.d_out, sc.state, sc.scratch, l.w, l.stats, l.scratch,
+                                       l.kind, l.variant, l.C, l.eps, l.lam, l.mean_update)
+        elif not skip_fit:
             Zp = self.preprocess(Z, True, protect_input)
             self.learner.fit_batch(Zp, **kw)
         if sync_due and self.driver.step():
             self.learner.after_sync()
+
+    def _fusable(self) -> bool:
+        if self._fused is None:
+            from .learners import GpuLinear
+            pp = self.preprocessors
+            self._fused = bool(
+                len(pp) == 2 and pp[0].name == "PolynomialFeatures" and pp[1].name == "StandardScaler"
+                and isinstance(self.learner, GpuLinear) and self.learner.mode != "exact"
+                and pp[0].degree <= 4 and pp[0].d_out <= 512
+                and str(cfg(self.request.trainingConfiguration, ["fusedPipeline"], "true")).lower() in ("1", "true", "yes"))
+        return self._fused
 
     def host_tick(self) -> None:
         """Host bookkeeping of one step; runs after the device work was enqueued (or replayed)."""

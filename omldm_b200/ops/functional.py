@@ -520,6 +520,26 @@ def axpy(y: torch.Tensor, x: torch.Tensor, alpha: float) -> None:
     y.add_(x, alpha=alpha)
 
 
+# ------------------------------------------------------------------------------ fused pipeline (config 3)
+def fused_poly_scaler_linear(Z: torch.Tensor, d_in: int, factors: torch.Tensor, d_out: int, scaler_state: torch.Tensor,
+                             scaler_scratch: torch.Tensor, w: torch.Tensor, stats: torch.Tensor,
+                             lin_scratch: torch.Tensor, kind: int, variant: int, C: float, eps: float, lam: float,
+                             mean_update: bool = True) -> None:
+    """PolynomialFeatures -> StandardScaler(fit) -> mini-batch linear update without materialising the
+    expanded rows (two passes over the raw batch).  Equivalent to the three separate ops."""
+    B = Z.shape[0]
+    if native(Z):
+        desc = LinearDesc(w.data_ptr(), stats.data_ptr(), d_out, kind, variant, C, eps, lam)
+        _lib.check(_k().omldm_fused_poly_scaler_linear(
+            _p(Z), _i(Z.stride(0)), _i(d_in), _i(B), _p(factors), _i(factors.shape[1]), _i(d_out), _p(scaler_state),
+            _p(scaler_scratch), ctypes.byref(desc), _p(lin_scratch), _i(1 if mean_update else 0), _lib.stream_ptr()),
+            "fused_poly_scaler_linear")
+        return
+    Zp = poly_features(Z, d_in, factors, d_out)
+    standard_scaler(Zp, d_out, scaler_state, scaler_scratch, True)
+    linear_minibatch(Zp, d_out, w, stats, lin_scratch, kind, variant, C, eps, lam, mean_update)
+
+
 # ------------------------------------------------------------------------------ Hoeffding tree
 def _ht_route_torch(Z, feature, threshold, left, right):
     node = torch.zeros(Z.shape[0], dtype=torch.long, device=Z.device)

@@ -228,3 +228,36 @@ def test_hoeffding_tree_kernels():
     assert torch.allclose(ref[1], nat[1], rtol=1e-4, atol=1e-3) and torch.allclose(ref[2], nat[2], rtol=1e-4, atol=1e-3)
     assert ref[3].item() == nat[3].item() == B - 1
     assert set(nat[5].unique().tolist()) == {2, 3, 4}
+
+
+@pytest.mark.parametrize("kind", [F.KIND_PA_REG, F.KIND_PA])
+@pytest.mark.parametrize("d_in,degree", [(28, 2), (6, 3)])
+def test_fused_poly_scaler_linear_equals_separate_kernels(kind, d_in, degree):
+    B = 4000
+    tab = torch.from_numpy(poly_factor_table(d_in, degree)).to(DEV)
+    d_out = tab.shape[0]
+    batches = [staged(R.KIND_REGRESSION if kind == F.KIND_PA_REG else R.KIND_BINARY, d_in, B, seed=s) for s in range(3)]
+    batches[1][5, d_in] = 0.0
+
+    def run(fused):
+        st = torch.zeros(1 + 2 * d_out, dtype=torch.float64, device=DEV)
+        sc = torch.zeros(3 + 4 * d_out, dtype=torch.float64, device=DEV)
+        w = torch.zeros(d_out + 1, device=DEV)
+        stats = torch.zeros(4, dtype=torch.float64, device=DEV)
+        ls = F.linear_minibatch_scratch(d_out, DEV)
+        for Z in batches:
+            if fused:
+                F.fused_poly_scaler_linear(Z, d_in, tab, d_out, st, sc, w, stats, ls, kind, 1, 0.5, 0.05, 0.01)
+            else:
+                Zp = F.poly_features(Z, d_in, tab, d_out)
+                F.standard_scaler(Zp, d_out, st, sc, True)
+                F.linear_minibatch(Zp, d_out, w, stats, ls, kind, 1, 0.5, 0.05, 0.01)
+        torch.cuda.synchronize()
+        return w, stats, st
+    w1, s1, st1 = run(True)
+    w0, s0, st0 = run(False)
+    with F.use_impl("torch"):
+        wt, stt, _ = run(False)
+    assert torch.allclose(st1, st0, rtol=1e-9, atol=1e-9)
+    assert torch.allclose(w1, w0, rtol=2e-3, atol=2e-5) and torch.allclose(w1, wt, rtol=5e-3, atol=5e-5)
+    assert torch.allclose(s1, s0, rtol=1e-3)
