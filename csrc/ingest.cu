@@ -57,9 +57,19 @@ holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restri
         else if (j < m) reinterpret_cast<float4*>(row_of(j + 1))[c4] = v[j];
       }
     } else {
+      // long chain: walk it from the tail in segments of MAXC rows; inside a segment every load is
+      // issued before the shifted stores, so only ceil(m / MAXC) phases are serialised
       *r4 = reinterpret_cast<float4*>(row_of(m))[c4];
-      for (int j = m; j >= 1; --j)
-        reinterpret_cast<float4*>(row_of(j))[c4] = reinterpret_cast<float4*>(row_of(j - 1))[c4];
+      for (int hi = m; hi >= 1; hi -= MAXC) {
+        const int lo = hi - MAXC + 1 > 1 ? hi - MAXC + 1 : 1;   // rows lo..hi receive rows lo-1..hi-1
+        float4 v[MAXC];
+#pragma unroll
+        for (int t = 0; t < MAXC; ++t)
+          if (lo + t <= hi) v[t] = reinterpret_cast<const float4*>(row_of(lo + t - 1))[c4];
+#pragma unroll
+        for (int t = 0; t < MAXC; ++t)
+          if (lo + t <= hi) reinterpret_cast<float4*>(row_of(lo + t))[c4] = v[t];
+      }
     }
     reinterpret_cast<float4*>(row_of(0))[c4] = old;
   }

@@ -29,7 +29,8 @@ def test_native_library_loaded():
     assert _lib.kernels().omldm_abi_version() == 1
 
 
-@pytest.mark.parametrize("B,count0,cap", [(100, 0, 16), (4096, 0, 256), (1000, 12345, 256), (37, 8, 4)])
+@pytest.mark.parametrize("B,count0,cap", [(100, 0, 16), (4096, 0, 256), (1000, 12345, 256), (37, 8, 4), (20000, 777, 64),
+                                          (65536, 65536 * 3, 256)])
 def test_holdout_swap(B, count0, cap):
     d = 12
     Z0 = staged(R.KIND_BINARY, d, B, seed=3)
