@@ -65,6 +65,9 @@ class Engine:
         self._seen: Dict[Any, int] = {}
         self._count_dev: Optional[torch.Tensor] = None
         self._sparse_key = None
+        self._hp_stream = None
+        # opt-in: measured no gain for the ORR refresh overlap, so the default stays the caller's stream
+        self.use_priority_stream = str(self.params.extra.get("priorityStream", "false")).lower() in ("1", "true", "yes")
         self._multi_key = None
         self._multi_desc = None
 
@@ -181,12 +184,25 @@ class Engine:
         nvtx = self.device.type == "cuda"
         if nvtx:
             torch.cuda.nvtx.range_push("omldm.step.replay" if g is not None else "omldm.step.eager")
-        if g is not None:
-            g.replay()
-            _lib.add_launch_count(self._graph_launches[key])
-        else:
-            self._seen[key] = self._seen.get(key, 0) + 1
-            self._device_step(Z, d, **kw)
+        hp = self._step_stream() if nvtx else None
+        if hp is not None:
+            # the step runs on a high-priority stream so that background work on ordinary streams (the
+            # ORR weight refresh, a checkpoint copy) cannot push the hot kernels out of the SMs
+            user = torch.cuda.current_stream(self.device)
+            hp.wait_stream(user)
+            ctx = torch.cuda.stream(hp)
+            ctx.__enter__()
+        try:
+            if g is not None:
+                g.replay()
+                _lib.add_launch_count(self._graph_launches[key])
+            else:
+                self._seen[key] = self._seen.get(key, 0) + 1
+                self._device_step(Z, d, **kw)
+        finally:
+            if hp is not None:
+                ctx.__exit__(None, None, None)
+                user.wait_stream(hp)
         if nvtx:
             torch.cuda.nvtx.range_pop()
         self.count += B
@@ -194,6 +210,13 @@ class Engine:
             if p.built and (p.protocol != "SingleLearner" or self.rank == 0):
                 p.host_tick()
         self.t_last = time.monotonic()
+
+    def _step_stream(self):
+        if not self.use_priority_stream:
+            return None
+        if self._hp_stream is None:
+            self._hp_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        return self._hp_stream
 
     def _graphable(self, Z: torch.Tensor) -> bool:
         if not (Z.is_cuda and F.native(Z)) or not self.pipelines:

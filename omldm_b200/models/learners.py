@@ -238,11 +238,17 @@ class GpuORR(GpuLearner):
             self._side = torch.cuda.Stream(device=self.device)
             self._fork = torch.cuda.Stream(device=self.device)
             self._w_next = torch.zeros(self.d + 1, device=self.device)
-            eye = torch.eye(self.d + 1, device=self.device)
-            for st in (torch.cuda.current_stream(self.device), self._side):
-                with torch.cuda.stream(st):
-                    L, _ = torch.linalg.cholesky_ex(eye, check_errors=False)
-                    torch.cholesky_solve(eye[:, :1], L)
+            # Run the real refresh path once on both streams now (G = 0, so A = lambda I): creates the
+            # cuSOLVER / cuBLAS handles, workspaces, stream-private allocator blocks and lazily loaded
+            # kernels here instead of inside somebody's timed region (the first refresh costs 10-20 ms).
+            lam0, self.lam = self.lam, max(self.lam, 1.0)     # keep the warm-up system non-singular
+            self.solve()
+            self.solve_async()
+            self._install()
+            self.lam = lam0
+            self.wt[: self.d + 1].zero_()
+            self._since = 0
+            self.solves = 0
             torch.cuda.synchronize(self.device)
 
     def fit_batch(self, Z):
@@ -336,7 +342,10 @@ class GpuORR(GpuLearner):
         if not bool(torch.isfinite(self.wt).all()):      # ill-conditioned in fp32: redo in fp64
             A = self._work[:d1, :d1].double()
             A.diagonal().add_(self.lam)
-            self.wt[:d1] = torch.linalg.solve(A, self._work[:d1, d1].double()).float()
+            try:
+                self.wt[:d1] = torch.linalg.solve(A, self._work[:d1, d1].double()).float()
+            except Exception:                             # singular (e.g. lambda = 0 before any data)
+                self.wt[:d1] = torch.linalg.lstsq(A, self._work[:d1, d1].double()[:, None]).solution[:, 0].float()
         self._since = 0
         self.solves += 1
 
