@@ -39,6 +39,8 @@ class Engine:
         if device is None:
             device = f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "cpu"
         self.device = torch.device(device)
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.pipeline_map = PipelineMap(world, self.params.distributedKMeans)
         self.pipelines: Dict[int, GpuPipeline] = {}
         self.pending_requests: List[Request] = []
@@ -160,6 +162,16 @@ class Engine:
             d = self.d
         if d is None:
             raise ValueError("feature dimension not known; pass d on the first batch")
+        if Z.dim() != 2 or Z.dtype != torch.float32 or Z.stride(1) != 1 or Z.stride(0) != Z.shape[1]:
+            raise ValueError("train_batch expects a contiguous 2-D fp32 tensor of staged rows")
+        if Z.shape[1] % 32 or Z.shape[1] < d + 2:
+            raise ValueError(f"staged rows need a pitch that is a multiple of 32 floats and >= d + 2 = {d + 2}; "
+                             f"got {Z.shape[1]} (use omldm_b200.ops.functional.stage_rows or stream.ring.Topic)")
+        if Z.device.type != self.device.type or (Z.device.index is not None and self.device.index is not None
+                                                 and Z.device.index != self.device.index):
+            raise ValueError(f"batch is on {Z.device}, engine on {self.device}; use train_batch_host for host batches")
+        if self.d is not None and self.d != d:
+            raise ValueError(f"this stream has {self.d} features, got d = {d}")
         self.d = d
         now = time.monotonic()
         if self.t_first is None:
