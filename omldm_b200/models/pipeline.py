@@ -58,6 +58,8 @@ class GpuPipeline:
         self._win_n = 0
         self._inplace = any(p.name != "PolynomialFeatures" for p in self.preprocessors[:1])
         self._fused = None
+        self._curve_every = int(cfg(tc, ["curveEvery", "learningCurveEvery"], 0))
+        self._curve_loss, self._curve_n = 0.0, 0
 
     @property
     def built(self) -> bool:
@@ -140,6 +142,13 @@ class GpuPipeline:
         self.batches += 1
         self.driver.host_tick()
         self.learner.host_tick()
+        if self._curve_every and self.batches % self._curve_every == 0:
+            # learning-curve sample (loss of the window, #fitted) as the hub records per mini-batch
+            # (FlinkHub.scala:101-107); reading the counters synchronises, hence opt-in (`curveEvery`)
+            c = self.learner.counters()
+            n = c["fitted"] - self._curve_n
+            self.curve.append(((c["loss_sum"] - self._curve_loss) / n if n > 0 else 0.0, c["fitted"]))
+            self._curve_loss, self._curve_n = c["loss_sum"], c["fitted"]
 
     def graph_safe(self) -> bool:
         return (self.built and self.protocol != "SingleLearner" and self.driver.graph_safe
