@@ -334,7 +334,8 @@ __global__ void __launch_bounds__(256) sync_easgd_kernel(Comm c, size_t n, float
 //   sub-round end  when the hub's global counter exceeds k it sums the published phi_i into psi;
 //                  psi >= eps_psi * k * phi(0) ends the round (allreduce + reset), otherwise a new
 //                  sub-round starts with the smaller quantum.
-// Hub = rank 0's pad.  FGM words: [0] counter(s32) [1] subround id [2] theta bits [3] round id.
+// Hub = rank 0's pad.  FGM words: [0] counter(s32) [1] subround id [2] theta bits [3] round id
+// (mirrored into every pad) [4] first step number at which the announced round end is acted on (every pad).
 // state_local (float[8], private): [0] round id [1] subround seen [2] zeta [3] counts sent [4] rounds [5] subrounds
 __global__ void __launch_bounds__(256)
 sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode, float threshold,
@@ -357,10 +358,16 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
       loc[L_STEP] = step;
       const float phi = sqrtf(nrm2) + phi0;
       uint32_t round = static_cast<uint32_t>(st[0]);
-      // Round-end flag is sampled BEFORE this step's hub logic: a round declared by the hub during
-      // step s is acted on by every rank (hub included) in its step s+1, so ranks that advance in
-      // lock-step all take the same branch.
+      // Round-end flag is sampled BEFORE this step's hub logic, and a round declared by the hub during
+      // its step s carries "act at step s+1" (word 4): a rank that happens to sample the flag after the
+      // hub wrote it within the same step number still waits one step, so ranks that advance in
+      // lock-step all take the same branch (a rank that runs ahead acts as soon as it sees the flag).
       const uint32_t seen_round = ld_acquire_sys(c.pads[me] + OMLDM_PAD_FGM + 3);
+      bool act = false;
+      if (seen_round != round) {
+        const uint32_t act_step = ld_relaxed_sys(c.pads[me] + OMLDM_PAD_FGM + 4);
+        act = static_cast<int32_t>(step - act_step) >= 0;
+      }
       // publish phi to the hub (push-based polling)
       asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + me), "r"(__float_as_uint(phi)) : "memory");
       const uint32_t sub = ld_acquire_sys(hub + 1);
@@ -385,6 +392,8 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
           float psi = 0.f;
           for (int i = 0; i < k; ++i) psi += __uint_as_float(ld_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + i));
           if (psi >= eps_psi * k * phi0) {
+            for (int p = 0; p < k; ++p)
+              asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[p] + OMLDM_PAD_FGM + 4), "r"(step + 1u) : "memory");
             for (int p = 0; p < k; ++p) st_release_sys(c.pads[p] + OMLDM_PAD_FGM + 3, round + 1);  // round end
           } else {
             asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub + 2), "r"(__float_as_uint(-psi / (2.f * k))) : "memory");
@@ -394,7 +403,7 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
           }
         }
       }
-      const uint32_t decision = 2 * step + ((seen_round != round) ? 1u : 0u);
+      const uint32_t decision = 2 * step + (act ? 1u : 0u);
       __threadfence();
       atomicExch(loc + L_DECISION, decision);
     }

@@ -175,7 +175,7 @@ enum {
   OMLDM_PAD_CLOCK = 32,    /* [32,48)  SSP clocks                                   */
   OMLDM_PAD_VOTE = 48,     /* [48,64)  GM / FGM round votes                         */
   OMLDM_PAD_PHI = 64,      /* [64,80)  FGM phi values (float bits), hub = rank 0    */
-  OMLDM_PAD_FGM = 80,      /* [80,96)  FGM hub state: counter, subround, theta, psi */
+  OMLDM_PAD_FGM = 80,      /* [80,96)  FGM: counter, subround, theta, round id, act-at-step */
   OMLDM_PAD_STATUS = 96,   /* [96,100) status bits: 1 barrier, 2 SSP, 4 FGM timeouts  */
   OMLDM_PAD_QUERY = 128,   /* [128,192) query scalars, 4 per peer                   */
   OMLDM_PAD_WORDS = 256
@@ -200,7 +200,9 @@ int omldm_sync_gm(const omldm_comm* comm_host, float* e_local, size_t n, float s
                   float threshold, uint32_t epoch, int blocks, void* stream);
 /* FGM monitor step: phi = ||buf - e|| - sqrt(threshold), counter increments to the hub,
  * sub-round / round bookkeeping, and the round-end allreduce, all inside one kernel.
- * `state_local` : float[8] private FGM state of this rank (zero-initialised); `step` counts from 1. */
+ * `state_local` : float[8] private FGM state of this rank (zero-initialised); `step` counts from 1.
+ * A round the hub announces in its step s is executed by every rank in its first step >= s+1, so
+ * ranks that make the same number of calls take the round-end branch in the same call. */
 int omldm_sync_fgm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
                    float threshold, float eps_psi, uint32_t step, float* state_local, int blocks,
                    void* stream);
