@@ -86,3 +86,69 @@ def test_checkpoint_resume_continues_identically(tmp_path):
     assert torch.allclose(wa, wb, atol=1e-6) and a.count == b_eng.count
     pc = PeriodicCheckpointer(a, str(tmp_path / "ck2"), interval_ms=0)
     assert pc.maybe_save(9) and os.path.exists(tmp_path / "ck2" / "rank000.pt")
+
+
+def _two_worker_checkpoint(tmp_path, learner, pre=None, d=7, kind=None):
+    """Two independent workers (the two subtasks of a parallelism-2 job between synchronisations)
+    write rank000.pt / rank001.pt plus a manifest that says world = 2."""
+    kind = R.KIND_REGRESSION if kind is None else kind
+    engines, data = [], []
+    for r in range(2):
+        e = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")
+        e.handle_request({"id": 1, "request": "Create", "learner": learner, "preProcessors": pre or [],
+                          "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": d}})
+        bs = [R.generate_batch(kind, d, 64, seed=20 + r, batch_index=i) for i in range(3)]
+        for b in bs:
+            e.train_batch(b.clone(), d)
+        e.rank = r
+        save_checkpoint(e, str(tmp_path / "ck"), step=3)
+        engines.append(e)
+        data.append(bs)
+    man = json.load(open(tmp_path / "ck" / "manifest.json"))
+    man["world"] = 2
+    json.dump(man, open(tmp_path / "ck" / "manifest.json", "w"))
+    return engines, data
+
+
+def test_restore_with_fewer_ranks_merges_worker_states(tmp_path):
+    """Rescaling restore (FlinkSpoke.scala:289-305): one new worker folds both old ones."""
+    d = 7
+    engines, _ = _two_worker_checkpoint(tmp_path, {"name": "ORR", "hyperParameters": {"lambda": 1.0}},
+                                        [{"name": "StandardScaler"}], d)
+    m = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")
+    assert load_checkpoint(m, str(tmp_path / "ck")) == 3
+    la, lb, lm = engines[0].pipelines[1].learner, engines[1].pipelines[1].learner, m.pipelines[1].learner
+    # additive statistics: the merged Gram delta is the sum of both workers' deltas
+    assert torch.allclose(lm.buf, la.buf + lb.buf, rtol=1e-5, atol=1e-5)
+    ca, cb, cm = la.counters(), lb.counters(), lm.counters()
+    assert cm["fitted"] == ca["fitted"] + cb["fitted"]
+    assert abs(cm["loss_sum"] - ca["loss_sum"] - cb["loss_sum"]) < 1e-6 * max(1.0, abs(cm["loss_sum"]))
+    # scaler moments merge exactly (Chan): count adds, mean is the weighted mean
+    sa, sb, sm = (e.pipelines[1].preprocessors[0].state for e in (*engines, m))
+    assert float(sm[0]) == float(sa[0]) + float(sb[0])
+    wmean = (sa[0] * sa[1:1 + d] + sb[0] * sb[1:1 + d]) / (sa[0] + sb[0])
+    assert torch.allclose(sm[1:1 + d], wmean, rtol=1e-10, atol=1e-12)
+    # holdout rings interleave, nothing beyond the filled rows counts as valid
+    assert m.holdout.shape == engines[0].holdout.shape
+    n_valid = m._holdout_rows().shape[0]
+    assert 0 < n_valid <= 16 and bool((m._holdout_rows()[:, d] == 1.0).all())
+    # and the merged worker keeps training
+    m.train_batch(R.generate_batch(R.KIND_REGRESSION, d, 64, seed=99, batch_index=0), d)
+    assert m.pipelines[1].learner.counters()["fitted"] > cm["fitted"]
+
+
+def test_restore_averaged_model_and_more_ranks(tmp_path):
+    d = 7
+    engines, _ = _two_worker_checkpoint(tmp_path, {"name": "PA", "hyperParameters": {"C": 0.1}}, None, d,
+                                        kind=R.KIND_BINARY)
+    m = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")
+    load_checkpoint(m, str(tmp_path / "ck"))
+    wa, wb, wm = (e.pipelines[1].learner.w for e in (*engines, m))
+    assert torch.allclose(wm, 0.5 * (wa + wb), atol=1e-6)
+    # a rank that did not exist before adopts the model of rank (r mod old_world) with empty history
+    g = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")
+    g.rank, g.world = 3, 4
+    load_checkpoint(g, str(tmp_path / "ck"))
+    assert torch.allclose(g.pipelines[1].learner.w, wb, atol=1e-7)
+    assert g.pipelines[1].learner.counters()["fitted"] == 0 and g.count == 0
+    assert g._holdout_rows().shape[0] == 0
