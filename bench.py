@@ -107,6 +107,9 @@ def main() -> None:
     ap.add_argument("--config", default="orr", choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--wire", default="f32", choices=["f32", "f16"],
+                    help="record format of the pinned host ring in the e2e measurement (f16: compact wire rows, "
+                         "half the H2D bytes, expanded on the GPU)")
     ap.add_argument("--tc", action="append", default=[], help="extra trainingConfiguration key=value")
     ap.add_argument("--hyper", action="append", default=[], help="extra learner hyper-parameter key=value")
     args = ap.parse_args()
@@ -209,7 +212,7 @@ def main() -> None:
             topic = R.SparseTopic(d, B, nnz, n_slots=8)
             topic.start_synthetic(seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_GENERATE, n_threads=2)
         else:
-            topic = R.Topic(d, B, n_slots=n_rot)
+            topic = R.Topic(d, B, n_slots=n_rot, wire=args.wire)
             topic.start_synthetic(cfg["kind"], seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_REPLAY, n_threads=2)
         pending = []   # (slot, event recorded after the slot's H2D copy)
 
@@ -237,7 +240,8 @@ def main() -> None:
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": world * B * args.steps / float(dt.item()), "unit": "records/s",
-               "h2d_bytes_per_step": (B * (2 * nnz + 1) * 4) if sparse else (B * ld * 4), "d2h_bytes_per_step": 32,
+               "h2d_bytes_per_step": topic.slot_bytes, "d2h_bytes_per_step": 32,
+               "wire": "sparse ELL (int32 index + fp32 value)" if sparse else args.wire,
                "last_loss_sum": float(loss_host[0])}
         topic.stop()
     clocks = sampler.stop() if sampler else None

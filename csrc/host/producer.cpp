@@ -52,11 +52,35 @@ struct Truth {
   }
 };
 
-void fill_batch(float* dst, const Truth& tr, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
-                uint64_t batch_index) {
+// fp32 -> fp16 bits, round to nearest even, overflow to infinity, subnormals kept
+inline uint16_t f32_to_f16(float f) {
+  uint32_t x;
+  std::memcpy(&x, &f, 4);
+  const uint32_t sign = (x >> 16) & 0x8000u;
+  x &= 0x7FFFFFFFu;
+  if (x >= 0x7F800000u) return static_cast<uint16_t>(sign | 0x7C00u | ((x > 0x7F800000u) ? 0x200u : 0u));
+  if (x >= 0x477FF000u) return static_cast<uint16_t>(sign | 0x7C00u);          // rounds to >= 65520 -> inf
+  if (x < 0x33000001u) return static_cast<uint16_t>(sign);                     // below half the smallest subnormal
+  if (x < 0x38800000u) {                                                       // subnormal half
+    const int shift = 126 - static_cast<int>(x >> 23);                         // 14..24
+    const uint32_t m = (x & 0x7FFFFFu) | 0x800000u;
+    const uint32_t q = m >> shift, rem = m & ((1u << shift) - 1u), half = 1u << (shift - 1);
+    return static_cast<uint16_t>(sign | (q + ((rem > half || (rem == half && (q & 1u))) ? 1u : 0u)));
+  }
+  const uint32_t q = (x - 0x38000000u) >> 13, rem = x & 0x1FFFu;
+  return static_cast<uint16_t>(sign | (q + ((rem > 0x1000u || (rem == 0x1000u && (q & 1u))) ? 1u : 0u)));
+}
+
+// wire = 0: staged fp32 rows (pitch ld floats).  wire = 1: compact rows [fp16 x d | pad | fp32 target],
+// pitch even(d) + 2 halves (include/omldm_host.h).
+void fill_batch(void* dst_any, const Truth& tr, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
+                uint64_t batch_index, int wire = 0) {
   Rng g(seed * 0x100000001B3ull + batch_index * 0x9E3779B97F4A7C15ull + 1);
+  float* dst = static_cast<float*>(dst_any);
+  std::vector<float> tmp(wire ? static_cast<size_t>(ld) : 0);
+  const int wld = ((d + 1) & ~1) + 2;
   for (int r = 0; r < batch; ++r) {
-    float* row = dst + static_cast<size_t>(r) * ld;
+    float* row = wire ? tmp.data() : dst + static_cast<size_t>(r) * ld;
     float y = 0.f;
     if (kind == 2) {
       const int c = static_cast<int>(g.next() % static_cast<uint64_t>(n_aux > 0 ? n_aux : 1));
@@ -84,6 +108,12 @@ void fill_batch(float* dst, const Truth& tr, int kind, int d, int ld, int batch,
     row[d] = 1.0f;
     row[d + 1] = y;
     for (int j = d + 2; j < ld; ++j) row[j] = 0.f;
+    if (wire) {
+      uint16_t* w = static_cast<uint16_t*>(dst_any) + static_cast<size_t>(r) * wld;
+      for (int j = 0; j < d; ++j) w[j] = f32_to_f16(row[j]);
+      if (d & 1) w[d] = 0;
+      std::memcpy(w + wld - 2, &y, 4);
+    }
   }
 }
 
@@ -118,7 +148,7 @@ void fill_sparse_batch(uint8_t* slot, const Truth& tr, int d, int nnz, int batch
 
 struct omldm_producer {
   omldm_ring* ring;
-  int kind, d, ld, batch, n_aux, mode, n_threads;
+  int kind, d, ld, batch, n_aux, mode, n_threads, wire = 0;
   uint64_t seed;
   int64_t max_batches;
   std::atomic<int64_t> next_batch{0};
@@ -146,7 +176,7 @@ static void producer_loop(omldm_producer* p) {
         fill_sparse_batch(reinterpret_cast<uint8_t*>(dst), p->truth, p->d, p->ld, p->batch, p->n_aux, p->seed,
                           static_cast<uint64_t>(b));
       else
-        fill_batch(dst, p->truth, p->kind, p->d, p->ld, p->batch, p->n_aux, p->seed, static_cast<uint64_t>(b));
+        fill_batch(dst, p->truth, p->kind, p->d, p->ld, p->batch, p->n_aux, p->seed, static_cast<uint64_t>(b), p->wire);
       p->filled[slot] = 1;
     }
     omldm_ring_commit_write(p->ring, slot, p->batch);
@@ -154,17 +184,25 @@ static void producer_loop(omldm_producer* p) {
   if (p->live.fetch_sub(1) == 1) omldm_ring_close(p->ring);
 }
 
-extern "C" omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
-                                                uint64_t seed, int mode, int64_t max_batches, int n_threads) {
+extern "C" omldm_producer* omldm_producer_start_wire(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
+                                                     uint64_t seed, int mode, int64_t max_batches, int n_threads,
+                                                     int wire) {
   if (!r || d <= 0 || batch <= 0 || (kind != 4 && ld < d + 2) || (kind == 4 && ld <= 0)) return nullptr;
+  if (wire != 0 && (wire != 1 || kind == 4)) return nullptr;
   auto* p = new omldm_producer(kind, d, n_aux, seed);
   p->ring = r; p->kind = kind; p->d = d; p->ld = ld; p->batch = batch; p->n_aux = n_aux; p->mode = mode;
+  p->wire = wire;
   p->seed = seed; p->max_batches = max_batches;
   p->n_threads = n_threads < 1 ? 1 : n_threads;
   p->filled.assign(1 << 16, 0);
   p->live.store(p->n_threads);
   for (int i = 0; i < p->n_threads; ++i) p->threads.emplace_back(producer_loop, p);
   return p;
+}
+
+extern "C" omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
+                                                uint64_t seed, int mode, int64_t max_batches, int n_threads) {
+  return omldm_producer_start_wire(r, kind, d, ld, batch, n_aux, seed, mode, max_batches, n_threads, 0);
 }
 
 extern "C" void omldm_producer_stop(omldm_producer* p) {
@@ -184,4 +222,21 @@ extern "C" void omldm_generate_batch(float* dst, int kind, int d, int ld, int ba
                                      uint64_t batch_index) {
   Truth tr(kind, d, n_aux, seed);
   fill_batch(dst, tr, kind, d, ld, batch, n_aux, seed, batch_index);
+}
+
+extern "C" void omldm_generate_batch_f16(void* dst, int kind, int d, int batch, int n_aux, uint64_t seed,
+                                         uint64_t batch_index) {
+  Truth tr(kind, d, n_aux, seed);
+  fill_batch(dst, tr, kind, d, d + 2, batch, n_aux, seed, batch_index, 1);
+}
+
+extern "C" void omldm_pack_wire_f16(const float* rows, int ld, int target_col, int batch, int d, void* dst) {
+  const int wld = ((d + 1) & ~1) + 2;
+  for (int r = 0; r < batch; ++r) {
+    const float* row = rows + static_cast<size_t>(r) * ld;
+    uint16_t* w = static_cast<uint16_t*>(dst) + static_cast<size_t>(r) * wld;
+    for (int j = 0; j < d; ++j) w[j] = f32_to_f16(row[j]);
+    if (d & 1) w[d] = 0;
+    std::memcpy(w + wld - 2, row + target_col, 4);
+  }
 }

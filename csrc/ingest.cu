@@ -6,6 +6,7 @@
 // record count, it is a pure index map: holdout #h lives in ring slot h % cap and evicts holdout
 // #(h - cap).  The kernel swaps rows in place, so after it runs the batch rows ARE the training
 // sequence in the original order (an empty row, bias column 0, where nothing was evicted yet).
+#include <cuda_fp16.h>
 #include "ptx.cuh"
 #include "host_common.h"
 #include "omldm_kernels.h"
@@ -122,6 +123,31 @@ __global__ void stage_rows_kernel(const float* __restrict__ raw, int raw_ld, int
   }
 }
 
+// Compact wire format -> staged rows.  A wire row is [x as fp16 x d | (pad to an even count) | target as
+// fp32 in two halves]; pitch `raw_ld` halves.  fp16 keeps 11 significand bits, one more than the tf32
+// products the Gram/score GEMMs use, so for features inside the fp16 range the learners see the same
+// inputs - at half the PCIe bytes per record (the e2e path is H2D bound).
+__global__ void stage_rows_f16_kernel(const __half* __restrict__ raw, int raw_ld, int B, int d,
+                                      float* __restrict__ Z, int ld) {
+  const int r = blockIdx.x;
+  const __half* src = raw + static_cast<size_t>(r) * raw_ld;
+  const __half2* src2 = reinterpret_cast<const __half2*>(src);
+  float2* dst2 = reinterpret_cast<float2*>(Z + static_cast<size_t>(r) * ld);
+  const int d_even = (d + 1) & ~1;
+  const float target = *reinterpret_cast<const float*>(src + d_even);
+  for (int c2 = threadIdx.x; c2 < (ld >> 1); c2 += blockDim.x) {
+    const int c = 2 * c2;
+    float2 v;
+    if (c + 1 < d) {
+      v = __half22float2(src2[c2]);
+    } else {
+      v.x = c < d ? __half2float(src[c]) : (c == d ? 1.f : (c == d + 1 ? target : 0.f));
+      v.y = (c + 1 == d) ? 1.f : (c + 1 == d + 1 ? target : 0.f);
+    }
+    dst2[c2] = v;
+  }
+}
+
 }  // namespace omldm
 
 using namespace omldm;
@@ -163,4 +189,14 @@ extern "C" int omldm_stage_rows(const float* raw, int raw_ld, int B, int d, floa
   if (B <= 0) return 0;
   stage_rows_kernel<<<B, 128, 0, static_cast<cudaStream_t>(stream)>>>(raw, raw_ld, B, d, Z, ld);
   return check_launch("stage_rows_kernel");
+}
+
+extern "C" int omldm_stage_rows_f16(const void* raw, int raw_ld, int B, int d, float* Z, int ld, void* stream) {
+  if (B <= 0) return 0;
+  if ((raw_ld & 1) || raw_ld < ((d + 1) & ~1) + 2) return set_error_msg("stage_rows_f16: raw_ld must be even and >= even(d) + 2");
+  if ((ld & 1) || ld < d + 2) return set_error_msg("stage_rows_f16: ld must be even and >= d + 2");
+  if (reinterpret_cast<uintptr_t>(raw) & 3) return set_error_msg("stage_rows_f16: raw must be 4-byte aligned");
+  stage_rows_f16_kernel<<<B, 128, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __half*>(raw), raw_ld, B, d,
+                                                                        Z, ld);
+  return check_launch("stage_rows_f16_kernel");
 }

@@ -36,6 +36,12 @@ void* omldm_ring_slot_ptr(omldm_ring* r, int slot);
 typedef struct omldm_producer omldm_producer;
 omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
                                      uint64_t seed, int mode, int64_t max_batches, int n_threads);
+/* Same, with a wire format: 0 = staged fp32 rows (above); 1 = compact rows for the host->device link,
+ * [x as fp16 x d | pad to an even count | y as fp32 in two halves], pitch even(d) + 2 halves (the ring's slot
+ * size must be batch * pitch * 2 bytes; `ld` >= d + 2 only sizes a scratch row).  Expanded on the GPU by
+ * omldm_stage_rows_f16.  Not available for kind 4. */
+omldm_producer* omldm_producer_start_wire(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
+                                          uint64_t seed, int mode, int64_t max_batches, int n_threads, int wire);
 void omldm_producer_stop(omldm_producer* p);
 
 /* kind 4 = sparse multiclass stream (BASELINE.json config 5): pass the non-zeros per record as `ld`;
@@ -46,6 +52,12 @@ void omldm_generate_sparse_batch(void* slot, int d, int nnz, int batch, int n_au
 /* Fill one caller buffer with a synthetic staged batch (same generators, no ring). */
 void omldm_generate_batch(float* dst, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
                           uint64_t batch_index);
+/* ... in the compact fp16 wire format (dst: batch * (even(d) + 2) halves). */
+void omldm_generate_batch_f16(void* dst, int kind, int d, int batch, int n_aux, uint64_t seed,
+                              uint64_t batch_index);
+/* fp32 rows (pitch ld floats, target in column `target_col`) -> compact fp16 wire rows (round to nearest even,
+ * overflow to infinity, subnormals kept). */
+void omldm_pack_wire_f16(const float* rows, int ld, int target_col, int batch, int d, void* dst);
 
 /* Parse newline-delimited JSON DataInstances (utils/parsers/DataInstanceParser.scala:12-22,
  * dataStream/DataPointParser.scala:16-55) into staged rows.  Malformed records and "EOS" are

@@ -95,6 +95,11 @@ int omldm_densify(const int* indptr, const int* indices, const float* values, in
                   const float* targets, float* Z, int ld, float* sqnorm, void* stream);
 /* raw ring slot [B, d+1] (features..., target) -> staged rows */
 int omldm_stage_rows(const float* raw, int raw_ld, int B, int d, float* Z, int ld, void* stream);
+/* Compact wire format -> staged rows.  A wire row is [x as fp16 x d | pad to an even count | target as fp32
+ * stored in two halves], pitch `raw_ld` halves (even, >= even(d) + 2); `raw` 4-byte aligned.  Halves the
+ * bytes per record on the host->device link; the reference's wire format is JSON text
+ * (utils/parsers/DataInstanceParser.scala:12-22), so this has no counterpart there. */
+int omldm_stage_rows_f16(const void* raw, int raw_ld, int B, int d, float* Z, int ld, void* stream);
 
 /* ------------------------------------------------------------------ preprocessors (preprocess.cu)
  * PolynomialFeatures / StandardScaler / MinMaxScaler, PipelineMap.scala:67. */

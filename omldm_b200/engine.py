@@ -56,6 +56,7 @@ class Engine:
         self._stage: List[Optional[torch.Tensor]] = [None, None]
         self._stage_evt: List[Any] = [None, None]
         self._stage_i = 0
+        self._wire_dense: List[Optional[torch.Tensor]] = [None, None]
         self._loss_host = None
         self.last_copy_event = None
         self.holdout_enabled = True
@@ -311,6 +312,8 @@ class Engine:
     def train_batch_host(self, Z_host: torch.Tensor, d: int, **kw) -> torch.Tensor:
         """One e2e step from a pinned host slot.  Returns a pinned fp64[4] tensor that will hold
         (loss_sum, aux, fitted, extra) of the first pipeline once the current stream has drained."""
+        if Z_host.dtype == torch.float16:
+            return self._train_batch_host_f16(Z_host, d, **kw)
         if self.device.type != "cuda":
             self.train_batch(Z_host.clone(), d, **kw)
             return self._read_stats_host()
@@ -319,7 +322,7 @@ class Engine:
         i = self._stage_i
         self._stage_i ^= 1
         cur = torch.cuda.current_stream(self.device)
-        if self._stage[i] is None or self._stage[i].shape != Z_host.shape:
+        if self._stage[i] is None or self._stage[i].shape != Z_host.shape or self._stage[i].dtype != torch.float32:
             self._stage[i] = torch.empty(Z_host.shape, dtype=torch.float32, device=self.device)
         self._copy_stream.wait_stream(cur)      # the compute that last used this buffer is ordered before
         with torch.cuda.stream(self._copy_stream):
@@ -328,6 +331,36 @@ class Engine:
             self.last_copy_event.record(self._copy_stream)
         cur.wait_stream(self._copy_stream)
         self.train_batch(self._stage[i], d, **kw)
+        return self._read_stats_host()
+
+    def _train_batch_host_f16(self, W_host: torch.Tensor, d: int, **kw) -> torch.Tensor:
+        """e2e step from a slot in the compact fp16 wire format (`stream.ring.Topic(wire="f16")`):
+        half the H2D bytes, expanded to staged fp32 rows on the GPU (csrc/ingest.cu::stage_rows_f16_kernel)
+        into one of two alternating buffers, then the normal step."""
+        if W_host.shape[1] != F.wire_f16_pitch(d):
+            raise ValueError(f"fp16 wire rows for d={d} must have {F.wire_f16_pitch(d)} halves per record, "
+                             f"got {W_host.shape[1]}")
+        if self.device.type != "cuda":
+            self.train_batch(F.stage_rows_f16(W_host, d), d, **kw)
+            return self._read_stats_host()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        i = self._stage_i
+        self._stage_i ^= 1
+        cur = torch.cuda.current_stream(self.device)
+        if self._stage[i] is None or self._stage[i].shape != W_host.shape or self._stage[i].dtype != torch.float16:
+            self._stage[i] = torch.empty(W_host.shape, dtype=torch.float16, device=self.device)
+        B, ld = W_host.shape[0], F.pad32(d + 2)
+        if self._wire_dense[i] is None or self._wire_dense[i].shape != (B, ld):
+            self._wire_dense[i] = torch.empty(B, ld, dtype=torch.float32, device=self.device)
+        self._copy_stream.wait_stream(cur)      # the expansion that last read this buffer is ordered before
+        with torch.cuda.stream(self._copy_stream):
+            self._stage[i].copy_(W_host, non_blocking=True)
+            self.last_copy_event = torch.cuda.Event()
+            self.last_copy_event.record(self._copy_stream)
+        cur.wait_stream(self._copy_stream)
+        F.stage_rows_f16(self._stage[i], d, out=self._wire_dense[i])
+        self.train_batch(self._wire_dense[i], d, **kw)
         return self._read_stats_host()
 
     # ---- sparse streams (BASELINE config 5: "100k-dim sparse-to-dense stream") ---------------------

@@ -154,6 +154,38 @@ def stage_rows(raw: torch.Tensor, d: int, ld: Optional[int] = None) -> torch.Ten
     return Z
 
 
+def wire_f16_pitch(d: int) -> int:
+    """Row pitch (in halves) of the compact fp16 wire format: even(d) features + fp32 target."""
+    return ((d + 1) & ~1) + 2
+
+
+def pack_wire_f16(Z: torch.Tensor, d: int) -> torch.Tensor:
+    """Staged fp32 rows (or [B, d+1] raw rows) -> compact wire rows [B, wire_f16_pitch(d)] of fp16.
+    Host-side helper for producers and tests; the target keeps its fp32 bits."""
+    B = Z.shape[0]
+    tgt_col = d + 1 if Z.shape[1] >= d + 2 else d
+    out = torch.zeros(B, wire_f16_pitch(d), dtype=torch.float16, device=Z.device)
+    out[:, :d] = Z[:, :d].to(torch.float16)
+    out[:, -2:] = Z[:, tgt_col].to(torch.float32).contiguous().view(torch.float16).reshape(B, 2)
+    return out
+
+
+def stage_rows_f16(raw: torch.Tensor, d: int, ld: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Compact fp16 wire rows -> staged fp32 rows [B, ld] (csrc/ingest.cu::stage_rows_f16_kernel)."""
+    B = raw.shape[0]
+    ld = ld or pad32(d + 2)
+    Z = out if out is not None else torch.empty(B, ld, device=raw.device, dtype=torch.float32)
+    if native(raw):
+        _lib.check(_k().omldm_stage_rows_f16(_p(raw), _i(raw.stride(0)), _i(B), _i(d), _p(Z), _i(ld),
+                                             _lib.stream_ptr()), "stage_rows_f16")
+        return Z
+    Z.zero_()
+    Z[:, :d] = raw[:, :d].to(torch.float32)
+    Z[:, d] = 1.0
+    Z[:, d + 1] = raw[:, -2:].contiguous().view(torch.float32).reshape(B)
+    return Z
+
+
 def densify(indptr: torch.Tensor, indices: torch.Tensor, values: torch.Tensor, targets: Optional[torch.Tensor],
             d: int, ld: Optional[int] = None, out: Optional[torch.Tensor] = None,
             sq_out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:

@@ -13,7 +13,7 @@ from typing import Optional, Tuple
 import torch
 
 from ..ops import _lib
-from ..ops.functional import pad32
+from ..ops.functional import pack_wire_f16, pad32, wire_f16_pitch
 
 KIND_BINARY, KIND_REGRESSION, KIND_CLUSTERS, KIND_MULTICLASS, KIND_SPARSE_MULTICLASS = 0, 1, 2, 3, 4
 MODE_GENERATE, MODE_REPLAY = 0, 1
@@ -42,7 +42,10 @@ def _h():
         h.omldm_ring_slot_ptr.argtypes = [vp, i]
         h.omldm_producer_start.restype = vp
         h.omldm_producer_start.argtypes = [vp, i, i, i, i, i, u64, i, i64, i]
+        h.omldm_producer_start_wire.restype = vp
+        h.omldm_producer_start_wire.argtypes = [vp, i, i, i, i, i, u64, i, i64, i, i]
         h.omldm_producer_stop.argtypes = [vp]
+        h.omldm_generate_batch_f16.argtypes = [vp, i, i, i, i, u64, u64]
         h.omldm_generate_batch.argtypes = [vp, i, i, i, i, i, u64, u64]
         h.omldm_generate_sparse_batch.argtypes = [vp, i, i, i, i, u64, u64]
         h.omldm_parse_json_records.restype = i
@@ -53,17 +56,28 @@ def _h():
 
 
 class Topic:
-    """Ring of `n_slots` batches of `batch` staged rows with `d` features."""
+    """Ring of `n_slots` batches of `batch` staged rows with `d` features.
 
-    def __init__(self, d: int, batch: int, n_slots: int = 8, pin: Optional[bool] = None):
-        self.d, self.batch, self.n_slots = d, batch, n_slots
+    `wire="f16"` keeps the slots in the compact wire format instead ([fp16 x d | pad | fp32 target],
+    `wire_f16_pitch(d)` halves per record): half the bytes per record on the host->device link, expanded to
+    staged fp32 rows on the GPU (`Engine.train_batch_host` recognises the dtype)."""
+
+    def __init__(self, d: int, batch: int, n_slots: int = 8, pin: Optional[bool] = None, wire: str = "f32"):
+        if wire not in ("f32", "f16"):
+            raise ValueError("wire must be 'f32' or 'f16'")
+        self.d, self.batch, self.n_slots, self.wire = d, batch, n_slots, wire
         self.ld = pad32(d + 2)
-        self.storage = torch.zeros(n_slots, batch, self.ld, dtype=torch.float32)
+        if wire == "f16":
+            self.wire_ld = wire_f16_pitch(d)
+            self.storage = torch.zeros(n_slots, batch, self.wire_ld, dtype=torch.float16)
+        else:
+            self.wire_ld = self.ld
+            self.storage = torch.zeros(n_slots, batch, self.ld, dtype=torch.float32)
         if pin is None:
             pin = torch.cuda.is_available()
         if pin:
             self.storage = self.storage.pin_memory()
-        self.slot_bytes = batch * self.ld * 4
+        self.slot_bytes = batch * self.wire_ld * self.storage.element_size()
         self._ring = _h().omldm_ring_create(self.storage.data_ptr(), n_slots, self.slot_bytes)
         if not self._ring:
             raise RuntimeError("ring creation failed")
@@ -72,8 +86,8 @@ class Topic:
     # ---- producer side -------------------------------------------------------------------------
     def start_synthetic(self, kind: int, seed: int = 0, n_aux: int = 0, mode: int = MODE_GENERATE,
                         max_batches: int = -1, n_threads: int = 1) -> None:
-        self._producer = _h().omldm_producer_start(self._ring, kind, self.d, self.ld, self.batch, n_aux, seed, mode,
-                                                   max_batches, n_threads)
+        self._producer = _h().omldm_producer_start_wire(self._ring, kind, self.d, self.ld, self.batch, n_aux, seed,
+                                                        mode, max_batches, n_threads, 1 if self.wire == "f16" else 0)
         if not self._producer:
             raise RuntimeError("producer start failed")
 
@@ -83,6 +97,8 @@ class Topic:
         if s < 0:
             return False
         n = rows.shape[0]
+        if self.wire == "f16" and rows.dtype != torch.float16:
+            rows = pack_wire_f16(rows, self.d)
         self.storage[s, :n].copy_(rows)
         if n < self.batch:
             self.storage[s, n:].zero_()
@@ -138,7 +154,7 @@ class SparseTopic(Topic):
 
     def __init__(self, d: int, batch: int, nnz: int, n_slots: int = 8, pin: Optional[bool] = None):
         self.d, self.batch, self.nnz, self.n_slots = d, batch, nnz, n_slots
-        self.ld = nnz
+        self.ld, self.wire = nnz, "f32"
         self.slot_bytes = batch * (2 * nnz + 1) * 4
         self.storage = torch.zeros(n_slots, self.slot_bytes, dtype=torch.uint8)
         if pin is None:
@@ -172,8 +188,14 @@ def generate_sparse_batch(d: int, batch: int, nnz: int, n_aux: int = 10, seed: i
 
 
 def generate_batch(kind: int, d: int, batch: int, seed: int = 0, batch_index: int = 0, n_aux: int = 0,
-                   pin: bool = False) -> torch.Tensor:
-    """One synthetic staged batch [batch, pad32(d+2)] on the host."""
+                   pin: bool = False, wire: str = "f32") -> torch.Tensor:
+    """One synthetic staged batch [batch, pad32(d+2)] on the host (`wire="f16"`: compact wire rows)."""
+    if wire == "f16":
+        out = torch.empty(batch, wire_f16_pitch(d), dtype=torch.float16)
+        if pin and torch.cuda.is_available():
+            out = out.pin_memory()
+        _h().omldm_generate_batch_f16(out.data_ptr(), kind, d, batch, n_aux, seed, batch_index)
+        return out
     ld = pad32(d + 2)
     out = torch.empty(batch, ld, dtype=torch.float32)
     if pin and torch.cuda.is_available():
