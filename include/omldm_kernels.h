@@ -217,6 +217,17 @@ int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stre
 int omldm_query_reduce(const omldm_comm* comm_host, const float* vals4, float* out4, uint32_t epoch,
                        void* stream);
 
+/* Ridge refresh without a factorisation (no counterpart in the reference): solve (A + lam I) x = b by
+ * Jacobi-preconditioned conjugate gradients started from the content of x.  A: n x n, symmetric, FULL storage,
+ * pitch ld floats; b: n floats with stride b_stride (a column of the same matrix is fine); n <= 4096.
+ * work: omldm_ridge_cg_work_floats(n) floats; scalars: omldm_ridge_cg_scalar_bytes(max_iter) bytes, 32-byte
+ * aligned; info <- (iterations done, ||r|| / ||b||).  One cooperative launch of `blocks` CTAs (0 = 32),
+ * stops at ||r|| <= tol ||b||, after max_iter (<= 128) iterations, or when p.Ap <= 0. */
+size_t omldm_ridge_cg_work_floats(int n);
+size_t omldm_ridge_cg_scalar_bytes(int max_iter);
+int omldm_ridge_cg(const float* A, int ld, int n, float lam, const float* b, int b_stride, float* x, float* work,
+                   void* scalars, int max_iter, float tol, float* info, int blocks, void* stream);
+
 /* CUDA IPC plumbing for the symmetric arena (one dedicated, zero-filled cudaMalloc per region) */
 int omldm_dev_malloc(size_t bytes, void** out);
 int omldm_dev_free(void* p);

@@ -217,6 +217,16 @@ class GpuORR(GpuLearner):
         self._pending = None
         self._install_at = 0
         self._w_next = None
+        # weight refresh: "cholesky" (cuSOLVER, ~0.6 ms at d = 1000) or "cg" (warm-started preconditioned
+        # conjugate gradients, csrc/ridge_cg.cu; falls back to Cholesky when it does not converge)
+        self.solver = str(_h(hyper, ["solver"], "cholesky")).lower()
+        self.cg_iters = int(_h(hyper, ["cgMaxIter"], 32))
+        self.cg_tol = float(_h(hyper, ["cgTol"], 1e-5))
+        self.cg_failures = 0
+        self.cg_last = (0, 0.0)          # (iterations, relative residual) of the last checked CG refresh
+        self._cg = None
+        self._cg_host = None
+        self._cg_evt = None
 
     def n_flat(self, d):
         ld = F.pad32(d + 2)
@@ -300,10 +310,18 @@ class GpuORR(GpuLearner):
             return
         torch.add(self.G, self.dG, out=self._work)
 
-    def _solve_into(self, out: torch.Tensor) -> None:
-        """out <- (G_A + lambda I)^-1 G_b by Cholesky on the mirrored upper triangle of _work."""
+    def _solve_into(self, out: torch.Tensor, use_cg: bool = False) -> None:
+        """out <- (G_A + lambda I)^-1 G_b from the mirrored upper triangle of _work: Cholesky, or CG started
+        from the current weights."""
         d1 = self.d + 1
         F.mirror_upper(self._work, self.d + 2)
+        if use_cg:
+            if self._cg is None:
+                self._cg = F.ridge_cg_workspace(d1, self.device, self.cg_iters)
+            if out.data_ptr() != self.wt.data_ptr():
+                out.copy_(self.wt[:d1])
+            F.ridge_cg(self._work, d1, self.lam, out, *self._cg, max_iter=self.cg_iters, tol=self.cg_tol)
+            return
         A = self._work[:d1, :d1].clone()
         A.diagonal().add_(self.lam)
         b = self._work[:d1, d1].clone()
@@ -315,11 +333,28 @@ class GpuORR(GpuLearner):
         mini-batches; the result is installed a few steps later (`_install_at`)."""
         if self._pending is not None:
             self._install()
+        use_cg = self.solver == "cg"
+        if use_cg and self._cg_evt is not None and self._cg_evt.query():
+            # verdict of the previous CG refresh, read without waiting: a refresh that did not reach the
+            # tolerance is repeated by Cholesky now, three of them switch the solver for good
+            self._cg_evt = None
+            self.cg_last = (int(self._cg_host[0]), float(self._cg_host[1]))
+            if not self.cg_last[1] <= 100.0 * self.cg_tol:
+                self.cg_failures += 1
+                use_cg = False
+                if self.cg_failures >= 3:
+                    self.solver = "cholesky"
         main = torch.cuda.current_stream(self.device)
         self._snapshot()                      # consistent copy, ordered with the Gram / sync kernels
         self._side.wait_stream(main)
         with torch.cuda.stream(self._side):
-            self._solve_into(self._w_next)
+            self._solve_into(self._w_next, use_cg)
+            if use_cg:
+                if self._cg_host is None:
+                    self._cg_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+                self._cg_host.copy_(self._cg[2], non_blocking=True)
+                self._cg_evt = torch.cuda.Event()
+                self._cg_evt.record(self._side)
             ev = torch.cuda.Event()
             ev.record(self._side)
         self._pending = ev
@@ -338,7 +373,15 @@ class GpuORR(GpuLearner):
             self._install()
         d1 = self.d + 1
         self._snapshot()
-        self._solve_into(self.wt[:d1])
+        if self.solver == "cg":
+            self._solve_into(self.wt[:d1], True)
+            it, rel = self._cg[2].tolist()
+            self.cg_last = (int(it), rel)
+            if not rel <= 100.0 * self.cg_tol:            # did not converge (or NaN): direct solve instead
+                self.cg_failures += 1
+                self._solve_into(self.wt[:d1])
+        else:
+            self._solve_into(self.wt[:d1])
         if not bool(torch.isfinite(self.wt).all()):      # ill-conditioned in fp32: redo in fp64
             A = self._work[:d1, :d1].double()
             A.diagonal().add_(self.lam)

@@ -433,6 +433,49 @@ def mirror_upper(A: torch.Tensor, n: int) -> None:
     A[:n, :n] = torch.triu(A[:n, :n]) + iu.t()
 
 
+def ridge_cg_workspace(n: int, device, max_iter: int = 32):
+    """(work floats, scalar block, info[2]) for `ridge_cg`; allocate once, reuse for every refresh."""
+    work = torch.empty(5 * n, dtype=torch.float32, device=device)
+    scal = torch.zeros(4 * (max_iter + 2), dtype=torch.float64, device=device)
+    info = torch.zeros(2, dtype=torch.float32, device=device)
+    return work, scal, info
+
+
+def ridge_cg(W: torch.Tensor, n: int, lam: float, x: torch.Tensor, work: torch.Tensor, scal: torch.Tensor,
+             info: torch.Tensor, max_iter: int = 32, tol: float = 1e-5, blocks: int = 32) -> None:
+    """Solve (A + lam I) x = b in place in `x` (its content is the starting point), where
+    A = W[:n, :n] (symmetric, full storage) and b = W[:n, n]: warm-started Jacobi-preconditioned
+    conjugate gradients, one cooperative kernel (csrc/ridge_cg.cu).  info <- (iterations, ||r|| / ||b||)."""
+    if native(W):
+        _lib.check(_k().omldm_ridge_cg(_p(W), _i(W.stride(0)), _i(n), _f(lam), ctypes.c_void_p(W.data_ptr() + 4 * n),
+                                       _i(W.stride(0)), _p(x), _p(work), _p(scal), _i(max_iter), _f(tol), _p(info),
+                                       _i(blocks), _lib.stream_ptr()), "ridge_cg")
+        return
+    A = W[:n, :n]
+    b = W[:n, n]
+    minv = 1.0 / torch.where(A.diagonal() + lam > 0, A.diagonal() + lam, torch.ones_like(A.diagonal()))
+    r = b - (A @ x[:n] + lam * x[:n])
+    z = minv * r
+    p = z.clone()
+    rz, rr = float(r.double() @ z.double()), float(r.double() @ r.double())
+    bb = float(b.double() @ b.double()) or 1.0
+    it = 0
+    while it < max_iter and rr > tol * tol * bb:
+        q = A @ p + lam * p
+        pq = float(q.double() @ p.double())
+        if not pq > 0.0:
+            break
+        alpha = rz / pq
+        x[:n] += alpha * p
+        r = r - alpha * q
+        z = minv * r
+        rz_new, rr = float(r.double() @ z.double()), float(r.double() @ r.double())
+        p = z + (rz_new / rz if rz > 0 else 0.0) * p
+        rz = rz_new
+        it += 1
+    info[0], info[1] = float(it), (rr / bb) ** 0.5
+
+
 # ------------------------------------------------------------------------------ k-means
 def kmeans_assign(Z, d, S, cnorm, K, T, stats, assign=None) -> None:
     B = Z.shape[0]
