@@ -14,14 +14,13 @@ this; requests are broadcast exactly like PipelineMap.scala:54-57 does).
 """
 from __future__ import annotations
 
-import json
 import time
 from typing import Any, Dict, List, Optional, Union
 
 import torch
 
 from .api.bucketing import bucket_response
-from .api.pojos import (DataInstance, JobStatistics, Prediction, QueryResponse, Request, Statistics)
+from .api.pojos import DataInstance, JobStatistics, Prediction, Request, Statistics
 from .api.registry import PipelineMap
 from .models.pipeline import GpuPipeline
 from .ops import functional as F

@@ -13,7 +13,6 @@ The maths mirrors `omldm_b200/oracle/learners.py` (fp64 oracle); kernels are in 
 """
 from __future__ import annotations
 
-import math
 from typing import Any, Dict, Optional
 
 import numpy as np

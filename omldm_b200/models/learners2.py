@@ -1,7 +1,6 @@
 """Device learners, part 2: k-means, multiclass PA, neural network, Hoeffding tree (see learners.py)."""
 from __future__ import annotations
 
-import math
 from typing import Optional
 
 import numpy as np

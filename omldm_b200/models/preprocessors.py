@@ -1,9 +1,8 @@
 """Device preprocessors on staged rows (whitelist PipelineMap.scala:67; kernels csrc/preprocess.cu)."""
 from __future__ import annotations
 
-from typing import Any, Dict, Optional, Tuple
+from typing import Any, Dict, Optional
 
-import numpy as np
 import torch
 
 from ..ops import functional as F

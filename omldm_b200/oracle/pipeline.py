@@ -8,7 +8,7 @@ In the reference the test set belongs to the spoke and is shared by its pipeline
 from __future__ import annotations
 
 from collections import deque
-from typing import Any, Deque, Dict, List, Optional, Tuple
+from typing import Deque, List, Optional, Tuple
 
 import numpy as np
 

@@ -19,7 +19,6 @@ from typing import Optional
 import torch
 
 from ..ops import _lib
-from ..ops.functional import native
 from .comm import PipelineComm
 from .host_protocols import cfg
 

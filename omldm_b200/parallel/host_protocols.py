@@ -23,7 +23,7 @@ from typing import Any, Dict, List, Optional, Tuple
 
 import numpy as np
 
-from ..api.pojos import DataInstance, Prediction, QueryResponse, Request
+from ..api.pojos import Prediction, Request
 from ..messages import NodeId, NodeType, RemoteCallIdentifier
 from ..oracle.pipeline import OraclePipeline
 

@@ -12,7 +12,7 @@ from collections import deque
 from typing import Any, Callable, Deque, Dict, Generic, List, Optional, TypeVar
 
 from ..api.bucketing import bucket_response
-from ..api.pojos import Prediction, QueryResponse
+from ..api.pojos import QueryResponse
 from ..messages import (HubMessage, NetworkDescriptor, NodeId, NodeType, RemoteCallIdentifier, SpokeMessage)
 
 T = TypeVar("T")

@@ -8,7 +8,7 @@ test mode :88-157), `generateHub` :166-195; state/StateAccumulators.scala:128-17
 from __future__ import annotations
 
 from collections import deque
-from typing import Any, Callable, Deque, Dict, Optional
+from typing import Any, Callable, Deque, Optional
 
 from ..api.pojos import Statistics
 from ..messages import HubMessage, NodeId, NodeType, SpokeMessage

@@ -10,7 +10,6 @@ the GPU engine (`omldm_b200/engine.py`) offers the same request/response surface
 """
 from __future__ import annotations
 
-import json
 import time
 from collections import deque
 from typing import Any, Callable, Deque, Dict, Iterable, List, Optional, Union

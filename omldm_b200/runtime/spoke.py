@@ -12,7 +12,7 @@ under SingleLearner the hub is created by worker 0 like for every other protocol
 from __future__ import annotations
 
 import copy
-from typing import Any, Callable, Dict, List, Optional
+from typing import Any, Callable, Dict, List
 
 import numpy as np
 

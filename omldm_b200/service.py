@@ -21,7 +21,6 @@ import threading
 import time
 from typing import Dict, List, Optional
 
-import torch
 
 from .utils.config import TOPICS, JobParameters
 

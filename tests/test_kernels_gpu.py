@@ -1,5 +1,4 @@
 """Each CUDA kernel against the plain-PyTorch implementation of the same op (fp32/fp64 reference)."""
-import numpy as np
 import pytest
 import torch
 

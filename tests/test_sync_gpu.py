@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from omldm_b200.ops import _lib
-from omldm_b200.parallel.comm import PAD_FGM, PAD_PHI, PAD_STATUS, PipelineComm
+from omldm_b200.parallel.comm import PAD_FGM, PAD_PHI, PipelineComm
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
