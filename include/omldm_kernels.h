@@ -217,6 +217,22 @@ int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stre
 int omldm_query_reduce(const omldm_comm* comm_host, const float* vals4, float* out4, uint32_t epoch,
                        void* stream);
 
+/* Sparse records against a dense model (BASELINE config 5; no counterpart in the reference, whose MultiClassPA
+ * works on dense Breeze vectors out of tree).  A sparse row has pitch ld floats (multiple of 32, >= 2 nnz + 2):
+ * [int32 column index bits x nnz | value x nnz | valid (1.0; 0 = empty row) | target | 0-pad], i.e. a staged row
+ * with the pseudo feature count 2 nnz, so omldm_holdout_swap applies unchanged.
+ * omldm_sparse_rows      : ELL slot (idx[B nnz], val[B nnz], target[B]) -> sparse rows.
+ * omldm_mcpa_sparse_step : mini-batch MultiClassPA (2 <= C <= 32): per record scores by gathering W[c, idx],
+ *   rival / hinge loss / step size and the statistics of omldm_mcpa_coef, then W[y, idx] += s tau v,
+ *   W[rival, idx] -= s tau v (+ bias column d) with red.add; s = 1 / (#active records of this call) when
+ *   mean_update (active_before = copy of stats[3] taken before the call).  coef: B x 4 floats scratch, 16-byte
+ *   aligned.  Duplicate column indices accumulate in the scores / update; the step size uses sum v^2. */
+int omldm_sparse_rows(const int* idx, const float* val, const float* targets, int B, int nnz, float* rows, int ld,
+                      void* stream);
+int omldm_mcpa_sparse_step(const float* rows, int ld, int B, int nnz, float* W, int ldw, int d, int C, int variant,
+                           float Creg, float* coef, double* stats, const double* active_before, int mean_update,
+                           void* stream);
+
 /* Ridge refresh without a factorisation (no counterpart in the reference): solve (A + lam I) x = b by
  * Jacobi-preconditioned conjugate gradients started from the content of x.  A: n x n, symmetric, FULL storage,
  * pitch ld floats; b: n floats with stride b_stride (a column of the same matrix is fine); n <= 4096.

@@ -72,6 +72,12 @@ class Engine:
         self.use_priority_stream = str(self.params.extra.get("priorityStream", "false")).lower() in ("1", "true", "yes")
         self._multi_key = None
         self._multi_desc = None
+        # sparse streams: train straight from the sparse rows when every pipeline can (csrc/sparse_mcpa.cu)
+        # instead of rebuilding the dense batch each step; opt-in until measured on hardware
+        self.sparse_direct = str(self.params.extra.get("sparseDirect", "false")).lower() in ("1", "true", "yes")
+        self._sparse_nnz: Optional[int] = None
+        self._srows: List[Optional[torch.Tensor]] = [None, None]
+        self._srows_i = 0
 
     # ============================================================================ control plane
     def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
@@ -148,6 +154,8 @@ class Engine:
         if self.holdout is None:
             return torch.zeros(0, 1, device=self.device)
         n = min(F.holdouts_before(self.count), self.holdout.shape[0])
+        if self._sparse_nnz is not None:      # the ring holds sparse rows: score on their dense form
+            return F.sparse_rows_to_dense(self.holdout[:n], self._sparse_nnz, self.d)
         return self.holdout[:n]
 
     def train_batch(self, Z: torch.Tensor, d: Optional[int] = None, **kw) -> None:
@@ -172,6 +180,12 @@ class Engine:
             raise ValueError(f"batch is on {Z.device}, engine on {self.device}; use train_batch_host for host batches")
         if self.d is not None and self.d != d:
             raise ValueError(f"this stream has {self.d} features, got d = {d}")
+        if self._sparse_nnz is not None:
+            raise ValueError("this engine trains from sparse rows (sparseDirect); dense batches cannot be mixed in")
+        self._train_rows(Z, d, None, **kw)
+
+    def _train_rows(self, Z: torch.Tensor, d: int, nnz: Optional[int], **kw) -> None:
+        """One step on validated rows: staged dense rows, or sparse rows when `nnz` is given."""
         self.d = d
         now = time.monotonic()
         if self.t_first is None:
@@ -180,14 +194,14 @@ class Engine:
         for p in self.pipelines.values():
             if p.protocol != "SingleLearner" or self.rank == 0:
                 self._build(p, d)
-        key = (Z.data_ptr(), B, ld) + tuple(p.driver.graph_key() for p in self.pipelines.values()
-                                            if p.built and hasattr(p.driver, "graph_key"))
+        key = (Z.data_ptr(), B, ld, nnz) + tuple(p.driver.graph_key() for p in self.pipelines.values()
+                                                 if p.built and hasattr(p.driver, "graph_key"))
         g = None
         if self.use_graphs and not kw and self._graphable(Z):
             g = self._graphs.get(key)
             if g is None and self._seen.get(key, 0) >= self.graph_after:
                 try:
-                    g = self._capture(key, Z, d)
+                    g = self._capture(key, Z, d, nnz)
                 except Exception as e:      # never lose a job over an optimisation: fall back to eager steps
                     import warnings
                     warnings.warn(f"CUDA graph capture failed ({e}); continuing with eager launches")
@@ -210,7 +224,7 @@ class Engine:
                 _lib.add_launch_count(self._graph_launches[key])
             else:
                 self._seen[key] = self._seen.get(key, 0) + 1
-                self._device_step(Z, d, **kw)
+                self._device_step(Z, d, nnz, **kw)
         finally:
             if hp is not None:
                 ctx.__exit__(None, None, None)
@@ -235,20 +249,22 @@ class Engine:
             return False
         return all(p.graph_safe() for p in self.pipelines.values())
 
-    def _capture(self, key, Z: torch.Tensor, d: int):
+    def _capture(self, key, Z: torch.Tensor, d: int, nnz: Optional[int] = None):
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
         before = _lib.launch_count()
         with torch.cuda.graph(g):
-            self._device_step(Z, d)
+            self._device_step(Z, d, nnz)
         self._graph_launches[key] = _lib.launch_count() - before
         _lib.add_launch_count(-self._graph_launches[key])   # capture does not execute anything
         self._graphs[key] = g
         return g
 
-    def _device_step(self, Z: torch.Tensor, d: int, **kw) -> None:
+    def _device_step(self, Z: torch.Tensor, d: int, nnz: Optional[int] = None, **kw) -> None:
         """All device work of one training step, in stream order."""
         B, ld = Z.shape
+        if nnz is not None:
+            kw = dict(kw, nnz=nnz)
         for p in self.pipelines.values():
             if p.built and hasattr(p.driver, "begin_step"):
                 p.driver.begin_step()          # fork: overlapped all-reduce of the previous step's delta
@@ -261,7 +277,7 @@ class Engine:
             else:
                 F.holdout_swap(Z, self.holdout, d, self.count)
         n_pipes = len(self.pipelines)
-        batched = self._batched_exact_fit(Z, d)
+        batched = self._batched_exact_fit(Z, d) if nnz is None else ()
         for p in self.pipelines.values():
             due = p.built and (p.driver._batches % p.driver.sync_every == p.driver.sync_every - 1)
             if p in batched:
@@ -368,6 +384,20 @@ class Engine:
         see stream.ring.SparseTopic): densify on the GPU (csrc/ingest.cu), then the normal step."""
         from .stream.ring import SparseTopic
         idx, val, tgt = SparseTopic.unpack(slot, batch, nnz)
+        if self.sparse_direct and self._sparse_capable(d):
+            if self.holdout is not None and self._sparse_nnz is None:
+                raise ValueError("this engine already trained on dense batches; sparseDirect cannot be mixed in")
+            if self.d is not None and self.d != d:
+                raise ValueError(f"this stream has {self.d} features, got d = {d}")
+            i = self._srows_i
+            self._srows_i ^= 1
+            shape = (batch, F.sparse_row_pitch(nnz))
+            if self._srows[i] is None or self._srows[i].shape != shape:
+                self._srows[i] = torch.empty(shape, dtype=torch.float32, device=self.device)
+            self._sparse_nnz = nnz
+            F.sparse_rows(idx, val, tgt, batch, nnz, out=self._srows[i])
+            self._train_rows(self._srows[i], d, nnz)
+            return
         key = (batch, nnz, d)
         if self._sparse_key != key:
             self._sparse_key = key
@@ -379,6 +409,11 @@ class Engine:
         self._dense_i ^= 1
         F.densify(self._indptr, idx, val, tgt, d, out=Z, sq_out=self._sqn)
         self.train_batch(Z, d)
+
+    def _sparse_capable(self, d: int) -> bool:
+        """Every pipeline can consume sparse rows (no preprocessors, a learner with a sparse step)."""
+        ps = list(self.pipelines.values())
+        return bool(ps) and all(p.sparse_capable() for p in ps)
 
     def train_sparse_host(self, slot_host: torch.Tensor, batch: int, nnz: int, d: int) -> torch.Tensor:
         """e2e sparse step: pinned host slot -> H2D (a few hundred KB instead of the dense batch) ->
@@ -497,10 +532,12 @@ class Engine:
         return {"rank": self.rank, "world": self.world, "count": self.count, "d": self.d,
                 "registry": self.pipeline_map.state_dict(),
                 "holdout": None if self.holdout is None else self.holdout.cpu().clone(),
+                "sparse_nnz": self._sparse_nnz,
                 "pipelines": {pid: p.state_dict() for pid, p in self.pipelines.items()}}
 
     def load_state_dict(self, sd: dict) -> None:
         self.count, self.d = sd["count"], sd["d"]
+        self._sparse_nnz = sd.get("sparse_nnz")
         self._count_dev = None
         self._graphs, self._seen = {}, {}
         self.pipeline_map.load_state_dict(sd["registry"])

@@ -130,6 +130,7 @@ class GpuMultiClassPA(GpuLearner):
     def _init(self):
         self.W = self.buf.view(self.n_classes, self.ld)
         self._T = None
+        self._coef = None
         self._act = torch.zeros(1, device=self.device)
 
     def _bufs(self, B):
@@ -155,6 +156,26 @@ class GpuMultiClassPA(GpuLearner):
 
     def graph_ready(self):
         return self.mode != "exact"
+
+    def supports_sparse(self) -> bool:
+        return self.mode != "exact" and 2 <= self.n_classes <= 32
+
+    def fit_sparse(self, rows, nnz):
+        """Mini-batch step straight from sparse rows (csrc/sparse_mcpa.cu): gathers and scatters against the
+        dense model instead of two GEMMs over a rebuilt dense batch."""
+        if rows.is_cuda and F.native(rows):
+            B = rows.shape[0]
+            if self._coef is None or self._coef.shape[0] < B:
+                self._coef = torch.empty(B, 4, device=self.device)
+            prev = self.stats[3].clone()
+            F.mcpa_sparse_step(rows, nnz, self.W, self.d, self.n_classes, self.variant, self.C, self._coef,
+                               self.stats, prev, self.mean_update)
+            return
+        Z = F.sparse_rows_to_dense(rows, nnz, self.d)
+        col = rows[:, :nnz].contiguous().view(torch.int32)
+        v = rows[:, nnz:2 * nnz]
+        sq = torch.where((col >= 0) & (col < self.d), v * v, torch.zeros_like(v)).sum(1) + 1.0
+        self._step(Z, sq)
 
     def fit_batch(self, Z, sqnorm=None):
         if self.mode == "exact":

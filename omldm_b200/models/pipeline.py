@@ -110,10 +110,18 @@ class GpuPipeline:
         self.device_train(Z, protect_input, due, **kw)
         self.host_tick()
 
-    def device_train(self, Z: torch.Tensor, protect_input: bool, sync_due: bool, skip_fit: bool = False, **kw) -> None:
+    def sparse_capable(self) -> bool:
+        """Can train straight from sparse rows (Engine.train_sparse with `sparseDirect`)."""
+        return (not self.preprocessors and self.protocol != "SingleLearner"
+                and getattr(self.learner, "supports_sparse", lambda: False)())
+
+    def device_train(self, Z: torch.Tensor, protect_input: bool, sync_due: bool, skip_fit: bool = False,
+                     nnz: Optional[int] = None, **kw) -> None:
         """Device work of one step (graph-capturable when `graph_safe()`).  `skip_fit`: the learner
-        update was already done by a batched multi-pipeline launch."""
-        if not skip_fit and self._fusable():
+        update was already done by a batched multi-pipeline launch.  `nnz`: Z holds sparse rows."""
+        if nnz is not None:
+            self.learner.fit_sparse(Z, nnz)
+        elif not skip_fit and self._fusable():
             # PolynomialFeatures -> StandardScaler -> mini-batch linear learner: two passes over the raw
             # rows, the expanded features only ever exist in registers (csrc/fused_pipeline.cu)
             from ..ops import functional as F

@@ -433,6 +433,58 @@ def mirror_upper(A: torch.Tensor, n: int) -> None:
     A[:n, :n] = torch.triu(A[:n, :n]) + iu.t()
 
 
+# ------------------------------------------------------------------------------ sparse rows (config 5)
+def sparse_row_pitch(nnz: int) -> int:
+    return pad32(2 * nnz + 2)
+
+
+def sparse_rows(idx: torch.Tensor, val: torch.Tensor, tgt: torch.Tensor, batch: int, nnz: int,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """ELL slot (idx[B*nnz] int32, val[B*nnz], target[B]) -> sparse rows [B, pad32(2 nnz + 2)]:
+    [index bits | values | valid = 1 | target | 0-pad].  With the pseudo feature count 2*nnz these obey the
+    staged-row conventions (valid flag in column d, target in d + 1), so the holdout kernel applies as is."""
+    ld = sparse_row_pitch(nnz)
+    rows = out if out is not None else torch.empty(batch, ld, dtype=torch.float32, device=idx.device)
+    if native(idx):
+        _lib.check(_k().omldm_sparse_rows(_p(idx), _p(val), _p(tgt), _i(batch), _i(nnz), _p(rows), _i(ld),
+                                          _lib.stream_ptr()), "sparse_rows")
+        return rows
+    rows.zero_()
+    rows[:, :nnz] = idx.view(batch, nnz).view(torch.float32)
+    rows[:, nnz:2 * nnz] = val.view(batch, nnz)
+    rows[:, 2 * nnz] = 1.0
+    rows[:, 2 * nnz + 1] = tgt
+    return rows
+
+
+def sparse_rows_to_dense(rows: torch.Tensor, nnz: int, d: int) -> torch.Tensor:
+    """Sparse rows -> staged dense rows [B, pad32(d + 2)] (duplicate indices accumulate, out-of-range ones are
+    dropped, empty rows stay empty).  Used for holdout scoring and as the reference of the sparse kernels."""
+    B = rows.shape[0]
+    Z = torch.zeros(B, pad32(d + 2), dtype=torch.float32, device=rows.device)
+    if B == 0:
+        return Z
+    col = rows[:, :nnz].contiguous().view(torch.int32).long()
+    v = rows[:, nnz:2 * nnz]
+    ok = (col >= 0) & (col < d)
+    Z.scatter_add_(1, torch.where(ok, col, torch.zeros_like(col)), torch.where(ok, v, torch.zeros_like(v)))
+    valid = rows[:, 2 * nnz] != 0
+    Z[:, d] = valid.float()
+    Z[:, d + 1] = rows[:, 2 * nnz + 1]
+    Z[~valid] = 0.0
+    return Z
+
+
+def mcpa_sparse_step(rows: torch.Tensor, nnz: int, W: torch.Tensor, d: int, C: int, variant: int, Creg: float,
+                     coef: torch.Tensor, stats: torch.Tensor, active_before: torch.Tensor, mean_update: bool) -> None:
+    """One mini-batch MultiClassPA step from sparse rows against the dense model W[C, ldw]
+    (csrc/sparse_mcpa.cu).  CUDA only; callers on CPU densify and use the dense step."""
+    B = rows.shape[0]
+    _lib.check(_k().omldm_mcpa_sparse_step(_p(rows), _i(rows.stride(0)), _i(B), _i(nnz), _p(W), _i(W.stride(0)), _i(d),
+                                           _i(C), _i(variant), _f(Creg), _p(coef), _p(stats), _p(active_before),
+                                           _i(1 if mean_update else 0), _lib.stream_ptr()), "mcpa_sparse_step")
+
+
 def ridge_cg_workspace(n: int, device, max_iter: int = 32):
     """(work floats, scalar block, info[2]) for `ridge_cg`; allocate once, reuse for every refresh."""
     work = torch.empty(5 * n, dtype=torch.float32, device=device)

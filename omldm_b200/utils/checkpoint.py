@@ -135,6 +135,7 @@ def merge_engine_states(states):
         while count > 0 and min(holdouts_before(count), cap) > m:   # never expose unfilled ring rows as valid
             count -= 1
     out = {"rank": first["rank"], "world": first["world"], "count": count, "d": first["d"],
+           "sparse_nnz": first.get("sparse_nnz"),
            "registry": first["registry"], "holdout": ring, "pipelines": {}}
     for pid in first["pipelines"]:
         out["pipelines"][pid] = _merge_pipeline([s["pipelines"][pid] for s in states if pid in s["pipelines"]])
