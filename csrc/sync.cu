@@ -335,11 +335,12 @@ __global__ void __launch_bounds__(256) sync_easgd_kernel(Comm c, size_t n, float
 //                  psi >= eps_psi * k * phi(0) ends the round (allreduce + reset), otherwise a new
 //                  sub-round starts with the smaller quantum.
 // Hub = rank 0's pad.  FGM words: [0] counter(s32) [1] subround id [2] theta bits [3] round id
-// (mirrored into every pad) [4] first step number at which the announced round end is acted on (every pad).
+// (mirrored into every pad) [4] the hub's step number when it announced the round (every pad)
+// [5] terminate word of the current flush generation (every pad).  Hub pad, VOTE words: per-rank "draining" marks.
 // state_local (float[8], private): [0] round id [1] subround seen [2] zeta [3] counts sent [4] rounds [5] subrounds
 __global__ void __launch_bounds__(256)
 sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, int mode, float threshold,
-                float eps_psi, uint32_t step_arg, float* state_base) {
+                float eps_psi, uint32_t step_arg, float* state_base, uint32_t drain) {
   const int me = my_rank(c);
   const int k = c.world;
   uint32_t* loc = my_local(c);
@@ -358,16 +359,15 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
       loc[L_STEP] = step;
       const float phi = sqrtf(nrm2) + phi0;
       uint32_t round = static_cast<uint32_t>(st[0]);
-      // Round-end flag is sampled BEFORE this step's hub logic, and a round declared by the hub during
-      // its step s carries "act at step s+1" (word 4): a rank that happens to sample the flag after the
-      // hub wrote it within the same step number still waits one step, so ranks that advance in
-      // lock-step all take the same branch (a rank that runs ahead acts as soon as it sees the flag).
+      // Round-end flag is sampled BEFORE this step's hub logic, and a round announced by the hub in ITS
+      // step s (word 4) is not executed by a rank whose own step number is s: ranks that advance in
+      // lock-step (one launch for all emulated ranks) then all execute it in step s+1, whether they sampled
+      // the flag before or after the hub wrote it; everybody else acts at first sight.
       const uint32_t seen_round = ld_acquire_sys(c.pads[me] + OMLDM_PAD_FGM + 3);
       bool act = false;
-      if (seen_round != round) {
-        const uint32_t act_step = ld_relaxed_sys(c.pads[me] + OMLDM_PAD_FGM + 4);
-        act = static_cast<int32_t>(step - act_step) >= 0;
-      }
+      if (seen_round != round) act = step != ld_relaxed_sys(c.pads[me] + OMLDM_PAD_FGM + 4);
+      // end of stream (flush generation `drain`): tell the hub this rank has no more data
+      if (drain) st_release_sys(c.pads[0] + OMLDM_PAD_VOTE + me, drain);
       // publish phi to the hub (push-based polling)
       asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + me), "r"(__float_as_uint(phi)) : "memory");
       const uint32_t sub = ld_acquire_sys(hub + 1);
@@ -388,12 +388,18 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
         // hub logic
         const int counter = static_cast<int>(ld_relaxed_sys(hub));
         const uint32_t hub_round = ld_relaxed_sys(hub + 3);
-        if (counter > k && hub_round == round && seen_round == round) {
+        bool all_done = drain != 0u && hub_round == round && seen_round == round;
+        for (int i = 0; all_done && i < k; ++i) all_done = ld_acquire_sys(c.pads[0] + OMLDM_PAD_VOTE + i) == drain;
+        if (all_done) {
+          // everybody is draining and no round is open: terminate this flush generation (the hub is the only
+          // one that announces rounds, so nothing can be announced after this)
+          for (int p = 0; p < k; ++p) st_release_sys(c.pads[p] + OMLDM_PAD_FGM + 5, drain);
+        } else if (counter > k && hub_round == round && seen_round == round) {
           float psi = 0.f;
           for (int i = 0; i < k; ++i) psi += __uint_as_float(ld_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + i));
           if (psi >= eps_psi * k * phi0) {
             for (int p = 0; p < k; ++p)
-              asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[p] + OMLDM_PAD_FGM + 4), "r"(step + 1u) : "memory");
+              asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[p] + OMLDM_PAD_FGM + 4), "r"(step) : "memory");
             for (int p = 0; p < k; ++p) st_release_sys(c.pads[p] + OMLDM_PAD_FGM + 3, round + 1);  // round end
           } else {
             asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub + 2), "r"(__float_as_uint(-psi / (2.f * k))) : "memory");
@@ -591,7 +597,21 @@ extern "C" int omldm_sync_fgm(const omldm_comm* h, float* e_local, size_t n, flo
   blocks = clamp_blocks(blocks, n, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_fgm_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_fgm_kernel",
-                     c, e_local, n, n, scale, mode, threshold, eps_psi, step, state_local);
+                     c, e_local, n, n, scale, mode, threshold, eps_psi, step, state_local, 0u);
+}
+
+// End-of-stream step of flush generation `drain` (> 0): like omldm_sync_fgm, plus the drain handshake.
+extern "C" int omldm_sync_fgm_drain(const omldm_comm* h, float* e_local, size_t n, float scale, int mode,
+                                    float threshold, float eps_psi, uint32_t step, float* state_local,
+                                    uint32_t drain, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  if (!e_local || !state_local) return set_error_msg("sync_fgm_drain: e and the FGM state are required");
+  if (drain == 0u) return set_error_msg("sync_fgm_drain: the flush generation must be > 0");
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_fgm_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_fgm_kernel",
+                     c, e_local, n, n, scale, mode, threshold, eps_psi, step, state_local, drain);
 }
 
 extern "C" int omldm_device_barrier(const omldm_comm* h, uint32_t epoch, void* stream) {

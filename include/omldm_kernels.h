@@ -180,7 +180,7 @@ enum {
   OMLDM_PAD_CLOCK = 32,    /* [32,48)  SSP clocks                                   */
   OMLDM_PAD_VOTE = 48,     /* [48,64)  GM / FGM round votes                         */
   OMLDM_PAD_PHI = 64,      /* [64,80)  FGM phi values (float bits), hub = rank 0    */
-  OMLDM_PAD_FGM = 80,      /* [80,96)  FGM: counter, subround, theta, round id, act-at-step */
+  OMLDM_PAD_FGM = 80,      /* [80,96)  FGM: counter, subround, theta, round id, announce step, terminate */
   OMLDM_PAD_STATUS = 96,   /* [96,100) status bits: 1 barrier, 2 SSP, 4 FGM timeouts  */
   OMLDM_PAD_QUERY = 128,   /* [128,192) query scalars, 4 per peer                   */
   OMLDM_PAD_WORDS = 256
@@ -206,11 +206,19 @@ int omldm_sync_gm(const omldm_comm* comm_host, float* e_local, size_t n, float s
 /* FGM monitor step: phi = ||buf - e|| - sqrt(threshold), counter increments to the hub,
  * sub-round / round bookkeeping, and the round-end allreduce, all inside one kernel.
  * `state_local` : float[8] private FGM state of this rank (zero-initialised); `step` counts from 1.
- * A round the hub announces in its step s is executed by every rank in its first step >= s+1, so
- * ranks that make the same number of calls take the round-end branch in the same call. */
+ * A round the hub announces in its step s is executed by a rank in its first step whose number is not s, so
+ * ranks that advance in lock-step take the round-end branch in the same call and everybody else at first sight. */
 int omldm_sync_fgm(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
                    float threshold, float eps_psi, uint32_t step, float* state_local, int blocks,
                    void* stream);
+/* End of stream.  The round-end all-reduce waits for every rank inside the kernel, so a rank must not simply stop
+ * calling while peers may still announce a round.  Instead it keeps calling this entry point with the flush
+ * generation `drain` (1, 2, ... per flush, same on all ranks): the step marks the rank as draining at the hub;
+ * once the hub sees that mark from everybody and no round is open it writes `drain` into word OMLDM_PAD_FGM + 5
+ * of every pad.  Call, wait for the stream, read that word of the own pad, repeat until it equals `drain`. */
+int omldm_sync_fgm_drain(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
+                         float threshold, float eps_psi, uint32_t step, float* state_local, uint32_t drain,
+                         int blocks, void* stream);
 /* device barrier over the signal pads (termination probe, utils/statistics/StatisticsOperator.scala:135-142) */
 int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stream);
 /* query reduce: out4 = sum over ranks of vals4 (utils/ResponseConstructor.scala:43-52) */

@@ -34,14 +34,24 @@ PAD_WORDS = 256
 class FakeWorld:
     """The symmetric arena: per rank a signal pad, a model/delta buffer and a hub buffer."""
 
-    def __init__(self, k: int, n: int, spin_timeout_s: float = 5.0):
+    def __init__(self, k: int, n: int, spin_timeout_s: float = 5.0, jitter: float = 0.0, seed: int = 0):
+        """`jitter` > 0 makes every rank pause for a random time (up to `jitter` seconds) at the points where
+        the kernels touch peer memory, so repeated runs explore different interleavings."""
         self.k, self.n = k, n
+        self.jitter = jitter
+        self._rngs = [np.random.default_rng(seed * 1000 + r) for r in range(k)]
         self.pads = [np.zeros(PAD_WORDS, dtype=np.float64) for _ in range(k)]   # words hold ints or floats
         self.bufs = [np.zeros(n, dtype=np.float64) for _ in range(k)]
         self.hubs = [np.zeros(n, dtype=np.float64) for _ in range(k)]
         self.lock = threading.Lock()            # stands in for hardware atomics
         self.spin_timeout_s = spin_timeout_s
         self.ranks = [FakeRank(self, r) for r in range(k)]
+
+    def pause(self, r: int) -> None:
+        if self.jitter > 0.0:
+            g = self._rngs[r]
+            if g.random() < 0.5:
+                time.sleep(float(g.random()) * self.jitter)
 
     def shard(self, r: int):
         per = (self.n + self.k - 1) // self.k
@@ -76,6 +86,7 @@ class FakeRank:
 
     # ---- flag primitives -------------------------------------------------------------------------
     def _signal_all(self, base: int, seq: int) -> None:
+        self.w.pause(self.me)
         for p in range(self.w.k):                      # st.release.sys into every peer's pad
             self.w.pads[p][base + self.me] = seq
 
@@ -129,6 +140,7 @@ class FakeRank:
         w = self.w
         scale = (1.0 if mode == 1 else 1.0 / w.k) if scale is None else scale
         for owner in range(w.k):
+            w.pause(self.me)
             lo, hi = w.shard(owner)
             d = scale * (self.buf[lo:hi] - self.e[lo:hi]) if mode == 0 else scale * self.buf[lo:hi]
             with w.lock:                               # atom.add returning the old value
@@ -167,7 +179,11 @@ class FakeRank:
         pad0[PAD_FGM + 2] = math.sqrt(threshold) / 2.0
         pad0[PAD_PHI:PAD_PHI + 16] = -math.sqrt(threshold)
 
-    def fgm_step(self, threshold: float, eps_psi: float = 0.01, mode: int = 0, scale: Optional[float] = None) -> bool:
+    def fgm_step(self, threshold: float, eps_psi: float = 0.01, mode: int = 0, scale: Optional[float] = None,
+                 drain: int = 0) -> bool:
+        """One monitoring step.  `drain` = g > 0 marks an end-of-stream step of flush generation g: the rank
+        tells the hub it has no more data; once the hub has heard that from everybody and no round is open it
+        writes g into every pad's terminate word instead of evaluating the counters."""
         w, me, k, st = self.w, self.me, self.w.k, self.fgm
         scale = (1.0 if mode == 1 else 1.0 / k) if scale is None else scale
         hub = w.pads[0]
@@ -177,7 +193,13 @@ class FakeRank:
         phi = math.sqrt(float(d @ d)) + phi0
         rnd = st["round"]
         seen_round = int(w.pads[me][PAD_FGM + 3])      # sampled BEFORE this step's hub logic
-        act = seen_round != rnd and self.step >= int(w.pads[me][PAD_FGM + 4])   # "act at step s+1"
+        # a round announced by the hub in ITS step s is not executed by a rank whose own step number is s: ranks
+        # that advance in lock-step (one launch for all emulated ranks) then all execute it in step s+1, whether
+        # they sampled the flag before or after the hub wrote it; everybody else acts at first sight
+        act = seen_round != rnd and self.step != int(w.pads[me][PAD_FGM + 4])
+        w.pause(me)
+        if drain:
+            hub[PAD_VOTE + me] = drain                 # "no more data from me" (hub's pad only)
         hub[PAD_PHI + me] = phi                        # push-based polling
         sub = int(hub[PAD_FGM + 1])
         theta = hub[PAD_FGM + 2] if hub[PAD_FGM + 2] > 0 else -phi0 / 2.0
@@ -188,13 +210,18 @@ class FakeRank:
             with w.lock:
                 hub[PAD_FGM + 0] += ci - st["sent"]
             st["sent"] = ci
+        w.pause(me)
         if me == 0:
             counter, hub_round = int(hub[PAD_FGM + 0]), int(hub[PAD_FGM + 3])
-            if counter > k and hub_round == rnd and seen_round == rnd:
+            if (drain and hub_round == rnd and seen_round == rnd
+                    and all(int(hub[PAD_VOTE + i]) == drain for i in range(k))):
+                for p in range(k):
+                    w.pads[p][PAD_FGM + 5] = drain     # everybody is done and no round is open: terminate
+            elif counter > k and hub_round == rnd and seen_round == rnd:
                 psi = float(sum(hub[PAD_PHI + i] for i in range(k)))
                 if psi >= eps_psi * k * phi0:
                     for p in range(k):
-                        w.pads[p][PAD_FGM + 4] = self.step + 1
+                        w.pads[p][PAD_FGM + 4] = self.step
                     for p in range(k):
                         w.pads[p][PAD_FGM + 3] = rnd + 1      # round end, visible to every rank
                 else:
@@ -226,6 +253,17 @@ class FakeRank:
         st["round"], st["sub"], st["sent"] = rnd + 1, -1, 0
         st["rounds"] += 1
         return True
+
+    def fgm_flush(self, threshold: float, gen: int, eps_psi: float = 0.01, mode: int = 0, max_steps: int = 100000) -> int:
+        """End of stream (FGMDriver.flush): keep stepping in drain mode - joining any round that is still
+        announced - until the hub's terminate word of this generation arrives.  Returns the steps used."""
+        for i in range(max_steps):
+            self.fgm_step(threshold, eps_psi, mode, drain=gen)
+            if int(self.w.pads[self.me][PAD_FGM + 5]) == gen:
+                return i + 1
+            time.sleep(0)
+        self.w.pads[self.me][PAD_STATUS] = 4
+        return max_steps
 
     def fgm_pending(self) -> bool:
         return int(self.w.pads[self.me][PAD_FGM + 3]) != self.fgm["round"]

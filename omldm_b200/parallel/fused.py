@@ -345,6 +345,10 @@ class FGMDriver(SyncDriver):
         self.state = torch.zeros(n_state, dtype=torch.float32, device=self.comm.device)
         self.state[1::8] = -1.0   # force re-anchoring on the first step
         self.rounds = 0
+        self.flush_mode = str(cfg(self.tc, ["fgmFlush"], "drain")).lower()
+        self.flush_timeout_s = float(cfg(self.tc, ["fgmFlushTimeout"], 5.0))
+        self.flush_timeouts = 0
+        self._drain_gen = 0
         if self.impl == "fused":
             # hub (rank 0) starts the first round: theta = sqrt(T)/2, every phi = phi(0)
             phi0 = -math.sqrt(self.threshold)
@@ -379,12 +383,37 @@ class FGMDriver(SyncDriver):
         return int(self.state[4].item()) if self.impl == "fused" else self.rounds
 
     def flush(self) -> None:
-        """End of stream.  A round the hub declared during the very last steps may have been seen by
-        some ranks only; those ranks would wait in the round-end barrier for peers that stopped
-        stepping.  Agree (host side) whether a round is pending anywhere and, if so, step once more
-        on every rank - the flag is in every pad, so everybody now takes the round-end branch."""
+        """End of stream (collective).  The round-end all-reduce waits for every rank inside the kernel, so a
+        rank must not simply stop stepping while a peer may still announce a round.  Drain handshake
+        (csrc/sync.cu, modelled and stress-tested in parallel/fake_backend.py): keep stepping in drain mode -
+        which joins any round still announced - until the hub, having heard "no more data" from everybody with no
+        round open, writes this flush generation into every pad.  Works for any skew and for unequal step counts."""
         if self.impl != "fused" or self.comm.k <= 1:
             return
+        if self.flush_mode == "legacy":
+            return self._flush_legacy()
+        from .comm import PAD_FGM
+        import time
+        self._drain_gen += 1
+        c, g = self.comm, self._drain_gen
+        deadline = time.monotonic() + self.flush_timeout_s
+        while True:
+            _lib.check(_lib.kernels().omldm_sync_fgm_drain(c.struct_ptr(), self._eptr(), _sz(c.n), _f(self.scale),
+                                                           _i(self.mode), _f(self.threshold), _f(self.eps_psi), _u(0),
+                                                           _lib.ptr(self.state), _u(g), _i(self.blocks),
+                                                           _lib.stream_ptr()), "sync_fgm_drain")
+            if int(c.pad[PAD_FGM + 5].item()) == g:      # .item() waits for the step just launched
+                return
+            if time.monotonic() > deadline:
+                import warnings
+                warnings.warn("FGM flush: no terminate word from the hub within %.1f s" % self.flush_timeout_s)
+                self.flush_timeouts += 1
+                return
+            time.sleep(2e-5)
+
+    def _flush_legacy(self) -> None:
+        """Round-1 flush: agree on the host whether a round is pending anywhere and, if so, step once more on
+        every rank.  Needs equal step counts and small skew between ranks."""
         from .comm import PAD_FGM
         d = self._dist()
         for _ in range(4):

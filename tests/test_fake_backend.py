@@ -253,3 +253,114 @@ def test_mixed_sequence_shares_the_flag_space():
             assert np.allclose(rk.buf, np.mean(range(k)) + it)
     w.run(body)
     assert _status(w) == [0] * k
+
+
+# ---------------------------------------------------------------------------------------------------------
+# The same invariants under randomised interleavings: every rank pauses for a random time wherever the kernels
+# touch peer memory (FakeWorld(jitter=...)), several seeds each.
+@pytest.mark.parametrize("seed", range(6))
+def test_fgm_lockstep_decisions_under_jitter(seed):
+    k, n, T = 4, 16, 1.0
+    w = FakeWorld(k, n, jitter=2e-4, seed=seed)
+    w.ranks[0].fgm_init_hub(T)
+    rounds = 0
+    for step in range(120):
+        for r in range(k):
+            w.bufs[r][:] += 0.004 * (r + 1)
+        done = []
+        w.run(lambda rk: done.append(rk.fgm_step(T)))
+        assert len(set(done)) == 1, f"step {step}: ranks took different branches {done}"
+        if done[0]:
+            rounds += 1
+            for r in range(1, k):
+                np.testing.assert_allclose(w.bufs[r], w.bufs[0], rtol=1e-12, atol=1e-12)
+    assert rounds >= 2 and _status(w) == [0] * k
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_free_running_fgm_with_drain_flush_under_jitter(seed):
+    """Ranks step without any per-step rendezvous (as separate GPUs do), with DIFFERENT numbers of steps; the
+    drain flush (done flags at the hub, hub-issued terminate word) leaves nobody inside a round-end barrier,
+    whatever the skew - including a rank that finishes long before the hub announces a round."""
+    k, n, T = 4, 16, 1.0
+    steps = [60, 25, 60, 48]
+    w = FakeWorld(k, n, jitter=3e-4, seed=seed, spin_timeout_s=30.0)
+    w.ranks[0].fgm_init_hub(T)
+
+    def body(rk):
+        for s in range(steps[rk.me]):
+            rk.buf[:] += 0.01 * (rk.me + 1)
+            rk.fgm_step(T)
+        rk.fgm_flush(T, gen=1)
+    w.run(body)
+    assert _status(w) == [0] * k
+    assert not any(rk.fgm_pending() for rk in w.ranks)
+    assert len({rk.fgm["rounds"] for rk in w.ranks}) == 1 and w.ranks[0].fgm["rounds"] >= 1
+    # a second stream segment and a second flush generation on the same pads
+    def body2(rk):
+        for s in range(10 + 5 * rk.me):
+            rk.buf[:] += 0.02
+            rk.fgm_step(T)
+        rk.fgm_flush(T, gen=2)
+    w.run(body2)
+    assert _status(w) == [0] * k and not any(rk.fgm_pending() for rk in w.ranks)
+    assert len({rk.fgm["rounds"] for rk in w.ranks}) == 1
+
+
+def test_drain_flush_in_lockstep_emulation():
+    """One launch for all ranks per step (emulate mode): the flush loop ends in the same launch on every rank."""
+    k, n, T = 4, 16, 1.0
+    w = FakeWorld(k, n, jitter=1e-4, seed=7)
+    w.ranks[0].fgm_init_hub(T)
+    for step in range(80):
+        for r in range(k):
+            w.bufs[r][:] += 0.01
+        w.run(lambda rk: rk.fgm_step(T))
+    for launch in range(20):
+        w.run(lambda rk: rk.fgm_step(T, drain=1))
+        term = [int(w.pads[r][PAD_FGM + 5]) == 1 for r in range(k)]
+        assert len(set(term)) == 1
+        if term[0]:
+            break
+    assert term[0] and launch <= 3
+    assert _status(w) == [0] * k and not any(rk.fgm_pending() for rk in w.ranks)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_gm_and_allreduce_under_jitter(seed):
+    k, n = 5, 37
+    w = FakeWorld(k, n, jitter=2e-4, seed=seed)
+    rng = np.random.default_rng(seed)
+    for it in range(10):
+        xs = [rng.standard_normal(n) * (3.0 if it % 3 == 0 else 0.01) for _ in range(k)]
+        for r in range(k):
+            w.bufs[r][:] = w.ranks[r].e + xs[r]
+        expect_sync = any(float(x @ x) > 0.5 for x in xs)
+        ref = np.mean([b.copy() for b in w.bufs], axis=0)
+        out = []
+        w.run(lambda rk: out.append(rk.gm(0.5)))
+        assert out == [expect_sync] * k
+        if expect_sync:
+            for r in range(k):
+                np.testing.assert_allclose(w.bufs[r], ref, rtol=1e-12, atol=1e-12)
+    assert _status(w) == [0] * k
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_async_conservation_under_jitter(seed):
+    """Whatever the interleaving of pushes, each hub shard ends up with the initial model plus the mean of all
+    pushed updates (additive atomics commute)."""
+    k, n, steps = 4, 24, 5
+    w = FakeWorld(k, n, jitter=2e-4, seed=seed)
+    rng = np.random.default_rng(10 + seed)
+    upd = rng.standard_normal((k, steps, n))
+
+    def body(rk):
+        for s in range(steps):
+            rk.buf[:] += upd[rk.me, s]
+            rk.async_push_pull(0)
+    w.run(body)
+    ref = upd.sum((0, 1)) / k
+    for r in range(k):
+        lo, hi = w.shard(r)
+        np.testing.assert_allclose(w.hubs[r][lo:hi], ref[lo:hi], rtol=1e-10, atol=1e-10)
