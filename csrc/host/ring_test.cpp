@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -50,6 +51,37 @@ int main() {
   size_t used = 0;
   int rows = omldm_parse_json_records(txt, std::strlen(txt), 3, out.data(), 32, 8, &nf, &used);
   if (rows != 2 || nf != 1 || used != std::strlen(txt)) { std::fprintf(stderr, "rows %d nf %d\n", rows, nf); return 7; }
+  // hostile fragments in an exactly-sized heap buffer (so ASan sees any read past the end): unterminated strings,
+  // a backslash as the very last byte, unbalanced brackets, huge exponents / mantissas, missing values
+  const char* bad[] = {"{\"numericalFeatures\":[1,2,3],\"s\":\"abc\\", "{\"numericalFeatures\":[1,2,3],\"t\":{\"a\":[1,2",
+                       "{\"numericalFeatures\":[1e99999,123456789012345678901234567890.5e-400,3]}", "{\"numericalFeatures\":",
+                       "{\"numericalFeatures\":[1,2,3],\"target\":", "{\"", "{\"a", "{\"numericalFeatures\":[-", "{\"operation\":\"tra"};
+  for (const char* frag : bad) {
+    const size_t n = std::strlen(frag);
+    std::vector<char> exact(frag, frag + n);
+    omldm_parse_json_records(exact.data(), n, 3, out.data(), 32, 8, &nf, &used);
+    if (used != n) return 8;
+  }
+  // threaded scanner on a large text with garbage lines; row order and counts must match the serial one
+  std::string big;
+  for (int i = 0; i < 5000; ++i) {
+    if (i % 11 == 0) big += "not json\n";
+    big += "{\"numericalFeatures\":[" + std::to_string(i) + ",0.5,-1e-3],\"target\":" + std::to_string(i % 7) + "}\n";
+  }
+  std::vector<float> o1(6000 * 32), o4(6000 * 32);
+  int nf1 = 0, nf4 = 0;
+  size_t u1 = 0, u4 = 0;
+  const int r1 = omldm_parse_json_records(big.data(), big.size(), 3, o1.data(), 32, 6000, &nf1, &u1);
+  const int r4 = omldm_parse_json_records_mt(big.data(), big.size(), 3, o4.data(), 32, 6000, &nf4, &u4, 4);
+  if (r1 != 5000 || r4 != 5000 || u1 != u4 || std::memcmp(o1.data(), o4.data(), sizeof(float) * 5000 * 32) != 0) return 9;
+
+  // compact fp16 wire rows: generator and packer stay inside their buffers (odd d exercises the pad half)
+  const int dw = 13, wld = ((dw + 1) & ~1) + 2;
+  std::vector<uint16_t> wire(static_cast<size_t>(batch) * wld);
+  omldm_generate_batch_f16(wire.data(), 1, dw, batch, 0, 9, 2);
+  std::vector<float> staged(static_cast<size_t>(batch) * 32, 1.0f);
+  omldm_pack_wire_f16(staged.data(), 32, dw + 1, batch, dw, wire.data());
+  if (wire[0] != 0x3C00) return 10;                                   // 1.0 in fp16
   std::printf("ring_test ok %lld %.3f\n", got, checksum);
   return 0;
 }

@@ -65,6 +65,11 @@ void omldm_pack_wire_f16(const float* rows, int ld, int target_col, int batch, i
  * *n_forecast counts rows whose operation was "forecasting" (their valid flag is 2.0). */
 int omldm_parse_json_records(const char* text, size_t len, int d, float* dst, int ld, int max_rows,
                              int* n_forecast, size_t* consumed);
+/* Same on n_threads threads (text split at line boundaries, row order = line order).  At most max_rows LINES are
+ * taken, so dst needs max_rows rows and fewer rows may come back when lines are skipped; *consumed says where to
+ * resume. */
+int omldm_parse_json_records_mt(const char* text, size_t len, int d, float* dst, int ld, int max_rows,
+                                int* n_forecast, size_t* consumed, int n_threads);
 
 #ifdef __cplusplus
 }

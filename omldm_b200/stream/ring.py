@@ -51,6 +51,9 @@ def _h():
         h.omldm_parse_json_records.restype = i
         h.omldm_parse_json_records.argtypes = [ctypes.c_char_p, sz, i, vp, i, i, ctypes.POINTER(i),
                                                ctypes.POINTER(sz)]
+        h.omldm_parse_json_records_mt.restype = i
+        h.omldm_parse_json_records_mt.argtypes = [ctypes.c_char_p, sz, i, vp, i, i, ctypes.POINTER(i),
+                                                  ctypes.POINTER(sz), i]
         _configured = True
     return h
 
@@ -204,12 +207,17 @@ def generate_batch(kind: int, d: int, batch: int, seed: int = 0, batch_index: in
     return out
 
 
-def parse_json_records(text: bytes, d: int, max_rows: int) -> Tuple[torch.Tensor, int, int]:
-    """(staged rows [n, ld], n_forecast, bytes consumed); rows with valid flag 2.0 are forecasts."""
+def parse_json_records(text: bytes, d: int, max_rows: int, n_threads: Optional[int] = None
+                       ) -> Tuple[torch.Tensor, int, int]:
+    """(staged rows [n, ld], n_forecast, bytes consumed); rows with valid flag 2.0 are forecasts.
+    Large inputs are parsed on several threads (default: up to 8, one per 64 KB of text)."""
     ld = pad32(d + 2)
-    out = torch.zeros(max_rows, ld, dtype=torch.float32)
+    out = torch.empty(max_rows, ld, dtype=torch.float32)
     nf = ctypes.c_int(0)
     used = ctypes.c_size_t(0)
-    n = _h().omldm_parse_json_records(text, len(text), d, out.data_ptr(), ld, max_rows, ctypes.byref(nf),
-                                      ctypes.byref(used))
+    if n_threads is None:
+        import os
+        n_threads = max(1, min(8, os.cpu_count() or 1, len(text) >> 16))
+    n = _h().omldm_parse_json_records_mt(text, len(text), d, out.data_ptr(), ld, max_rows, ctypes.byref(nf),
+                                         ctypes.byref(used), n_threads)
     return out[:n], int(nf.value), int(used.value)
