@@ -150,7 +150,7 @@ def run_gpu(params: JobParameters) -> int:
         d = len(json.loads(lines[0])["numericalFeatures"]) + len(json.loads(lines[0]).get("discreteFeatures") or [])
         off = 0
         while off < len(text):
-            rows, nf, used = R.parse_json_records(text[off:], d, B)
+            rows, nf, used = R.parse_json_records(text, d, B, offset=off)
             off += max(used, 1)
             if rows.shape[0]:
                 eng.train_batch(rows[rows[:, d] == 1.0].to(dev), d)

@@ -52,8 +52,7 @@ def _h():
         h.omldm_parse_json_records.argtypes = [ctypes.c_char_p, sz, i, vp, i, i, ctypes.POINTER(i),
                                                ctypes.POINTER(sz)]
         h.omldm_parse_json_records_mt.restype = i
-        h.omldm_parse_json_records_mt.argtypes = [ctypes.c_char_p, sz, i, vp, i, i, ctypes.POINTER(i),
-                                                  ctypes.POINTER(sz), i]
+        h.omldm_parse_json_records_mt.argtypes = [vp, sz, i, vp, i, i, ctypes.POINTER(i), ctypes.POINTER(sz), i]
         _configured = True
     return h
 
@@ -207,17 +206,22 @@ def generate_batch(kind: int, d: int, batch: int, seed: int = 0, batch_index: in
     return out
 
 
-def parse_json_records(text: bytes, d: int, max_rows: int, n_threads: Optional[int] = None
+def parse_json_records(text: bytes, d: int, max_rows: int, n_threads: Optional[int] = None, offset: int = 0
                        ) -> Tuple[torch.Tensor, int, int]:
     """(staged rows [n, ld], n_forecast, bytes consumed); rows with valid flag 2.0 are forecasts.
-    Large inputs are parsed on several threads (default: up to 8, one per 64 KB of text)."""
+    Parsing starts at byte `offset` of `text` (no copy of the remainder).  Large inputs are parsed on several
+    threads (default: up to 8, one per 64 KB of text)."""
     ld = pad32(d + 2)
     out = torch.empty(max_rows, ld, dtype=torch.float32)
     nf = ctypes.c_int(0)
     used = ctypes.c_size_t(0)
+    n_bytes = len(text) - offset
+    if n_bytes <= 0:
+        return out[:0], 0, 0
     if n_threads is None:
         import os
-        n_threads = max(1, min(8, os.cpu_count() or 1, len(text) >> 16))
-    n = _h().omldm_parse_json_records_mt(text, len(text), d, out.data_ptr(), ld, max_rows, ctypes.byref(nf),
+        n_threads = max(1, min(8, os.cpu_count() or 1, n_bytes >> 16))
+    base = ctypes.cast(ctypes.c_char_p(text), ctypes.c_void_p).value      # `text` stays alive for the call
+    n = _h().omldm_parse_json_records_mt(base + offset, n_bytes, d, out.data_ptr(), ld, max_rows, ctypes.byref(nf),
                                          ctypes.byref(used), n_threads)
     return out[:n], int(nf.value), int(used.value)
