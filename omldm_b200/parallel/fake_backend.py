@@ -268,6 +268,39 @@ class FakeRank:
     def fgm_pending(self) -> bool:
         return int(self.w.pads[self.me][PAD_FGM + 3]) != self.fgm["round"]
 
+    # ---- design model: reduce-scatter fused into the producer (ROADMAP item 0) -----------------------
+    def fused_scatter_step(self, delta: np.ndarray) -> None:
+        """One ORR-like step of the planned GEMM+reduce-scatter fusion, as a protocol model:
+        (1) the producer (the GEMM epilogue) adds this rank's delta, shard by shard, straight into the shard
+            OWNER's rotating buffer t mod 3 (remote reduce-add, no local copy);
+        (2) ONE flag barrier;
+        (3) every rank adds each owner's reduced shard to its private global vector `e`;
+        (4) the owner clears buffer (t+2) mod 3 - the one read in step t-1 - which is safe exactly because the
+            barrier of step t proves that every peer has finished step t-1, and nobody accumulates into that
+            buffer before the barrier of step t+1, which needs this rank's arrival.
+        `w.rot[r]` (3 x n per rank, shard-owner rows only are used) is created on first use."""
+        w, me, k = self.w, self.me, self.w.k
+        with w.lock:
+            if not hasattr(w, "rot"):
+                w.rot = [np.zeros((3, w.n)) for _ in range(k)]
+        self.epoch += 1
+        t = self.epoch
+        cur, nxt = t % 3, (t + 2) % 3
+        for owner in range(k):                         # (1) tile-by-tile remote reduce-add
+            lo, hi = w.shard(owner)
+            w.pause(me)
+            with w.lock:
+                w.rot[owner][cur, lo:hi] += delta[lo:hi]
+        self._signal_all(PAD_ENTRY, t)                 # (2) the only barrier of the step
+        self._wait_all(PAD_ENTRY, t)
+        for owner in range(k):                         # (3) gather-add of the reduced shards
+            lo, hi = w.shard(owner)
+            w.pause(me)
+            self.e[lo:hi] += w.rot[owner][cur, lo:hi]
+        lo, hi = w.shard(me)                           # (4) clear the buffer of step t-1 for step t+2
+        w.pause(me)
+        w.rot[me][nxt, lo:hi] = 0.0
+
     # ---- barrier / query ---------------------------------------------------------------------------
     def barrier(self) -> None:
         self.epoch += 1

@@ -364,3 +364,66 @@ def test_async_conservation_under_jitter(seed):
     for r in range(k):
         lo, hi = w.shard(r)
         np.testing.assert_allclose(w.hubs[r][lo:hi], ref[lo:hi], rtol=1e-10, atol=1e-10)
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_design_model_fused_reduce_scatter_three_buffers(seed):
+    """Protocol model of the planned GEMM + reduce-scatter fusion (ROADMAP item 0): one barrier per step and
+    three rotating delta buffers are race free - every rank's global vector is the exact running sum of all
+    deltas after every step, under free-running ranks and random pauses."""
+    k, n, steps = 4, 24, 40
+    w = FakeWorld(k, n, jitter=2e-4, seed=seed)
+    rng = np.random.default_rng(50 + seed)
+    deltas = rng.integers(-3, 4, size=(steps, k, n)).astype(float)      # integers: sums are exact in fp64
+    snaps = [[None] * steps for _ in range(k)]
+
+    def body(rk):
+        for t in range(steps):
+            rk.fused_scatter_step(deltas[t, rk.me])
+            snaps[rk.me][t] = rk.e.copy()
+    w.run(body)
+    assert _status(w) == [0] * k
+    run = np.cumsum(deltas.sum(1), axis=0)
+    for r in range(k):
+        for t in range(steps):
+            np.testing.assert_array_equal(snaps[r][t], run[t])
+
+
+def test_design_model_two_buffers_are_not_enough():
+    """The same protocol with the clear aimed at the buffer of the NEXT step (what two buffers would force) loses
+    updates once ranks run freely - the reason for the third buffer."""
+    k, n, steps = 4, 8, 20
+    lost = False
+    for seed in range(8):
+        w = FakeWorld(k, n, jitter=3e-4, seed=seed)
+        w.rot = [np.zeros((2, n)) for _ in range(k)]
+
+        def step2(rk, delta):
+            rk.epoch += 1
+            t = rk.epoch
+            cur, nxt = t % 2, (t + 1) % 2
+            for owner in range(k):
+                lo, hi = w.shard(owner)
+                w.pause(rk.me)
+                with w.lock:
+                    w.rot[owner][cur, lo:hi] += delta[lo:hi]
+            rk._signal_all(0, t)
+            rk._wait_all(0, t)
+            for owner in range(k):
+                lo, hi = w.shard(owner)
+                w.pause(rk.me)
+                rk.e[lo:hi] += w.rot[owner][cur, lo:hi]
+            lo, hi = w.shard(rk.me)
+            if rk.me == 0:
+                import time
+                time.sleep(0.002)                # a slow owner: its peers are already accumulating step t+1
+            w.rot[rk.me][nxt, lo:hi] = 0.0
+
+        def body(rk):
+            for t in range(steps):
+                step2(rk, np.ones(n))
+        w.run(body)
+        if any(not np.array_equal(rk.e, np.full(n, float(k * steps))) for rk in w.ranks):
+            lost = True
+            break
+    assert lost
