@@ -46,7 +46,7 @@ class ResponseConstructor:
             return sum(vals) / n if vals else None
 
         return QueryResponse(
-            responseId=lst[0].responseId, bucketIndex=None, mlpId=lst[0].mlpId,
+            responseId=lst[0].responseId, bucketIndex=lst[0].bucketIndex, mlpId=lst[0].mlpId,   # head's index kept (:35)
             preprocessors=first("preprocessors"), learner=first("learner"), protocol=first("protocol"),
             dataFitted=sum(int(r.dataFitted or 0) for r in lst),
             loss=mean("loss"), cumulativeLoss=mean("cumulativeLoss"), score=mean("score"))
