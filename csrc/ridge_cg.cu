@@ -182,10 +182,17 @@ extern "C" int omldm_ridge_cg(const float* A, int ld, int n, float lam, const fl
   if (grid > sms * per_sm) grid = sms * per_sm;
   if (grid < 1) return set_error_msg("ridge_cg: kernel cannot be resident");
   CgScalars* sc = static_cast<CgScalars*>(scalars);
+#ifdef OMLDM_EMU   // tools/cuda_emu: one block (its grid barrier is a block barrier), plain launch
+  ridge_pcg_kernel<<<1, CG_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(A, ld, n, lam, b, b_stride, x, work, sc,
+                                                                            max_iter, tol, info);
+  (void)grid;
+  return check_launch("ridge_pcg_kernel");
+#else
   void* args[] = {&A, &ld, &n, &lam, &b, &b_stride, &x, &work, &sc, &max_iter, &tol, &info};
   cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(ridge_pcg_kernel), dim3(grid), dim3(CG_THREADS),
                                               args, 0, static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) return set_error("ridge_pcg_kernel", e);
   count_launch(1);
   return 0;
+#endif
 }

@@ -16,6 +16,7 @@ import torch
 _LIBDIR = Path(__file__).resolve().parents[1] / "lib"
 _kernels = None
 _host = None
+_emulated = False
 
 
 class NativeError(RuntimeError):
@@ -51,6 +52,33 @@ def kernels() -> ctypes.CDLL:
     return _kernels
 
 
+def use_emulator(asan: bool = False) -> ctypes.CDLL:
+    """Route `kernels()` to the CUDA-on-CPU emulation of the PTX-free kernel files (tools/cuda_emu): the real
+    kernel sources compiled by g++, one host thread per CUDA thread, operating on host tensors.  For tests on
+    machines without a GPU (`functional.use_impl("emu")`); never used on a GPU box."""
+    global _kernels, _emulated
+    import importlib.util
+    root = Path(__file__).resolve().parents[2]
+    spec = importlib.util.spec_from_file_location("omldm_build_emu", root / "tools" / "cuda_emu" / "build_emu.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = mod.OUT / ("libomldm_emu_asan.so" if asan else "libomldm_emu.so")
+    srcs = [root / "csrc" / s for s in mod.SOURCES] + list((root / "tools" / "cuda_emu").glob("*"))
+    if not out.exists() or any(p.stat().st_mtime > out.stat().st_mtime for p in srcs):
+        mod.build(asan)
+    _kernels = ctypes.CDLL(str(out))
+    _kernels.omldm_last_error.restype = ctypes.c_char_p
+    _kernels.omldm_launch_count.restype = ctypes.c_longlong
+    _emulated = True
+    return _kernels
+
+
+def stop_emulator() -> None:
+    global _kernels, _emulated
+    if _emulated:
+        _kernels, _emulated = None, False
+
+
 def host() -> ctypes.CDLL:
     """The host runtime library (ring buffers, record parser); no CUDA dependency."""
     global _host
@@ -80,6 +108,8 @@ def check(rc: int, what: str) -> None:
 
 
 def stream_ptr() -> ctypes.c_void_p:
+    if _emulated:
+        return ctypes.c_void_p(0)
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

@@ -44,6 +44,8 @@ def set_impl(name: str) -> None:
 def native(*tensors: torch.Tensor) -> bool:
     if _IMPL == "torch":
         return False
+    if _IMPL == "emu":          # CUDA-on-CPU emulation of the kernel sources (_lib.use_emulator), host tensors
+        return True
     on_gpu = any(t is not None and t.is_cuda for t in tensors)
     if _IMPL == "native" and not on_gpu:
         raise _lib.NativeError("native implementation requested for CPU tensors")

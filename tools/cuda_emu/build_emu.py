@@ -1,0 +1,70 @@
+"""Builds build/emu/libomldm_emu.so: the PTX-free kernel files of csrc/ compiled by g++ against the CUDA-on-CPU
+shim (emu_cuda.h), exposing the same `omldm_*` C ABI on host pointers.
+
+    python tools/cuda_emu/build_emu.py            # plain build, used by tests/test_emu_kernels.py
+    python tools/cuda_emu/build_emu.py --asan     # AddressSanitizer + UBSan build (libomldm_emu_asan.so)
+
+Source rewriting (nothing else is touched):
+  kernel<<<grid, block, smem, stream>>>(args)  ->  emu::launcher(kernel, grid, block, smem, stream)(args)
+  extern __shared__ T name[];                  ->  T* name = reinterpret_cast<T*>(emu::dyn_smem());
+Headers <cuda.h>, <cuda_runtime.h>, <cuda_fp16.h>, <cooperative_groups.h>, <math_constants.h>, "ptx.cuh" and
+"host_common.h" resolve to stand-ins in the build directory.
+"""
+from __future__ import annotations
+
+import re
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[2]
+HERE = Path(__file__).resolve().parent
+OUT = ROOT / "build" / "emu"
+# kernel files without inline PTX (umma_gemm.cu and sync.cu are tensor-core / peer-memory code: hardware only)
+SOURCES = ["ingest.cu", "sparse_mcpa.cu", "cluster.cu", "linear_learners.cu", "preprocess.cu", "tree.cu",
+           "fused_pipeline.cu", "ridge_cg.cu"]
+
+_LAUNCH = re.compile(r"([A-Za-z_][\w:]*(?:<[^<>;(){}]*>)?)\s*<<<(.+?)>>>", re.S)
+_DYN_SMEM = re.compile(r"extern\s+__shared__\s+([\w:]+)\s+(\w+)\s*\[\s*\]\s*;")
+
+
+def rewrite(text: str) -> str:
+    text = _DYN_SMEM.sub(r"\1* \2 = reinterpret_cast<\1*>(emu::dyn_smem());", text)
+    return _LAUNCH.sub(r"emu::launcher(\1, \2)", text)
+
+
+def build(asan: bool = False) -> Path:
+    src_dir = OUT / ("src_asan" if asan else "src")
+    if src_dir.exists():
+        shutil.rmtree(src_dir)
+    src_dir.mkdir(parents=True)
+    shutil.copy(HERE / "emu_cuda.h", src_dir / "emu_cuda.h")
+    shutil.copy(HERE / "stub_ptx.cuh", src_dir / "ptx.cuh")
+    shutil.copy(HERE / "stub_host_common.h", src_dir / "host_common.h")
+    shutil.copy(HERE / "emu_host.cpp", src_dir / "emu_host.cpp")
+    for h in ("cuda.h", "cuda_runtime.h", "cuda_fp16.h", "cooperative_groups.h", "math_constants.h"):
+        (src_dir / h).write_text('#pragma once\n#include "emu_cuda.h"\n')
+    for h in (ROOT / "csrc").glob("*.cuh"):
+        if h.name != "ptx.cuh":
+            (src_dir / h.name).write_text(rewrite(h.read_text()))
+    cpps = [src_dir / "emu_host.cpp"]
+    for name in SOURCES:
+        dst = src_dir / (Path(name).stem + ".cpp")
+        dst.write_text(rewrite((ROOT / "csrc" / name).read_text()))
+        cpps.append(dst)
+    out = OUT / ("libomldm_emu_asan.so" if asan else "libomldm_emu.so")
+    flags = ["-std=c++17", "-fPIC", "-shared", "-pthread", "-I", str(src_dir), "-I", str(ROOT / "include"),
+             "-Wall", "-Wno-unknown-pragmas", "-Wno-unused-variable", "-Wno-sign-compare"]
+    flags += ["-O1", "-g", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
+    cmd = ["g++", *flags, *map(str, cpps), "-o", str(out)]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    if p.returncode != 0:
+        raise RuntimeError("emulator build failed:\n" + p.stdout + p.stderr)
+    if p.stderr.strip():
+        print(p.stderr, file=sys.stderr)
+    return out
+
+
+if __name__ == "__main__":
+    print(build("--asan" in sys.argv))

@@ -1,0 +1,293 @@
+// CUDA-on-CPU emulation shim: lets the REAL kernel sources of csrc/*.cu (the ones without inline PTX) be compiled
+// by g++ and run on host memory, one std::thread per CUDA thread, so that
+//   * kernels can be compared against their PyTorch references on a box without a GPU, and
+//   * AddressSanitizer / UBSan see every global and shared memory access of the kernel code
+//     (compute-sanitizer is not available on the GPU pool this project is developed on).
+// Semantics: blocks of a launch run one after the other; the threads of a block run concurrently and are
+// NOT warp-synchronous (like independent thread scheduling); __syncthreads / __syncwarp / shuffles are real
+// barriers that tolerate threads which already returned; `__shared__` variables become function-level statics
+// (one block at a time), dynamic shared memory is an exactly-sized heap block; atomics are host atomics.
+// Not emulated: inline PTX, tensor cores, TMA, cooperative multi-block grids, streams (everything is synchronous).
+#pragma once
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <condition_variable>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <thread>
+#include <type_traits>
+#include <vector>
+
+#define OMLDM_EMU 1
+
+// ---------------------------------------------------------------- vector types
+struct uint3 { unsigned x, y, z; };
+struct dim3 {
+  unsigned x = 1, y = 1, z = 1;
+  dim3() = default;
+  dim3(unsigned a, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {}
+};
+struct alignas(8) float2 { float x, y; };
+struct alignas(16) float4 { float x, y, z, w; };
+struct alignas(16) double2 { double x, y; };
+struct alignas(16) int4 { int x, y, z, w; };
+struct alignas(8) int2 { int x, y; };
+inline float2 make_float2(float x, float y) { return {x, y}; }
+inline float4 make_float4(float x, float y, float z, float w) { return {x, y, z, w}; }
+inline double2 make_double2(double x, double y) { return {x, y}; }
+inline int4 make_int4(int x, int y, int z, int w) { return {x, y, z, w}; }
+inline int2 make_int2(int x, int y) { return {x, y}; }
+
+// ---------------------------------------------------------------- qualifiers
+#define __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __launch_bounds__(...)
+#define __align__(n) __attribute__((aligned(n)))
+#define __shared__ static
+#define __grid_constant__
+#ifndef __restrict__
+#define __restrict__ __restrict
+#endif
+
+namespace emu {
+
+// barrier that tolerates participants leaving for good (threads that returned from the kernel)
+struct Barrier {
+  std::mutex m;
+  std::condition_variable cv;
+  int active = 0, waiting = 0;
+  unsigned gen = 0;
+  void reset(int n) { active = n; waiting = 0; }
+  void sync() {
+    std::unique_lock<std::mutex> l(m);
+    const unsigned g = gen;
+    if (++waiting >= active) { waiting = 0; ++gen; cv.notify_all(); }
+    else cv.wait(l, [&] { return gen != g; });
+  }
+  void drop() {
+    std::unique_lock<std::mutex> l(m);
+    --active;
+    if (active > 0 && waiting >= active) { waiting = 0; ++gen; cv.notify_all(); }
+  }
+};
+struct Warp {
+  Barrier bar;
+  uint64_t slot[32];
+};
+struct BlockCtx {
+  Barrier bar;
+  std::vector<Warp> warps;
+  char* dyn = nullptr;
+};
+
+inline thread_local uint3 t_threadIdx, t_blockIdx;
+inline thread_local dim3 t_blockDim, t_gridDim;
+inline thread_local BlockCtx* t_ctx = nullptr;
+inline thread_local int t_lane = 0, t_warp = 0;
+
+inline void* dyn_smem() { return t_ctx->dyn; }
+
+template <class Body>
+void run_grid(dim3 g, dim3 b, size_t smem, Body&& body) {
+  const int T = static_cast<int>(b.x * b.y * b.z);
+  if (T <= 0 || g.x * g.y * g.z == 0) return;
+  BlockCtx ctx;
+  ctx.warps = std::vector<Warp>(static_cast<size_t>((T + 31) / 32));
+  ctx.dyn = smem ? static_cast<char*>(std::malloc(smem)) : nullptr;   // exact size: overruns are visible to ASan
+  Barrier fence;                                                      // never dropped: block boundaries
+  fence.reset(T);
+  auto arm = [&] {
+    ctx.bar.reset(T);
+    for (size_t w = 0; w < ctx.warps.size(); ++w)
+      ctx.warps[w].bar.reset(std::min(32, T - static_cast<int>(w) * 32));
+  };
+  arm();
+  auto worker = [&](int t) {
+    t_blockDim = b;
+    t_gridDim = g;
+    t_ctx = &ctx;
+    t_threadIdx = {static_cast<unsigned>(t) % b.x, (static_cast<unsigned>(t) / b.x) % b.y, static_cast<unsigned>(t) / (b.x * b.y)};
+    t_lane = t & 31;
+    t_warp = t >> 5;
+    for (unsigned z = 0; z < g.z; ++z)
+      for (unsigned y = 0; y < g.y; ++y)
+        for (unsigned x = 0; x < g.x; ++x) {
+          t_blockIdx = {x, y, z};
+          body();
+          ctx.warps[static_cast<size_t>(t_warp)].bar.drop();
+          ctx.bar.drop();
+          fence.sync();            // every thread has left block (x, y, z)
+          if (t == 0) arm();
+          fence.sync();
+        }
+  };
+  std::vector<std::thread> th;
+  th.reserve(static_cast<size_t>(T) - 1);
+  for (int t = 1; t < T; ++t) th.emplace_back(worker, t);
+  worker(0);
+  for (auto& x : th) x.join();
+  std::free(ctx.dyn);
+}
+
+template <class... KArgs>
+struct Launcher {
+  void (*k)(KArgs...);
+  dim3 g, b;
+  size_t smem;
+  template <class... A>
+  void operator()(A&&... a) const {
+    auto kk = k;
+    run_grid(g, b, smem, [&] { kk(static_cast<KArgs>(a)...); });
+  }
+};
+template <class... KArgs>
+Launcher<KArgs...> launcher(void (*k)(KArgs...), dim3 g, dim3 b, size_t smem = 0, void* = nullptr) {
+  return Launcher<KArgs...>{k, g, b, smem};
+}
+
+template <class T>
+inline uint64_t to_bits(T v) { uint64_t u = 0; static_assert(sizeof(T) <= 8, "shuffle payload"); std::memcpy(&u, &v, sizeof(T)); return u; }
+template <class T>
+inline T from_bits(uint64_t u) { T v; std::memcpy(&v, &u, sizeof(T)); return v; }
+
+template <class T>
+inline T shfl(T v, int src_lane) {
+  Warp& w = t_ctx->warps[static_cast<size_t>(t_warp)];
+  w.slot[t_lane] = to_bits(v);
+  w.bar.sync();
+  const T r = from_bits<T>(w.slot[src_lane & 31]);
+  w.bar.sync();
+  return r;
+}
+
+}  // namespace emu
+
+#define threadIdx (emu::t_threadIdx)
+#define blockIdx (emu::t_blockIdx)
+#define blockDim (emu::t_blockDim)
+#define gridDim (emu::t_gridDim)
+#define warpSize 32
+
+// ---------------------------------------------------------------- synchronisation / warp primitives
+inline void __syncthreads() { emu::t_ctx->bar.sync(); }
+inline void __syncwarp(unsigned = 0xffffffffu) { emu::t_ctx->warps[static_cast<size_t>(emu::t_warp)].bar.sync(); }
+inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
+inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
+inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
+template <class T> inline T __shfl_xor_sync(unsigned, T v, int mask) { return emu::shfl(v, emu::t_lane ^ mask); }
+template <class T> inline T __shfl_sync(unsigned, T v, int lane) { return emu::shfl(v, lane); }
+template <class T> inline T __shfl_down_sync(unsigned, T v, int d) { return emu::shfl(v, emu::t_lane + d < 32 ? emu::t_lane + d : emu::t_lane); }
+
+// ---------------------------------------------------------------- atomics (host atomics on plain memory)
+template <class T>
+inline T emu_atomic_add(T* p, T v) {
+  if constexpr (std::is_integral<T>::value) {
+    return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST);
+  } else {
+    using U = typename std::conditional<sizeof(T) == 4, uint32_t, uint64_t>::type;
+    U* up = reinterpret_cast<U*>(p);
+    U old = __atomic_load_n(up, __ATOMIC_SEQ_CST);
+    for (;;) {
+      T cur;
+      std::memcpy(&cur, &old, sizeof(T));
+      const T nv = cur + v;
+      U nb;
+      std::memcpy(&nb, &nv, sizeof(T));
+      if (__atomic_compare_exchange_n(up, &old, nb, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) return cur;
+    }
+  }
+}
+inline float atomicAdd(float* p, float v) { return emu_atomic_add(p, v); }
+inline double atomicAdd(double* p, double v) { return emu_atomic_add(p, v); }
+inline int atomicAdd(int* p, int v) { return emu_atomic_add(p, v); }
+inline unsigned atomicAdd(unsigned* p, unsigned v) { return emu_atomic_add(p, v); }
+inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { return emu_atomic_add(p, v); }
+template <class T>
+inline T atomicCAS(T* p, T cmp, T val) {
+  __atomic_compare_exchange_n(p, &cmp, val, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
+  return cmp;
+}
+template <class T> inline T atomicExch(T* p, T v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicOr(T* p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicMax(T* p, T v) {
+  T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
+  while (old < v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+  return old;
+}
+template <class T> inline T atomicMin(T* p, T v) {
+  T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
+  while (old > v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+  return old;
+}
+
+// ---------------------------------------------------------------- loads, bit casts, math
+template <class T> inline T __ldcg(const T* p) { return *p; }
+template <class T> inline T __ldg(const T* p) { return *p; }
+template <class T> inline T __ldcs(const T* p) { return *p; }
+template <class T> inline void __stcg(T* p, T v) { *p = v; }
+inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
+inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
+inline unsigned __float_as_uint(float f) { unsigned i; std::memcpy(&i, &f, 4); return i; }
+inline float __uint_as_float(unsigned i) { float f; std::memcpy(&f, &i, 4); return f; }
+inline long long __double_as_longlong(double d) { long long i; std::memcpy(&i, &d, 8); return i; }
+inline double __longlong_as_double(long long i) { double d; std::memcpy(&d, &i, 8); return d; }
+template <class A, class B> inline typename std::common_type<A, B>::type min(A a, B b) { return b < a ? b : a; }
+template <class A, class B> inline typename std::common_type<A, B>::type max(A a, B b) { return a < b ? b : a; }
+inline float rsqrtf(float x) { return 1.0f / std::sqrt(x); }
+inline double rsqrt(double x) { return 1.0 / std::sqrt(x); }
+inline float __fdividef(float a, float b) { return a / b; }
+inline float __expf(float x) { return std::exp(x); }
+inline float __frcp_rn(float x) { return 1.0f / x; }
+inline int __popc(unsigned x) { return __builtin_popcount(x); }
+inline int __clz(int x) { return x ? __builtin_clz(static_cast<unsigned>(x)) : 32; }
+#define CUDART_INF_F (__builtin_inff())
+#define CUDART_INF (__builtin_inf())
+using std::isfinite;
+using std::isnan;
+
+// ---------------------------------------------------------------- fp16 (storage type + conversions only)
+struct __half { uint16_t x; };
+struct alignas(4) __half2 { __half x, y; };
+inline float __half2float(__half h) {
+  const uint32_t s = (h.x & 0x8000u) << 16, e = (h.x >> 10) & 31u, m = h.x & 1023u;
+  uint32_t u;
+  if (e == 0) {
+    if (m == 0) u = s;
+    else { int k = 0; uint32_t mm = m; while (!(mm & 1024u)) { mm <<= 1; ++k; } u = s | ((113u - k) << 23) | ((mm & 1023u) << 13); }
+  } else if (e == 31) u = s | 0x7F800000u | (m << 13);
+  else u = s | ((e + 112u) << 23) | (m << 13);
+  float f;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+inline float2 __half22float2(__half2 h) { return {__half2float(h.x), __half2float(h.y)}; }
+
+// ---------------------------------------------------------------- the slice of the runtime API the host wrappers use
+typedef void* cudaStream_t;
+typedef int cudaError_t;
+enum { cudaSuccess = 0, cudaErrorInvalidValue = 1 };
+enum { cudaDevAttrMultiProcessorCount = 16, cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
+inline cudaError_t cudaGetLastError() { return cudaSuccess; }
+inline cudaError_t cudaPeekAtLastError() { return cudaSuccess; }
+inline const char* cudaGetErrorString(cudaError_t) { return "emulated"; }
+inline cudaError_t cudaGetDevice(int* d) { *d = 0; return cudaSuccess; }
+inline cudaError_t cudaDeviceGetAttribute(int* v, int, int) { *v = 1; return cudaSuccess; }
+inline cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t = nullptr) { std::memset(p, v, n); return cudaSuccess; }
+inline cudaError_t cudaMemset(void* p, int v, size_t n) { std::memset(p, v, n); return cudaSuccess; }
+inline cudaError_t cudaMalloc(void** p, size_t n) { *p = std::malloc(n); return *p ? cudaSuccess : cudaErrorInvalidValue; }
+inline cudaError_t cudaFree(void* p) { std::free(p); return cudaSuccess; }
+template <class F> inline cudaError_t cudaFuncSetAttribute(F, int, int) { return cudaSuccess; }
+template <class F> inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) { *n = 1; return cudaSuccess; }
+template <class T> inline cudaError_t cudaGetSymbolAddress(void** p, T& sym) { *p = const_cast<void*>(static_cast<const void*>(&sym)); return cudaSuccess; }
+
+// cooperative groups: grids are emulated with ONE block, so a grid barrier is a block barrier
+namespace cooperative_groups {
+struct grid_group { void sync() const { __syncthreads(); } };
+inline grid_group this_grid() { return {}; }
+}  // namespace cooperative_groups

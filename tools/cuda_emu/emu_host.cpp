@@ -1,0 +1,21 @@
+// Error reporting / launch accounting of the emulated kernel library (mirrors csrc/host_common.cu).
+#include "host_common.h"
+
+#include <atomic>
+#include <cstdio>
+
+namespace omldm {
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+int set_error(const char* what, cudaError_t e) { snprintf(g_err, sizeof(g_err), "%s: error %d", what, e); return -1; }
+int set_error_msg(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); return -1; }
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int check_launch(const char*) { count_launch(1); return 0; }
+}  // namespace omldm
+
+extern "C" const char* omldm_last_error() { return omldm::g_err; }
+extern "C" long long omldm_launch_count() { return omldm::g_launches.load(); }
+extern "C" void omldm_add_launch_count(long long n) { omldm::g_launches.fetch_add(n); }
+extern "C" void omldm_reset_launch_count() { omldm::g_launches.store(0); }
+extern "C" int omldm_abi_version() { return 1; }
+extern "C" int omldm_is_emulator() { return 1; }
