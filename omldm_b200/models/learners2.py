@@ -163,7 +163,7 @@ class GpuMultiClassPA(GpuLearner):
     def fit_sparse(self, rows, nnz):
         """Mini-batch step straight from sparse rows (csrc/sparse_mcpa.cu): gathers and scatters against the
         dense model instead of two GEMMs over a rebuilt dense batch."""
-        if rows.is_cuda and F.native(rows):
+        if F.native(rows):
             B = rows.shape[0]
             if self._coef is None or self._coef.shape[0] < B:
                 self._coef = torch.empty(B, 4, device=self.device)

@@ -375,3 +375,61 @@ def test_ridge_cg_kernel(n, m):
         x2 = torch.zeros(n)
         F.ridge_cg(W, n, 1.0, x2, *F.ridge_cg_workspace(n, DEV, 64), max_iter=64, tol=1e-6)
     assert torch.allclose(x, x2, rtol=1e-3, atol=1e-4)
+
+
+# ---- engine-level: the Python glue of the kernel paths that normally only run on a GPU ---------------------------
+def _mk_engine(learner, tc=None, pre=None, extra=None, d=12):
+    from omldm_b200.engine import Engine
+    from omldm_b200.utils.config import JobParameters
+    jp = JobParameters(parallelism=1, testSetSize=16)
+    jp.extra.update(extra or {})
+    e = Engine(jp, device="cpu")
+    e.handle_request({"id": 1, "request": "Create", "learner": learner, "preProcessors": pre or [],
+                      "trainingConfiguration": dict({"protocol": "Synchronous", "nFeatures": d}, **(tc or {}))})
+    return e
+
+
+def test_engine_sparse_direct_on_emulated_kernels():
+    d, B, nnz, C = 800, 40, 10, 5
+    slots = []
+    for i in range(5):
+        idx, val, y = _sparse_slot(i, d, B, nnz, C, unique=False)
+        slots.append(torch.cat([idx.view(torch.uint8), val.view(torch.uint8), y.view(torch.uint8)]))
+    learner = {"name": "MultiClassPA", "hyperParameters": {"nClasses": C, "C": 0.1}}
+    out = []
+    for impl in ("torch", "emu"):
+        with F.use_impl(impl):
+            e = _mk_engine(learner, extra={"sparseDirect": "true"}, d=d)
+            for s in slots:
+                e.train_sparse(s.clone(), B, nnz, d)
+            out.append((e.pipelines[1].learner.W.clone(), e.pipelines[1].learner.counters(), e.holdout.clone()))
+    (Wt, ct, ht), (We, ce, he) = out
+    assert torch.allclose(Wt, We, rtol=1e-4, atol=1e-6) and torch.equal(ht, he)
+    assert ct["fitted"] == ce["fitted"] and abs(ct["loss_sum"] - ce["loss_sum"]) < 1e-4 * ct["loss_sum"]
+
+
+@pytest.mark.parametrize("learner,kind,pre", [
+    ({"name": "PA", "hyperParameters": {"C": 0.1}}, R.KIND_BINARY, None),
+    ({"name": "RegressorPA", "hyperParameters": {"C": 0.1, "epsilon": 0.05}}, R.KIND_REGRESSION,
+     [{"name": "PolynomialFeatures", "hyperParameters": {"degree": 2}}, {"name": "StandardScaler"}]),
+    ({"name": "SVM", "hyperParameters": {"C": 0.1}}, R.KIND_BINARY, [{"name": "MinMaxScaler"}]),
+    ({"name": "K-means", "hyperParameters": {"k": 4}}, R.KIND_CLUSTERS, None),
+    ({"name": "ORR", "hyperParameters": {"lambda": 1.0, "solver": "cg", "solveEvery": 2}}, R.KIND_REGRESSION, None),
+])
+def test_engine_pipelines_on_emulated_kernels(learner, kind, pre):
+    d, B = 12, 96
+    batches = [R.generate_batch(kind, d, B, seed=11, batch_index=i, n_aux=4) for i in range(5)]
+    out = []
+    for impl in ("torch", "emu"):
+        with F.use_impl(impl):
+            e = _mk_engine(learner, pre=pre, d=d)
+            for b in batches:
+                e.train_batch(b.clone(), d)
+            l = e.pipelines[1].learner
+            if hasattr(l, "solve"):
+                l.solve()
+            out.append((l.buf.clone() if l.name != "ORR" else l.wt.clone(), l.counters()))
+    (bt, ct), (be, ce) = out
+    assert ct["fitted"] == ce["fitted"] > 0
+    assert torch.allclose(bt, be, rtol=5e-3, atol=5e-4)
+    assert abs(ct["loss_sum"] - ce["loss_sum"]) <= 5e-3 * max(1.0, abs(ct["loss_sum"]))
