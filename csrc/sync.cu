@@ -68,28 +68,6 @@ __device__ __forceinline__ void wait_all(const Comm& c, int me, int base, uint32
 __device__ __forceinline__ float4 f4_add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 __device__ __forceinline__ float4 f4_scale(float4 a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
 
-__device__ __forceinline__ float4 mc_ld_reduce(const float* mc) {
-  float4 r;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-               : "l"(mc)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ void mc_st(float* mc, float4 v) {
-  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y),
-               "f"(v.z), "f"(v.w)
-               : "memory");
-}
-__device__ __forceinline__ float4 atom_add_sys_v4(float* a, float4 v) {
-  float4 r;
-  asm volatile("atom.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4], {%5,%6,%7,%8};"
-               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-               : "l"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
-  return r;
-}
-
 // ------------------------------------------------------------------------------------------
 // Phase: owner-side reduce of this rank's shard over all peers and write-back to all peers.
 // n4 = number of float4 elements.  Shards are contiguous: shard r = [r*per, min(n4,(r+1)*per)).
@@ -235,7 +213,7 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
       if (threadIdx.x == 0) { loc[L_NORM] = 0; loc[L_EPOCH] = epoch; }
       const uint32_t vote = 2 * epoch + (nrm2 > gm_threshold ? 1u : 0u);
       if (threadIdx.x < c.world) {
-        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[threadIdx.x] + OMLDM_PAD_VOTE + me), "r"(vote) : "memory");
+        st_relaxed_sys(c.pads[threadIdx.x] + OMLDM_PAD_VOTE + me, vote);
       }
       __threadfence_system();
       __syncthreads();
@@ -369,7 +347,7 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
       // end of stream (flush generation `drain`): tell the hub this rank has no more data
       if (drain) st_release_sys(c.pads[0] + OMLDM_PAD_VOTE + me, drain);
       // publish phi to the hub (push-based polling)
-      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + me), "r"(__float_as_uint(phi)) : "memory");
+      st_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + me, __float_as_uint(phi));
       const uint32_t sub = ld_acquire_sys(hub + 1);
       float theta = __uint_as_float(ld_relaxed_sys(hub + 2));
       if (theta <= 0.f) theta = -phi0 / 2.f;  // first sub-round of the very first round
@@ -399,11 +377,11 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
           for (int i = 0; i < k; ++i) psi += __uint_as_float(ld_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + i));
           if (psi >= eps_psi * k * phi0) {
             for (int p = 0; p < k; ++p)
-              asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[p] + OMLDM_PAD_FGM + 4), "r"(step) : "memory");
+              st_relaxed_sys(c.pads[p] + OMLDM_PAD_FGM + 4, step);
             for (int p = 0; p < k; ++p) st_release_sys(c.pads[p] + OMLDM_PAD_FGM + 3, round + 1);  // round end
           } else {
-            asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub + 2), "r"(__float_as_uint(-psi / (2.f * k))) : "memory");
-            asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub), "r"(0u) : "memory");
+            st_relaxed_sys(hub + 2, __float_as_uint(-psi / (2.f * k)));
+            st_relaxed_sys(hub, 0u);
             st_release_sys(hub + 1, sub + 1);
             st[5] += 1.f;
           }
@@ -436,10 +414,10 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
   if (grid_done(loc + L_DONE)) {
     if (threadIdx.x == 0) {
       if (me == 0) {  // hub resets the monitoring state for the new round
-        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub), "r"(0u) : "memory");
-        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(hub + 2), "r"(__float_as_uint(-phi0 / 2.f)) : "memory");
+        st_relaxed_sys(hub, 0u);
+        st_relaxed_sys(hub + 2, __float_as_uint(-phi0 / 2.f));
         for (int i = 0; i < k; ++i)
-          asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[0] + OMLDM_PAD_PHI + i), "r"(__float_as_uint(phi0)) : "memory");
+          st_relaxed_sys(c.pads[0] + OMLDM_PAD_PHI + i, __float_as_uint(phi0));
         const uint32_t sub = ld_relaxed_sys(hub + 1);
         st_release_sys(hub + 1, sub + 1);
       }
@@ -482,7 +460,7 @@ __global__ void query_reduce_kernel(Comm c, const float* vals_base, float* out_b
   float* out = out_base + 4 * (c.emulate > 1 ? me : 0);
   if (threadIdx.x < c.world * 4) {
     const int p = threadIdx.x / 4, j = threadIdx.x % 4;
-    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.pads[p] + OMLDM_PAD_QUERY + 4 * me + j), "r"(__float_as_uint(vals[j])) : "memory");
+    st_relaxed_sys(c.pads[p] + OMLDM_PAD_QUERY + 4 * me + j, __float_as_uint(vals[j]));
   }
   __threadfence_system();
   __syncthreads();
@@ -516,6 +494,10 @@ static int clamp_blocks(int blocks, size_t n, int emulate) {
 // kernels whose blocks wait on one another must be co-resident: cooperative launch
 template <typename... Args>
 static int launch_coop(void (*kern)(Args...), dim3 grid, dim3 block, cudaStream_t st, const char* name, Args... args) {
+#ifdef OMLDM_EMU   // tools/cuda_emu: every block of the launch runs concurrently (blocks and ranks wait on one another)
+  emu::launcher_concurrent(kern, grid, block, 0, st)(args...);
+  return check_launch(name);
+#endif
   if (grid.y == 1) {
     // one rank per launch: the grid is far below one wave, every block is resident, and a plain
     // launch can be captured into a CUDA graph
@@ -627,6 +609,7 @@ extern "C" int omldm_query_reduce(const omldm_comm* h, const float* vals4, float
                      c, vals4, out4, epoch);
 }
 
+#ifndef OMLDM_EMU   // CUDA IPC has no meaning in the CPU emulation
 extern "C" int omldm_ipc_export(void* dev_ptr, void* handle64_host) {
   cudaIpcMemHandle_t hnd;
   cudaError_t e = cudaIpcGetMemHandle(&hnd, dev_ptr);
@@ -653,6 +636,8 @@ extern "C" int omldm_enable_peer_access(int peer_device) {
   if (e != cudaSuccess) return set_error("cudaDeviceEnablePeerAccess", e);
   return 0;
 }
+
+#endif  // !OMLDM_EMU
 
 // Arena memory for the symmetric buffers: a dedicated cudaMalloc so that the IPC handle maps the
 // whole region at offset 0 in every peer.

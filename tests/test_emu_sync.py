@@ -1,0 +1,202 @@
+"""The fused protocol kernels of csrc/sync.cu executed on the CPU (tools/cuda_emu): k ranks emulated inside one
+launch whose blocks all run concurrently as host threads, sys-scope loads / stores / atomics mapped to host
+atomics with the same ordering.  Same checks as tests/test_sync_gpu.py, plus the FGM drain handshake."""
+import ctypes
+import math
+
+import pytest
+import torch
+
+from omldm_b200.ops import _lib
+from omldm_b200.parallel.comm import PAD_CLOCK, PAD_FGM, PAD_PHI, PipelineComm
+
+_i, _f, _u, _sz = ctypes.c_int, ctypes.c_float, ctypes.c_uint32, ctypes.c_size_t
+DEV = "cpu"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def emulator():
+    if torch.cuda.is_available():
+        pytest.skip("the emulator is for machines without a GPU")
+    import os
+    _lib.use_emulator(asan=bool(os.environ.get("OMLDM_EMU_ASAN")))
+    yield
+    _lib.stop_emulator()
+
+
+def make(k, n):
+    comm = PipelineComm(n, DEV, 0, 1, None, emulate=k)
+    return comm, torch.zeros(k, comm.n)
+
+
+def K():
+    return _lib.kernels()
+
+
+def sp():
+    return _lib.stream_ptr()
+
+
+@pytest.mark.parametrize("k", [2, 4])
+@pytest.mark.parametrize("n", [32, 1000, 5000])
+def test_allreduce_mean(k, n):
+    comm, e = make(k, n)
+    xs = [torch.randn(comm.n) for _ in range(k)]
+    for r in range(k):
+        comm.bufs[r].copy_(xs[r])
+    ref = torch.stack(xs).mean(0)
+    for _ in range(2):   # two epochs back to back: flags are monotonic
+        _lib.check(K().omldm_sync_allreduce(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0),
+                                            _u(comm.next_epoch()), _i(2), sp()), "allreduce")
+    for r in range(k):
+        assert torch.allclose(comm.bufs[r], ref, rtol=1e-5, atol=1e-6)
+        assert torch.allclose(e[r], ref, rtol=1e-5, atol=1e-6)
+    assert comm.status() == 0
+
+
+def test_allreduce_sum_delta_device_managed_epochs():
+    k, n = 3, 4096
+    comm, e = make(k, n)
+    g0 = torch.randn(comm.n)
+    e[:] = g0
+    tot = torch.zeros(comm.n)
+    for step in range(3):                       # epoch argument 0: the kernel keeps its own sequence numbers
+        deltas = [torch.randn(comm.n) for _ in range(k)]
+        for r in range(k):
+            comm.bufs[r].copy_(deltas[r])
+        tot += torch.stack(deltas).sum(0)
+        _lib.check(K().omldm_sync_allreduce(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0), _i(1), _u(0), _i(2),
+                                            sp()), "allreduce")
+        for r in range(k):
+            assert torch.allclose(e[r], g0 + tot, rtol=1e-5, atol=1e-5)
+            assert float(comm.bufs[r].abs().max()) == 0.0
+    assert comm.status() == 0
+
+
+def test_async_and_easgd():
+    k, n = 4, 2048
+    comm, e = make(k, n)
+    w0 = torch.randn(comm.n)
+    for r in range(k):
+        comm.bufs[r].copy_(w0)
+        comm.hubs[r].copy_(w0)
+        e[r] = w0
+    upd = [torch.randn(comm.n) for _ in range(k)]
+    for r in range(k):
+        comm.bufs[r].add_(upd[r])
+    _lib.check(K().omldm_sync_async(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _i(1), sp()), "async")
+    ref = w0 + torch.stack(upd).mean(0)
+    for r in range(k):
+        lo, hi = comm.shard_bounds(r)
+        assert torch.allclose(comm.hubs[r][lo:hi], ref[lo:hi], rtol=1e-5, atol=1e-5)
+        assert torch.equal(comm.bufs[r], e[r])
+    xs = [comm.bufs[r].clone() for r in range(k)]
+    centre = torch.cat([comm.hubs[r][slice(*comm.shard_bounds(r))] for r in range(k)])
+    _lib.check(K().omldm_sync_easgd(comm.struct_ptr(), _sz(comm.n), _f(0.25), _i(1), sp()), "easgd")
+    new_centre = torch.cat([comm.hubs[r][slice(*comm.shard_bounds(r))] for r in range(k)])
+    assert torch.allclose(sum(xs) + centre, sum(comm.bufs[r] for r in range(k)) + new_centre, rtol=1e-4, atol=1e-4)
+    assert sum(float((comm.bufs[r] - new_centre).norm()) for r in range(k)) < sum(float((x - centre).norm()) for x in xs)
+
+
+def test_ssp_clock_wait():
+    k, n = 4, 1024
+    comm, e = make(k, n)
+    for c in range(1, 4):
+        _lib.check(K().omldm_sync_ssp(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _u(c), _i(1),
+                                      _i(1), sp()), "ssp")
+    assert comm.status() == 0
+    for r in range(k):
+        assert comm.pads[r][PAD_CLOCK:PAD_CLOCK + k].tolist() == [3] * k
+
+
+def test_gm_votes():
+    k, n = 4, 512
+    comm, e = make(k, n)
+    for r in range(k):
+        comm.bufs[r].fill_(0.001 * (r + 1))
+    before = [b.clone() for b in comm.bufs]
+    _lib.check(K().omldm_sync_gm(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(10.0),
+                                 _u(comm.next_epoch()), _i(1), sp()), "gm")
+    for r in range(k):   # nobody violated: nothing moves
+        assert torch.equal(comm.bufs[r], before[r])
+    comm.bufs[2].fill_(1.0)
+    ref = torch.stack([b.clone() for b in comm.bufs]).mean(0)
+    _lib.check(K().omldm_sync_gm(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(10.0),
+                                 _u(comm.next_epoch()), _i(1), sp()), "gm")
+    for r in range(k):
+        assert torch.allclose(comm.bufs[r], ref, rtol=1e-5) and torch.allclose(e[r], ref, rtol=1e-5)
+    assert comm.status() == 0
+
+
+def _fgm_setup(k, n, T):
+    comm, e = make(k, n)
+    state = torch.zeros(8 * k)
+    state[1::8] = -1.0
+    fl = comm.pads[0].view(torch.float32)
+    fl[PAD_FGM + 2] = math.sqrt(T) / 2
+    fl[PAD_PHI:PAD_PHI + 16] = -math.sqrt(T)
+    return comm, e, state
+
+
+@pytest.mark.parametrize("blocks", [1, 2])
+def test_fgm_rounds(blocks):
+    k, n, T = 4, 256, 1.0
+    comm, e, state = _fgm_setup(k, n, T)
+    rounds_seen = 0
+    for step in range(1, 81):
+        for r in range(k):
+            comm.bufs[r].add_(0.0015 * (r + 1))
+        _lib.check(K().omldm_sync_fgm(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(T),
+                                      _f(0.01), _u(step), _lib.ptr(state), _i(blocks), sp()), "fgm")
+        rounds = int(state[4].item())
+        if rounds > rounds_seen:
+            rounds_seen = rounds
+            for r in range(1, k):   # after a round every replica equals the new estimate
+                assert torch.allclose(comm.bufs[r], comm.bufs[0], rtol=1e-5, atol=1e-6)
+                assert torch.allclose(e[r], comm.bufs[r], rtol=1e-5, atol=1e-6)
+        assert len(set(state.view(k, 8)[:, 0].tolist())) == 1, "ranks executed different numbers of rounds"
+        avg = torch.stack([comm.bufs[r] - e[r] for r in range(k)]).mean(0)
+        assert float(avg.norm()) <= math.sqrt(T) * 1.5
+    assert rounds_seen >= 3
+    assert comm.status() == 0
+
+
+def test_fgm_drain_terminates_and_leaves_no_round_open():
+    k, n, T = 4, 256, 1.0
+    comm, e, state = _fgm_setup(k, n, T)
+    step = 0
+    for gen in (1, 2):
+        for _ in range(30):
+            step += 1
+            for r in range(k):
+                comm.bufs[r].add_(0.004 * (r + 1))
+            _lib.check(K().omldm_sync_fgm(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(T), _f(0.01),
+                                          _u(step), _lib.ptr(state), _i(1), sp()), "fgm")
+        launches = 0
+        while True:
+            step += 1
+            launches += 1
+            _lib.check(K().omldm_sync_fgm_drain(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(T),
+                                                _f(0.01), _u(step), _lib.ptr(state), _u(gen), _i(1), sp()), "fgm_drain")
+            term = [int(comm.pads[r][PAD_FGM + 5].item()) for r in range(k)]
+            if all(t == gen for t in term):
+                break
+            assert launches < 8, f"no terminate word after {launches} drain steps: {term}"
+        assert comm.status() == 0
+        rounds = state.view(k, 8)[:, 0].tolist()
+        assert len(set(rounds)) == 1
+        for r in range(k):
+            assert int(comm.pads[r][PAD_FGM + 3].item()) == int(rounds[0])
+    assert state[4].item() >= 1
+
+
+def test_barrier_and_query_reduce():
+    k = 8
+    comm, _ = make(k, 16)
+    _lib.check(K().omldm_device_barrier(comm.struct_ptr(), _u(comm.next_epoch()), sp()), "barrier")
+    vals = torch.arange(4 * k, dtype=torch.float32)
+    out = torch.zeros(4 * k)
+    _lib.check(K().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals), _lib.ptr(out), _u(comm.next_epoch()), sp()),
+               "query_reduce")
+    assert torch.allclose(out.view(k, 4), vals.view(k, 4).sum(0).expand(k, 4))
+    assert comm.status() == 0

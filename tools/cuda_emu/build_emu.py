@@ -7,6 +7,7 @@ shim (emu_cuda.h), exposing the same `omldm_*` C ABI on host pointers.
 Source rewriting (nothing else is touched):
   kernel<<<grid, block, smem, stream>>>(args)  ->  emu::launcher(kernel, grid, block, smem, stream)(args)
   extern __shared__ T name[];                  ->  T* name = reinterpret_cast<T*>(emu::dyn_smem());
+  __shared__ T a[N], b;                        ->  T (&a)[N] = *emu::block_shared<T[N]>(id); T& b = ...  (per block)
 Headers <cuda.h>, <cuda_runtime.h>, <cuda_fp16.h>, <cooperative_groups.h>, <math_constants.h>, "ptx.cuh" and
 "host_common.h" resolve to stand-ins in the build directory.
 """
@@ -21,16 +22,37 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parents[2]
 HERE = Path(__file__).resolve().parent
 OUT = ROOT / "build" / "emu"
-# kernel files without inline PTX (umma_gemm.cu and sync.cu are tensor-core / peer-memory code: hardware only)
+# kernel files whose PTX lives behind ptx.cuh helpers that have a host meaning (sys-scope loads / stores / atomics
+# become host atomics); umma_gemm.cu (tcgen05 / TMA) is hardware only
 SOURCES = ["ingest.cu", "sparse_mcpa.cu", "cluster.cu", "linear_learners.cu", "preprocess.cu", "tree.cu",
-           "fused_pipeline.cu", "ridge_cg.cu"]
+           "fused_pipeline.cu", "ridge_cg.cu", "sync.cu"]
 
 _LAUNCH = re.compile(r"([A-Za-z_][\w:]*(?:<[^<>;(){}]*>)?)\s*<<<(.+?)>>>", re.S)
 _DYN_SMEM = re.compile(r"extern\s+__shared__\s+([\w:]+)\s+(\w+)\s*\[\s*\]\s*;")
 
 
+_SHARED = re.compile(r"(?<!extern )__shared__\s+([\w:]+)\s+([^;]+);")
+_DECL = re.compile(r"\s*(\w+)\s*((?:\[[^\]]*\])*)\s*$")
+
+
+def _shared(m: "re.Match") -> str:
+    """`__shared__ T a[N], b;` -> references bound to per-block storage (emu::block_shared)."""
+    ty, out = m.group(1), []
+    for decl in m.group(2).split(","):
+        d = _DECL.match(decl)
+        if d is None:
+            raise RuntimeError("cannot rewrite shared declaration: " + m.group(0))
+        name, dims = d.group(1), d.group(2)
+        if dims:
+            out.append(f"{ty} (&{name}){dims} = *emu::block_shared<{ty}{dims}>(__COUNTER__);")
+        else:
+            out.append(f"{ty}& {name} = *emu::block_shared<{ty}>(__COUNTER__);")
+    return " ".join(out)
+
+
 def rewrite(text: str) -> str:
     text = _DYN_SMEM.sub(r"\1* \2 = reinterpret_cast<\1*>(emu::dyn_smem());", text)
+    text = _SHARED.sub(_shared, text)
     return _LAUNCH.sub(r"emu::launcher(\1, \2)", text)
 
 
@@ -54,7 +76,9 @@ def build(asan: bool = False) -> Path:
         dst.write_text(rewrite((ROOT / "csrc" / name).read_text()))
         cpps.append(dst)
     out = OUT / ("libomldm_emu_asan.so" if asan else "libomldm_emu.so")
-    flags = ["-std=c++17", "-fPIC", "-shared", "-pthread", "-I", str(src_dir), "-I", str(ROOT / "include"),
+    # -Bsymbolic: the real kernel library may already be loaded RTLD_GLOBAL in the same process and defines the
+    # same symbols (check_launch, the kernels themselves); the emulator must call its own
+    flags = ["-std=c++17", "-fPIC", "-shared", "-pthread", "-Wl,-Bsymbolic", "-I", str(src_dir), "-I", str(ROOT / "include"),
              "-Wall", "-Wno-unknown-pragmas", "-Wno-unused-variable", "-Wno-sign-compare"]
     flags += ["-O1", "-g", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
     cmd = ["g++", *flags, *map(str, cpps), "-o", str(out)]

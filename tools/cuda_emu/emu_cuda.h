@@ -5,12 +5,14 @@
 //     (compute-sanitizer is not available on the GPU pool this project is developed on).
 // Semantics: blocks of a launch run one after the other; the threads of a block run concurrently and are
 // NOT warp-synchronous (like independent thread scheduling); __syncthreads / __syncwarp / shuffles are real
-// barriers that tolerate threads which already returned; `__shared__` variables become function-level statics
-// (one block at a time), dynamic shared memory is an exactly-sized heap block; atomics are host atomics.
-// Not emulated: inline PTX, tensor cores, TMA, cooperative multi-block grids, streams (everything is synchronous).
+// barriers that tolerate threads which already returned; every `__shared__` declaration gets per-block storage
+// (filled with 0xCD, like uninitialised memory), dynamic shared memory is an exactly-sized heap block; atomics are
+// host atomics.  `launcher_concurrent` runs all blocks of a grid at once, for kernels whose blocks (or emulated
+// ranks) wait on one another.  Not emulated: tensor cores, TMA, NVLS multimem, streams (everything is synchronous).
 #pragma once
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <condition_variable>
 #include <cstdint>
@@ -49,7 +51,6 @@ inline int2 make_int2(int x, int y) { return {x, y}; }
 #define __forceinline__ inline
 #define __launch_bounds__(...)
 #define __align__(n) __attribute__((aligned(n)))
-#define __shared__ static
 #define __grid_constant__
 #ifndef __restrict__
 #define __restrict__ __restrict
@@ -84,6 +85,9 @@ struct BlockCtx {
   Barrier bar;
   std::vector<Warp> warps;
   char* dyn = nullptr;
+  std::mutex shared_m;
+  std::vector<std::pair<int, void*>> shared;        // (declaration id, storage) of the `__shared__` variables
+  ~BlockCtx() { for (auto& kv : shared) std::free(kv.second); }
 };
 
 inline thread_local uint3 t_threadIdx, t_blockIdx;
@@ -92,6 +96,21 @@ inline thread_local BlockCtx* t_ctx = nullptr;
 inline thread_local int t_lane = 0, t_warp = 0;
 
 inline void* dyn_smem() { return t_ctx->dyn; }
+
+// storage of one `__shared__` declaration (build_emu.py rewrites `__shared__ T x[N];` into a reference bound to this):
+// one instance per block, created by the first thread that reaches the declaration, filled with 0xCD like
+// uninitialised memory so that a read-before-write shows up as garbage rather than as a convenient zero
+template <class T>
+inline T* block_shared(int id) {
+  BlockCtx* c = t_ctx;
+  std::lock_guard<std::mutex> l(c->shared_m);
+  for (auto& kv : c->shared)
+    if (kv.first == id) return static_cast<T*>(kv.second);
+  void* p = std::malloc(sizeof(T));
+  std::memset(p, 0xCD, sizeof(T));
+  c->shared.emplace_back(id, p);
+  return static_cast<T*>(p);
+}
 
 template <class Body>
 void run_grid(dim3 g, dim3 b, size_t smem, Body&& body) {
@@ -151,6 +170,54 @@ Launcher<KArgs...> launcher(void (*k)(KArgs...), dim3 g, dim3 b, size_t smem = 0
   return Launcher<KArgs...>{k, g, b, smem};
 }
 
+// Every block of the grid at once (kernels whose blocks - or emulated ranks - wait on one another).
+template <class Body>
+void run_grid_concurrent(dim3 g, dim3 b, size_t smem, Body&& body) {
+  const int T = static_cast<int>(b.x * b.y * b.z);
+  const int nb = static_cast<int>(g.x * g.y * g.z);
+  if (T <= 0 || nb <= 0) return;
+  std::vector<BlockCtx> ctx(static_cast<size_t>(nb));
+  for (auto& c : ctx) {
+    c.warps = std::vector<Warp>(static_cast<size_t>((T + 31) / 32));
+    c.dyn = smem ? static_cast<char*>(std::malloc(smem)) : nullptr;
+    c.bar.reset(T);
+    for (size_t w = 0; w < c.warps.size(); ++w) c.warps[w].bar.reset(std::min(32, T - static_cast<int>(w) * 32));
+  }
+  auto worker = [&](int blk, int t) {
+    t_blockDim = b;
+    t_gridDim = g;
+    t_ctx = &ctx[static_cast<size_t>(blk)];
+    t_threadIdx = {static_cast<unsigned>(t) % b.x, (static_cast<unsigned>(t) / b.x) % b.y, static_cast<unsigned>(t) / (b.x * b.y)};
+    t_blockIdx = {static_cast<unsigned>(blk) % g.x, (static_cast<unsigned>(blk) / g.x) % g.y, static_cast<unsigned>(blk) / (g.x * g.y)};
+    t_lane = t & 31;
+    t_warp = t >> 5;
+    body();
+    t_ctx->warps[static_cast<size_t>(t_warp)].bar.drop();
+    t_ctx->bar.drop();
+  };
+  std::vector<std::thread> th;
+  th.reserve(static_cast<size_t>(nb) * T);
+  for (int blk = 0; blk < nb; ++blk)
+    for (int t = 0; t < T; ++t) th.emplace_back(worker, blk, t);
+  for (auto& x : th) x.join();
+  for (auto& c : ctx) std::free(c.dyn);
+}
+template <class... KArgs>
+struct ConcurrentLauncher {
+  void (*k)(KArgs...);
+  dim3 g, b;
+  size_t smem;
+  template <class... A>
+  void operator()(A&&... a) const {
+    auto kk = k;
+    run_grid_concurrent(g, b, smem, [&] { kk(static_cast<KArgs>(a)...); });
+  }
+};
+template <class... KArgs>
+ConcurrentLauncher<KArgs...> launcher_concurrent(void (*k)(KArgs...), dim3 g, dim3 b, size_t smem = 0, void* = nullptr) {
+  return ConcurrentLauncher<KArgs...>{k, g, b, smem};
+}
+
 template <class T>
 inline uint64_t to_bits(T v) { uint64_t u = 0; static_assert(sizeof(T) <= 8, "shuffle payload"); std::memcpy(&u, &v, sizeof(T)); return u; }
 template <class T>
@@ -177,6 +244,9 @@ inline T shfl(T v, int src_lane) {
 // ---------------------------------------------------------------- synchronisation / warp primitives
 inline void __syncthreads() { emu::t_ctx->bar.sync(); }
 inline void __syncwarp(unsigned = 0xffffffffu) { emu::t_ctx->warps[static_cast<size_t>(emu::t_warp)].bar.sync(); }
+// a real sleep: spin loops are bounded by iteration counts calibrated for GPU time, and thousands of host threads
+// share a few cores - a waiting thread must get out of the way of the one it waits for
+inline void __nanosleep(unsigned) { std::this_thread::sleep_for(std::chrono::microseconds(20)); }
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
@@ -284,6 +354,7 @@ inline cudaError_t cudaMalloc(void** p, size_t n) { *p = std::malloc(n); return 
 inline cudaError_t cudaFree(void* p) { std::free(p); return cudaSuccess; }
 template <class F> inline cudaError_t cudaFuncSetAttribute(F, int, int) { return cudaSuccess; }
 template <class F> inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) { *n = 1; return cudaSuccess; }
+inline cudaError_t cudaLaunchCooperativeKernel(const void*, dim3, dim3, void**, size_t, cudaStream_t) { return cudaErrorInvalidValue; }
 template <class T> inline cudaError_t cudaGetSymbolAddress(void** p, T& sym) { *p = const_cast<void*>(static_cast<const void*>(&sym)); return cudaSuccess; }
 
 // cooperative groups: grids are emulated with ONE block, so a grid barrier is a block barrier
