@@ -52,7 +52,7 @@ def kernels() -> ctypes.CDLL:
     return _kernels
 
 
-def use_emulator(asan: bool = False) -> ctypes.CDLL:
+def use_emulator(asan: bool = False, tsan: bool = False) -> ctypes.CDLL:
     """Route `kernels()` to the CUDA-on-CPU emulation of the PTX-free kernel files (tools/cuda_emu): the real
     kernel sources compiled by g++, one host thread per CUDA thread, operating on host tensors.  For tests on
     machines without a GPU (`functional.use_impl("emu")`); never used on a GPU box."""
@@ -62,10 +62,11 @@ def use_emulator(asan: bool = False) -> ctypes.CDLL:
     spec = importlib.util.spec_from_file_location("omldm_build_emu", root / "tools" / "cuda_emu" / "build_emu.py")
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
-    out = mod.OUT / ("libomldm_emu_asan.so" if asan else "libomldm_emu.so")
+    tsan = tsan or bool(os.environ.get("OMLDM_EMU_TSAN"))
+    out = mod.OUT / ("libomldm_emu_tsan.so" if tsan else "libomldm_emu_asan.so" if asan else "libomldm_emu.so")
     srcs = [root / "csrc" / s for s in mod.SOURCES] + list((root / "tools" / "cuda_emu").glob("*"))
     if not out.exists() or any(p.stat().st_mtime > out.stat().st_mtime for p in srcs):
-        mod.build(asan)
+        mod.build(asan, tsan)
     _kernels = ctypes.CDLL(str(out))
     _kernels.omldm_last_error.restype = ctypes.c_char_p
     _kernels.omldm_launch_count.restype = ctypes.c_longlong

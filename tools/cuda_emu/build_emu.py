@@ -56,8 +56,8 @@ def rewrite(text: str) -> str:
     return _LAUNCH.sub(r"emu::launcher(\1, \2)", text)
 
 
-def build(asan: bool = False) -> Path:
-    src_dir = OUT / ("src_asan" if asan else "src")
+def build(asan: bool = False, tsan: bool = False) -> Path:
+    src_dir = OUT / ("src_tsan" if tsan else "src_asan" if asan else "src")
     if src_dir.exists():
         shutil.rmtree(src_dir)
     src_dir.mkdir(parents=True)
@@ -75,12 +75,15 @@ def build(asan: bool = False) -> Path:
         dst = src_dir / (Path(name).stem + ".cpp")
         dst.write_text(rewrite((ROOT / "csrc" / name).read_text()))
         cpps.append(dst)
-    out = OUT / ("libomldm_emu_asan.so" if asan else "libomldm_emu.so")
+    out = OUT / ("libomldm_emu_tsan.so" if tsan else "libomldm_emu_asan.so" if asan else "libomldm_emu.so")
     # -Bsymbolic: the real kernel library may already be loaded RTLD_GLOBAL in the same process and defines the
     # same symbols (check_launch, the kernels themselves); the emulator must call its own
     flags = ["-std=c++17", "-fPIC", "-shared", "-pthread", "-Wl,-Bsymbolic", "-I", str(src_dir), "-I", str(ROOT / "include"),
              "-Wall", "-Wno-unknown-pragmas", "-Wno-unused-variable", "-Wno-sign-compare"]
-    flags += ["-O1", "-g", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
+    if tsan:
+        flags += ["-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer"]
+    else:
+        flags += ["-O1", "-g", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
     cmd = ["g++", *flags, *map(str, cpps), "-o", str(out)]
     p = subprocess.run(cmd, capture_output=True, text=True)
     if p.returncode != 0:
@@ -91,4 +94,4 @@ def build(asan: bool = False) -> Path:
 
 
 if __name__ == "__main__":
-    print(build("--asan" in sys.argv))
+    print(build("--asan" in sys.argv, "--tsan" in sys.argv))

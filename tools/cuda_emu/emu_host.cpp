@@ -19,3 +19,17 @@ extern "C" void omldm_add_launch_count(long long n) { omldm::g_launches.fetch_ad
 extern "C" void omldm_reset_launch_count() { omldm::g_launches.store(0); }
 extern "C" int omldm_abi_version() { return 1; }
 extern "C" int omldm_is_emulator() { return 1; }
+
+// ---- sanitizer self-tests: a kernel with a missing __syncthreads (data race on shared memory) and its fixed twin
+namespace {
+void race_kernel(float* out, int with_barrier) {
+  float (&s)[64] = *emu::block_shared<float[64]>(900001);
+  s[threadIdx.x] = static_cast<float>(threadIdx.x);
+  if (with_barrier) __syncthreads();
+  out[threadIdx.x] = s[(threadIdx.x + 1) & 63];
+}
+}  // namespace
+extern "C" int omldm_emu_selftest_shared(float* out64, int with_barrier) {
+  emu::launcher(race_kernel, dim3(1), dim3(64))(out64, with_barrier);
+  return 0;
+}
