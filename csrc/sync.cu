@@ -30,7 +30,7 @@ struct Comm {
 
 constexpr int LOCAL_WORDS = 64;  // private scratch words per (emulated) rank
 // local scratch word indices
-enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4, L_EPOCH = 5, L_CLOCK = 6, L_STEP = 7 };
+enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4, L_EPOCH = 5, L_CLOCK = 6, L_STEP = 7, L_ROT = 8 };
 
 // A sequence number passed as 0 means "device managed": the kernel uses (stored value + 1) and the
 // block that finishes last stores it back, so the identical launch can be replayed from a CUDA graph.
@@ -243,6 +243,67 @@ sync_allreduce_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float sc
   }
   wait_all(c, me, OMLDM_PAD_EXIT, seq_exit);
   local_tail(buf, e, n, mode);
+}
+
+// ------------------------------------------------------------------------------------------
+// Synchronous for additive statistics with the reduce-scatter moved INTO the producer
+// (ROADMAP item 0; protocol modelled and race-tested in parallel/fake_backend.py::fused_scatter_step).
+// The symmetric buffer of every rank holds THREE rotating copies of the model-sized delta, bufs[p] + r*n.
+//   push   (step s, rotation cur = s mod 3): the producer adds its delta, shard by shard, straight into the shard
+//          OWNER's copy `cur` with system-scope reductions - no barrier before it, so it overlaps the skew
+//          between ranks.  Today a stand-alone kernel over the local delta; the Gram GEMM's TMA reduce-add
+//          epilogue takes this role once it addresses the owners' buffers directly.
+//   gather: ONE flag barrier, then every rank adds each owner's reduced shard to its private global vector e
+//          and the owner clears its shard of copy (s+2) mod 3 - the copy read in step s-1.  The barrier of step s
+//          proves that every peer has finished step s-1, and nobody accumulates into that copy before the barrier
+//          of step s+1, which needs this rank's arrival: no exit barrier.
+__global__ void __launch_bounds__(256)
+sync_scatter_push_kernel(Comm c, float* delta_base, size_t delta_stride, size_t n, uint32_t step_arg) {
+  const int me = my_rank(c);
+  const uint32_t* loc = my_local(c);
+  const uint32_t step = resolve_seq(step_arg, loc + L_ROT);
+  const size_t cur = step % 3u;
+  float4* d4 = reinterpret_cast<float4*>(delta_base + delta_stride * (c.emulate > 1 ? me : 0));
+  const size_t n4 = n / 4;
+  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    const float4 v = d4[i];
+    const int owner = static_cast<int>(i / per);
+    if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)       // e.g. the unused lower triangle of a Gram delta
+      red_add_sys_v4(c.bufs[owner] + cur * n + 4 * i, v);
+    d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+sync_scatter_gather_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, uint32_t epoch_arg,
+                           uint32_t step_arg) {
+  const int me = my_rank(c);
+  uint32_t* loc = my_local(c);
+  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_EPOCH);
+  const uint32_t step = resolve_seq(step_arg, loc + L_ROT);
+  const size_t cur = step % 3u, clr = (step + 2u) % 3u;
+  float4* e4 = reinterpret_cast<float4*>(e_base + e_stride * (c.emulate > 1 ? me : 0));
+  const size_t n4 = n / 4;
+  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t lo = per * me, hi = lo + per < n4 ? lo + per : n4;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const uint32_t seq_entry = 2 * epoch + 1;
+  if (blockIdx.x == 0) {
+    __threadfence_system();                     // this rank's pushes (previous kernel on the stream) before its flag
+    signal_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+  }
+  wait_all(c, me, OMLDM_PAD_ENTRY, seq_entry);
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    const int owner = static_cast<int>(i / per);
+    const float4 v = ld_peer_v4(reinterpret_cast<const float4*>(c.bufs[owner] + cur * n) + i);
+    e4[i] = f4_add(e4[i], f4_scale(v, scale));
+    if (i >= lo && i < hi) reinterpret_cast<float4*>(c.bufs[me] + clr * n)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (grid_done(loc + L_DONE)) {
+    if (threadIdx.x == 0) { loc[L_EPOCH] = epoch; loc[L_ROT] = step; }
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -540,6 +601,28 @@ extern "C" int omldm_sync_gm(const omldm_comm* h, float* e_local, size_t n, floa
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_allreduce_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_gm_kernel",
                      c, e_local, n, n, scale, mode, epoch, threshold);
+}
+
+// `n` = model size; the symmetric buffers hold 3 * n floats.  step / epoch 0 = device managed.
+extern "C" int omldm_sync_scatter_push(const omldm_comm* h, float* delta_local, size_t n, uint32_t step, int blocks,
+                                       void* stream) {
+  if (check_world(h, n)) return -1;
+  if (!delta_local) return set_error_msg("sync_scatter_push: the local delta is required");
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_scatter_push_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream),
+                     "sync_scatter_push_kernel", c, delta_local, n, n, step);
+}
+extern "C" int omldm_sync_scatter_gather(const omldm_comm* h, float* e_local, size_t n, float scale, uint32_t epoch,
+                                         uint32_t step, int blocks, void* stream) {
+  if (check_world(h, n)) return -1;
+  if (!e_local) return set_error_msg("sync_scatter_gather: the global vector e is required");
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_scatter_gather_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream),
+                     "sync_scatter_gather_kernel", c, e_local, n, n, scale, epoch, step);
 }
 
 extern "C" int omldm_sync_async(const omldm_comm* h, float* e_local, size_t n, float scale, int mode, int blocks,

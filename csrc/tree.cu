@@ -46,7 +46,7 @@ ht_accumulate_kernel(const float* __restrict__ Z, int ld, int d, int B, const in
       // prequential prediction = majority class of the leaf before this record is added
       float best = 0.f; int pred = -1;
       for (int k = 0; k < C; ++k) {
-        const float v = cnt[s * C + k];
+        const float v = __ldcg(&cnt[s * C + k]);   // other warps add to these counts concurrently (mini-batch semantics)
         if (v > best) { best = v; pred = k; }
       }
       miss = pred != c;

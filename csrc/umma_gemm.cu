@@ -39,11 +39,17 @@ struct GemmSmem {
   static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-template <int BN, bool MN_MAJOR>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, int ldc, int M, int N, int K,
-                 int k_per_split, int flags) {
+// Per-peer output maps of the scatter variant: the 128-row tile block-row [m0, m0 + 128) is reduced into the
+// accumulation buffer of the GPU that owns those rows (rows_per_owner rows each, a multiple of 32).
+struct PeerMaps {
+  CUtensorMap tm[16];
+  int rows_per_owner;
+};
+
+template <int BN, bool MN_MAJOR, bool PEER>
+__device__ __forceinline__ void umma_gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                                               const PeerMaps* pm, float* __restrict__ C, int ldc, int M, int N, int K,
+                                               int k_per_split, int flags) {
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * BN;
   if ((flags & GEMM_UPPER_ONLY) && m0 > n0 + BN - 1) return;  // tile strictly below the diagonal
@@ -67,7 +73,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (flags & GEMM_TMA_EPILOGUE) tma_prefetch_desc(&tmC);
+    if (!PEER && (flags & GEMM_TMA_EPILOGUE)) tma_prefetch_desc(&tmC);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -184,8 +190,14 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         fence_proxy_async();
         __syncwarp();
         if (r == 0) {
-          if (accumulate) tma_reduce_add_2d(&tmC, slot, col0, m0 + q * 32);
-          else tma_store_2d(&tmC, slot, col0, m0 + q * 32);
+          if constexpr (PEER) {
+            // reduce-scatter inside the GEMM: this 32-row strip goes to its owner's buffer over NVLink
+            const int row0 = m0 + q * 32;
+            tma_reduce_add_2d(&pm->tm[row0 / pm->rows_per_owner], slot, col0, row0);
+          } else {
+            if (accumulate) tma_reduce_add_2d(&tmC, slot, col0, m0 + q * 32);
+            else tma_store_2d(&tmC, slot, col0, m0 + q * 32);
+          }
           tma_commit_group();
         }
       }
@@ -227,6 +239,24 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tc_fence_after();
     tmem_dealloc<TMEM_COLS>(tmem_base);
   }
+}
+
+template <int BN, bool MN_MAJOR>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, int ldc, int M, int N, int K,
+                 int k_per_split, int flags) {
+  umma_gemm_body<BN, MN_MAJOR, false>(tmA, tmB, tmC, nullptr, C, ldc, M, N, K, k_per_split, flags);
+}
+
+// Gram / outer-product GEMM whose epilogue IS the reduce-scatter: every output strip is TMA-reduce-added into the
+// buffer of the GPU that owns its rows (peer memory), so the transfer rides under the MMAs tile by tile.
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+umma_gemm_scatter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ PeerMaps pm, int M, int N, int K, int k_per_split, int flags) {
+  umma_gemm_body<BN, true, true>(tmA, tmB, pm.tm[0], &pm, nullptr, 0, M, N, K, k_per_split,
+                                 flags | GEMM_ACCUMULATE | GEMM_TMA_EPILOGUE);
 }
 
 // ------------------------------------------------------------------ host side
@@ -344,4 +374,49 @@ extern "C" int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb
   }
   return dispatch_bn<true>(tmA, tmB, bn, C, ldc, M, N, K, ksplit, flags,
                            static_cast<cudaStream_t>(stream));
+}
+
+// C_peers[p] = base of GPU p's accumulation matrix (M x N, pitch ldc, peer-mapped; the caller picks the rotating
+// copy).  Rows [p * rows_per_owner, (p + 1) * rows_per_owner) of the product are reduced into C_peers[p] only.
+extern "C" int omldm_gemm_outer_scatter(const float* A, int lda, const float* B, int ldb, float* const* C_peers,
+                                        int n_peers, int rows_per_owner, int ldc, int M, int N, int K, int ksplit,
+                                        int flags, void* stream) {
+  if ((lda & 31) || (ldb & 31))
+    return set_error_msg("gemm_outer_scatter: lda/ldb must be multiples of 32 floats (padded record rows)");
+  if ((reinterpret_cast<uintptr_t>(A) & 127) || (reinterpret_cast<uintptr_t>(B) & 127))
+    return set_error_msg("gemm_outer_scatter: operands must be 128-byte aligned");
+  if (M > lda || N > ldb) return set_error_msg("gemm_outer_scatter: M/N exceed the row pitch");
+  if (n_peers < 1 || n_peers > 16) return set_error_msg("gemm_outer_scatter: 1..16 peers");
+  if (rows_per_owner < 32 || (rows_per_owner & 31) || static_cast<long long>(rows_per_owner) * n_peers < M)
+    return set_error_msg("gemm_outer_scatter: rows_per_owner must be a multiple of 32 and cover M");
+  if (ldc & 3) return set_error_msg("gemm_outer_scatter: ldc must be a multiple of 4 floats");
+  if (flags & GEMM_MN_SLAB2D) return set_error_msg("gemm_outer_scatter: the 2-D slab producer is not supported");
+  PeerMaps pm;
+  memset(&pm, 0, sizeof(pm));
+  pm.rows_per_owner = rows_per_owner;
+  for (int p = 0; p < n_peers; ++p) {
+    if (reinterpret_cast<uintptr_t>(C_peers[p]) & 15) return set_error_msg("gemm_outer_scatter: C must be 16-byte aligned");
+    if (encode_c(&pm.tm[p], C_peers[p], M, N, ldc)) return -1;
+  }
+  for (int p = n_peers; p < 16; ++p) pm.tm[p] = pm.tm[0];
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB;
+  if (encode_mnmajor(&tmA, A, K, lda, BM / 32)) return -1;
+  if (encode_mnmajor(&tmB, B, K, ldb, bn / 32)) return -1;
+  if (ksplit < 1) ksplit = 1;
+  const int k_per_split = ((K + ksplit - 1) / ksplit + BK - 1) / BK * BK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto go = [&](auto kern, int smem, int BNv) -> int {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm scatter)", e);
+    dim3 grid((M + BM - 1) / BM, (N + BNv - 1) / BNv, (K + k_per_split - 1) / k_per_split);
+    kern<<<grid, GEMM_THREADS, smem, st>>>(tmA, tmB, pm, M, N, K, k_per_split, flags);
+    return check_launch("umma_gemm_scatter_kernel");
+  };
+  switch (bn) {
+    case 32: return go(umma_gemm_scatter_kernel<32>, GemmSmem<32>::TOTAL, 32);
+    case 64: return go(umma_gemm_scatter_kernel<64>, GemmSmem<64>::TOTAL, 64);
+    case 128: return go(umma_gemm_scatter_kernel<128>, GemmSmem<128>::TOTAL, 128);
+    default: return go(umma_gemm_scatter_kernel<256>, GemmSmem<256>::TOTAL, 256);
+  }
 }

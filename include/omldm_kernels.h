@@ -191,6 +191,23 @@ enum {
  * mode 1 (additive statistics): buf holds a delta; e += scale * sum(buf_i); buf <- 0. */
 int omldm_sync_allreduce(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
                          uint32_t epoch, int blocks, void* stream);
+/* gemm_outer whose epilogue IS the reduce-scatter (ROADMAP item 0; no counterpart in the reference): the rows
+ * [p * rows_per_owner, (p + 1) * rows_per_owner) of C (+)= A^T B are TMA-reduce-added into C_peers[p] (host array of
+ * n_peers peer-mapped base pointers, all with pitch ldc), so the transfer to the shard owners overlaps the MMAs tile
+ * by tile.  rows_per_owner: multiple of 32.  Pair with omldm_sync_scatter_gather (explicit step). */
+int omldm_gemm_outer_scatter(const float* A, int lda, const float* B, int ldb, float* const* C_peers, int n_peers,
+                             int rows_per_owner, int ldc, int M, int N, int K, int ksplit, int flags, void* stream);
+/* Synchronous for additive statistics with the reduce-scatter moved into the producer (no counterpart in the
+ * reference).  The symmetric buffers hold THREE rotating copies of the n-float delta (bufs[p] + r * n).
+ * push  : adds the local delta (then cleared) shard by shard into the shard owners' copy `step mod 3` with
+ *         system-scope reductions; needs no barrier.  Stand-in for a producer that reduces into the owners itself.
+ * gather: one flag barrier, e += scale * (every owner's reduced shard), owner clears its shard of copy
+ *         (step + 2) mod 3; no exit barrier.  Call push then gather on the same stream, once per step, on every rank.
+ * step / epoch = 0: device managed (replayable from a CUDA graph). */
+int omldm_sync_scatter_push(const omldm_comm* comm_host, float* delta_local, size_t n, uint32_t step, int blocks,
+                            void* stream);
+int omldm_sync_scatter_gather(const omldm_comm* comm_host, float* e_local, size_t n, float scale, uint32_t epoch,
+                              uint32_t step, int blocks, void* stream);
 /* Asynchronous push/pull of one worker. mode 0: hub += scale*(buf - e); buf = e = hub.
  * mode 1 (additive delta): hub += scale*buf; e = hub; buf = 0.  No barrier. */
 int omldm_sync_async(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,

@@ -226,6 +226,7 @@ class GpuORR(GpuLearner):
         self._cg = None
         self._cg_host = None
         self._cg_evt = None
+        self._scatter = None
 
     def n_flat(self, d):
         ld = F.pad32(d + 2)
@@ -260,6 +261,21 @@ class GpuORR(GpuLearner):
             self.solves = 0
             torch.cuda.synchronize(self.device)
 
+    def use_scatter_gemm(self, driver) -> None:
+        """`syncFusion: "gemm"`: the Gram update reduces straight into the shard owners' rotating copies
+        (ops.gemm.gemm_outer_scatter) instead of the local delta."""
+        k = driver.k
+        if self.ld % k or (self.ld // k) % 32:
+            raise ValueError(f"syncFusion=gemm needs ld / world to be a multiple of 32 (ld = {self.ld}, world = {k})")
+        self._scatter = driver
+
+    def _gram(self, Z, ks, n):
+        if self._scatter is not None and Z.is_cuda:
+            F.gemm_outer_scatter(Z, Z, self._scatter.peer_copy_ptrs(), self.ld // self._scatter.k, self.ld,
+                                 ksplit=ks, upper_only=True, m=n, n=n)
+        else:
+            F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+
     def fit_batch(self, Z):
         n = self.d + 2
         ks = max(1, min(self.ksplit, Z.shape[0] // 64))
@@ -268,13 +284,13 @@ class GpuORR(GpuLearner):
             # they touch disjoint outputs and both only read Z
             main = torch.cuda.current_stream(self.device)
             self._fork.wait_stream(main)
-            F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+            self._gram(Z, ks, n)
             with torch.cuda.stream(self._fork):
                 F.sq_residual(Z, self.d, self.wt, self.stats)
             main.wait_stream(self._fork)
             return
         F.sq_residual(Z, self.d, self.wt, self.stats)    # prequential squared error with current w
-        F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+        self._gram(Z, ks, n)
 
     def host_tick(self):
         self._since += 1

@@ -77,13 +77,29 @@ class GpuPipeline:
         n = lrn.n_flat(d)
         single = self.protocol == "SingleLearner"
         world = 1 if single else self.world
-        self.comm = PipelineComm(n, self.device, self.rank if not single else 0, world, self.group,
-                                 emulate=1, with_hub=True)
-        e = torch.zeros(self.comm.n, device=self.device) if lrn.needs_e() else None
-        lrn.bind(d, self.comm.buf, e)
+        from ..parallel.fused import wants_scatter
+        scatter_delta = None
+        if wants_scatter(self.protocol, lrn.merge_mode, self.request.trainingConfiguration, world, self.impl) \
+                and lrn.needs_e() and n % 4 == 0:
+            # reduce-scatter moved into the producer: the learner keeps a private delta, the symmetric region holds
+            # three rotating copies of it (parallel/fused.py::ScatterSynchronousDriver)
+            self.comm = PipelineComm(3 * n, self.device, self.rank, world, self.group, emulate=1, with_hub=False)
+            scatter_delta = torch.zeros(n, device=self.device)
+            e = torch.zeros(n, device=self.device)
+            lrn.bind(d, scatter_delta, e)
+        else:
+            self.comm = PipelineComm(n, self.device, self.rank if not single else 0, world, self.group,
+                                     emulate=1, with_hub=True)
+            e = torch.zeros(self.comm.n, device=self.device) if lrn.needs_e() else None
+            lrn.bind(d, self.comm.buf, e)
         self.driver = make_driver(self.protocol, self.comm, e, lrn.merge_mode,
                                   self.request.trainingConfiguration, self.impl, self.group, self.max_msg_params,
-                                  pipelined_ok=hasattr(lrn, "use_delta_buffers"))
+                                  pipelined_ok=hasattr(lrn, "use_delta_buffers"), scatter_delta=scatter_delta)
+        if getattr(self.driver, "gemm_fused", False):
+            if hasattr(lrn, "use_scatter_gemm"):
+                lrn.use_scatter_gemm(self.driver)
+            else:
+                self.driver.gemm_fused = False          # learners without a scatter GEMM keep the push kernel
         if hasattr(self.driver, "on_switch"):
             lrn.use_delta_buffers(self.driver.bufs, self.driver.drain)
             self.driver.on_switch = lrn.switch_delta

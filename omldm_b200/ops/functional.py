@@ -20,7 +20,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
-from .gemm import gemm_outer, gemm_tn  # noqa: F401  (re-exported)
+from .gemm import gemm_outer, gemm_outer_scatter, gemm_tn  # noqa: F401  (re-exported)
 
 _IMPL = "auto"
 

@@ -95,3 +95,21 @@ def gemm_outer(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None
         ctypes.c_int(K), ctypes.c_int(ksplit), ctypes.c_int(flags), _lib.stream_ptr())
     _lib.check(rc, "omldm_gemm_outer")
     return out
+
+
+def gemm_outer_scatter(a: torch.Tensor, b: torch.Tensor, peer_ptrs, rows_per_owner: int, ldc: int, *,
+                       ksplit: int = 1, upper_only: bool = False, m: int | None = None, n: int | None = None) -> None:
+    """C (+)= a[K,:M]^T @ b[K,:N] with the rows of C reduced straight into their owners' buffers: `peer_ptrs[p]` is
+    the (peer-mapped) base address of GPU p's accumulation matrix with pitch `ldc`, which receives the rows
+    [p * rows_per_owner, (p + 1) * rows_per_owner).  CUDA only (csrc/umma_gemm.cu::umma_gemm_scatter_kernel)."""
+    _check2d(a, "a"); _check2d(b, "b")
+    K = a.shape[0]
+    M = a.shape[1] if m is None else m
+    N = b.shape[1] if n is None else n
+    arr = (ctypes.c_void_p * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
+    flags = ACCUMULATE | (UPPER_ONLY if upper_only else 0)
+    rc = _lib.kernels().omldm_gemm_outer_scatter(
+        _lib.ptr(a), ctypes.c_int(a.stride(0)), _lib.ptr(b), ctypes.c_int(b.stride(0)), arr,
+        ctypes.c_int(len(peer_ptrs)), ctypes.c_int(rows_per_owner), ctypes.c_int(ldc), ctypes.c_int(M),
+        ctypes.c_int(N), ctypes.c_int(K), ctypes.c_int(ksplit), ctypes.c_int(flags), _lib.stream_ptr())
+    _lib.check(rc, "omldm_gemm_outer_scatter")

@@ -207,6 +207,78 @@ class PipelinedSynchronousDriver(SyncDriver):
         self.counters.ship(self.comm.n, self.k)
 
 
+class ScatterSynchronousDriver(SyncDriver):
+    """Synchronous protocol for ADDITIVE statistics with the reduce-scatter moved into the producer (opt-in
+    `syncFusion: "scatter"`; csrc/sync.cu::sync_scatter_push_kernel / sync_scatter_gather_kernel, protocol modelled
+    in parallel/fake_backend.py::fused_scatter_step).  The learner accumulates into a PRIVATE delta; the symmetric
+    region holds three rotating copies into which every rank's delta is reduced at the shard owners without a
+    barrier, then one flag barrier and a gather-add into the private global vector - one barrier per step instead
+    of two and no separate reduce pass.  The push is a stand-alone kernel today; it disappears once the Gram GEMM's
+    TMA reduce-add epilogue addresses the owners' buffers itself (ROADMAP item 0)."""
+    protocol = "Synchronous"
+
+    def __init__(self, comm, e, merge_mode, tc, impl="fused", group=None, max_msg_params=2000, delta=None):
+        super().__init__(comm, e, merge_mode, tc, impl, group, max_msg_params)
+        if self.mode != 1 or delta is None or e is None:
+            raise ValueError("the scatter-fused synchronisation needs additive statistics, a private delta and e")
+        if comm.n % 3 or (comm.n // 3) % 4 or delta.numel() != comm.n // 3:
+            raise ValueError("the symmetric region must hold three copies of the delta")
+        self.n = comm.n // 3
+        self.delta = delta
+        # `syncFusion: "gemm"`: the learner's GEMM reduces into the owners' copies itself (gemm_outer_scatter), the push
+        # kernel disappears.  The rotating copy is then chosen on the HOST (it is baked into the GEMM's tensor maps):
+        # `hstep` counts protocol steps, one CUDA graph per hstep mod 3 (`graph_key`).
+        self.gemm_fused = (str(cfg(tc, ["syncFusion"], "none")).lower() == "gemm" and self.impl == "fused")
+        self.hstep = 1
+
+    def account(self):
+        self.counters.ship(self.n, self.k)
+
+    def graph_key(self):
+        return self.hstep % 3 if self.gemm_fused else 0
+
+    def peer_copy_ptrs(self):
+        """Base addresses (one per rank) of the rotating copy that the current step accumulates into."""
+        off = 4 * self.n * (self.hstep % 3)
+        return [int(b) + self.comm._off_buf + off for b in self.comm.region.bases]
+
+    def host_tick(self) -> bool:
+        due = super().host_tick()
+        if due:
+            self.hstep += 1
+        return due
+
+    def step(self) -> bool:
+        c = self.comm
+        if self.impl == "fused":
+            k = _lib.kernels()
+            if self.gemm_fused:
+                # explicit rotation step (non-zero, congruent to hstep mod 3) so that a captured launch stays valid
+                # for every later step with the same hstep mod 3; the epoch stays device managed
+                _lib.check(k.omldm_sync_scatter_gather(c.struct_ptr(), self._eptr(), _sz(self.n), _f(self.scale), _u(0),
+                                                       _u(3 + self.hstep % 3), _i(self.blocks), _lib.stream_ptr()),
+                           "sync_scatter_gather")
+                return True
+            _lib.check(k.omldm_sync_scatter_push(c.struct_ptr(), _lib.ptr(self.delta), _sz(self.n), _u(0),
+                                                 _i(self.blocks), _lib.stream_ptr()), "sync_scatter_push")
+            _lib.check(k.omldm_sync_scatter_gather(c.struct_ptr(), self._eptr(), _sz(self.n), _f(self.scale), _u(0),
+                                                   _u(0), _i(self.blocks), _lib.stream_ptr()), "sync_scatter_gather")
+            return True
+        d = self._dist()
+        if d is not None:
+            d.all_reduce(self.delta, group=self.group)
+        self.e.add_(self.delta, alpha=self.scale)
+        self.delta.zero_()
+        return True
+
+
+def wants_scatter(protocol: str, merge_mode: str, tc, world: int, impl: str) -> bool:
+    """`syncFusion: "scatter"` / `"gemm"` apply to Synchronous pipelines of additive learners on more than one GPU."""
+    return (protocol == "Synchronous" and merge_mode == "sum" and world > 1
+            and str(cfg(tc, ["syncFusion"], "none")).lower() in ("scatter", "gemm")
+            and int(cfg(tc, ["syncEvery", "syncPeriod"], 1)) == 1)
+
+
 class AsynchronousDriver(SyncDriver):
     protocol = "Asynchronous"
 
@@ -433,7 +505,11 @@ DRIVERS = {"CentralizedTraining": LocalDriver, "SingleLearner": LocalDriver, "Sy
 
 
 def make_driver(protocol: str, comm: PipelineComm, e, merge_mode: str, tc, impl: str = "fused", group=None,
-                max_msg_params: int = 2000, pipelined_ok: bool = False) -> SyncDriver:
+                max_msg_params: int = 2000, pipelined_ok: bool = False, scatter_delta=None) -> SyncDriver:
+    if scatter_delta is not None:
+        drv = ScatterSynchronousDriver(comm, e, merge_mode, tc, impl, group, max_msg_params, delta=scatter_delta)
+        drv.counters.protocol = protocol
+        return drv
     cls = DRIVERS.get(protocol, AsynchronousDriver)
     if comm.k == 1:
         cls = LocalDriver

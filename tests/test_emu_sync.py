@@ -200,3 +200,35 @@ def test_barrier_and_query_reduce():
                "query_reduce")
     assert torch.allclose(out.view(k, 4), vals.view(k, 4).sum(0).expand(k, 4))
     assert comm.status() == 0
+
+
+@pytest.mark.parametrize("k,blocks", [(2, 1), (4, 1), (3, 2)])
+def test_scatter_push_gather_three_rotating_copies(k, blocks):
+    """Reduce-scatter moved into the producer (sync_scatter_push / sync_scatter_gather): after every step each rank's
+    global vector is the exact running sum of all deltas; device-managed step and epoch counters; a barrier-type
+    kernel in between (a query) must not disturb the rotation."""
+    n = 96 * k                                   # model size; the symmetric buffers hold three copies
+    comm = PipelineComm(3 * n, DEV, 0, 1, None, emulate=k)
+    e = torch.zeros(k, n)
+    delta = torch.zeros(k, n)
+    run = torch.zeros(n)
+    g = torch.Generator().manual_seed(k)
+    for step in range(7):
+        d = torch.randint(-3, 4, (k, n), generator=g).float()       # integers: every partial sum is exact
+        d[:, 5:9] = 0.0                                             # zero vectors are skipped by the push
+        delta.copy_(d)
+        run += d.sum(0)
+        _lib.check(K().omldm_sync_scatter_push(comm.struct_ptr(), _lib.ptr(delta), _sz(n), _u(0), _i(blocks), sp()), "push")
+        _lib.check(K().omldm_sync_scatter_gather(comm.struct_ptr(), _lib.ptr(e), _sz(n), _f(1.0), _u(0), _u(0),
+                                                 _i(blocks), sp()), "gather")
+        for r in range(k):
+            assert torch.equal(e[r], run), f"step {step}, rank {r}"
+        assert float(delta.abs().max()) == 0.0                      # the push clears the local delta
+        if step == 3:                                               # consumes an epoch, not a rotation step
+            _lib.check(K().omldm_device_barrier(comm.struct_ptr(), _u(0), sp()), "barrier")
+    assert comm.status() == 0
+    # at rest exactly one copy per owner still holds data (the one the next-but-one step clears)
+    per = (n // 4 + k - 1) // k * 4
+    for r in range(k):
+        copies = comm.bufs[r].view(3, n)[:, r * per:(r + 1) * per]
+        assert int((copies.abs().sum(1) > 0).sum()) <= 1

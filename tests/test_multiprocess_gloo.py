@@ -19,7 +19,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, proto, learner, hyper, kind, q):
+def _worker(rank, world, port, proto, learner, hyper, kind, q, tc_extra=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from omldm_b200.engine import Engine
@@ -28,22 +28,23 @@ def _worker(rank, world, port, proto, learner, hyper, kind, q):
     d = 10
     eng = Engine(JobParameters(parallelism=world, testSetSize=16), rank, world, "cpu", impl="nccl")
     eng.handle_request({"id": 1, "request": "Create", "learner": {"name": learner, "hyperParameters": hyper},
-                        "trainingConfiguration": {"protocol": proto, "nFeatures": d, "threshold": 0.01}})
+                        "trainingConfiguration": dict({"protocol": proto, "nFeatures": d, "threshold": 0.01},
+                                                      **(tc_extra or {}))})
     for i in range(12):
         eng.train_batch(R.generate_batch(kind, d, 64, seed=3, batch_index=2 * i + rank, n_aux=3), d)
     out = eng.handle_request({"id": 1, "request": "Query", "requestId": 4})
     js = eng.terminate()
     p = eng.pipelines[1]
-    flat = p.comm.buf.clone() if p.built else None
+    flat = (p.learner.e.clone() if getattr(p.driver, "delta", None) is not None else p.comm.buf.clone()) if p.built else None
     q.put((rank, out, None if js is None else js.to_dict(), None if flat is None else flat.numpy()))
     dist.destroy_process_group()
 
 
-def _launch(proto, learner, hyper, kind):
+def _launch(proto, learner, hyper, kind, tc_extra=None):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, proto, learner, hyper, kind, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, proto, learner, hyper, kind, q, tc_extra)) for r in range(2)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
@@ -75,3 +76,14 @@ def test_two_workers_orr_sum_merge_and_single_learner():
     resp = json.loads(out0[0])
     assert resp["protocol"] == "SingleLearner" and out1 == []
     assert resp["dataFitted"] == 2 * (12 * 64 - 16)         # both workers forwarded to the one learner
+
+
+def test_scatter_fused_synchronisation_matches_plain_synchronous():
+    """`syncFusion: "scatter"` (private delta + three rotating symmetric copies) on the torch.distributed path:
+    same global statistics and the same answer as the plain Synchronous driver."""
+    plain = _launch("Synchronous", "ORR", {"lambda": 1.0, "solveEvery": 1}, 1)
+    fused = _launch("Synchronous", "ORR", {"lambda": 1.0, "solveEvery": 1}, 1, {"syncFusion": "scatter"})
+    assert np.allclose(fused[0][3], fused[1][3])                       # both replicas hold the same global matrix
+    fp, ff = [json.loads(o) for o in plain[0][1]], [json.loads(o) for o in fused[0][1]]
+    assert len(fp) == len(ff) and fp[-1]["dataFitted"] == ff[-1]["dataFitted"] == 2 * (12 * 64 - 16)
+    assert abs(fp[-1]["score"] - ff[-1]["score"]) < 1e-4 and abs(fp[-1]["cumulativeLoss"] - ff[-1]["cumulativeLoss"]) < 1e-3

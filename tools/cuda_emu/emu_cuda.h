@@ -297,7 +297,18 @@ template <class T> inline T atomicMin(T* p, T v) {
 }
 
 // ---------------------------------------------------------------- loads, bit casts, math
-template <class T> inline T __ldcg(const T* p) { return *p; }
+// ld.global.cg is a single-copy-atomic access at L2: kernels use it for words that other threads update with atomics
+template <class T> inline T __ldcg(const T* p) {
+  if constexpr (std::is_arithmetic<T>::value && (sizeof(T) == 4 || sizeof(T) == 8)) {
+    using U = typename std::conditional<sizeof(T) == 4, uint32_t, uint64_t>::type;
+    const U u = __atomic_load_n(reinterpret_cast<const U*>(p), __ATOMIC_RELAXED);
+    T v;
+    std::memcpy(&v, &u, sizeof(T));
+    return v;
+  } else {
+    return *p;
+  }
+}
 template <class T> inline T __ldg(const T* p) { return *p; }
 template <class T> inline T __ldcs(const T* p) { return *p; }
 template <class T> inline void __stcg(T* p, T v) { *p = v; }
