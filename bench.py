@@ -189,7 +189,9 @@ def main() -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(3 * n_rot + 1):     # untimed set-up: every batch buffer gets its CUDA graph captured
+    # untimed set-up: every batch buffer gets its CUDA graph captured (one per rotating copy with syncFusion=gemm)
+    n_keys = n_rot * (3 if str(tc.get("syncFusion", "")).lower() == "gemm" else 1)
+    for i in range(3 * n_keys + 1):
         step_device(i)
     for i in range(args.warmup):
         step_device(i)
@@ -271,7 +273,8 @@ def main() -> None:
                               f"(sparse->dense on the GPU); working set per step > 126 MB L2") if sparse else
                              f"inputs rotate over {n_rot} distinct batches = {n_rot * B * ld * 4 / 1e6:.0f} MB > 126 MB L2",
                        "sparse_direct": bool(sparse and args.sparse_direct),
-                       "sync_every": p.driver.sync_every, "model_bytes": p.comm.n * 4,
+                       "sync_every": p.driver.sync_every, "model_bytes": getattr(p.driver, "n", p.comm.n) * 4,
+                       "sync_fusion": str(tc.get("syncFusion", "none")),
                        "sync_transport": "NVLS multimem" if getattr(p.comm, "multicast", False) else "P2P ld/st over NVLink"},
             "clocks": clocks, "numa_node": numa, "e2e": e2e, "gpu_launches": launches, "comm_status": status,
         }
