@@ -270,7 +270,7 @@ class Engine:
                 p.driver.begin_step()          # fork: overlapped all-reduce of the previous step's delta
         if self.holdout_enabled and self.params.testSetSize > 0:
             self._ensure_holdout(ld)
-            if Z.is_cuda and F.native(Z):
+            if F.native(Z):                     # (true for CUDA batches; also under the CPU kernel emulation)
                 if self._count_dev is None:
                     self._count_dev = torch.tensor([self.count], dtype=torch.int64, device=self.device)
                 F.holdout_swap_dev(Z, self.holdout, d, self._count_dev)   # 2-in-10 holdout, evict-then-train
@@ -294,7 +294,7 @@ class Engine:
         """Multi-tenant fast path: all exact-mode linear pipelines without preprocessors advance in ONE
         kernel launch, one warp per pipeline (tiny models are latency bound; the launch is shared)."""
         from .models.learners import GpuLinear
-        if not (Z.is_cuda and F.native(Z)):
+        if not F.native(Z):
             return ()
         group = [p for p in self.pipelines.values()
                  if p.built and p.protocol != "SingleLearner" and isinstance(p.learner, GpuLinear)
@@ -307,7 +307,8 @@ class Engine:
             self._multi_desc = F.make_linear_descs(
                 [(p.learner.w, p.learner.stats, p.learner.d, p.learner.kind, p.learner.variant, p.learner.C,
                   p.learner.eps, p.learner.lam) for p in group], self.device)
-        with torch.cuda.nvtx.range("linear_exact_multi"):
+        import contextlib
+        with (torch.cuda.nvtx.range("linear_exact_multi") if Z.is_cuda else contextlib.nullcontext()):
             F.linear_exact_multi(Z, d, self._multi_desc, len(group))
         return group
 

@@ -433,3 +433,28 @@ def test_engine_pipelines_on_emulated_kernels(learner, kind, pre):
     assert ct["fitted"] == ce["fitted"] > 0
     assert torch.allclose(bt, be, rtol=5e-3, atol=5e-4)
     assert abs(ct["loss_sum"] - ce["loss_sum"]) <= 5e-3 * max(1.0, abs(ct["loss_sum"]))
+
+
+def test_engine_multi_tenant_exact_and_device_count_holdout_on_emulated_kernels():
+    """Three exact-mode linear pipelines advance in ONE launch (one warp each), the holdout uses the device-resident
+    record count (the graph-replayable variant): same models as three separate torch-path pipelines."""
+    d, B = 12, 40
+    batches = [R.generate_batch(R.KIND_BINARY, d, B, seed=21, batch_index=i) for i in range(4)]
+    specs = [{"name": "PA", "hyperParameters": {"C": 0.1, "trainingMode": "exact"}},
+             {"name": "SVM", "hyperParameters": {"C": 0.5, "trainingMode": "exact"}},
+             {"name": "PA", "hyperParameters": {"C": 1.0, "updateType": "PA-II", "trainingMode": "exact"}}]
+    out = []
+    for impl in ("torch", "emu"):
+        with F.use_impl(impl):
+            e = _mk_engine(specs[0], d=d)
+            for j, sp_ in enumerate(specs[1:], start=2):
+                e.handle_request({"id": j, "request": "Create", "learner": sp_,
+                                  "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": d}})
+            for b in batches:
+                e.train_batch(b.clone(), d)
+            out.append(([e.pipelines[i].learner.w.clone() for i in (1, 2, 3)], e.holdout.clone(), e.count,
+                        None if e._count_dev is None else int(e._count_dev.item())))
+    (wt, ht, ct, _), (we, he, ce, cdev) = out
+    assert ct == ce == cdev == 4 * B and torch.equal(ht, he)
+    for a, b in zip(wt, we):
+        assert torch.allclose(a, b, rtol=2e-3, atol=2e-4)
