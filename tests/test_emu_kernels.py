@@ -458,3 +458,21 @@ def test_engine_multi_tenant_exact_and_device_count_holdout_on_emulated_kernels(
     assert ct == ce == cdev == 4 * B and torch.equal(ht, he)
     for a, b in zip(wt, we):
         assert torch.allclose(a, b, rtol=2e-3, atol=2e-4)
+
+
+def test_engine_hoeffding_tree_on_emulated_kernels():
+    d, B, C = 6, 120, 3
+    batches = [R.generate_batch(R.KIND_CLUSTERS, d, B, seed=31, batch_index=i, n_aux=C) for i in range(6)]   # y = cluster id
+    probe = R.generate_batch(R.KIND_CLUSTERS, d, 64, seed=31, batch_index=9, n_aux=C)
+    out = []
+    for impl in ("torch", "emu"):
+        with F.use_impl(impl):
+            e = _mk_engine({"name": "HT", "hyperParameters": {"nClasses": C, "gracePeriod": 60, "delta": 1e-3, "tieThreshold": 0.2}}, d=d)
+            for b in batches:
+                e.train_batch(b.clone(), d)
+            l = e.pipelines[1].learner
+            out.append((list(l.tree.feature), [round(float(t), 4) for t in l.tree.threshold], l.counters(),
+                        l.predict(probe.clone()).clone()))
+    (ft, tt, ct, pt), (fe, te, ce, pe) = out
+    assert ft == fe and tt == te and len(ft) >= 3, "the same splits must be chosen"
+    assert ct["fitted"] == ce["fitted"] and torch.equal(pt, pe)
