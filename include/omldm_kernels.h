@@ -155,6 +155,14 @@ int omldm_ht_accumulate(const float* Z, int ld, int d, int B, const int* feature
                         float* sq, int* leaf_out, double* stats, void* stream);
 int omldm_ht_route(const float* Z, int ld, int B, const int* feature, const float* threshold, const int* left,
                    const int* right, int* leaf_out, void* stream);
+/* Hoeffding split test + tree growth on the device (SURVEY K-L8): per leaf with >= grace new records, best / runner-up
+ * information gain over features x n_points Gaussian thresholds, Hoeffding bound (delta, tie), then the accepted
+ * splits are applied in ascending leaf order (node numbering as in the sequential algorithm).  2 <= C <= 16.
+ * n_nodes_dev: device int, nodes in use (updated); checked: per-node record total at its last test;
+ * decision: cap x int4 scratch (16-byte aligned); n_splits_out: optional device int. */
+int omldm_ht_split(int* feature, float* threshold, int* left, int* right, int* n_nodes_dev, int cap, int C, int d,
+                   float* cnt, const float* sum, const float* sq, float* checked, float grace, float delta, float tie,
+                   int n_points, void* decision, int* n_splits_out, void* stream);
 
 /* ------------------------------------------------------------------ fused protocol kernels (sync.cu)
  * worker<->hub synchronisation, network/FlinkNetwork.scala:242-293 (send / broadcast) and the

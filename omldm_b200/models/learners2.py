@@ -359,6 +359,15 @@ class GpuHT(GpuLearner):
         self.sum = torch.zeros(cap, C, d, device=dev)
         self.sq = torch.zeros(cap, C, d, device=dev)
         self.checked = {0: 0.0}
+        # on-device split test (csrc/tree.cu::omldm_ht_split): the tree then grows without a host round trip and the
+        # host mirror is refreshed lazily (`_pull_tree`)
+        self.split_on_device = (str(_h(self.hyper, ["splitOnDevice"], "true")).lower() in ("1", "true", "yes")
+                                and 2 <= C <= 16)
+        self.n_nodes_dev = torch.ones(1, dtype=torch.int32, device=dev)
+        self.checked_dev = torch.zeros(cap, device=dev)
+        self._decision = torch.zeros(cap, 4, dtype=torch.int32, device=dev)
+        self._n_splits = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._mirror_stale = False
 
     # ---- training ---------------------------------------------------------------------------------------
     def fit_batch(self, Z):
@@ -375,8 +384,35 @@ class GpuHT(GpuLearner):
                         self.cnt, self.sum, self.sq, self.stats)
         self._maybe_split()
 
+    def _pull_tree(self) -> None:
+        """Refresh the host mirror (structure + leaf class counts) from the device arrays."""
+        if not self._mirror_stale:
+            return
+        t = self.tree
+        n = int(self.n_nodes_dev.item())
+        t.feature = self.feature[:n].tolist()
+        t.threshold = [float(v) for v in self.threshold[:n].tolist()]
+        t.left, t.right = self.left[:n].tolist(), self.right[:n].tolist()
+        cnt_h = self.cnt[:n].detach().cpu().double().numpy()
+        chk = self.checked_dev[:n].tolist()
+        t.leaves = {}
+        self.checked = {}
+        for i in range(n):
+            if t.feature[i] < 0:
+                lf = O._Leaf(t.n_classes, self.d)
+                lf.counts = cnt_h[i].copy()
+                t.leaves[i] = lf
+                self.checked[i] = float(chk[i])
+        self._mirror_stale = False
+
     def _maybe_split(self):
         t = self.tree
+        if self.split_on_device and F.native(self.cnt):
+            F.ht_split(self.feature, self.threshold, self.left, self.right, self.n_nodes_dev, t.n_classes, self.d,
+                       self.cnt, self.sum, self.sq, self.checked_dev, float(t.grace), float(t.delta), float(t.tie),
+                       int(t.n_split_points), self._decision, self._n_splits)
+            self._mirror_stale = True
+            return
         n_nodes = len(t.feature)
         cnt_h = self.cnt[:n_nodes].detach().cpu().double().numpy()
         for leaf in [i for i in range(n_nodes) if t.feature[i] < 0]:
@@ -423,6 +459,9 @@ class GpuHT(GpuLearner):
     def to_oracle(self):
         t = self.tree
         if self.mode != "exact":
+            self._pull_tree()
+            t.fitted = int(self.stats[2].item())
+            t.cum_loss = float(self.stats[0].item())
             cnt_h = self.cnt[: len(t.feature)].detach().cpu().double().numpy()
             for i in range(len(t.feature)):
                 if t.feature[i] < 0:
@@ -442,7 +481,7 @@ class GpuHT(GpuLearner):
         sd["tree"] = self.to_oracle()
         if self.mode != "exact":
             sd["ht"] = {k: getattr(self, k).detach().cpu().clone() for k in
-                        ("feature", "threshold", "left", "right", "cnt", "sum", "sq")}
+                        ("feature", "threshold", "left", "right", "cnt", "sum", "sq", "n_nodes_dev", "checked_dev")}
             sd["checked"] = dict(self.checked)
         return sd
 
@@ -453,6 +492,10 @@ class GpuHT(GpuLearner):
             for k, v in sd["ht"].items():
                 getattr(self, k).copy_(v.to(self.device))
             self.checked = dict(sd["checked"])
+            if "n_nodes_dev" not in sd["ht"]:          # checkpoint written before the on-device split test
+                self.n_nodes_dev.fill_(len(self.tree.feature))
+                for i, v in self.checked.items():
+                    self.checked_dev[int(i)] = float(v)
 
 
 GPU_LEARNERS = {c.name: c for c in (GpuPA, GpuRegressorPA, GpuSVM, GpuORR, GpuKMeans, GpuMultiClassPA, GpuNN, GpuHT)}

@@ -691,6 +691,16 @@ def ht_class(y: torch.Tensor, C: int) -> torch.Tensor:
     return c.clamp(0, C - 1)
 
 
+def ht_split(feature, threshold, left, right, n_nodes_dev, C, d, cnt, sums, sq, checked, grace, delta, tie,
+             n_points, decision, n_splits) -> None:
+    """Hoeffding split test and tree growth on the device (csrc/tree.cu::ht_split_eval_kernel /
+    ht_split_apply_kernel): no host round trip.  Native only; the torch path keeps the host oracle's split test."""
+    cap = feature.shape[0]
+    _lib.check(_k().omldm_ht_split(_p(feature), _p(threshold), _p(left), _p(right), _p(n_nodes_dev), _i(cap), _i(C),
+                                   _i(d), _p(cnt), _p(sums), _p(sq), _p(checked), _f(grace), _f(delta), _f(tie),
+                                   _i(n_points), _p(decision), _p(n_splits), _lib.stream_ptr()), "ht_split")
+
+
 def ht_accumulate(Z, d, feature, threshold, left, right, slot, C, cnt, sums, sq, stats, leaf_out=None) -> None:
     """Route every record to its leaf and add it to the leaf's (count, sum, sum-of-squares) statistics."""
     B = Z.shape[0]

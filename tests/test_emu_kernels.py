@@ -471,6 +471,7 @@ def test_engine_hoeffding_tree_on_emulated_kernels():
             for b in batches:
                 e.train_batch(b.clone(), d)
             l = e.pipelines[1].learner
+            l.to_oracle()                                   # pulls the device-grown tree into the host mirror
             out.append((list(l.tree.feature), [round(float(t), 4) for t in l.tree.threshold], l.counters(),
                         l.predict(probe.clone()).clone()))
     (ft, tt, ct, pt), (fe, te, ce, pe) = out
@@ -478,3 +479,63 @@ def test_engine_hoeffding_tree_on_emulated_kernels():
     # summation order of the float atomics may legitimately tip the choice
     assert len(ft) >= 3 and len(fe) >= 3 and ft[0] == fe[0] and abs(tt[0] - te[0]) < 1e-3
     assert ct["fitted"] == ce["fitted"] and float((pt == pe).float().mean()) >= 0.9
+
+
+def test_ht_split_kernel_matches_the_host_split_test():
+    """On-device Hoeffding split test (ht_split_eval / ht_split_apply) against the fp64 host oracle on the same leaf
+    statistics: same decision, feature and threshold for the root, children seeded with the same class priors, node
+    numbering in ascending leaf order."""
+    import numpy as np
+    from omldm_b200.oracle import learners as O
+    d, C, B = 7, 3, 600
+    Z = staged(R.KIND_CLUSTERS, d, B, seed=41, n_aux=C)
+    cap = 15
+    for grace, expect_split in ((200, True), (5000, False)):
+        hyper = {"nClasses": C, "gracePeriod": grace, "delta": 1e-3, "tieThreshold": 0.2}
+        feature = torch.full((cap,), -1, dtype=torch.int32)
+        threshold = torch.zeros(cap)
+        left = torch.full((cap,), -1, dtype=torch.int32)
+        right = torch.full((cap,), -1, dtype=torch.int32)
+        slot = torch.arange(cap, dtype=torch.int32)
+        cnt, sm, sq = torch.zeros(cap, C), torch.zeros(cap, C, d), torch.zeros(cap, C, d)
+        st = torch.zeros(4, dtype=torch.float64)
+        with F.use_impl("torch"):
+            F.ht_accumulate(Z, d, feature, threshold, left, right, slot, C, cnt, sm, sq, st)
+        # host oracle on the same statistics
+        t = O.HoeffdingTree(hyper)
+        t.ensure_init(d)
+        lf = O._Leaf(C, d)
+        lf.counts = cnt[0].double().numpy().copy()
+        n = np.maximum(lf.counts[:, None], 0.0) * np.ones((1, d))
+        s_, q_ = sm[0].double().numpy(), sq[0].double().numpy()
+        lf.n = n
+        lf.mean = np.divide(s_, n, out=np.zeros_like(s_), where=n > 0)
+        lf.m2 = np.maximum(q_ - n * lf.mean ** 2, 0.0)
+        t.leaves[0] = lf
+        if lf.counts.sum() >= grace:
+            t._try_split(0, lf)
+        # device
+        n_nodes = torch.ones(1, dtype=torch.int32)
+        checked = torch.zeros(cap)
+        decision = torch.zeros(cap, 4, dtype=torch.int32)
+        n_splits = torch.zeros(1, dtype=torch.int32)
+        cnt_before = cnt.clone()
+        with F.use_impl("emu"):
+            F.ht_split(feature, threshold, left, right, n_nodes, C, d, cnt, sm, sq, checked, float(grace), 1e-3, 0.2, 10,
+                       decision, n_splits)
+        assert (int(n_splits) == 1) == expect_split == (len(t.feature) == 3)
+        if not expect_split:
+            assert int(n_nodes) == 1 and int(feature[0]) == -1 and torch.equal(cnt, cnt_before)
+            continue
+        assert int(n_nodes) == 3 and int(feature[0]) == t.feature[0]
+        assert abs(float(threshold[0]) - t.threshold[0]) < 1e-3 * max(1.0, abs(t.threshold[0]))
+        assert (int(left[0]), int(right[0])) == (1, 2) and feature[1:3].tolist() == [-1, -1]
+        for ch in (1, 2):
+            assert np.allclose(cnt[ch].numpy(), t.leaves[ch].counts, rtol=2e-3, atol=1e-2)
+            assert abs(float(checked[ch]) - float(cnt[ch].sum())) < 1e-3
+        assert float(checked[0]) == float(cnt_before[0].sum())
+        # a second call right away: nothing has changed since the last check, nothing splits
+        with F.use_impl("emu"):
+            F.ht_split(feature, threshold, left, right, n_nodes, C, d, cnt, sm, sq, checked, float(grace), 1e-3, 0.2, 10,
+                       decision, n_splits)
+        assert int(n_splits) == 0 and int(n_nodes) == 3
