@@ -406,9 +406,16 @@ extern "C" int omldm_gemm_outer_scatter(const float* A, int lda, const float* B,
   if (ksplit < 1) ksplit = 1;
   const int k_per_split = ((K + ksplit - 1) / ksplit + BK - 1) / BK * BK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static bool attr_set[16][4] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
   auto go = [&](auto kern, int smem, int BNv) -> int {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm scatter)", e);
+    bool& done = attr_set[dev & 15][BNv == 32 ? 0 : BNv == 64 ? 1 : BNv == 128 ? 2 : 3];
+    if (!done) {                                   // once per device and tile shape, never inside a graph capture
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm scatter)", e);
+      done = true;
+    }
     dim3 grid((M + BM - 1) / BM, (N + BNv - 1) / BNv, (K + k_per_split - 1) / k_per_split);
     kern<<<grid, GEMM_THREADS, smem, st>>>(tmA, tmB, pm, M, N, K, k_per_split, flags);
     return check_launch("umma_gemm_scatter_kernel");
