@@ -467,7 +467,7 @@ def test_engine_hoeffding_tree_on_emulated_kernels():
     out = []
     for impl in ("torch", "emu"):
         with F.use_impl(impl):
-            e = _mk_engine({"name": "HT", "hyperParameters": {"nClasses": C, "gracePeriod": 60, "delta": 1e-3, "tieThreshold": 0.2}}, d=d)
+            e = _mk_engine({"name": "HT", "hyperParameters": {"nClasses": C, "gracePeriod": 60, "delta": 1e-3, "tieThreshold": 0.2, "maxNodes": 31}}, d=d)
             for b in batches:
                 e.train_batch(b.clone(), d)
             l = e.pipelines[1].learner
