@@ -307,6 +307,39 @@ sync_scatter_gather_kernel(Comm c, float* e_base, size_t e_stride, size_t n, flo
 }
 
 // ------------------------------------------------------------------------------------------
+// SingleLearner forwarding (ForwardingWorker -> CentralizedMLServer, MLNodeGenerator.scala:27,56; forced for HT and
+// centralised K-means, FlinkSpoke.scala:204-209): every worker stores its mini-batch into rank 0's symmetric
+// buffer, slot (seq & 1), position `me`; rank 0 trains on the k concatenated batches.  Flags: arrival of batch
+// `seq` in rank 0's ENTRY words; rank 0 announces "batches <= seq - 1 are consumed" in every pad's EXIT word 0 when
+// it enters step seq, and a sender waits for "seq - 2 consumed" before it overwrites that slot - senders may run two
+// steps ahead, nobody else waits.
+__global__ void __launch_bounds__(256)
+sync_forward_kernel(Comm c, const float* z_base, size_t z_stride, size_t n, uint32_t seq) {
+  const int me = my_rank(c);
+  uint32_t* loc = my_local(c);
+  if (me == 0 && blockIdx.x == 0 && threadIdx.x < c.world)     // everything up to seq - 1 was trained on (stream order)
+    st_release_sys(c.pads[threadIdx.x] + OMLDM_PAD_EXIT, seq - 1u);
+  if (threadIdx.x == 0 && seq > 2u) {
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(c.pads[me] + OMLDM_PAD_EXIT) - (seq - 2u)) < 0) {
+      if (++spins > 64) __nanosleep(spins > 4096 ? 256 : 32);
+      if (spins > SPIN_LIMIT) { flag_timeout(c, me, 1u); break; }
+    }
+  }
+  __syncthreads();
+  const float4* src = reinterpret_cast<const float4*>(z_base + z_stride * (c.emulate > 1 ? me : 0));
+  float4* dst = reinterpret_cast<float4*>(c.bufs[0] + (static_cast<size_t>(seq & 1u) * c.world + me) * n);
+  const size_t n4 = n / 4;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride)
+    st_peer_v4(dst + i, src[i]);
+  if (grid_done(loc + L_DONE)) {                 // includes __threadfence_system(): the rows before the flag
+    if (threadIdx.x == 0) st_release_sys(c.pads[0] + OMLDM_PAD_ENTRY + me, seq);
+  }
+  if (me == 0) wait_all(c, me, OMLDM_PAD_ENTRY, seq);
+}
+
+// ------------------------------------------------------------------------------------------
 // Asynchronous / SSP: one worker pushes scale*(buf - e) into the owning hub shards with
 // returning vector atomics and installs the fresh hub value locally.  No rendezvous.
 __global__ void __launch_bounds__(256)
@@ -623,6 +656,18 @@ extern "C" int omldm_sync_scatter_gather(const omldm_comm* h, float* e_local, si
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_scatter_gather_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream),
                      "sync_scatter_gather_kernel", c, e_local, n, n, scale, epoch, step);
+}
+
+// n floats per rank and batch (multiple of 4); rank 0's symmetric buffer holds 2 * world * n floats; seq = 1, 2, ...
+extern "C" int omldm_sync_forward(const omldm_comm* h, const float* z_local, size_t n, uint32_t seq, int blocks,
+                                  void* stream) {
+  if (check_world(h, n)) return -1;
+  if (!z_local || seq == 0u) return set_error_msg("sync_forward: a batch and a sequence number >= 1 are required");
+  Comm c = to_comm(h);
+  blocks = clamp_blocks(blocks, n, h->emulate);
+  dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(sync_forward_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_forward_kernel",
+                     c, z_local, n, n, seq);
 }
 
 extern "C" int omldm_sync_async(const omldm_comm* h, float* e_local, size_t n, float scale, int mode, int blocks,

@@ -216,6 +216,12 @@ int omldm_sync_scatter_push(const omldm_comm* comm_host, float* delta_local, siz
                             void* stream);
 int omldm_sync_scatter_gather(const omldm_comm* comm_host, float* e_local, size_t n, float scale, uint32_t epoch,
                               uint32_t step, int blocks, void* stream);
+/* SingleLearner forwarding (mlworkers.ForwardingWorker -> CentralizedMLServer, MLNodeGenerator.scala:27,56): every
+ * rank stores its n-float mini-batch into rank 0's symmetric buffer (2 * world * n floats: slot seq & 1, position =
+ * rank); rank 0 returns once all world batches of `seq` have arrived and trains on them.  seq = 1, 2, ... (same on
+ * every rank); senders may run two steps ahead of rank 0. */
+int omldm_sync_forward(const omldm_comm* comm_host, const float* z_local, size_t n, uint32_t seq, int blocks,
+                       void* stream);
 /* Asynchronous push/pull of one worker. mode 0: hub += scale*(buf - e); buf = e = hub.
  * mode 1 (additive delta): hub += scale*buf; e = hub; buf = 0.  No barrier. */
 int omldm_sync_async(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,

@@ -78,6 +78,10 @@ class Engine:
         self._sparse_nnz: Optional[int] = None
         self._srows: List[Optional[torch.Tensor]] = [None, None]
         self._srows_i = 0
+        self.forward_peer = str(self.params.extra.get("forwardTransport", "peer")).lower() != "nccl"
+        self._fwd_comm = None            # SingleLearner forwarding channel (created on first use, collective)
+        self._fwd_n = 0
+        self._fwd_seq = 0
 
     # ============================================================================ control plane
     def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
@@ -316,6 +320,8 @@ class Engine:
         """SingleLearner: workers forward raw records to the one learner at hub 0."""
         if self.world == 1:
             return Z
+        if self.impl == "fused" and Z.is_cuda and F.native(Z) and self.forward_peer:
+            return self._forward_fused(Z)
         import torch.distributed as dist
         if self.rank == 0:
             parts = [torch.empty_like(Z) for _ in range(self.world)]
@@ -323,6 +329,29 @@ class Engine:
             return torch.cat(parts, 0)
         dist.gather(Z, None, dst=0, group=self.group)
         return Z
+
+    def _forward_fused(self, Z: torch.Tensor) -> torch.Tensor:
+        """Forwarding over NVLink peer memory (csrc/sync.cu::sync_forward_kernel): every rank stores its batch into
+        rank 0's symmetric buffer, rank 0 gets a view of the world concatenated batches.  Collective; every rank
+        must pass batches of the same shape."""
+        import ctypes
+        from .parallel.comm import PipelineComm
+        B, ld = Z.shape
+        n = B * ld
+        if self._fwd_comm is None or self._fwd_n != n:
+            if self._fwd_comm is not None:
+                self._fwd_comm.close()
+            self._fwd_comm = PipelineComm(2 * self.world * n, self.device, self.rank, self.world, self.group,
+                                          emulate=1, with_hub=False)
+            self._fwd_n, self._fwd_seq = n, 0
+        self._fwd_seq += 1
+        c = self._fwd_comm
+        _lib.check(_lib.kernels().omldm_sync_forward(c.struct_ptr(), _lib.ptr(Z), ctypes.c_size_t(n),
+                                                     ctypes.c_uint32(self._fwd_seq), ctypes.c_int(0),
+                                                     _lib.stream_ptr()), "sync_forward")
+        if self.rank != 0:
+            return Z
+        return c.buf.view(2, self.world * B, ld)[self._fwd_seq & 1]
 
     # ---- end-to-end path: pinned host slot -> device -> train -> loss back to the host -------------
     def train_batch_host(self, Z_host: torch.Tensor, d: int, **kw) -> torch.Tensor:
@@ -526,6 +555,8 @@ class Engine:
         for p in self.pipelines.values():
             if p.built and p.comm.device.type == "cuda":
                 st |= p.comm.status()
+        if self._fwd_comm is not None and self.device.type == "cuda":
+            st |= self._fwd_comm.status()
         return st
 
     # ============================================================================ checkpoint
@@ -554,3 +585,6 @@ class Engine:
         for p in self.pipelines.values():
             p.close()
         self.pipelines = {}
+        if self._fwd_comm is not None:
+            self._fwd_comm.close()
+            self._fwd_comm = None

@@ -92,6 +92,28 @@ check("fgm drain: every rank executed the same rounds, none left open, status 0"
       float(lo) == float(hi) >= 1 and comm.status() == 0 and drv.flush_timeouts == 0)
 dist.barrier(); comm.close()
 
+# ---- SingleLearner forwarding over peer memory vs the NCCL gather
+res = {}
+for transport in ("peer", "nccl"):
+    jp = JobParameters(parallelism=world, testSetSize=16)
+    jp.extra["forwardTransport"] = transport
+    eng = Engine(jp, rank, world, dev, impl="fused")
+    eng.handle_request({"id": 1, "request": "Create",
+                        "learner": {"name": "HT", "hyperParameters": {"nClasses": 3, "gracePeriod": 100, "tieThreshold": 0.2}},
+                        "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": 6}})
+    for i in range(10):
+        eng.train_batch(R.generate_batch(R.KIND_CLUSTERS, 6, 256, seed=5, batch_index=world * i + rank, n_aux=3).to(dev), 6)
+    out = eng.handle_request({"id": 1, "request": "Query", "requestId": 2})
+    res[transport] = (json.loads(out[-1]) if out else None, eng.comm_status())
+    eng.close(); dist.barrier()
+if rank == 0:
+    same = res["peer"][0]["dataFitted"] == res["nccl"][0]["dataFitted"] == world * (10 * 256 - 16) \
+        and abs(res["peer"][0]["score"] - res["nccl"][0]["score"]) < 0.05
+else:
+    same = True
+check("single learner: peer-memory forwarding == NCCL gather (records fitted, score)", same)
+check("single learner: comm status 0", res["peer"][1] == 0)
+
 # ---- step time of the three Synchronous variants (ms per step, max over ranks)
 for label, tc in (("two-barrier all-reduce", {}), ("scatter", {"syncFusion": "scatter"}), ("gemm", {"syncFusion": "gemm"})):
     r = run_orr("fused", tc, B=16384, steps=16, timed=True)

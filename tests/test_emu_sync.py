@@ -232,3 +232,24 @@ def test_scatter_push_gather_three_rotating_copies(k, blocks):
     for r in range(k):
         copies = comm.bufs[r].view(3, n)[:, r * per:(r + 1) * per]
         assert int((copies.abs().sum(1) > 0).sum()) <= 1
+
+
+@pytest.mark.parametrize("k,blocks", [(2, 1), (4, 2)])
+def test_single_learner_forwarding(k, blocks):
+    """sync_forward_kernel: every emulated worker stores its batch into rank 0's buffer (slot seq & 1, position = rank);
+    rank 0 sees all k batches of the step, the other slot still holds the previous step."""
+    n = 8 * 32                                   # floats per batch (8 staged rows of pitch 32)
+    comm = PipelineComm(2 * k * n, DEV, 0, 1, None, emulate=k)
+    prev = None
+    for seq in range(1, 6):
+        Z = torch.randn(k, n)
+        _lib.check(K().omldm_sync_forward(comm.struct_ptr(), _lib.ptr(Z), _sz(n), _u(seq), _i(blocks), sp()), "forward")
+        slots = comm.bufs[0].view(2, k, n)
+        assert torch.equal(slots[seq & 1], Z)
+        if prev is not None:
+            assert torch.equal(slots[(seq & 1) ^ 1], prev)
+        prev = Z
+        for r in range(k):                      # rank 0 announced what it has consumed
+            from omldm_b200.parallel.comm import PAD_EXIT
+            assert int(comm.pads[r][PAD_EXIT]) == seq - 1
+    assert comm.status() == 0
