@@ -168,7 +168,8 @@ def pack_wire_f16(Z: torch.Tensor, d: int) -> torch.Tensor:
     tgt_col = d + 1 if Z.shape[1] >= d + 2 else d
     out = torch.zeros(B, wire_f16_pitch(d), dtype=torch.float16, device=Z.device)
     out[:, :d] = Z[:, :d].to(torch.float16)
-    out[:, -2:] = Z[:, tgt_col].to(torch.float32).contiguous().view(torch.float16).reshape(B, 2)
+    tgt = torch.empty(B, dtype=torch.float32, device=Z.device).copy_(Z[:, tgt_col])     # unit stride even for B = 1
+    out[:, -2:] = tgt.view(torch.float16).reshape(B, 2)
     return out
 
 

@@ -70,3 +70,62 @@ def test_poly_table_counts_and_torch_op(d, degree):
     out = F.poly_features(Z, d, torch.from_numpy(tab), len(tab))
     ref = np.stack([np.prod(np.concatenate([xi, [1.0]])[tab], axis=1) for xi in x.numpy().astype(np.float64)])
     assert np.allclose(out[:, : len(tab)].numpy(), ref, rtol=1e-4, atol=1e-5)
+
+
+@settings(max_examples=40, deadline=None)
+@given(st.integers(1, 70), st.integers(1, 40), st.integers(0, 2 ** 31 - 1))
+def test_wire_f16_roundtrip_properties(d, B, seed):
+    """Compact wire rows: pitch is even and holds d features + an fp32 target; expanding them gives the staged row of the
+    fp16-rounded features with the target's bits untouched, whatever d (odd d exercises the pad half)."""
+    g = torch.Generator().manual_seed(seed)
+    raw = torch.randn(B, d + 1, generator=g) * 10.0 ** float(torch.randint(-3, 4, (1,), generator=g))
+    w = F.pack_wire_f16(raw, d)
+    assert w.shape == (B, F.wire_f16_pitch(d)) and w.shape[1] % 2 == 0 and w.shape[1] - d in (2, 3)
+    Z = F.stage_rows_f16(w, d)
+    assert Z.shape == (B, F.pad32(d + 2))
+    assert torch.equal(Z[:, :d], raw[:, :d].to(torch.float16).float())
+    assert torch.equal(Z[:, d], torch.ones(B)) and torch.equal(Z[:, d + 1], raw[:, d])
+    assert float(Z[:, d + 2:].abs().sum()) == 0.0
+
+
+@settings(max_examples=40, deadline=None)
+@given(st.integers(1, 12), st.integers(1, 30), st.integers(3, 200), st.integers(0, 2 ** 31 - 1))
+def test_sparse_rows_dense_form_properties(nnz, B, d, seed):
+    """Sparse rows -> dense rows: duplicate indices accumulate, out-of-range ones vanish, x.w computed from the sparse
+    row equals the dense dot product."""
+    g = torch.Generator().manual_seed(seed)
+    idx = torch.randint(-2, d + 3, (B * nnz,), generator=g).int()       # some indices out of range on purpose
+    val = torch.randn(B * nnz, generator=g)
+    tgt = torch.randint(0, 4, (B,), generator=g).float()
+    rows = F.sparse_rows(idx, val, tgt, B, nnz)
+    assert rows.shape == (B, F.sparse_row_pitch(nnz)) and rows.shape[1] % 32 == 0
+    Z = F.sparse_rows_to_dense(rows, nnz, d)
+    w = torch.randn(d, generator=g)
+    ok = (idx >= 0) & (idx < d)
+    safe = torch.where(ok, idx, torch.zeros_like(idx)).long()
+    sparse_dot = (torch.where(ok, val, torch.zeros_like(val)) * w[safe]).view(B, nnz).sum(1)
+    assert torch.allclose(Z[:, :d] @ w, sparse_dot, rtol=1e-4, atol=1e-4)
+    assert torch.equal(Z[:, d], torch.ones(B)) and torch.equal(Z[:, d + 1], tgt)
+
+
+@settings(max_examples=30, deadline=None)
+@given(st.integers(1, 9), st.lists(st.integers(0, 60), min_size=2, max_size=5), st.integers(0, 2 ** 31 - 1))
+def test_scaler_moment_merge_equals_moments_of_the_union(d, sizes, seed):
+    """Checkpoint rescaling: Chan's pairwise merge of (count, mean, M2) over several workers == one pass over all data."""
+    from omldm_b200.utils.checkpoint import _merge_scaler
+    rng = np.random.default_rng(seed)
+    parts = [rng.standard_normal((n, d)) * 3.0 + 1.0 for n in sizes]
+    states = []
+    for X in parts:
+        s = torch.zeros(1 + 2 * d, dtype=torch.float64)
+        if len(X):
+            s[0] = len(X)
+            s[1:1 + d] = torch.from_numpy(X.mean(0))
+            s[1 + d:] = torch.from_numpy(((X - X.mean(0)) ** 2).sum(0))
+        states.append(s)
+    merged = _merge_scaler(states)
+    allx = np.concatenate(parts)
+    assert float(merged[0]) == len(allx)
+    if len(allx):
+        assert np.allclose(merged[1:1 + d].numpy(), allx.mean(0), rtol=1e-9, atol=1e-9)
+        assert np.allclose(merged[1 + d:].numpy(), ((allx - allx.mean(0)) ** 2).sum(0), rtol=1e-8, atol=1e-8)
