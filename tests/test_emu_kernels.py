@@ -539,3 +539,39 @@ def test_ht_split_kernel_matches_the_host_split_test():
             F.ht_split(feature, threshold, left, right, n_nodes, C, d, cnt, sm, sq, checked, float(grace), 1e-3, 0.2, 10,
                        decision, n_splits)
         assert int(n_splits) == 0 and int(n_nodes) == 3
+
+
+@pytest.mark.parametrize("d,B", [(1, 1), (3, 2), (33, 5), (31, 33), (65, 1)])
+def test_edge_shapes(d, B):
+    """d not a multiple of 8, batch 1, odd sizes - through the real kernels (and, in the sanitizer runs,
+    under ASan / TSan)."""
+    Z = staged(R.KIND_BINARY, d, B, seed=d * 100 + B)
+    w0 = 0.1 * torch.randn(d + 1)
+
+    def run():
+        outs = []
+        w = w0.clone()
+        st = torch.zeros(4, dtype=torch.float64)
+        sc = F.linear_minibatch_scratch(d, DEV)
+        F.linear_minibatch(Z, d, w, st, sc, F.KIND_PA, 1, 0.5, 0.05, 0.01)
+        outs += [w, st]
+        w2 = w0.clone()
+        st2 = torch.zeros(4, dtype=torch.float64)
+        F.linear_exact(Z, d, w2, st2, F.KIND_PA, 1, 0.5, 0.05, 0.01)
+        outs += [w2, st2, F.linear_predict(Z, d, w0)]
+        ring = torch.zeros(1, Z.shape[1])
+        Zh = Z.clone()
+        F.holdout_swap(Zh, ring, d, 7)                      # capacity 1, count starting mid-decade
+        outs += [Zh, ring]
+        ss = torch.zeros(1 + 2 * d, dtype=torch.float64)
+        sx = torch.zeros(3 + 4 * d, dtype=torch.float64)
+        Zs = Z.clone()
+        F.standard_scaler(Zs, d, ss, sx, True)
+        outs += [Zs, ss]
+        stq = torch.zeros(4, dtype=torch.float64)
+        F.sq_residual(Z, d, torch.cat([w0, -torch.ones(1)]), stq)
+        outs += [stq, F.row_sqnorm(Z, d + 1)]
+        return outs
+    ref, nat = both(run)
+    for i, (r, n) in enumerate(zip(ref, nat)):
+        assert torch.allclose(r.double(), n.double(), rtol=2e-3, atol=2e-4, equal_nan=True), (i, d, B)
