@@ -531,6 +531,13 @@ sync_fgm_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale, i
 }
 
 // ------------------------------------------------------------------------------------------
+// Liveness beacon: one relaxed store per peer, no waiting (see omldm_heartbeat in the header).
+__global__ void heartbeat_kernel(Comm c, uint32_t beat) {
+  const int me = my_rank(c);
+  if (threadIdx.x < c.world) st_relaxed_sys(c.pads[threadIdx.x] + OMLDM_PAD_HEART + me, beat);
+}
+
+// ------------------------------------------------------------------------------------------
 __global__ void device_barrier_kernel(Comm c, uint32_t epoch_arg) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
@@ -722,6 +729,13 @@ extern "C" int omldm_sync_fgm_drain(const omldm_comm* h, float* e_local, size_t 
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_fgm_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_fgm_kernel",
                      c, e_local, n, n, scale, mode, threshold, eps_psi, step, state_local, drain);
+}
+
+extern "C" int omldm_heartbeat(const omldm_comm* h, uint32_t beat, void* stream) {
+  if (h->world < 1 || h->world > 16) return set_error_msg("comm: world must be in [1,16]");
+  Comm c = to_comm(h);
+  dim3 grid(1, h->emulate > 1 ? h->emulate : 1);
+  return launch_coop(heartbeat_kernel, grid, dim3(32), static_cast<cudaStream_t>(stream), "heartbeat_kernel", c, beat);
 }
 
 extern "C" int omldm_device_barrier(const omldm_comm* h, uint32_t epoch, void* stream) {

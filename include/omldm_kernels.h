@@ -190,6 +190,7 @@ enum {
   OMLDM_PAD_PHI = 64,      /* [64,80)  FGM phi values (float bits), hub = rank 0    */
   OMLDM_PAD_FGM = 80,      /* [80,96)  FGM: counter, subround, theta, round id, announce step, terminate */
   OMLDM_PAD_STATUS = 96,   /* [96,100) status bits: 1 barrier, 2 SSP, 4 FGM timeouts  */
+  OMLDM_PAD_HEART = 100,   /* [100,116) heartbeat counters, one word per peer (omldm_heartbeat) */
   OMLDM_PAD_QUERY = 128,   /* [128,192) query scalars, 4 per peer                   */
   OMLDM_PAD_WORDS = 256
 };
@@ -250,6 +251,10 @@ int omldm_sync_fgm(const omldm_comm* comm_host, float* e_local, size_t n, float 
 int omldm_sync_fgm_drain(const omldm_comm* comm_host, float* e_local, size_t n, float scale, int mode,
                          float threshold, float eps_psi, uint32_t step, float* state_local, uint32_t drain,
                          int blocks, void* stream);
+/* Liveness (no counterpart in the reference, which leaves failure detection to Flink): stores `beat` into word
+ * OMLDM_PAD_HEART + rank of EVERY peer's pad.  Never waits.  A host watchdog calls it periodically on a side stream
+ * and reads its own pad: a peer whose word stops advancing while the others move is stalled or gone. */
+int omldm_heartbeat(const omldm_comm* comm_host, uint32_t beat, void* stream);
 /* device barrier over the signal pads (termination probe, utils/statistics/StatisticsOperator.scala:135-142) */
 int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stream);
 /* query reduce: out4 = sum over ranks of vals4 (utils/ResponseConstructor.scala:43-52) */

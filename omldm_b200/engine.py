@@ -559,6 +559,21 @@ class Engine:
             st |= self._fwd_comm.status()
         return st
 
+    def start_watchdog(self, period_s: float = 0.5, stall_after_s: float = 5.0, on_stall=None):
+        """Peer liveness (utils/watchdog.py): heartbeat counters in the signal pads of the first distributed pipeline.
+        Returns the running `Watchdog`, or None when there is nothing to watch (one rank, no pipeline built yet)."""
+        from .utils.watchdog import Watchdog
+        for p in self.pipelines.values():
+            if p.built and p.comm.k > 1:
+                self.watchdog = Watchdog(p.comm, self.rank, period_s, stall_after_s, on_stall).start()
+                return self.watchdog
+        return None
+
+    def health(self) -> Dict[str, Any]:
+        """Timeout bits of the protocol kernels and, if a watchdog runs, the heartbeat picture."""
+        wd = getattr(self, "watchdog", None)
+        return {"rank": self.rank, "comm_status": self.comm_status(), "watchdog": None if wd is None else wd.snapshot()}
+
     # ============================================================================ checkpoint
     def state_dict(self) -> dict:
         return {"rank": self.rank, "world": self.world, "count": self.count, "d": self.d,
@@ -582,6 +597,9 @@ class Engine:
             self.pipelines[pid].load_state_dict(ps)
 
     def close(self) -> None:
+        if getattr(self, "watchdog", None) is not None:
+            self.watchdog.stop()
+            self.watchdog = None
         for p in self.pipelines.values():
             p.close()
         self.pipelines = {}

@@ -33,6 +33,7 @@ PAD_WORDS = 256
 LOCAL_WORDS = 64
 # pad word offsets (must match include/omldm_kernels.h)
 PAD_ENTRY, PAD_EXIT, PAD_CLOCK, PAD_VOTE, PAD_PHI, PAD_FGM, PAD_STATUS, PAD_QUERY = 0, 16, 32, 48, 64, 80, 96, 128
+PAD_HEART = 100
 
 
 class _RawCuda:
@@ -188,6 +189,18 @@ class PipelineComm:
     def status(self) -> int:
         """Timeout bits recorded by the kernels (0 = healthy)."""
         return int(self.pad[PAD_STATUS].item())
+
+    def heartbeat(self, beat: int, stream_ptr=None) -> None:
+        """Publish this rank's liveness counter in every peer's pad (csrc/sync.cu::heartbeat_kernel; never waits)."""
+        if self.k <= 1 or not (self.device.type == "cuda" or _lib._emulated):
+            return
+        _lib.check(_lib.kernels().omldm_heartbeat(self.struct_ptr(), ctypes.c_uint32(beat & 0xFFFFFFFF),
+                                                  stream_ptr if stream_ptr is not None else _lib.stream_ptr()),
+                   "heartbeat")
+
+    def heartbeats(self) -> List[int]:
+        """Last counter seen from every rank (own pad; index = rank)."""
+        return [int(v) & 0xFFFFFFFF for v in self.pad[PAD_HEART:PAD_HEART + self.k].tolist()]
 
     def shard_bounds(self, r: int):
         n4 = self.n // 4

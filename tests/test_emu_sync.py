@@ -253,3 +253,28 @@ def test_single_learner_forwarding(k, blocks):
             from omldm_b200.parallel.comm import PAD_EXIT
             assert int(comm.pads[r][PAD_EXIT]) == seq - 1
     assert comm.status() == 0
+
+
+def test_heartbeat_and_stall_detection():
+    """heartbeat_kernel publishes every emulated rank's counter in every pad; the monitor flags a peer whose counter
+    stops advancing (fake clock)."""
+    from omldm_b200.parallel.comm import PAD_HEART
+    from omldm_b200.utils.watchdog import HeartbeatMonitor
+    k = 4
+    comm, _ = make(k, 16)
+    for beat in (1, 2, 7):
+        comm.heartbeat(beat)
+        for r in range(k):
+            assert comm.pads[r][PAD_HEART:PAD_HEART + k].tolist() == [beat] * k
+    assert comm.heartbeats() == [7] * k
+    now = [0.0]
+    mon = HeartbeatMonitor(k, rank=0, stall_after_s=5.0, clock=lambda: now[0])
+    beats = [0, 0, 0, 0]
+    for t in range(1, 13):
+        now[0] = float(t)
+        for r in (0, 1, 3):                       # rank 2 stops beating after t = 4
+            beats[r] = t
+        if t <= 4:
+            beats[2] = t
+        mon.observe(list(beats))
+        assert mon.stalled() == ([2] if t > 9 else [])
