@@ -84,12 +84,26 @@ def build(asan: bool = False, tsan: bool = False) -> Path:
         flags += ["-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer"]
     else:
         flags += ["-O1", "-g", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
-    cmd = ["g++", *flags, *map(str, cpps), "-o", str(out)]
-    p = subprocess.run(cmd, capture_output=True, text=True)
+    # one object per source, compiled in parallel, then one link
+    import concurrent.futures as cf
+    cflags = [f for f in flags if f not in ("-shared", "-Wl,-Bsymbolic")]
+
+    def compile_one(src: Path):
+        obj = src.with_suffix(".o")
+        p = subprocess.run(["g++", *cflags, "-c", str(src), "-o", str(obj)], capture_output=True, text=True)
+        return obj, p
+
+    errs, objs = [], []
+    with cf.ThreadPoolExecutor(max_workers=min(8, len(cpps))) as ex:
+        for obj, p in ex.map(compile_one, cpps):
+            objs.append(obj)
+            if p.returncode != 0:
+                errs.append(p.stdout + p.stderr)
+    if errs:
+        raise RuntimeError("emulator build failed:\n" + "\n".join(errs))
+    p = subprocess.run(["g++", *flags, *map(str, objs), "-o", str(out)], capture_output=True, text=True)
     if p.returncode != 0:
-        raise RuntimeError("emulator build failed:\n" + p.stdout + p.stderr)
-    if p.stderr.strip():
-        print(p.stderr, file=sys.stderr)
+        raise RuntimeError("emulator link failed:\n" + p.stdout + p.stderr)
     return out
 
 
