@@ -278,3 +278,36 @@ def test_heartbeat_and_stall_detection():
             beats[2] = t
         mon.observe(list(beats))
         assert mon.stalled() == ([2] if t > 9 else [])
+
+
+def test_fgm_kernel_and_python_model_take_the_same_decisions():
+    """The Python model of the protocol (parallel/fake_backend.py, used for the interleaving stress tests) and the CUDA
+    kernel (emulated) are driven with the same drift sequence in lock-step: rounds end in the same steps, sub-rounds
+    advance alike and the replicas agree after every round - so what the model proves carries over to the kernel."""
+    import numpy as np
+    from omldm_b200.parallel.fake_backend import FakeWorld
+    k, n, T = 4, 64, 1.0
+    comm, e, state = _fgm_setup(k, n, T)
+    w = FakeWorld(k, comm.n)
+    w.ranks[0].fgm_init_hub(T)
+    rng = np.random.default_rng(5)
+    kernel_rounds, model_rounds = [], []
+    for step in range(1, 201):
+        drift = rng.uniform(0.0005, 0.004, size=(k, 1)) * np.ones((k, comm.n))
+        for r in range(k):
+            comm.bufs[r].add_(torch.from_numpy(drift[r]).float())
+            w.bufs[r][:] += drift[r]
+        _lib.check(K().omldm_sync_fgm(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(T),
+                                      _f(0.01), _u(step), _lib.ptr(state), _i(1), sp()), "fgm")
+        done = []
+        w.run(lambda rk: done.append(rk.fgm_step(T)))
+        assert len(set(done)) == 1
+        if done[0]:
+            model_rounds.append(step)
+        if int(state[4].item()) > len(kernel_rounds):
+            kernel_rounds.append(step)
+        for r in range(k):
+            assert np.allclose(comm.bufs[r].numpy(), w.bufs[r], rtol=1e-4, atol=1e-5), (step, r)
+    assert kernel_rounds == model_rounds and len(kernel_rounds) >= 2, (kernel_rounds, model_rounds)
+    assert int(comm.pads[0][PAD_FGM + 1].item()) == int(w.pads[0][PAD_FGM + 1])       # same sub-round counter
+    assert comm.status() == 0
