@@ -113,6 +113,9 @@ def main() -> None:
     ap.add_argument("--sparse-direct", action="store_true",
                     help="sparse configs: train straight from the sparse rows (gathers / scatters against the dense "
                          "model) instead of rebuilding the dense batch every step")
+    ap.add_argument("--dry-run-cpu", action="store_true",
+                    help="exercise this script on the CPU path (no GPU, wall-clock timing, tiny shapes); the line it "
+                         "prints is marked dry_run and is not a measurement")
     ap.add_argument("--tc", action="append", default=[], help="extra trainingConfiguration key=value")
     ap.add_argument("--hyper", action="append", default=[], help="extra learner hyper-parameter key=value")
     args = ap.parse_args()
@@ -134,16 +137,34 @@ def main() -> None:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
+    dry = args.dry_run_cpu
+    if not dry and not torch.cuda.is_available():
         print(json.dumps({"error": "no CUDA device", "metric": "records/sec"}))
         return
-    torch.cuda.set_device(local)
-    from omldm_b200.utils.numa import bind_to_gpu_numa
-    numa = bind_to_gpu_numa(local)      # pinned ring + producer threads on the GPU's socket
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+    if dry:
+        dev, numa = torch.device("cpu"), None
+        if world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("gloo")
+    else:
+        torch.cuda.set_device(local)
+        from omldm_b200.utils.numa import bind_to_gpu_numa
+        numa = bind_to_gpu_numa(local)      # pinned ring + producer threads on the GPU's socket
+        dev = torch.device("cuda", local)
+        if world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=dev)
+
+    class _WallEvent:                       # stand-in for torch.cuda.Event in the CPU dry run
+        def record(self):
+            self.t = time.perf_counter()
+
+        def elapsed_time(self, other):
+            return 1000.0 * (other.t - self.t)
+
+    def dev_sync():
+        if not dry:
+            torch.cuda.synchronize()
     cfg = CONFIGS[args.config]
     B = args.batch or cfg["batch"]
     d = cfg["d"]
@@ -187,7 +208,7 @@ def main() -> None:
     def sync_all() -> None:
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+        dev_sync()
 
     # untimed set-up: every batch buffer gets its CUDA graph captured (one per rotating copy with syncFusion=gemm)
     n_keys = n_rot * (3 if str(tc.get("syncFusion", "")).lower() == "gemm" else 1)
@@ -197,15 +218,16 @@ def main() -> None:
         step_device(i)
     eng.flush()
     sync_all()
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = ClockSampler(local) if (rank == 0 and not dry) else None
     _lib.reset_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0, e1 = (_WallEvent(), _WallEvent()) if dry else (torch.cuda.Event(enable_timing=True),
+                                                       torch.cuda.Event(enable_timing=True))
     e0.record()
     for i in range(args.steps):
         step_device(args.warmup + i)
     eng.flush()          # inside the timed region: the protocol's end-of-stream settlement is part of the work
     e1.record()
-    torch.cuda.synchronize()
+    dev_sync()
     launches = _lib.launch_count()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     sync_all()
@@ -245,7 +267,7 @@ def main() -> None:
             for _ in range(args.steps):
                 loss_host = step_e2e()
             eng.flush()
-            torch.cuda.synchronize()
+            dev_sync()
             dt = torch.tensor([time.perf_counter() - t0], device=dev)
             if world > 1:
                 dist.all_reduce(dt, op=dist.ReduceOp.MAX)
@@ -281,6 +303,7 @@ def main() -> None:
                        "sync_every": p.driver.sync_every, "model_bytes": getattr(p.driver, "n", p.comm.n) * 4,
                        "sync_fusion": str(tc.get("syncFusion", "none")),
                        "sync_transport": "NVLS multimem" if getattr(p.comm, "multicast", False) else "P2P ld/st over NVLink"},
+            **({"dry_run": "CPU path of the script, not a measurement"} if dry else {}),
             "clocks": clocks, "numa_node": numa, "e2e": e2e, "gpu_launches": launches, "comm_status": status,
         }
         print(json.dumps(out))
