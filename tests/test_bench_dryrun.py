@@ -58,3 +58,11 @@ def test_bench_reference_arm_and_two_ranks():
     assert out["n_gpus"] == 2 and out["config"]["global_batch"] == 128 and out["e2e"] is None
     out = _run(["--config", "orr", "--batch", "64", "--no-e2e", "--tc", "syncFusion=scatter"], nproc=2)
     assert out["config"]["sync_fusion"] == "scatter"
+
+
+def test_graft_entry_build_and_smoke_script():
+    """`build()` as the driver runs it on this CPU box, and the steps of `smoke()` on the CPU path."""
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as g
+    g.build()
+    g.smoke("cpu")
