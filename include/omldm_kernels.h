@@ -277,6 +277,20 @@ int omldm_mcpa_sparse_step(const float* rows, int ld, int B, int nnz, float* W, 
                            float Creg, float* coef, double* stats, const double* active_before, int mean_update,
                            void* stream);
 
+/* ------------------------------------------------------------------ neural network glue (nn.cu)
+ * Element-wise steps between the GEMMs of the small MLP learner "NN" (whitelist PipelineMap.scala:68).
+ * hidden_act : H[:, :od] <- relu, H[:, od] <- 1 (bias input of the next layer).
+ * out_grad   : output layer (B x ldo, od outputs) + staged rows Z -> gradient rows G (B x ldg, columns >= od and
+ *              invalid rows cleared), stats[0] += loss, stats[2] += #valid, *n_valid += #valid.
+ *              classes > 1: soft-max cross entropy, target = class id; else squared error on output 0.
+ * relu_mask  : g[r, c] <- 0 where act[r, c] <= 0 (first n columns).
+ * sgd_step   : W <- W - lr / max(*n_valid, 1) * gW over n floats. */
+int omldm_nn_hidden_act(float* H, int ldh, int B, int od, void* stream);
+int omldm_nn_out_grad(const float* out, int ldo, const float* Z, int ld, int d, int B, int od, int classes, float* G,
+                      int ldg, double* stats, float* n_valid, void* stream);
+int omldm_nn_relu_mask(float* g, int ldg, const float* act, int lda, int B, int n, void* stream);
+int omldm_nn_sgd_step(float* W, const float* gW, size_t n, float lr, const float* n_valid, void* stream);
+
 /* Ridge refresh without a factorisation (no counterpart in the reference): solve (A + lam I) x = b by
  * Jacobi-preconditioned conjugate gradients started from the content of x.  A: n x n, symmetric, FULL storage,
  * pitch ld floats; b: n floats with stride b_stride (a column of the same matrix is fine); n <= 4096.

@@ -210,7 +210,8 @@ class GpuMultiClassPA(GpuLearner):
 
 class GpuNN(GpuLearner):
     """Small MLP (ReLU) trained by mini-batch SGD; forward X W^T and weight gradients dH^T A run on
-    the tcgen05 GEMMs, the element-wise glue is torch."""
+    the tcgen05 GEMMs, the element-wise steps between them (activation, output loss / gradient, relu mask, SGD
+    step with the batch normalisation read from device memory) are fused kernels (csrc/nn.cu)."""
     name, merge_mode = "NN", "mean"
 
     def __init__(self, hyper, device):
@@ -242,59 +243,64 @@ class GpuNN(GpuLearner):
             self.layers.append(W)
             o += s[i + 1] * ldw
         self.sizes = s
+        self._bufB = {}
+        self._gW = None
         if self.e is not None:
             self.e.copy_(self.buf)
 
+    def _buffers(self, B):
+        """Per-batch-size work buffers (activations, gradient rows, weight gradients); a few sizes are kept (training
+        batch, holdout, forecast) so alternating between them does not re-allocate."""
+        if not isinstance(self._bufB, dict):
+            self._bufB = {}
+        b = self._bufB.get(B)
+        if b is None:
+            if len(self._bufB) >= 4:
+                self._bufB.pop(next(iter(self._bufB)))
+            dev = self.device
+            b = ([torch.zeros(B, F.pad32(self.sizes[i + 1] + 1), device=dev) for i in range(len(self.layers))],
+                 [torch.zeros(B, F.pad32(self.sizes[i + 1]), device=dev) for i in range(len(self.layers))])
+            self._bufB[B] = b
+        if self._gW is None:
+            self._gW = [torch.zeros_like(W) for W in self.layers]
+            self._nv = torch.zeros(1, device=self.device)
+        return b[0], b[1], self._gW
+
     def _forward(self, Z):
-        """Returns activations with a trailing ones column (pitch pad32)."""
-        B = Z.shape[0]
+        """Returns activations with a trailing ones column (pitch pad32); GEMMs on tcgen05, activation fused
+        (csrc/nn.cu::nn_hidden_act_kernel)."""
+        hs, _, _ = self._buffers(Z.shape[0])
         acts = [Z]
         a, fan_in = Z, self.d
         for i, W in enumerate(self.layers):
             out_dim = self.sizes[i + 1]
-            H = torch.zeros(B, F.pad32(out_dim + 1), device=self.device)
+            H = hs[i]
             F.gemm_tn(a[:, : fan_in + 1], W[:, : fan_in + 1], H[:, :out_dim])
             if i < len(self.layers) - 1:
-                H[:, :out_dim].clamp_(min=0)
-                H[:, out_dim] = 1.0
+                F.nn_hidden_act(H, out_dim)
             acts.append(H)
             a, fan_in = H, out_dim
         return acts
 
     def fit_batch(self, Z):
         d = self.d
-        valid = (Z[:, d] != 0).float()
-        nv = valid.sum().clamp_min(1.0)
         acts = self._forward(Z)
-        out_dim = self.sizes[-1]
-        out = acts[-1][:, :out_dim]
-        y = Z[:, d + 1]
-        if self.n_classes > 1:
-            p = torch.softmax(out, 1)
-            yi = torch.round(y).long().clamp(0, out_dim - 1)
-            ll = -torch.log(p.gather(1, yi[:, None]).squeeze(1).clamp_min(1e-30))
-            g = p.clone()
-            g[torch.arange(Z.shape[0], device=self.device), yi] -= 1.0
-            loss = (ll * valid).sum()
-        else:
-            err = out[:, 0] - y
-            g = (2.0 * err)[:, None]
-            loss = (err * err * valid).sum()
-        g = g * (valid / nv)[:, None]
-        self.stats[0] += loss.double()
-        self.stats[2] += valid.sum().double()
-        for i in range(len(self.layers) - 1, -1, -1):
+        _, Gs, gWs = self._buffers(Z.shape[0])
+        last = len(self.layers) - 1
+        self._nv.zero_()
+        # loss statistics + dL/d(out) for the valid rows; the 1 / n_valid of the mean goes into the SGD step
+        F.nn_out_grad(acts[-1], Z, d, self.sizes[-1], self.n_classes, Gs[last], self.stats, self._nv)
+        for i in range(last, -1, -1):
             fan_in, od = self.sizes[i], self.sizes[i + 1]
-            G = torch.zeros(Z.shape[0], F.pad32(od), device=self.device)
-            G[:, :od] = g
-            W = self.layers[i]
-            g_prev = None
+            W, G = self.layers[i], Gs[i]
             if i > 0:
-                g_prev = (G[:, :od] @ W[:, :fan_in]) * (acts[i][:, :fan_in] > 0)
-            gW = torch.zeros(od, W.shape[1], device=self.device)
+                # gradient w.r.t. the previous activations, through the relu (library GEMM: G and W are both K-major here)
+                torch.mm(G[:, :od], W[:, :fan_in], out=Gs[i - 1][:, :fan_in])
+                F.nn_relu_mask(Gs[i - 1], acts[i], fan_in)
+            gW = gWs[i]
+            gW.zero_()
             F.gemm_outer(G, acts[i], gW, accumulate=True, m=od, n=fan_in + 1)
-            W.sub_(gW, alpha=self.lr)
-            g = g_prev
+            F.nn_sgd_step(W, gW, self.lr, self._nv)
 
     def predict(self, Z):
         out = self._forward(Z)[-1][:, : self.sizes[-1]]

@@ -650,6 +650,63 @@ def axpy(y: torch.Tensor, x: torch.Tensor, alpha: float) -> None:
     y.add_(x, alpha=alpha)
 
 
+# ------------------------------------------------------------------------------ neural network glue (csrc/nn.cu)
+def nn_hidden_act(H: torch.Tensor, od: int) -> None:
+    """In place: relu on the first `od` columns, constant 1 in column `od` (bias input of the next layer)."""
+    if native(H):
+        _lib.check(_k().omldm_nn_hidden_act(_p(H), _i(H.stride(0)), _i(H.shape[0]), _i(od), _lib.stream_ptr()),
+                   "nn_hidden_act")
+        return
+    H[:, :od].clamp_(min=0)
+    H[:, od] = 1.0
+
+
+def nn_out_grad(out: torch.Tensor, Z: torch.Tensor, d: int, od: int, classes: int, G: torch.Tensor,
+                stats: torch.Tensor, n_valid: torch.Tensor) -> None:
+    """Loss statistics and un-normalised gradient rows of the output layer (see include/omldm_kernels.h)."""
+    B = Z.shape[0]
+    if native(out):
+        _lib.check(_k().omldm_nn_out_grad(_p(out), _i(out.stride(0)), _p(Z), _i(Z.stride(0)), _i(d), _i(B), _i(od),
+                                          _i(classes), _p(G), _i(G.stride(0)), _p(stats), _p(n_valid),
+                                          _lib.stream_ptr()), "nn_out_grad")
+        return
+    valid = Z[:, d] != 0
+    y = Z[:, d + 1]
+    G.zero_()
+    o = out[:, :od]
+    if classes > 1:
+        p = torch.softmax(o, 1)
+        yi = torch.round(y).long().clamp(0, od - 1)
+        ll = -torch.log(p.gather(1, yi[:, None]).squeeze(1).clamp_min(1e-30))
+        g = p.clone()
+        g[torch.arange(B, device=Z.device), yi] -= 1.0
+        G[:, :od] = g * valid[:, None]
+        stats[0] += (ll * valid).sum().double()
+    else:
+        err = o[:, 0] - y
+        G[:, 0] = 2.0 * err * valid
+        stats[0] += (err * err * valid).sum().double()
+    stats[2] += valid.sum().double()
+    n_valid += valid.sum().float()
+
+
+def nn_relu_mask(g: torch.Tensor, act: torch.Tensor, n: int) -> None:
+    if native(g):
+        _lib.check(_k().omldm_nn_relu_mask(_p(g), _i(g.stride(0)), _p(act), _i(act.stride(0)), _i(g.shape[0]), _i(n),
+                                           _lib.stream_ptr()), "nn_relu_mask")
+        return
+    g[:, :n].mul_((act[:, :n] > 0).float())
+
+
+def nn_sgd_step(W: torch.Tensor, gW: torch.Tensor, lr: float, n_valid: torch.Tensor) -> None:
+    """W -= lr / max(n_valid, 1) * gW with n_valid on the device."""
+    if native(W):
+        _lib.check(_k().omldm_nn_sgd_step(_p(W), _p(gW), ctypes.c_size_t(W.numel()), _f(lr), _p(n_valid),
+                                          _lib.stream_ptr()), "nn_sgd_step")
+        return
+    W.sub_(gW * (lr / n_valid.clamp_min(1.0)))
+
+
 # ------------------------------------------------------------------------------ fused pipeline (config 3)
 def fused_poly_scaler_linear(Z: torch.Tensor, d_in: int, factors: torch.Tensor, d_out: int, scaler_state: torch.Tensor,
                              scaler_scratch: torch.Tensor, w: torch.Tensor, stats: torch.Tensor,

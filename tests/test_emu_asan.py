@@ -18,7 +18,7 @@ import torch
 ROOT = os.path.join(os.path.dirname(__file__), "..")
 FULL = bool(os.environ.get("OMLDM_SANITIZERS_FULL"))
 QUICK = ("stage_rows_f16 or sparse_mcpa or ridge_cg or holdout_swap or edge_shapes or ht_split or sum_delta or gm_votes or "
-         "async_and_easgd or barrier or forwarding or scatter_push")
+         "async_and_easgd or barrier or forwarding or scatter_push or nn_glue")
 FULL_SEL = "not engine_pipelines and not (fgm_rounds and 2)"
 
 pytestmark = pytest.mark.skipif(torch.cuda.is_available(), reason="the emulator is for machines without a GPU")

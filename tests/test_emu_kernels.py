@@ -575,3 +575,47 @@ def test_edge_shapes(d, B):
     ref, nat = both(run)
     for i, (r, n) in enumerate(zip(ref, nat)):
         assert torch.allclose(r.double(), n.double(), rtol=2e-3, atol=2e-4, equal_nan=True), (i, d, B)
+
+
+@pytest.mark.parametrize("classes", [0, 4])
+def test_nn_glue_kernels(classes):
+    """csrc/nn.cu: activation, output loss / gradient (soft-max cross entropy and squared error), relu mask, SGD step."""
+    B, d, od = 37, 9, (classes if classes > 1 else 1)
+    Z = staged(R.KIND_MULTICLASS if classes > 1 else R.KIND_REGRESSION, d, B, seed=3, n_aux=max(classes, 1))
+    Z[5, d] = 0.0                                            # an invalid row contributes nothing
+    H0 = torch.randn(B, F.pad32(od + 6))
+    out0 = torch.randn(B, F.pad32(od + 1))
+    W0, gW0 = torch.randn(6, 32), torch.randn(6, 32)
+
+    def run():
+        H = H0.clone()
+        F.nn_hidden_act(H, od + 3)
+        G = torch.full((B, F.pad32(od)), 7.0)
+        st = torch.zeros(4, dtype=torch.float64)
+        nv = torch.zeros(1)
+        F.nn_out_grad(out0, Z, d, od, classes, G, st, nv)
+        g = torch.randn(B, 32, generator=torch.Generator().manual_seed(1))
+        F.nn_relu_mask(g, H0, 20)
+        W = W0.clone()
+        F.nn_sgd_step(W, gW0, 0.1, nv)
+        return H, G, st, nv, g, W
+    ref, nat = both(run)
+    for i, (r, n) in enumerate(zip(ref, nat)):
+        assert torch.allclose(r.double(), n.double(), rtol=1e-4, atol=1e-5), i
+    assert float(nat[3]) == B - 1 and float(nat[1][5].abs().sum()) == 0.0
+
+
+def test_engine_nn_on_emulated_kernels():
+    d, B = 10, 64
+    batches = [R.generate_batch(R.KIND_REGRESSION, d, B, seed=13, batch_index=i) for i in range(5)]
+    out = []
+    for impl in ("torch", "emu"):
+        with F.use_impl(impl):
+            e = _mk_engine({"name": "NN", "hyperParameters": {"hiddenLayers": [8, 5], "learningRate": 0.05}}, d=d)
+            for b in batches:
+                e.train_batch(b.clone(), d)
+            l = e.pipelines[1].learner
+            out.append((l.buf.clone(), l.counters(), l.predict(batches[0].clone()).clone()))
+    (bt, ct, pt), (be, ce, pe) = out
+    assert ct["fitted"] == ce["fitted"] > 0 and abs(ct["loss_sum"] - ce["loss_sum"]) <= 1e-3 * abs(ct["loss_sum"])
+    assert torch.allclose(bt, be, rtol=1e-3, atol=1e-5) and torch.allclose(pt, pe, rtol=1e-3, atol=1e-4)
