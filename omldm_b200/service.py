@@ -15,8 +15,8 @@ utils/statistics/StatisticsOperator.scala - when `--test true` and the input has
 """
 from __future__ import annotations
 
+import collections
 import json
-import queue
 import threading
 import time
 from typing import Dict, List, Optional
@@ -26,34 +26,47 @@ from .utils.config import TOPICS, JobParameters
 
 
 class MessageTopic:
-    """Unbounded FIFO of strings with blocking reads (one Kafka topic, one partition)."""
+    """Unbounded FIFO of strings with blocking reads (one Kafka topic, one partition).  `put_many` / `drain` move whole
+    chunks under one lock acquisition - the per-record cost of a Python queue would otherwise bound the stream."""
 
     def __init__(self, name: str):
         self.name = name
-        self._q: "queue.Queue[str]" = queue.Queue()
+        self._d: "collections.deque[str]" = collections.deque()
+        self._cv = threading.Condition()
         self.produced = 0
 
     def put(self, msg) -> None:
-        self._q.put(msg if isinstance(msg, str) else json.dumps(msg))
-        self.produced += 1
+        m = msg if isinstance(msg, str) else json.dumps(msg)
+        with self._cv:
+            self._d.append(m)
+            self.produced += 1
+            self._cv.notify()
+
+    def put_many(self, msgs) -> None:
+        ms = [m if isinstance(m, str) else json.dumps(m) for m in msgs]
+        with self._cv:
+            self._d.extend(ms)
+            self.produced += len(ms)
+            self._cv.notify_all()
 
     def get(self, timeout: Optional[float] = None) -> Optional[str]:
-        try:
-            return self._q.get(timeout=timeout) if timeout else self._q.get_nowait()
-        except queue.Empty:
-            return None
+        with self._cv:
+            if not self._d and timeout:
+                self._cv.wait_for(lambda: bool(self._d), timeout)
+            return self._d.popleft() if self._d else None
 
     def drain(self, limit: int = 1 << 30) -> List[str]:
-        out = []
-        while len(out) < limit:
-            try:
-                out.append(self._q.get_nowait())
-            except queue.Empty:
-                break
+        with self._cv:
+            n = min(limit, len(self._d))
+            if n == len(self._d):
+                out = list(self._d)
+                self._d.clear()
+            else:
+                out = [self._d.popleft() for _ in range(n)]
         return out
 
     def __len__(self) -> int:
-        return self._q.qsize()
+        return len(self._d)
 
 
 class OnlineLearningService:
