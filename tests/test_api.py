@@ -117,3 +117,26 @@ def test_statistics_and_prediction_json():
     assert d["parallelism"] == 4 and d["statistics"][0]["bytes"] == 100 and d["statistics"][0]["blocks"] == 3
     p = Prediction(1, DataInstance([1.0, 2.0], operation="forecasting"), 0.25)
     assert json.loads(str(p))["prediction"] == 0.25
+
+
+def test_compat_api_surface():
+    """Names of the out-of-tree API the reference touches: VectorBias, Parsing, CountableSerial, Mergeable."""
+    import numpy as np
+    from omldm_b200.api.compat import (CountableSerial, Mergeable, VectorBias, double_parsing, integer_parsing)
+    from omldm_b200.api.pojos import Request
+    from omldm_b200.oracle.learners import make_oracle_learner
+    from omldm_b200.parallel.network import DataSet
+    pa = make_oracle_learner("PA", {"C": 0.1})
+    pa.ensure_init(3)
+    pa.w[:] = [1.0, -2.0, 0.5, 0.25]
+    vb = VectorBias.from_flat(pa.w)
+    assert vb.bias == 0.25 and vb.to_parameters() == pa.to_parameters() and vb == VectorBias.from_parameters(pa.to_parameters())
+    assert vb.predict([1, 1, 2]) == 1.0 - 2.0 + 1.0 + 0.25 and vb.get_size() == 32 and len(vb) == 4
+    avg = 0.5 * (vb + VectorBias([3.0, 0.0, 0.5], 0.75))
+    assert np.allclose(avg.flat(), [2.0, -1.0, 0.5, 0.5])
+    assert integer_parsing({"HubParallelism": "3"}, "HubParallelism", 1) == 3
+    assert integer_parsing({"HubParallelism": "x"}, "HubParallelism", 1) == 1 and integer_parsing(None, "k", 7) == 7
+    assert double_parsing({"t": "0.5"}, "t", 1.0) == 0.5 and double_parsing({}, "t", 1.0) == 1.0
+    req = Request.from_dict({"id": 1, "request": "Create", "learner": {"name": "PA"}})
+    assert isinstance(req, CountableSerial) and isinstance(vb, CountableSerial)
+    assert isinstance(DataSet(4), Mergeable)
