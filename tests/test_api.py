@@ -140,3 +140,24 @@ def test_compat_api_surface():
     req = Request.from_dict({"id": 1, "request": "Create", "learner": {"name": "PA"}})
     assert isinstance(req, CountableSerial) and isinstance(vb, CountableSerial)
     assert isinstance(DataSet(4), Mergeable)
+
+
+def test_math_vector_and_point_types():
+    """`mlAPI.math` names registered by the reference (CommonUtils.scala:17-23) and built by DataPointParser.scala:20-46."""
+    import numpy as np
+    import pytest
+    from omldm_b200.stream.points import (DenseVector, ForecastingPoint, LabeledPoint, SparseVector, TrainingPoint,
+                                          UnlabeledPoint)
+    s = SparseVector(10, [3, 1, 3], [1.0, 2.0, 0.5])             # duplicate indices accumulate
+    d = DenseVector(np.arange(10))
+    assert s.indices.tolist() == [1, 3] and s.values.tolist() == [2.0, 1.5]
+    assert s.dot(d) == d.dot(s) == 2.0 * 1 + 1.5 * 3 and s.to_dense() == s and len(s) == 10
+    assert s.dot(SparseVector(10, [3, 7], [2.0, 9.0])) == 3.0
+    idx, val = s.to_ell(4)
+    assert idx.dtype == np.int32 and idx.tolist() == [1, 3, 0, 0] and val.tolist() == [2.0, 1.5, 0.0, 0.0]
+    with pytest.raises(ValueError):
+        SparseVector(3, [5], [1.0])
+    lp = LabeledPoint(1.0, s, [1, 2], ["a"], "raw")
+    assert isinstance(lp, TrainingPoint) and lp.target == 1.0 and lp.features().shape == (12,)
+    up = lp.as_unlabeled_point()
+    assert isinstance(up, UnlabeledPoint) and isinstance(up, ForecastingPoint) and up.raw == "raw"
