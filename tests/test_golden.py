@@ -59,7 +59,6 @@ def test_golden_bucket_contract():
 
 def test_gpu_engine_answers_in_the_same_layout():
     """The GPU engine (here on its CPU path) fragments an ORR answer exactly like the host engine's golden file."""
-    import torch
     from omldm_b200.engine import Engine
     from omldm_b200.stream import ring as R
     from omldm_b200.utils.config import JobParameters

@@ -2,7 +2,6 @@
 First hardware run pending (written after round 1's GPU budget was spent); the kernels have run on the CPU emulator
 (tests/test_emu_kernels.py::test_ht_split_kernel_matches_the_host_split_test)."""
 import pytest
-import torch
 
 from omldm_b200.engine import Engine
 from omldm_b200.stream import ring as R
