@@ -182,9 +182,9 @@ extern "C" int omldm_ridge_cg(const float* A, int ld, int n, float lam, const fl
   if (grid > sms * per_sm) grid = sms * per_sm;
   if (grid < 1) return set_error_msg("ridge_cg: kernel cannot be resident");
   CgScalars* sc = static_cast<CgScalars*>(scalars);
-#ifdef OMLDM_EMU   // tools/cuda_emu: one block (its grid barrier is a block barrier), plain launch
-  ridge_pcg_kernel<<<1, CG_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(A, ld, n, lam, b, b_stride, x, work, sc,
-                                                                            max_iter, tol, info);
+#ifdef OMLDM_EMU   // tools/cuda_emu: a few blocks run concurrently as host threads, the grid barrier spans all of them
+  emu::launcher_concurrent(ridge_pcg_kernel, dim3(blocks > 0 && blocks <= 8 ? blocks : 2), dim3(CG_THREADS), 0, nullptr)(
+      A, ld, n, lam, b, b_stride, x, work, sc, max_iter, tol, info);
   (void)grid;
   return check_launch("ridge_pcg_kernel");
 #else

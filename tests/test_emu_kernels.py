@@ -352,8 +352,9 @@ def test_sparse_mcpa_step(unique, mean):
     assert torch.allclose(se, sr, rtol=1e-5) and se[2].item() == 3 * (B - 1)
 
 
+@pytest.mark.parametrize("blocks", [1, 3])
 @pytest.mark.parametrize("n,m", [(5, 40), (33, 300), (130, 900)])
-def test_ridge_cg_kernel(n, m):
+def test_ridge_cg_kernel(n, m, blocks):
     g = torch.Generator().manual_seed(n)
     X = torch.randn(m, n, generator=g) * (1.0 + 3.0 * torch.rand(n, generator=g))
     y = X @ torch.randn(n, generator=g) + 0.1 * torch.randn(m, generator=g)
@@ -365,11 +366,11 @@ def test_ridge_cg_kernel(n, m):
     with F.use_impl("emu"):
         x = torch.zeros(n)
         work, scal, info = F.ridge_cg_workspace(n, DEV, 64)
-        F.ridge_cg(W, n, 1.0, x, work, scal, info, max_iter=64, tol=1e-6)
+        F.ridge_cg(W, n, 1.0, x, work, scal, info, max_iter=64, tol=1e-6, blocks=blocks)
         it1, rel1 = info.tolist()
         assert rel1 <= 1e-6 and 0 < it1 <= 64
         assert torch.allclose(x, ref, rtol=2e-3, atol=2e-4)
-        F.ridge_cg(W, n, 1.0, x, work, scal, info, max_iter=64, tol=1e-4)     # warm start: already converged
+        F.ridge_cg(W, n, 1.0, x, work, scal, info, max_iter=64, tol=1e-4, blocks=blocks)     # warm start: already converged
         assert int(info[0]) == 0
     with F.use_impl("torch"):                                                  # same iteration count as the model
         x2 = torch.zeros(n)

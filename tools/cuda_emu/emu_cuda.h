@@ -8,7 +8,7 @@
 // barriers that tolerate threads which already returned; every `__shared__` declaration gets per-block storage
 // (filled with 0xCD, like uninitialised memory), dynamic shared memory is an exactly-sized heap block; atomics are
 // host atomics.  `launcher_concurrent` runs all blocks of a grid at once, for kernels whose blocks (or emulated
-// ranks) wait on one another.  Not emulated: tensor cores, TMA, NVLS multimem, streams (everything is synchronous).
+// ranks) wait on one another; there a cooperative-groups grid barrier spans the whole grid.  Not emulated: tensor cores, TMA, NVLS multimem, streams (everything is synchronous).
 #pragma once
 #include <algorithm>
 #include <atomic>
@@ -85,6 +85,7 @@ struct BlockCtx {
   Barrier bar;
   std::vector<Warp> warps;
   char* dyn = nullptr;
+  Barrier* grid_bar = nullptr;                      // set by run_grid_concurrent: barrier over every thread of the grid
   std::mutex shared_m;
   std::vector<std::pair<int, void*>> shared;        // (declaration id, storage) of the `__shared__` variables
   ~BlockCtx() { for (auto& kv : shared) std::free(kv.second); }
@@ -177,7 +178,10 @@ void run_grid_concurrent(dim3 g, dim3 b, size_t smem, Body&& body) {
   const int nb = static_cast<int>(g.x * g.y * g.z);
   if (T <= 0 || nb <= 0) return;
   std::vector<BlockCtx> ctx(static_cast<size_t>(nb));
+  Barrier grid_bar;
+  grid_bar.reset(nb * T);
   for (auto& c : ctx) {
+    c.grid_bar = &grid_bar;
     c.warps = std::vector<Warp>(static_cast<size_t>((T + 31) / 32));
     c.dyn = smem ? static_cast<char*>(std::malloc(smem)) : nullptr;
     c.bar.reset(T);
@@ -194,6 +198,7 @@ void run_grid_concurrent(dim3 g, dim3 b, size_t smem, Body&& body) {
     body();
     t_ctx->warps[static_cast<size_t>(t_warp)].bar.drop();
     t_ctx->bar.drop();
+    grid_bar.drop();
   };
   std::vector<std::thread> th;
   th.reserve(static_cast<size_t>(nb) * T);
@@ -368,8 +373,15 @@ template <class F> inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiproces
 inline cudaError_t cudaLaunchCooperativeKernel(const void*, dim3, dim3, void**, size_t, cudaStream_t) { return cudaErrorInvalidValue; }
 template <class T> inline cudaError_t cudaGetSymbolAddress(void** p, T& sym) { *p = const_cast<void*>(static_cast<const void*>(&sym)); return cudaSuccess; }
 
-// cooperative groups: grids are emulated with ONE block, so a grid barrier is a block barrier
+// cooperative groups: under launcher_concurrent a grid barrier spans every thread of the grid; under the sequential
+// launcher a grid has to be ONE block and the grid barrier is the block barrier
 namespace cooperative_groups {
-struct grid_group { void sync() const { __syncthreads(); } };
+struct grid_group {
+  void sync() const {
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+    if (emu::t_ctx->grid_bar) emu::t_ctx->grid_bar->sync();
+    else __syncthreads();
+  }
+};
 inline grid_group this_grid() { return {}; }
 }  // namespace cooperative_groups
