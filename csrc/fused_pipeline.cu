@@ -195,6 +195,10 @@ poly_scale_linear_kernel(const float* __restrict__ Z, int ld, int d_in, int B, c
     const float v = s_delta[c];
     if (v != 0.f) atomicAdd(&lin_scratch[c], v);
   }
+  // every thread's additions must be out before thread 0 announces this block as done: without the barrier the last
+  // block could read (and then clear) the accumulator while a slower warp of this block is still adding to it
+  __threadfence();
+  __syncthreads();
   if (threadIdx.x == 0) {
     double l = 0, a = 0; int f = 0, ac = 0;
     for (int i = 0; i < FL_WARPS; ++i) { l += s_loss[i]; a += s_aux[i]; f += s_fit[i]; ac += s_act[i]; }

@@ -359,6 +359,8 @@ class FGMWorker(WorkerNode):
 
 # ============================================================================== parameter servers
 class ParameterServerNode:
+    """Base of the hub-side nodes: `mlParameterServers.MLParameterServer[_,_]` in the reference's out-of-tree API
+    (accessors read at FlinkHub.scala:98-127: protocol statistics, fitted count, node id, learning curve, idx)."""
     protocol = "Asynchronous"
 
     def __init__(self):
@@ -394,6 +396,15 @@ class ParameterServerNode:
 
     def get_learning_curve(self):
         return self.learning_curve
+
+    def get_node_id(self):
+        return self.node_id
+
+    def get_idx(self) -> int:
+        return self.idx
+
+    def set_idx(self, idx: int) -> None:
+        self.idx = int(idx)
 
     def n_workers(self) -> int:
         return self.network.describe().n_spokes
@@ -659,6 +670,10 @@ SERVERS = {"CentralizedTraining": SimplePS, "SingleLearner": CentralizedMLServer
            "Asynchronous": AsynchronousParameterServer, "Synchronous": SynchronousParameterServer,
            "SSP": SSPParameterServer, "EASGD": EASGDParameterServer, "GM": GMParameterServer,
            "FGM": FGMParameterServer}
+
+
+MLParameterServer = ParameterServerNode      # the reference's name for the base class (FlinkHub.scala:98)
+NodeInstance = (WorkerNode, ParameterServerNode)   # `NodeInstance[_,_]`, base of every worker / PS (NodeGenerator.scala:8-9)
 
 
 class MLNodeGenerator:

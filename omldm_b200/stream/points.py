@@ -152,3 +152,11 @@ class UnlabeledPoint(ForecastingPoint):
     def __init__(self, numerical, discrete=None, categorical=None, raw: Optional[str] = None):
         super().__init__(_arr(numerical), _arr(discrete if discrete is not None else []), list(categorical or []), None)
         self.raw = raw
+
+
+# ---- remaining names of `mlAPI.math`: the reference's hierarchy is Point > {LearningPoint > {LabeledPoint,
+# UnlabeledPoint}, UsablePoint > {TrainingPoint, ForecastingPoint}} with a UsablePoint WRAPPING a LearningPoint; here the
+# wrapper and the wrapped point are one object, so the trait names are aliases of the common base.
+Point = UsablePoint
+LearningPoint = UsablePoint
+Vector = (DenseVector, SparseVector)        # for isinstance checks: `isinstance(v, Vector)`

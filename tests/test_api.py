@@ -161,3 +161,17 @@ def test_math_vector_and_point_types():
     assert isinstance(lp, TrainingPoint) and lp.target == 1.0 and lp.features().shape == (12,)
     up = lp.as_unlabeled_point()
     assert isinstance(up, UnlabeledPoint) and isinstance(up, ForecastingPoint) and up.raw == "raw"
+    from omldm_b200.stream.points import LearningPoint, Point, Vector
+    assert isinstance(lp, Point) and isinstance(up, LearningPoint) and isinstance(s, Vector) and isinstance(d, Vector)
+
+
+def test_parameter_server_base_names():
+    """`MLParameterServer` accessors the hub reads (FlinkHub.scala:98-127) and the `NodeInstance` base (NodeGenerator.scala:8-9)."""
+    from omldm_b200.parallel.host_protocols import (AsynchronousWorker, MLParameterServer, NodeInstance,
+                                                    SynchronousParameterServer)
+    ps = SynchronousParameterServer()
+    assert isinstance(ps, MLParameterServer) and isinstance(ps, NodeInstance)
+    ps.set_idx(3)
+    assert ps.get_idx() == 3 and ps.get_node_id() is None and ps.get_number_of_fitted_data() == 0
+    assert ps.get_protocol_statistics().protocol == "Synchronous" and ps.get_learning_curve() == []
+    assert issubclass(AsynchronousWorker, NodeInstance)

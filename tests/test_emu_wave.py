@@ -1,0 +1,27 @@
+"""Kernels whose blocks meet in global memory (accumulators, "last block finishes the job" counters), re-run through
+the CUDA-on-CPU emulation with the blocks of a launch running CONCURRENTLY (OMLDM_EMU_WAVE, tools/cuda_emu/README.md).
+The default emulation runs blocks one after the other, which hides every inter-block ordering problem; this mode found
+the missing block barrier before the completion counter of linear_minibatch_kernel / poly_scale_linear_kernel
+(DESIGN.md).  The wave size is read once per process, hence the subprocess."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.join(os.path.dirname(__file__), "..")
+SELECTION = ("linear_minibatch or fused_poly or kmeans or standard_scaler or sparse_mcpa or hoeffding or mcpa_coef or "
+             "sq_residual or nn_glue or holdout_swap or stage_rows")
+
+pytestmark = pytest.mark.skipif(torch.cuda.is_available(), reason="the emulator is for machines without a GPU")
+
+
+@pytest.mark.parametrize("wave", [4, 7] if os.environ.get("OMLDM_SANITIZERS_FULL") else [4])
+def test_inter_block_kernels_with_concurrent_blocks(wave):
+    env = dict(os.environ, OMLDM_EMU_WAVE=str(wave), PYTHONPATH=ROOT)
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(ROOT, "tests", "test_emu_kernels.py"), "-x", "-q",
+                        "-p", "no:cacheprovider", "-k", SELECTION],
+                       capture_output=True, text=True, env=env, cwd=ROOT, timeout=1800)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
+    assert " passed" in p.stdout and "no tests ran" not in p.stdout

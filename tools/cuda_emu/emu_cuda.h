@@ -113,10 +113,54 @@ inline T* block_shared(int id) {
   return static_cast<T*>(p);
 }
 
+// OMLDM_EMU_WAVE=w (> 1): plain launches run their blocks in waves of w concurrent blocks instead of one after the
+// other, which exposes the inter-block protocols ("the last block to finish applies the update") to real interleavings
+// and to ThreadSanitizer.
+inline int wave_size() {
+  static const int w = [] { const char* e = std::getenv("OMLDM_EMU_WAVE"); const int v = e ? std::atoi(e) : 1; return v < 1 ? 1 : v; }();
+  return w;
+}
+
+template <class Body>
+void run_grid_waves(dim3 g, dim3 b, size_t smem, int wave, Body&& body) {
+  const int T = static_cast<int>(b.x * b.y * b.z);
+  const int nb = static_cast<int>(g.x * g.y * g.z);
+  for (int b0 = 0; b0 < nb; b0 += wave) {
+    const int w = std::min(wave, nb - b0);
+    std::vector<BlockCtx> ctx(static_cast<size_t>(w));
+    for (auto& c : ctx) {
+      c.warps = std::vector<Warp>(static_cast<size_t>((T + 31) / 32));
+      c.dyn = smem ? static_cast<char*>(std::malloc(smem)) : nullptr;
+      c.bar.reset(T);
+      for (size_t i = 0; i < c.warps.size(); ++i) c.warps[i].bar.reset(std::min(32, T - static_cast<int>(i) * 32));
+    }
+    auto worker = [&](int k, int t) {
+      const int blk = b0 + k;
+      t_blockDim = b;
+      t_gridDim = g;
+      t_ctx = &ctx[static_cast<size_t>(k)];
+      t_threadIdx = {static_cast<unsigned>(t) % b.x, (static_cast<unsigned>(t) / b.x) % b.y, static_cast<unsigned>(t) / (b.x * b.y)};
+      t_blockIdx = {static_cast<unsigned>(blk) % g.x, (static_cast<unsigned>(blk) / g.x) % g.y, static_cast<unsigned>(blk) / (g.x * g.y)};
+      t_lane = t & 31;
+      t_warp = t >> 5;
+      body();
+      t_ctx->warps[static_cast<size_t>(t_warp)].bar.drop();
+      t_ctx->bar.drop();
+    };
+    std::vector<std::thread> th;
+    th.reserve(static_cast<size_t>(w) * T);
+    for (int k = 0; k < w; ++k)
+      for (int t = 0; t < T; ++t) th.emplace_back(worker, k, t);
+    for (auto& x : th) x.join();
+    for (auto& c : ctx) std::free(c.dyn);
+  }
+}
+
 template <class Body>
 void run_grid(dim3 g, dim3 b, size_t smem, Body&& body) {
   const int T = static_cast<int>(b.x * b.y * b.z);
   if (T <= 0 || g.x * g.y * g.z == 0) return;
+  if (wave_size() > 1 && g.x * g.y * g.z > 1) return run_grid_waves(g, b, smem, wave_size(), body);
   BlockCtx ctx;
   ctx.warps = std::vector<Warp>(static_cast<size_t>((T + 31) / 32));
   ctx.dyn = smem ? static_cast<char*>(std::malloc(smem)) : nullptr;   // exact size: overruns are visible to ASan
