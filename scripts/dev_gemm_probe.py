@@ -1,5 +1,5 @@
 """Developer probe: correctness + timing of the tcgen05 GEMMs (prints, never asserts)."""
-import sys, os, time
+import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from omldm_b200.ops import gemm

@@ -121,6 +121,24 @@ inline int wave_size() {
   return w;
 }
 
+// OMLDM_EMU_JITTER=p (per mille, 0 = off): every atomic, every sys-scope access of ptx.cuh and every block-barrier exit
+// pauses the calling thread with probability p / 1000 for 1..100 us.  Host threads that run freely interleave far less
+// adversarially than warps on 148 SMs do; the pauses widen the windows in which an unordered pair of accesses can be
+// observed in the wrong order (same idea as the `jitter` of parallel/fake_backend.py, applied to the real kernels).
+inline int jitter_permille() {
+  static const int p = [] { const char* e = std::getenv("OMLDM_EMU_JITTER"); const int v = e ? std::atoi(e) : 0; return v < 0 ? 0 : v; }();
+  return p;
+}
+inline void jitter(int scale = 1) {                                // scale: 16 for per-element data accesses
+  const int p = jitter_permille() / scale;
+  if (p == 0) return;
+  static std::atomic<uint64_t> streams{0x9E3779B97F4A7C15ull};
+  thread_local uint64_t s = streams.fetch_add(0xBF58476D1CE4E5B9ull, std::memory_order_relaxed) | 1u;
+  s ^= s << 13; s ^= s >> 7; s ^= s << 17;                       // xorshift64
+  if (static_cast<int>(s % 1000u) < p)
+    std::this_thread::sleep_for(std::chrono::microseconds(1 + static_cast<int>((s >> 32) % 100u)));
+}
+
 template <class Body>
 void run_grid_waves(dim3 g, dim3 b, size_t smem, int wave, Body&& body) {
   const int T = static_cast<int>(b.x * b.y * b.z);
@@ -134,7 +152,9 @@ void run_grid_waves(dim3 g, dim3 b, size_t smem, int wave, Body&& body) {
       c.bar.reset(T);
       for (size_t i = 0; i < c.warps.size(); ++i) c.warps[i].bar.reset(std::min(32, T - static_cast<int>(i) * 32));
     }
+    std::atomic<int> go{0};           // start gate: thread creation takes longer than a small kernel runs
     auto worker = [&](int k, int t) {
+      while (!go.load(std::memory_order_acquire)) std::this_thread::yield();
       const int blk = b0 + k;
       t_blockDim = b;
       t_gridDim = g;
@@ -151,6 +171,7 @@ void run_grid_waves(dim3 g, dim3 b, size_t smem, int wave, Body&& body) {
     th.reserve(static_cast<size_t>(w) * T);
     for (int k = 0; k < w; ++k)
       for (int t = 0; t < T; ++t) th.emplace_back(worker, k, t);
+    go.store(1, std::memory_order_release);
     for (auto& x : th) x.join();
     for (auto& c : ctx) std::free(c.dyn);
   }
@@ -291,7 +312,7 @@ inline T shfl(T v, int src_lane) {
 #define warpSize 32
 
 // ---------------------------------------------------------------- synchronisation / warp primitives
-inline void __syncthreads() { emu::t_ctx->bar.sync(); }
+inline void __syncthreads() { emu::t_ctx->bar.sync(); emu::jitter(); }
 inline void __syncwarp(unsigned = 0xffffffffu) { emu::t_ctx->warps[static_cast<size_t>(emu::t_warp)].bar.sync(); }
 // a real sleep: spin loops are bounded by iteration counts calibrated for GPU time, and thousands of host threads
 // share a few cores - a waiting thread must get out of the way of the one it waits for
@@ -306,6 +327,7 @@ template <class T> inline T __shfl_down_sync(unsigned, T v, int d) { return emu:
 // ---------------------------------------------------------------- atomics (host atomics on plain memory)
 template <class T>
 inline T emu_atomic_add(T* p, T v) {
+  emu::jitter();
   if constexpr (std::is_integral<T>::value) {
     return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST);
   } else {
@@ -329,11 +351,12 @@ inline unsigned atomicAdd(unsigned* p, unsigned v) { return emu_atomic_add(p, v)
 inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { return emu_atomic_add(p, v); }
 template <class T>
 inline T atomicCAS(T* p, T cmp, T val) {
+  emu::jitter();
   __atomic_compare_exchange_n(p, &cmp, val, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
   return cmp;
 }
-template <class T> inline T atomicExch(T* p, T v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
-template <class T> inline T atomicOr(T* p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicExch(T* p, T v) { emu::jitter(); return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicOr(T* p, T v) { emu::jitter(); return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
 template <class T> inline T atomicMax(T* p, T v) {
   T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
   while (old < v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}

@@ -33,3 +33,24 @@ extern "C" int omldm_emu_selftest_shared(float* out64, int with_barrier) {
   emu::launcher(race_kernel, dim3(1), dim3(64))(out64, with_barrier);
   return 0;
 }
+
+// ---- wave / jitter self-test: the "last block applies the sum" idiom of linear_minibatch_kernel, with and without the
+// block barrier that must precede the completion counter.  scratch: 64 accumulators + 1 counter (zeroed by the caller).
+// Every block adds 1 to each accumulator; the last block copies them to out.  Correct result: out[i] == gridDim.x.
+namespace {
+void lastblock_kernel(float* scratch, float* out, int with_barrier) {
+  bool& s_last = *emu::block_shared<bool>(900002);
+  atomicAdd(&scratch[threadIdx.x], 1.0f);
+  if (with_barrier) { __threadfence(); __syncthreads(); }
+  if (threadIdx.x == 0) {
+    const unsigned done = atomicAdd(reinterpret_cast<unsigned*>(&scratch[64]), 1u);
+    s_last = done == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (s_last) out[threadIdx.x] = __ldcg(&scratch[threadIdx.x]);
+}
+}  // namespace
+extern "C" int omldm_emu_selftest_lastblock(float* scratch65, float* out64, int blocks, int with_barrier) {
+  emu::launcher(lastblock_kernel, dim3(blocks), dim3(64))(scratch65, out64, with_barrier);
+  return 0;
+}
