@@ -56,7 +56,9 @@ class SyncDriver:
         self.mode = 1 if merge_mode == "sum" else 0
         self.k = comm.k
         self.scale = 1.0 if self.mode == 1 else 1.0 / self.k
-        self.impl = impl if comm.device.type == "cuda" else "nccl"
+        # host tensors have no fused path - except under the CPU emulation of the kernels with k emulated ranks
+        # (tools/cuda_emu), which is how these driver classes are tested without GPUs
+        self.impl = impl if (comm.device.type == "cuda" or (_lib._emulated and comm.emulate > 1)) else "nccl"
         self.group = group
         self.sync_every = int(cfg(tc, ["syncEvery", "syncPeriod"], 1))
         self.blocks = int(cfg(tc, ["syncBlocks"], 0))

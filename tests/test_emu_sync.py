@@ -316,3 +316,26 @@ def test_fgm_kernel_and_python_model_take_the_same_decisions():
     for a, b in zip(kernel_rounds, model_rounds):
         assert abs(a - b) <= 2 * (1 + kernel_rounds.index(a)), (kernel_rounds, model_rounds)
     assert comm.status() == 0
+
+
+@pytest.mark.parametrize("k", [2, 4])
+def test_fgm_driver_runs_the_multigpu_check_scenario(k):
+    """scripts/multigpu_check.py's FGM case through the real driver class (parallel/fused.py::FGMDriver): device-managed
+    step counter (step argument 0), 150 steps of per-rank drift, drain flush; then a second stream on the same driver."""
+    from omldm_b200.parallel.fused import make_driver
+    comm = PipelineComm(256, DEV, 0, 1, None, emulate=k)
+    e = torch.zeros(k, comm.n)
+    drv = make_driver("FGM", comm, e, "mean", {"threshold": 1.0}, "fused")
+    for gen in (1, 2):
+        for s in range(150):
+            for r in range(k):
+                comm.bufs[r].add_(0.001 * (r + 1))
+            drv.step()
+        drv.flush()
+        assert drv.flush_timeouts == 0 and comm.status() == 0
+        assert drv.device_rounds() >= 2 * gen
+        rounds = drv.state.view(k, 8)[:, 0].tolist()
+        assert len(set(rounds)) == 1, rounds
+        for r in range(k):
+            assert int(comm.pads[r][PAD_FGM + 5].item()) == gen
+            assert int(comm.pads[r][PAD_FGM + 3].item()) == int(rounds[0])      # no round left open
