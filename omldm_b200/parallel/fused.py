@@ -223,7 +223,7 @@ class ScatterSynchronousDriver(SyncDriver):
         super().__init__(comm, e, merge_mode, tc, impl, group, max_msg_params)
         if self.mode != 1 or delta is None or e is None:
             raise ValueError("the scatter-fused synchronisation needs additive statistics, a private delta and e")
-        if comm.n % 3 or (comm.n // 3) % 4 or delta.numel() != comm.n // 3:
+        if comm.n % 3 or (comm.n // 3) % 4 or delta.numel() != (comm.n // 3) * max(comm.emulate, 1):
             raise ValueError("the symmetric region must hold three copies of the delta")
         self.n = comm.n // 3
         self.delta = delta

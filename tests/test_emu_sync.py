@@ -339,3 +339,90 @@ def test_fgm_driver_runs_the_multigpu_check_scenario(k):
         for r in range(k):
             assert int(comm.pads[r][PAD_FGM + 5].item()) == gen
             assert int(comm.pads[r][PAD_FGM + 3].item()) == int(rounds[0])      # no round left open
+
+
+def test_driver_classes_on_emulated_kernels():
+    """The Python driver classes (parallel/fused.py) as the engine uses them on hardware - device-managed epochs /
+    clocks (sequence argument 0), default block counts - against the checks of scripts/multigpu_check.py."""
+    from omldm_b200.parallel.fused import ScatterSynchronousDriver, make_driver
+    k, n = 3, 1000
+    # Synchronous, averaged model: two steps back to back
+    comm, e = make(k, n)
+    xs = [torch.randn(comm.n) for _ in range(k)]
+    for r in range(k):
+        comm.bufs[r].copy_(xs[r])
+    drv = make_driver("Synchronous", comm, e, "mean", {}, "fused")
+    assert drv.impl == "fused"
+    drv.step(); drv.step()
+    ref = torch.stack(xs).mean(0)
+    for r in range(k):
+        assert torch.allclose(comm.bufs[r], ref, rtol=1e-5, atol=1e-6) and torch.allclose(e[r], ref, rtol=1e-5, atol=1e-6)
+    assert comm.status() == 0
+    # Synchronous, additive statistics: e <- e + sum of deltas, deltas cleared
+    comm, e = make(k, n)
+    g0 = torch.randn(comm.n)
+    e[:] = g0
+    ds = [torch.randn(comm.n) for _ in range(k)]
+    for r in range(k):
+        comm.bufs[r].copy_(ds[r])
+    drv = make_driver("Synchronous", comm, e, "sum", {}, "fused")
+    drv.step()
+    for r in range(k):
+        assert torch.allclose(e[r], g0 + sum(ds), rtol=1e-5, atol=1e-4) and float(comm.bufs[r].abs().max()) == 0
+    # Asynchronous: the hub shards hold the mean of all pushes, every worker installed a hub value
+    comm, e = make(k, n)
+    drv = make_driver("Asynchronous", comm, e, "mean", {}, "fused")
+    for r in range(k):
+        comm.bufs[r].add_(float(r + 1))
+    drv.step()
+    for r in range(k):
+        lo, hi = comm.shard_bounds(r)
+        assert torch.allclose(comm.hubs[r][lo:hi], torch.full((hi - lo,), sum(range(1, k + 1)) / k))
+        assert torch.equal(comm.bufs[r], e[r])
+    # SSP: clocks advance without a timeout
+    comm, e = make(k, n)
+    drv = make_driver("SSP", comm, e, "mean", {"staleness": 1}, "fused")
+    for _ in range(5):
+        for r in range(k):
+            comm.bufs[r].add_(0.1)
+        drv.step()
+    assert comm.status() == 0
+    for r in range(k):
+        assert comm.pads[r][PAD_CLOCK:PAD_CLOCK + k].tolist() == [5] * k
+    # EASGD: what the workers lose the centre gains
+    comm, e = make(k, n)
+    drv = make_driver("EASGD", comm, None, "mean", {"alpha": 0.25}, "fused")
+    for r in range(k):
+        comm.bufs[r].fill_(float(r + 1))
+    total = sum(comm.bufs[r].clone() for r in range(k))
+    drv.step()
+    centre = torch.cat([comm.hubs[r][slice(*comm.shard_bounds(r))] for r in range(k)])
+    assert torch.allclose(sum(comm.bufs[r] for r in range(k)) + centre, total, rtol=1e-5, atol=1e-5)
+    assert float(centre.abs().min()) > 0
+    # GM: nothing moves inside the ball, a violation triggers the averaging round
+    comm, e = make(k, n)
+    drv = make_driver("GM", comm, e, "mean", {"threshold": 10.0}, "fused")
+    for r in range(k):
+        comm.bufs[r].fill_(0.001 * (r + 1))
+    before = [b.clone() for b in comm.bufs]
+    drv.step()
+    assert all(torch.equal(comm.bufs[r], before[r]) for r in range(k))
+    comm.bufs[k - 1].fill_(1.0)
+    ref = torch.stack([b.clone() for b in comm.bufs]).mean(0)
+    drv.step()
+    assert all(torch.allclose(comm.bufs[r], ref, rtol=1e-5) for r in range(k))
+    assert comm.status() == 0
+    # scatter-fused Synchronous: private deltas, three rotating copies
+    m = 96 * k
+    comm = PipelineComm(3 * m, DEV, 0, 1, None, emulate=k)
+    e, delta, run = torch.zeros(k, m), torch.zeros(k, m), torch.zeros(m)
+    drv = make_driver("Synchronous", comm, e, "sum", {"syncFusion": "scatter"}, "fused", scatter_delta=delta)
+    assert isinstance(drv, ScatterSynchronousDriver) and not drv.gemm_fused
+    g = torch.Generator().manual_seed(1)
+    for _ in range(5):
+        d = torch.randint(-3, 4, (k, m), generator=g).float()
+        delta.copy_(d)
+        run += d.sum(0)
+        drv.step()
+        assert all(torch.equal(e[r], run) for r in range(k)) and float(delta.abs().max()) == 0.0
+    assert comm.status() == 0
