@@ -17,6 +17,12 @@ def pytest_collection_modifyitems(config, items):
     except Exception:
         has_cuda = False
     if has_cuda:
+        # a kernel that never returns must not hold the GPU box until the caller's own limit: give every GPU test a
+        # ceiling (pytest-timeout, thread method: the process exits, which tears the CUDA context down)
+        if config.pluginmanager.hasplugin("timeout"):
+            for item in items:
+                if "gpu" in item.keywords and item.get_closest_marker("timeout") is None:
+                    item.add_marker(pytest.mark.timeout(600, method="thread"))
         return
     skip = pytest.mark.skip(reason="no CUDA device")
     for item in items:
