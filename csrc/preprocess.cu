@@ -129,7 +129,7 @@ __global__ void scaler_commit_kernel(double* __restrict__ state, const double* _
 // ---------------------------------------------------------------- MinMaxScaler
 __device__ __forceinline__ void atomic_min_f(float* a, float v) {
   int* ai = reinterpret_cast<int*>(a);
-  int old = *ai;
+  int old = __ldcg(ai);     // other blocks update this word atomically: read it from L2, not as a plain load
   while (__int_as_float(old) > v) {
     const int assumed = old;
     old = atomicCAS(ai, assumed, __float_as_int(v));
@@ -138,7 +138,7 @@ __device__ __forceinline__ void atomic_min_f(float* a, float v) {
 }
 __device__ __forceinline__ void atomic_max_f(float* a, float v) {
   int* ai = reinterpret_cast<int*>(a);
-  int old = *ai;
+  int old = __ldcg(ai);     // other blocks update this word atomically: read it from L2, not as a plain load
   while (__int_as_float(old) < v) {
     const int assumed = old;
     old = atomicCAS(ai, assumed, __float_as_int(v));

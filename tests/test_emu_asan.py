@@ -92,3 +92,25 @@ def test_negative_control_missing_syncthreads_is_caught(with_barrier):
         assert "[1.0, 2.0, 3.0]" in p.stdout
     else:
         assert p.returncode == 66 and "data race" in p.stderr, p.stderr[-2000:]
+
+
+@pytest.mark.parametrize("with_barrier", [1, 0])
+def test_negative_control_unordered_last_block_is_caught(with_barrier):
+    """Inter-block ordering: blocks run concurrently (OMLDM_EMU_WAVE) and the floating-point atomics of the shim are
+    relaxed like CUDA's, so a last block that reads / clears an accumulator without being ordered after every adder
+    is a ThreadSanitizer report in every run - the bug fixed in linear_minibatch_kernel / poly_scale_linear_kernel."""
+    code = (
+        "import torch\n"
+        "from omldm_b200.ops import _lib\n"
+        "k = _lib.use_emulator(tsan=True)\n"
+        "for it in range(10):\n"
+        "    scratch, out = torch.zeros(65), torch.zeros(64)\n"
+        f"    k.omldm_emu_selftest_lastblock(_lib.ptr(scratch), _lib.ptr(out), 8, {with_barrier})\n"
+        "print('ran')\n")
+    env = dict(_env("tsan"), OMLDM_EMU_WAVE="8")
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, cwd=ROOT, timeout=900)
+    assert "ran" in p.stdout
+    if with_barrier:
+        assert p.returncode == 0 and "ThreadSanitizer" not in p.stderr, p.stderr[-2000:]
+    else:
+        assert p.returncode == 66 and "data race" in p.stderr, p.stderr[-2000:]

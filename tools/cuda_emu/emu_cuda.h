@@ -333,14 +333,17 @@ inline T emu_atomic_add(T* p, T v) {
   } else {
     using U = typename std::conditional<sizeof(T) == 4, uint32_t, uint64_t>::type;
     U* up = reinterpret_cast<U*>(p);
-    U old = __atomic_load_n(up, __ATOMIC_SEQ_CST);
+    // floating-point accumulators: RELAXED like CUDA's atomicAdd, so that ThreadSanitizer does not take a chain of
+    // additions to one address for synchronisation (it would hide a reader that is not ordered after every adder);
+    // the integer atomics above stay seq_cst - they are the counters of the fence + atomic idioms
+    U old = __atomic_load_n(up, __ATOMIC_RELAXED);
     for (;;) {
       T cur;
       std::memcpy(&cur, &old, sizeof(T));
       const T nv = cur + v;
       U nb;
       std::memcpy(&nb, &nv, sizeof(T));
-      if (__atomic_compare_exchange_n(up, &old, nb, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) return cur;
+      if (__atomic_compare_exchange_n(up, &old, nb, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) return cur;
     }
   }
 }

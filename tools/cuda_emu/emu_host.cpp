@@ -36,7 +36,9 @@ extern "C" int omldm_emu_selftest_shared(float* out64, int with_barrier) {
 
 // ---- wave / jitter self-test: the "last block applies the sum" idiom of linear_minibatch_kernel, with and without the
 // block barrier that must precede the completion counter.  scratch: 64 accumulators + 1 counter (zeroed by the caller).
-// Every block adds 1 to each accumulator; the last block copies them to out.  Correct result: out[i] == gridDim.x.
+// Every block adds 1 to each accumulator; the last block copies them to out and clears them.  Correct result:
+// out[i] == gridDim.x.  Without the barrier the result is wrong in some launches (timing) and ThreadSanitizer reports
+// the clearing store against a late addition in every run (no happens-before path).
 namespace {
 void lastblock_kernel(float* scratch, float* out, int with_barrier) {
   bool& s_last = *emu::block_shared<bool>(900002);
@@ -47,7 +49,10 @@ void lastblock_kernel(float* scratch, float* out, int with_barrier) {
     s_last = done == gridDim.x - 1;
   }
   __syncthreads();
-  if (s_last) out[threadIdx.x] = __ldcg(&scratch[threadIdx.x]);
+  if (s_last) {
+    out[threadIdx.x] = __ldcg(&scratch[threadIdx.x]);
+    scratch[threadIdx.x] = 0.f;          // reset for the next call, as the real kernels do
+  }
 }
 }  // namespace
 extern "C" int omldm_emu_selftest_lastblock(float* scratch65, float* out64, int blocks, int with_barrier) {
