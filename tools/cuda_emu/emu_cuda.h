@@ -152,9 +152,16 @@ void run_grid_waves(dim3 g, dim3 b, size_t smem, int wave, Body&& body) {
       c.bar.reset(T);
       for (size_t i = 0; i < c.warps.size(); ++i) c.warps[i].bar.reset(std::min(32, T - static_cast<int>(i) * 32));
     }
-    std::atomic<int> go{0};           // start gate: thread creation takes longer than a small kernel runs
+    // start gate: thread creation takes longer than a small kernel runs.  The waiters sleep (a thousand spinning
+    // threads starve the creator, badly so under ThreadSanitizer).
+    std::mutex gate_m;
+    std::condition_variable gate_cv;
+    bool go = false;
     auto worker = [&](int k, int t) {
-      while (!go.load(std::memory_order_acquire)) std::this_thread::yield();
+      {
+        std::unique_lock<std::mutex> l(gate_m);
+        gate_cv.wait(l, [&] { return go; });
+      }
       const int blk = b0 + k;
       t_blockDim = b;
       t_gridDim = g;
@@ -171,7 +178,11 @@ void run_grid_waves(dim3 g, dim3 b, size_t smem, int wave, Body&& body) {
     th.reserve(static_cast<size_t>(w) * T);
     for (int k = 0; k < w; ++k)
       for (int t = 0; t < T; ++t) th.emplace_back(worker, k, t);
-    go.store(1, std::memory_order_release);
+    {
+      std::lock_guard<std::mutex> l(gate_m);
+      go = true;
+    }
+    gate_cv.notify_all();
     for (auto& x : th) x.join();
     for (auto& c : ctx) std::free(c.dyn);
   }

@@ -28,14 +28,24 @@ inline void red_add_sys_v4(float* a, float4 v) { red_add_v4(a, v.x, v.y, v.z, v.
 inline float4 atom_add_sys_v4(float* a, float4 v) {
   return make_float4(atomicAdd(a, v.x), atomicAdd(a + 1, v.y), atomicAdd(a + 2, v.z), atomicAdd(a + 3, v.w));
 }
+// ld.relaxed.sys / st.relaxed.sys: strong (atomic-like) accesses per 32-bit element, not plain loads / stores - the
+// asynchronous protocols read a centre variable that peers are adding to, by design
 inline float4 ld_peer_v4(const float4* p) {
   emu::jitter(16);
-  const float* f = reinterpret_cast<const float*>(p);
+  const uint32_t* u = reinterpret_cast<const uint32_t*>(p);
+  uint32_t w[4];
+  for (int i = 0; i < 4; ++i) w[i] = __atomic_load_n(u + i, __ATOMIC_RELAXED);
   float4 r;
-  std::memcpy(&r, f, sizeof(r));
+  std::memcpy(&r, w, sizeof(r));
   return r;
 }
-inline void st_peer_v4(float4* p, float4 v) { emu::jitter(16); std::memcpy(p, &v, sizeof(v)); }
+inline void st_peer_v4(float4* p, float4 v) {
+  emu::jitter(16);
+  uint32_t w[4];
+  std::memcpy(w, &v, sizeof(v));
+  uint32_t* u = reinterpret_cast<uint32_t*>(p);
+  for (int i = 0; i < 4; ++i) __atomic_store_n(u + i, w[i], __ATOMIC_RELAXED);
+}
 // NVLS multimem needs a switch: never reached in the emulation (the multicast pointer is null)
 inline float4 mc_ld_reduce(const float*) { std::abort(); }
 inline void mc_st(float*, float4) { std::abort(); }
