@@ -6,7 +6,7 @@ the GPU pool this project is developed on; this is its stand-in.  Ne
 are live.
 
 By default a quick selection runs (the kernels written last, the core of the protocol kernels); set
-OMLDM_SANITIZERS_FULL=1 for everything (about ten minutes; the log of such a run is profiles/sanitizers_emu.txt) or
+OMLDM_SANITIZERS_FULL=1 for everything, including ThreadSanitizer with concurrent blocks (about fifteen minutes; the log of such a run is profiles/sanitizers_emu.txt) or
 OMLDM_SKIP_EMU_SANITIZERS=1 to skip."""
 import os
 import subprocess
@@ -114,3 +114,13 @@ def test_negative_control_unordered_last_block_is_caught(with_barrier):
         assert p.returncode == 0 and "ThreadSanitizer" not in p.stderr, p.stderr[-2000:]
     else:
         assert p.returncode == 66 and "data race" in p.stderr, p.stderr[-2000:]
+
+
+@pytest.mark.skipif(not FULL, reason="set OMLDM_SANITIZERS_FULL=1 (about four minutes)")
+def test_kernels_are_race_free_under_tsan_with_concurrent_blocks():
+    """Everything again under ThreadSanitizer with the blocks of plain launches running concurrently
+    (OMLDM_EMU_WAVE=4): inter-block ordering, and the emulated ranks of the asynchronous protocol kernels at once."""
+    p = _run_suites(dict(_env("tsan"), OMLDM_EMU_WAVE="4"))
+    out = p.stdout + p.stderr
+    assert "WARNING: ThreadSanitizer" not in out, out[-4000:]
+    assert p.returncode == 0, out[-3000:]
