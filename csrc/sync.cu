@@ -30,7 +30,7 @@ struct Comm {
 
 constexpr int LOCAL_WORDS = 64;  // private scratch words per (emulated) rank
 // local scratch word indices
-enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4, L_EPOCH = 5, L_CLOCK = 6, L_STEP = 7, L_ROT = 8 };
+enum { L_DONE = 0, L_DONE2 = 1, L_NORM = 2, L_DECISION = 3, L_DONE3 = 4, L_EPOCH = 5, L_CLOCK = 6, L_STEP = 7, L_ROT = 8, L_QEPOCH = 9, L_GSTEP = 10, L_GEPOCH = 11, L_DONE4 = 12 };
 
 // A sequence number passed as 0 means "device managed": the kernel uses (stored value + 1) and the
 // block that finishes last stores it back, so the identical launch can be replayed from a CUDA graph.
@@ -538,43 +538,46 @@ __global__ void heartbeat_kernel(Comm c, uint32_t beat) {
 }
 
 // ------------------------------------------------------------------------------------------
+// The termination probe and the query reduce rendezvous on their OWN pad words (QENTRY / QEXIT) with their OWN
+// device-managed counter (L_QEPOCH): the all-reduce epoch, the FGM round number and the query number advance
+// independently, so none of them may share a flag word with another.
 __global__ void device_barrier_kernel(Comm c, uint32_t epoch_arg) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
-  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_EPOCH);
+  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_QEPOCH);
   __syncthreads();
-  if (threadIdx.x == 0) loc[L_EPOCH] = epoch;
-  signal_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
-  wait_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
-  signal_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
-  wait_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
+  if (threadIdx.x == 0) loc[L_QEPOCH] = epoch;
+  signal_all(c, me, OMLDM_PAD_QENTRY, 2 * epoch + 1);
+  wait_all(c, me, OMLDM_PAD_QENTRY, 2 * epoch + 1);
+  signal_all(c, me, OMLDM_PAD_QEXIT, 2 * epoch + 2);
+  wait_all(c, me, OMLDM_PAD_QEXIT, 2 * epoch + 2);
 }
 
-// Each rank scatters its 4 query scalars into every peer's pad, barrier, then sums locally.
+// Each rank scatters its 8 query scalars into every peer's pad, barrier, then sums locally.
 __global__ void query_reduce_kernel(Comm c, const float* vals_base, float* out_base, uint32_t epoch_arg) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
-  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_EPOCH);
+  const uint32_t epoch = resolve_seq(epoch_arg, loc + L_QEPOCH);
   __syncthreads();
-  if (threadIdx.x == 0) loc[L_EPOCH] = epoch;
-  const float* vals = vals_base + 4 * (c.emulate > 1 ? me : 0);
-  float* out = out_base + 4 * (c.emulate > 1 ? me : 0);
-  if (threadIdx.x < c.world * 4) {
-    const int p = threadIdx.x / 4, j = threadIdx.x % 4;
-    st_relaxed_sys(c.pads[p] + OMLDM_PAD_QUERY + 4 * me + j, __float_as_uint(vals[j]));
+  if (threadIdx.x == 0) loc[L_QEPOCH] = epoch;
+  const float* vals = vals_base + 8 * (c.emulate > 1 ? me : 0);
+  float* out = out_base + 8 * (c.emulate > 1 ? me : 0);
+  if (threadIdx.x < c.world * 8) {
+    const int p = threadIdx.x / 8, j = threadIdx.x % 8;
+    st_relaxed_sys(c.pads[p] + OMLDM_PAD_QUERY + 8 * me + j, __float_as_uint(vals[j]));
   }
   __threadfence_system();
   __syncthreads();
-  signal_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
-  wait_all(c, me, OMLDM_PAD_ENTRY, 2 * epoch + 1);
-  if (threadIdx.x < 4) {
+  signal_all(c, me, OMLDM_PAD_QENTRY, 2 * epoch + 1);
+  wait_all(c, me, OMLDM_PAD_QENTRY, 2 * epoch + 1);
+  if (threadIdx.x < 8) {
     float s = 0.f;
-    for (int p = 0; p < c.world; ++p) s += __uint_as_float(ld_acquire_sys(c.pads[me] + OMLDM_PAD_QUERY + 4 * p + threadIdx.x));
+    for (int p = 0; p < c.world; ++p) s += __uint_as_float(ld_acquire_sys(c.pads[me] + OMLDM_PAD_QUERY + 8 * p + threadIdx.x));
     out[threadIdx.x] = s;
   }
   __syncthreads();
-  signal_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
-  wait_all(c, me, OMLDM_PAD_EXIT, 2 * epoch + 2);
+  signal_all(c, me, OMLDM_PAD_QEXIT, 2 * epoch + 2);
+  wait_all(c, me, OMLDM_PAD_QEXIT, 2 * epoch + 2);
 }
 
 static Comm to_comm(const omldm_comm* h) {
@@ -744,11 +747,11 @@ extern "C" int omldm_device_barrier(const omldm_comm* h, uint32_t epoch, void* s
   return launch_coop(device_barrier_kernel, grid, dim3(32), static_cast<cudaStream_t>(stream), "device_barrier_kernel", c, epoch);
 }
 
-extern "C" int omldm_query_reduce(const omldm_comm* h, const float* vals4, float* out4, uint32_t epoch, void* stream) {
+extern "C" int omldm_query_reduce(const omldm_comm* h, const float* vals8, float* out8, uint32_t epoch, void* stream) {
   Comm c = to_comm(h);
   dim3 grid(1, h->emulate > 1 ? h->emulate : 1);
-  return launch_coop(query_reduce_kernel, grid, dim3(64), static_cast<cudaStream_t>(stream), "query_reduce_kernel",
-                     c, vals4, out4, epoch);
+  return launch_coop(query_reduce_kernel, grid, dim3(128), static_cast<cudaStream_t>(stream), "query_reduce_kernel",
+                     c, vals8, out8, epoch);
 }
 
 #ifndef OMLDM_EMU   // CUDA IPC has no meaning in the CPU emulation

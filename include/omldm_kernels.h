@@ -191,8 +191,14 @@ enum {
   OMLDM_PAD_FGM = 80,      /* [80,96)  FGM: counter, subround, theta, round id, announce step, terminate */
   OMLDM_PAD_STATUS = 96,   /* [96,100) status bits: 1 barrier, 2 SSP, 4 FGM timeouts  */
   OMLDM_PAD_HEART = 100,   /* [100,116) heartbeat counters, one word per peer (omldm_heartbeat) */
-  OMLDM_PAD_QUERY = 128,   /* [128,192) query scalars, 4 per peer                   */
-  OMLDM_PAD_WORDS = 256
+  OMLDM_PAD_QUERY = 128,   /* [128,256) query scalars, 8 per peer                   */
+  OMLDM_PAD_QENTRY = 256,  /* [256,272) entry arrivals of the query / termination barrier (own words and own
+                              sequence counter: an FGM round or an all-reduce never shares a flag with a query) */
+  OMLDM_PAD_QEXIT = 272,   /* [272,288) exit arrivals of the query / termination barrier */
+  OMLDM_PAD_GSTEP = 288,   /* [288,304) sharded-Gram protocol: last step each peer has pushed completely */
+  OMLDM_PAD_GENTRY = 304,  /* [304,320) sharded-Gram gather: entry arrivals */
+  OMLDM_PAD_GEXIT = 320,   /* [320,336) sharded-Gram gather: exit arrivals  */
+  OMLDM_PAD_WORDS = 512
 };
 
 /* Synchronous: every shard owner reduces all peers' buffers and writes the result back to all
@@ -257,8 +263,9 @@ int omldm_sync_fgm_drain(const omldm_comm* comm_host, float* e_local, size_t n, 
 int omldm_heartbeat(const omldm_comm* comm_host, uint32_t beat, void* stream);
 /* device barrier over the signal pads (termination probe, utils/statistics/StatisticsOperator.scala:135-142) */
 int omldm_device_barrier(const omldm_comm* comm_host, uint32_t epoch, void* stream);
-/* query reduce: out4 = sum over ranks of vals4 (utils/ResponseConstructor.scala:43-52) */
-int omldm_query_reduce(const omldm_comm* comm_host, const float* vals4, float* out4, uint32_t epoch,
+/* query reduce: out8 = sum over ranks of vals8 (utils/ResponseConstructor.scala:43-52).  Eight fp32 words per
+ * rank; integer counts travel as 20-bit chunks so that their sum over up to 16 ranks stays exact in fp32. */
+int omldm_query_reduce(const omldm_comm* comm_host, const float* vals8, float* out8, uint32_t epoch,
                        void* stream);
 
 /* Sparse records against a dense model (BASELINE config 5; no counterpart in the reference, whose MultiClassPA

@@ -25,7 +25,7 @@ from .api.registry import PipelineMap
 from .models.pipeline import GpuPipeline
 from .ops import functional as F
 from .ops import _lib
-from .parallel.fused import device_barrier, query_reduce
+from .parallel.fused import device_barrier, join_count, query_reduce, split_count
 from .stream.parsers import parse_request
 from .utils.config import JobParameters
 
@@ -136,11 +136,11 @@ class Engine:
         ring = self._holdout_rows()
         resp = p.local_response(response_id, ring)
         if self.world > 1 and not single and p.built:
-            vals = torch.tensor([float(resp.dataFitted or 0), float(resp.loss or 0.0),
-                                 float(resp.cumulativeLoss or 0.0), float(resp.score or 0.0)],
-                                dtype=torch.float32, device=self.device)
+            lo, mid, hi = split_count(resp.dataFitted or 0)      # exact SUM of the counts (fp32 words, 20-bit chunks)
+            vals = torch.tensor([lo, float(resp.loss or 0.0), float(resp.cumulativeLoss or 0.0),
+                                 float(resp.score or 0.0), mid, hi], dtype=torch.float32, device=self.device)
             tot = query_reduce(p.comm, vals, self.impl, self.group).tolist()
-            resp.dataFitted = int(round(tot[0]))                      # SUM (ResponseConstructor.scala:43)
+            resp.dataFitted = join_count(tot[0], tot[4], tot[5])      # SUM (ResponseConstructor.scala:43)
             resp.loss, resp.cumulativeLoss, resp.score = (tot[1] / self.world, tot[2] / self.world,
                                                           tot[3] / self.world)     # MEAN (:44-52)
         if self.rank != 0:

@@ -29,11 +29,12 @@ import torch
 from ..ops import _lib
 from ..ops.functional import CommStruct
 
-PAD_WORDS = 256
+PAD_WORDS = 512
 LOCAL_WORDS = 64
 # pad word offsets (must match include/omldm_kernels.h)
 PAD_ENTRY, PAD_EXIT, PAD_CLOCK, PAD_VOTE, PAD_PHI, PAD_FGM, PAD_STATUS, PAD_QUERY = 0, 16, 32, 48, 64, 80, 96, 128
 PAD_HEART = 100
+PAD_QENTRY, PAD_QEXIT, PAD_GSTEP, PAD_GENTRY, PAD_GEXIT = 256, 272, 288, 304, 320
 
 
 class _RawCuda:

@@ -28,7 +28,8 @@ from typing import List, Optional
 import numpy as np
 
 PAD_ENTRY, PAD_EXIT, PAD_CLOCK, PAD_VOTE, PAD_PHI, PAD_FGM, PAD_STATUS, PAD_QUERY = 0, 16, 32, 48, 64, 80, 96, 128
-PAD_WORDS = 256
+PAD_QENTRY, PAD_QEXIT = 256, 272
+PAD_WORDS = 512
 
 
 class FakeWorld:
@@ -80,6 +81,7 @@ class FakeRank:
         self.w, self.me = world, me
         self.e = np.zeros(world.n, dtype=np.float64)   # private estimate / global statistics
         self.epoch = 0        # device-managed sequence numbers (the kernels keep them in `local`)
+        self.qepoch = 0       # query / termination barrier: its own counter and flag words
         self.clock = 0
         self.step = 0
         self.fgm = {"round": 0, "sub": -1, "zeta": 0.0, "sent": 0, "rounds": 0}
@@ -303,19 +305,23 @@ class FakeRank:
 
     # ---- barrier / query ---------------------------------------------------------------------------
     def barrier(self) -> None:
-        self.epoch += 1
-        self._signal_all(PAD_ENTRY, 2 * self.epoch + 1)
-        self._wait_all(PAD_ENTRY, 2 * self.epoch + 1)
-        self._signal_all(PAD_EXIT, 2 * self.epoch + 2)
-        self._wait_all(PAD_EXIT, 2 * self.epoch + 2)
+        """Own flag words and own counter (sync.cu: L_QEPOCH, QENTRY / QEXIT): independent of all-reduce epochs and
+        FGM rounds."""
+        self.qepoch += 1
+        self._signal_all(PAD_QENTRY, 2 * self.qepoch + 1)
+        self._wait_all(PAD_QENTRY, 2 * self.qepoch + 1)
+        self._signal_all(PAD_QEXIT, 2 * self.qepoch + 2)
+        self._wait_all(PAD_QEXIT, 2 * self.qepoch + 2)
 
-    def query_reduce(self, vals4) -> np.ndarray:
-        self.epoch += 1
+    def query_reduce(self, vals) -> np.ndarray:
+        self.qepoch += 1
+        v = np.zeros(8)
+        v[:len(vals)] = vals
         for p in range(self.w.k):
-            self.w.pads[p][PAD_QUERY + 4 * self.me:PAD_QUERY + 4 * self.me + 4] = vals4
-        self._signal_all(PAD_ENTRY, 2 * self.epoch + 1)
-        self._wait_all(PAD_ENTRY, 2 * self.epoch + 1)
-        out = sum(self.w.pads[self.me][PAD_QUERY + 4 * p:PAD_QUERY + 4 * p + 4].copy() for p in range(self.w.k))
-        self._signal_all(PAD_EXIT, 2 * self.epoch + 2)
-        self._wait_all(PAD_EXIT, 2 * self.epoch + 2)
-        return out
+            self.w.pads[p][PAD_QUERY + 8 * self.me:PAD_QUERY + 8 * self.me + 8] = v
+        self._signal_all(PAD_QENTRY, 2 * self.qepoch + 1)
+        self._wait_all(PAD_QENTRY, 2 * self.qepoch + 1)
+        out = sum(self.w.pads[self.me][PAD_QUERY + 8 * p:PAD_QUERY + 8 * p + 8].copy() for p in range(self.w.k))
+        self._signal_all(PAD_QEXIT, 2 * self.qepoch + 2)
+        self._wait_all(PAD_QEXIT, 2 * self.qepoch + 2)
+        return out[:len(vals)]

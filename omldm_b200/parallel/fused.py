@@ -534,15 +534,33 @@ def device_barrier(comm: PipelineComm) -> None:
                    "device_barrier")
 
 
-def query_reduce(comm: PipelineComm, vals4: torch.Tensor, impl: str = "fused", group=None) -> torch.Tensor:
-    """Sum of (fitted, loss, cumLoss, score) over ranks (ResponseConstructor.scala:43-52)."""
-    out = torch.empty_like(vals4)
+def split_count(c: int):
+    """A record count as three 20-bit chunks: their sums over up to 16 ranks stay exact in fp32 (the query words are
+    fp32; a count above 2^24 would not)."""
+    c = int(c)
+    return float(c & 0xFFFFF), float((c >> 20) & 0xFFFFF), float(c >> 40)
+
+
+def join_count(lo: float, mid: float, hi: float) -> int:
+    return int(round(lo)) + (int(round(mid)) << 20) + (int(round(hi)) << 40)
+
+
+def query_reduce(comm: PipelineComm, vals: torch.Tensor, impl: str = "fused", group=None) -> torch.Tensor:
+    """Sum of up to 8 query scalars over ranks (ResponseConstructor.scala:43-52); `vals` is padded to 8 words."""
+    v8 = torch.zeros(8, dtype=torch.float32, device=vals.device)
+    v8[: vals.numel()] = vals
+    out = torch.empty_like(v8)
     if comm.device.type == "cuda" and comm.k > 1 and impl == "fused":
-        _lib.check(_lib.kernels().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals4), _lib.ptr(out),
+        _lib.check(_lib.kernels().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(v8), _lib.ptr(out),
                                                      _u(0), _lib.stream_ptr()), "query_reduce")
-        return out
-    out.copy_(vals4)
+        return out[: vals.numel()]
+    out.copy_(v8)
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized() and comm.world > 1:
-        dist.all_reduce(out, group=group)
-    return out
+        if out.device.type == "cpu":
+            o64 = out.double()          # gloo path: exact sums
+            dist.all_reduce(o64, group=group)
+            out = o64.float()
+        else:
+            dist.all_reduce(out, group=group)
+    return out[: vals.numel()]

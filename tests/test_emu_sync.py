@@ -190,15 +190,47 @@ def test_fgm_drain_terminates_and_leaves_no_round_open():
     assert state[4].item() >= 1
 
 
+@pytest.mark.parametrize("queries_per_step", [0.25, 3])
+def test_fgm_rounds_interleaved_with_queries(queries_per_step):
+    """FGM round-end rendezvous and the query / termination barrier advance independent counters (round number vs
+    query number).  They used to share the ENTRY / EXIT flag words, so after two rounds a query fell through its
+    barrier (or, with more queries than rounds, a round-end wait did).  Both orders: fewer queries than rounds and
+    more queries than rounds; every query must return the exact sum and no timeout bit may be set."""
+    k, n, T = 4, 256, 1.0
+    comm, e, state = _fgm_setup(k, n, T)
+    vals = torch.zeros(8 * k)
+    out = torch.zeros(8 * k)
+    nq = 0
+    acc = 0.0
+    for step in range(1, 61):
+        for r in range(k):
+            comm.bufs[r].add_(0.004 * (r + 1))
+        _lib.check(K().omldm_sync_fgm(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _f(T),
+                                      _f(0.01), _u(0), _lib.ptr(state), _i(1), sp()), "fgm")
+        acc += queries_per_step
+        while acc >= 1.0:
+            acc -= 1.0
+            nq += 1
+            vals.copy_(torch.arange(8 * k, dtype=torch.float32) + nq)
+            out.zero_()
+            _lib.check(K().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals), _lib.ptr(out), _u(0), sp()), "query")
+            assert torch.equal(out.view(k, 8), vals.view(k, 8).sum(0).expand(k, 8)), f"query {nq} at step {step}"
+            if nq % 5 == 0:
+                _lib.check(K().omldm_device_barrier(comm.struct_ptr(), _u(0), sp()), "barrier")
+        assert comm.status() == 0, f"timeout bit at step {step}"
+        assert len(set(state.view(k, 8)[:, 0].tolist())) == 1
+    assert state[4].item() >= 3 and nq >= 10
+
+
 def test_barrier_and_query_reduce():
     k = 8
     comm, _ = make(k, 16)
     _lib.check(K().omldm_device_barrier(comm.struct_ptr(), _u(comm.next_epoch()), sp()), "barrier")
-    vals = torch.arange(4 * k, dtype=torch.float32)
-    out = torch.zeros(4 * k)
+    vals = torch.arange(8 * k, dtype=torch.float32)
+    out = torch.zeros(8 * k)
     _lib.check(K().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals), _lib.ptr(out), _u(comm.next_epoch()), sp()),
                "query_reduce")
-    assert torch.allclose(out.view(k, 4), vals.view(k, 4).sum(0).expand(k, 4))
+    assert torch.allclose(out.view(k, 8), vals.view(k, 8).sum(0).expand(k, 8))
     assert comm.status() == 0
 
 

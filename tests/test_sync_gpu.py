@@ -172,12 +172,12 @@ def test_barrier_and_query_reduce():
     k = 8
     comm, _ = make(k, 16)
     _lib.check(K().omldm_device_barrier(comm.struct_ptr(), _u(comm.next_epoch()), sp()), "barrier")
-    vals = torch.arange(4 * k, device=DEV, dtype=torch.float32)
-    out = torch.zeros(4 * k, device=DEV)
+    vals = torch.arange(8 * k, device=DEV, dtype=torch.float32)
+    out = torch.zeros(8 * k, device=DEV)
     _lib.check(K().omldm_query_reduce(comm.struct_ptr(), _lib.ptr(vals), _lib.ptr(out), _u(comm.next_epoch()), sp()),
                "query_reduce")
     torch.cuda.synchronize()
-    ref = vals.view(k, 4).sum(0)
-    assert torch.allclose(out.view(k, 4), ref.expand(k, 4))
+    ref = vals.view(k, 8).sum(0)
+    assert torch.allclose(out.view(k, 8), ref.expand(k, 8))
     assert comm.status() == 0
     comm.close()
