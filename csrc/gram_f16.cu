@@ -1,0 +1,316 @@
+// Gram update of online ridge regression on fp16 record rows: G (+)= Z^T Z, straight from the rows as they arrive.
+//
+// Replaces the per-record `A += x x^T, b += y x` behind `node.receiveTuple`
+// (reference call site: src/main/scala/omldm/operators/spoke/FlinkSpoke.scala:101) and, on more than one GPU, the
+// worker -> hub push of the model delta (network/FlinkNetwork.scala:260-261): the kernel that computes the
+// update also delivers it to the hub shards that own its rows.  The reference has no native code.
+//
+// Z is the mini-batch as it sits in the staged ring slot: [K records, ld halves], a record = [x | 1 | y_hi | y_lo | 0..]
+// (fp16, 11-bit significand = the tf32 product precision; the target is split into two halves so that b = X^T y keeps
+// 22 bits).  Both operands of Z^T Z are MN-major views of the SAME matrix, so no transpose pass exists anywhere.
+//
+// Blackwell structure
+//   * CTA pairs (cluster 2x1x1, tcgen05 cta_group::2): one pair owns one 256 x 256 output tile of the upper triangle
+//     and one slice of the batch axis (split-K).  Each CTA TMA-loads its 128 columns of the A side and its 128
+//     columns of the B side per 64-record stage (plain loads from this GPU's memory, no multicast); the pair's MMAs
+//     read both CTAs' shared memory, which halves the L2 -> smem traffic per flop against 128 x 256 single-CTA tiles.
+//     On diagonal tiles the A side and the B side are the same columns: loaded once, used for both descriptors.
+//   * one elected thread of the leader CTA issues tcgen05.mma.cta_group::2.kind::f16 (M 256, N 256, K 16);
+//     accumulators live in TMEM (128 lanes x 256 columns per CTA); tcgen05.commit (multicast to both CTAs) frees the
+//     smem stages and publishes the accumulator.
+//   * epilogue: tcgen05.ld -> registers -> swizzled smem -> TMA reduce-add (fp32 adds at L2), upper 32 x 32 blocks only.
+//   * hub push (world > 1): the split-K partials are first reduced in the local L2-resident delta; the LAST CTA to
+//     finish a 128-row half tile moves it, 32 x 32 block by block, with TMA (load -> reduce-add into the owner GPU's
+//     shard over NVLink -> zero the local block), so every element crosses NVLink once.  When every half tile of
+//     the step has been pushed, the last pusher publishes the step number in all peers' signal pads
+//     (st.release.sys after __threadfence_system).  No CTA ever waits for another CTA or GPU.
+#include <cuda_fp16.h>
+#include <cstring>
+#include "ptx.cuh"
+#include "host_common.h"
+#include "omldm_kernels.h"
+
+namespace omldm {
+
+constexpr int G_BK = 64;                          // records per stage
+constexpr int G_STAGES = 6;
+constexpr int G_THREADS = 192;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2..5 epilogue
+constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 64 halves x 64 records = 16 KB
+constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
+constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int G_TMEM_COLS = 256;
+constexpr int G_ZERO_SLOT = 32;                   // epilogue slots 0..31 (4 KB each), slot 32 = zeros for the reset
+enum { GS_STEP = 0, GS_PUSHED = 1, GS_TILE0 = 8 }; // scratch words: step counter, pushers done, per half-tile arrivals
+
+struct GramPush {
+  CUtensorMap owner[16];     // every owner's full-size accumulation matrix (peer mapped), 32 x 32 fp32 boxes
+  uint32_t* pads[16];
+  int world, rank, rows_per_owner, enabled;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G_THREADS, 1)
+gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ CUtensorMap tmC,
+                const __grid_constant__ GramPush push, int n, int K, int k_per_split, int T,
+                uint32_t* __restrict__ scratch) {
+  const uint32_t rank = cluster_ctarank();        // 0 = leader of the pair
+  const int tile = blockIdx.x >> 1;
+  int ti = 0, tj = 0;
+  {
+    int t = tile;
+    for (ti = 0; ti < T; ++ti) {
+      const int len = T - ti;
+      if (t < len) { tj = ti + t; break; }
+      t -= len;
+    }
+  }
+  const bool diag = ti == tj;
+  const int m0 = ti * 256 + static_cast<int>(rank) * 128;    // A-side columns of this CTA = its accumulator rows
+  const int b0 = tj * 256 + static_cast<int>(rank) * 128;    // B-side columns this CTA feeds
+  const int n0 = tj * 256;                                   // accumulator columns (all 256 in each CTA)
+  const int k_begin = blockIdx.y * k_per_split;
+  const int k_end = min(K, k_begin + k_per_split);
+  const int num_kb = (k_end - k_begin + G_BK - 1) / G_BK;
+  if (num_kb <= 0) return;                                   // same decision in both CTAs of the pair
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + G_STAGES * G_STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + G_STAGES;
+  uint64_t* accum_bar = empty_bar + G_STAGES;
+  uint64_t* push_bar = accum_bar + 1;                        // 4, one per epilogue warp
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(push_bar + 4);
+  uint32_t* s_flag = tmem_slot + 1;
+
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmZ);
+    tma_prefetch_desc(&tmC);
+    for (int s = 0; s < G_STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(accum_bar, 1);
+    for (int q = 0; q < 4; ++q) mbar_init(&push_bar[q], 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_pair<G_TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();                 // barrier inits of both CTAs are visible before any remote arrival
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * G_STAGE_BYTES;
+        uint8_t* sb = sa + G_HALF_BYTES;
+        // the leader's barrier counts the bytes of both CTAs
+        if (rank == 0) mbar_expect_tx(&full_bar[stage], diag ? 2 * G_HALF_BYTES : 2 * G_STAGE_BYTES);
+        const int k0 = k_begin + kb * G_BK;
+        tma_load_3d_pair(sa, &tmZ, &full_bar[stage], 0, k0, m0 / 64);
+        if (!diag) tma_load_3d_pair(sb, &tmZ, &full_bar[stage], 0, k0, b0 / 64);
+        if (++stage == G_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(256, 256, true, true);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + stage * G_STAGE_BYTES);
+          const uint32_t sb = diag ? sa : sa + G_HALF_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < G_BK / 16; ++kk) {
+            // MN-major, 128-byte swizzle: 64-column chunks are G_BK * 128 B apart (LBO), 8-record groups 1024 B
+            // apart (SBO); one MMA consumes 16 records = 2048 B
+            const uint64_t da = make_smem_desc_sw128(sa + kk * 2048, G_BK * 128, 1024, 2);
+            const uint64_t db = make_smem_desc_sw128(sb + kk * 2048, G_BK * 128, 1024, 2);
+            umma_f16_pair(tmem_base, da, db, idesc, (kb | kk) != 0);
+          }
+          umma_commit_pair(&empty_bar[stage], 3);               // frees this stage in both CTAs
+          if (kb == num_kb - 1) umma_commit_pair(accum_bar, 3);  // accumulators complete, both CTAs
+        }
+        __syncwarp();
+        if (++stage == G_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
+    const int q = warp & 3;                        // TMEM lane quadrant this warp may read
+    const uint32_t r = lane_id();
+    const int row0 = m0 + q * 32;
+    mbar_wait(accum_bar, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int c = 0; c < 8; ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= n || row0 >= n || col0 + 31 < row0) continue;   // outside the matrix / strictly below the diagonal
+      float v[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
+      tmem_ld_wait();
+      uint8_t* slot = smem + (q * 8 + c) * 4096;
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(slot + r * 128 + ((j ^ (r & 7)) << 4)) =
+            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      fence_proxy_async();
+      __syncwarp();
+      if (r == 0) {
+        tma_reduce_add_2d(&tmC, slot, col0, row0);
+        tma_commit_group();
+      }
+    }
+    if (r == 0) tma_wait_group0();
+    __syncwarp();
+
+    if (push.enabled) {
+      // -------------------------------------------------------- hub push by the last CTA of this half tile
+      named_bar_sync(1, 128);                      // the reductions of all four epilogue warps are complete
+      if (threadIdx.x == 64) {
+        __threadfence();
+        uint32_t* cnt = scratch + GS_TILE0 + 2 * tile + rank;
+        const uint32_t prev = atomicAdd(cnt, 1u);
+        const bool last = prev == gridDim.y - 1;
+        if (last) *cnt = 0;                        // self-reset for the next launch
+        *s_flag = last ? 1u : 0u;
+      }
+      named_bar_sync(1, 128);
+      if (*s_flag) {
+        __threadfence();
+        float4* z4 = reinterpret_cast<float4*>(smem + G_ZERO_SLOT * 4096);
+        for (int i = threadIdx.x - 64; i < 256; i += 128) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        fence_proxy_async();
+        named_bar_sync(1, 128);
+        if (r == 0 && row0 < n) {
+          int nblk = 0;
+          for (int c = 0; c < 8; ++c) {
+            const int col0 = n0 + c * 32;
+            if (col0 >= n || col0 + 31 < row0) continue;
+            ++nblk;
+          }
+          if (nblk) {
+            mbar_expect_tx(&push_bar[q], nblk * 4096);
+            for (int c = 0; c < 8; ++c) {
+              const int col0 = n0 + c * 32;
+              if (col0 >= n || col0 + 31 < row0) continue;
+              tma_load_2d(smem + (q * 8 + c) * 4096, &tmC, &push_bar[q], col0, row0);
+            }
+            mbar_wait(&push_bar[q], 0);
+            const CUtensorMap* om = &push.owner[row0 / push.rows_per_owner];
+            for (int c = 0; c < 8; ++c) {
+              const int col0 = n0 + c * 32;
+              if (col0 >= n || col0 + 31 < row0) continue;
+              tma_reduce_add_2d(om, smem + (q * 8 + c) * 4096, col0, row0);       // to the owner's shard (NVLink)
+              tma_store_2d(&tmC, smem + G_ZERO_SLOT * 4096, col0, row0);          // local delta block back to zero
+            }
+            tma_commit_group();
+            tma_wait_group0();
+          }
+          __threadfence_system();
+        }
+        named_bar_sync(1, 128);
+        if (threadIdx.x == 64) {
+          const uint32_t done = atomicAdd(scratch + GS_PUSHED, 1u);
+          if (done == gridDim.x - 1) {             // every half tile of this step has reached its owner
+            scratch[GS_PUSHED] = 0;
+            const uint32_t step = scratch[GS_STEP] + 1u;
+            scratch[GS_STEP] = step;
+            __threadfence_system();
+            for (int p = 0; p < push.world; ++p) st_release_sys(push.pads[p] + OMLDM_PAD_GSTEP + push.rank, step);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();                 // the peer's MMAs no longer read this CTA's smem; both are done with TMEM
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair<G_TMEM_COLS>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+static int encode_z(CUtensorMap* tm, const void* Z, int K, int ld) {
+  // [K, ld] halves row-major viewed as {64 halves, K records, ld / 64 chunks}; one box = 2 chunks x 64 records
+  cuuint64_t dims[3] = {64, static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(ld / 64)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 2, 128};
+  cuuint32_t box[3] = {64, static_cast<cuuint32_t>(G_BK), 2};
+  cuuint32_t estr[3] = {1, 1, 1};
+  return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(Z), dims, strides, box, estr,
+                          CU_TENSOR_MAP_SWIZZLE_128B);
+}
+static int encode_g(CUtensorMap* tm, float* C, int rows, int cols, int ldc) {
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ldc) * 4};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  return tensormap_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, C, dims, strides, box, estr, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+}  // namespace omldm
+
+using namespace omldm;
+
+extern "C" size_t omldm_gram_f16_scratch_words(void) { return 512; }
+
+extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers,
+                              uint32_t* scratch, int ksplit, void* stream) {
+  if (K <= 0) return 0;
+  if (ld < 64 || (ld & 63)) return set_error_msg("gram_f16: the row pitch must be a multiple of 64 halves");
+  if (reinterpret_cast<uintptr_t>(Z) & 127) return set_error_msg("gram_f16: rows must be 128-byte aligned");
+  if (n < 1 || n > ld || n > ldc) return set_error_msg("gram_f16: n exceeds the row pitch or the pitch of C");
+  if ((ldc & 3) || (reinterpret_cast<uintptr_t>(C) & 15)) return set_error_msg("gram_f16: C needs a 16-byte aligned base and pitch");
+  const int T = (n + 255) / 256;
+  const int tiles = T * (T + 1) / 2;
+  if (GS_TILE0 + 2 * tiles > 512) return set_error_msg("gram_f16: n too large for the scratch words (n <= 5632)");
+  if (peers && !scratch) return set_error_msg("gram_f16: the hub push needs the scratch words");
+  CUtensorMap tmZ, tmC;
+  if (encode_z(&tmZ, Z, K, ld)) return -1;
+  if (encode_g(&tmC, C, n, n, ldc)) return -1;
+  GramPush push;
+  memset(&push, 0, sizeof(push));
+  if (peers) {
+    if (peers->world < 1 || peers->world > 16) return set_error_msg("gram_f16: world must be in [1,16]");
+    if (peers->rows_per_owner < 32 || (peers->rows_per_owner & 31) ||
+        static_cast<long long>(peers->rows_per_owner) * peers->world < n)
+      return set_error_msg("gram_f16: rows_per_owner must be a multiple of 32 and cover n");
+    push.world = peers->world; push.rank = peers->rank; push.rows_per_owner = peers->rows_per_owner; push.enabled = 1;
+    for (int p = 0; p < peers->world; ++p) {
+      if (encode_g(&push.owner[p], peers->owner_base[p], n, n, ldc)) return -1;
+      push.pads[p] = peers->pads[p];
+    }
+    for (int p = peers->world; p < 16; ++p) push.owner[p] = push.owner[0];
+  }
+  // split the batch axis so that the pairs fill the 74 SM pairs; at least 4 stages of work per CTA
+  if (ksplit <= 0) {
+    ksplit = 74 / tiles;
+    if (ksplit < 1) ksplit = 1;
+  }
+  const int max_split = (K + 4 * G_BK - 1) / (4 * G_BK);
+  if (ksplit > max_split) ksplit = max_split;
+  const int k_per_split = ((K + ksplit - 1) / ksplit + G_BK - 1) / G_BK * G_BK;
+  const int gy = (K + k_per_split - 1) / k_per_split;
+  static bool attr_set[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 15]) {                       // once per device, never inside a graph capture
+    cudaError_t e = cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gram_f16)", e);
+    attr_set[dev & 15] = true;
+  }
+  dim3 grid(2 * tiles, gy);
+  gram_f16_kernel<<<grid, G_THREADS, G_SMEM, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, n, K, k_per_split, T,
+                                                                                scratch);
+  return check_launch("gram_f16_kernel");
+}

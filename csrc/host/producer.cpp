@@ -71,8 +71,38 @@ inline uint16_t f32_to_f16(float f) {
   return static_cast<uint16_t>(sign | (q + ((rem > 0x1000u || (rem == 0x1000u && (q & 1u))) ? 1u : 0u)));
 }
 
+// fp16 bits -> fp32 (exact)
+inline float f16_to_f32(uint16_t h) {
+  const uint32_t sign = (static_cast<uint32_t>(h) & 0x8000u) << 16;
+  uint32_t e = (h >> 10) & 0x1Fu, m = h & 0x3FFu, x;
+  if (e == 0) {
+    if (m == 0) x = sign;
+    else {
+      int sh = 0;
+      while (!(m & 0x400u)) { m <<= 1; ++sh; }
+      x = sign | ((113u - sh) << 23) | ((m & 0x3FFu) << 13);
+    }
+  } else if (e == 31) x = sign | 0x7F800000u | (m << 13);
+  else x = sign | ((e + 112u) << 23) | (m << 13);
+  float f;
+  std::memcpy(&f, &x, 4);
+  return f;
+}
+
+// one fp16 staged row ("f16s", include/omldm_kernels.h): [x | 1 | y_hi | y_lo | 0-pad], pitch `pitch` halves
+inline void write_f16s_row(uint16_t* w, const float* x, float y, int d, int pitch) {
+  for (int j = 0; j < d; ++j) w[j] = f32_to_f16(x[j]);
+  w[d] = 0x3C00u;                                     // 1.0
+  const uint16_t yh = f32_to_f16(y);
+  w[d + 1] = yh;
+  w[d + 2] = f32_to_f16(y - f16_to_f32(yh));
+  for (int j = d + 3; j < pitch; ++j) w[j] = 0;
+}
+inline int f16s_pitch(int d) { return (d + 3 + 63) / 64 * 64; }
+
 // wire = 0: staged fp32 rows (pitch ld floats).  wire = 1: compact rows [fp16 x d | pad | fp32 target],
-// pitch even(d) + 2 halves (include/omldm_host.h).
+// pitch even(d) + 2 halves.  wire = 2: fp16 staged rows [x | 1 | y_hi | y_lo | 0-pad], pitch pad64(d + 3) halves
+// (include/omldm_host.h).
 void fill_batch(void* dst_any, const Truth& tr, int kind, int d, int ld, int batch, int n_aux, uint64_t seed,
                 uint64_t batch_index, int wire = 0) {
   Rng g(seed * 0x100000001B3ull + batch_index * 0x9E3779B97F4A7C15ull + 1);
@@ -108,7 +138,10 @@ void fill_batch(void* dst_any, const Truth& tr, int kind, int d, int ld, int bat
     row[d] = 1.0f;
     row[d + 1] = y;
     for (int j = d + 2; j < ld; ++j) row[j] = 0.f;
-    if (wire) {
+    if (wire == 2) {
+      const int pitch = f16s_pitch(d);
+      write_f16s_row(static_cast<uint16_t*>(dst_any) + static_cast<size_t>(r) * pitch, row, y, d, pitch);
+    } else if (wire) {
       uint16_t* w = static_cast<uint16_t*>(dst_any) + static_cast<size_t>(r) * wld;
       for (int j = 0; j < d; ++j) w[j] = f32_to_f16(row[j]);
       if (d & 1) w[d] = 0;
@@ -188,7 +221,7 @@ extern "C" omldm_producer* omldm_producer_start_wire(omldm_ring* r, int kind, in
                                                      uint64_t seed, int mode, int64_t max_batches, int n_threads,
                                                      int wire) {
   if (!r || d <= 0 || batch <= 0 || (kind != 4 && ld < d + 2) || (kind == 4 && ld <= 0)) return nullptr;
-  if (wire != 0 && (wire != 1 || kind == 4)) return nullptr;
+  if (wire != 0 && ((wire != 1 && wire != 2) || kind == 4)) return nullptr;
   auto* p = new omldm_producer(kind, d, n_aux, seed);
   p->ring = r; p->kind = kind; p->d = d; p->ld = ld; p->batch = batch; p->n_aux = n_aux; p->mode = mode;
   p->wire = wire;
@@ -228,6 +261,25 @@ extern "C" void omldm_generate_batch_f16(void* dst, int kind, int d, int batch, 
                                          uint64_t batch_index) {
   Truth tr(kind, d, n_aux, seed);
   fill_batch(dst, tr, kind, d, d + 2, batch, n_aux, seed, batch_index, 1);
+}
+
+extern "C" void omldm_generate_batch_f16s(void* dst, int kind, int d, int batch, int n_aux, uint64_t seed,
+                                          uint64_t batch_index) {
+  Truth tr(kind, d, n_aux, seed);
+  fill_batch(dst, tr, kind, d, d + 2, batch, n_aux, seed, batch_index, 2);
+}
+
+extern "C" void omldm_pack_f16s(const float* rows, int ld, int target_col, int batch, int d, void* dst) {
+  const int pitch = f16s_pitch(d);
+  for (int r = 0; r < batch; ++r) {
+    const float* row = rows + static_cast<size_t>(r) * ld;
+    uint16_t* w = static_cast<uint16_t*>(dst) + static_cast<size_t>(r) * pitch;
+    if (ld > d + 1 && target_col == d + 1 && row[d] == 0.f) {       // empty staged row stays empty
+      for (int j = 0; j < pitch; ++j) w[j] = 0;
+      continue;
+    }
+    write_f16s_row(w, row, row[target_col], d, pitch);
+  }
 }
 
 extern "C" void omldm_pack_wire_f16(const float* rows, int ld, int target_col, int batch, int d, void* dst) {

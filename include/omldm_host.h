@@ -39,7 +39,8 @@ omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int
 /* Same, with a wire format: 0 = staged fp32 rows (above); 1 = compact rows for the host->device link,
  * [x as fp16 x d | pad to an even count | y as fp32 in two halves], pitch even(d) + 2 halves (the ring's slot
  * size must be batch * pitch * 2 bytes; `ld` >= d + 2 only sizes a scratch row).  Expanded on the GPU by
- * omldm_stage_rows_f16.  Not available for kind 4. */
+ * omldm_stage_rows_f16.  2 = fp16 staged rows [x | 1 | y_hi | y_lo | 0-pad], pitch pad64(d + 3) halves, consumed in
+ * place by the fp16 Gram kernel.  Neither is available for kind 4. */
 omldm_producer* omldm_producer_start_wire(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
                                           uint64_t seed, int mode, int64_t max_batches, int n_threads, int wire);
 void omldm_producer_stop(omldm_producer* p);
@@ -55,6 +56,12 @@ void omldm_generate_batch(float* dst, int kind, int d, int ld, int batch, int n_
 /* ... in the compact fp16 wire format (dst: batch * (even(d) + 2) halves). */
 void omldm_generate_batch_f16(void* dst, int kind, int d, int batch, int n_aux, uint64_t seed,
                               uint64_t batch_index);
+/* ... as fp16 staged rows ("f16s": [x | 1 | y_hi | y_lo | 0-pad], pitch pad64(d + 3) halves; producer wire = 2).
+ * This is the layout the fp16 Gram kernel reads in place, so a slot needs no expansion on the GPU. */
+void omldm_generate_batch_f16s(void* dst, int kind, int d, int batch, int n_aux, uint64_t seed,
+                               uint64_t batch_index);
+/* fp32 rows (pitch ld, target in column target_col; staged rows with valid flag 0 stay empty) -> f16s rows */
+void omldm_pack_f16s(const float* rows, int ld, int target_col, int batch, int d, void* dst);
 /* fp32 rows (pitch ld floats, target in column `target_col`) -> compact fp16 wire rows (round to nearest even,
  * overflow to infinity, subnormals kept). */
 void omldm_pack_wire_f16(const float* rows, int ld, int target_col, int batch, int d, void* dst);

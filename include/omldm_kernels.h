@@ -37,6 +37,39 @@ int omldm_gemm_tn(const float* A, int lda, const float* B, int ldb, float* C, in
 int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                      int M, int N, int K, int ksplit, int flags, void* stream);
 
+/* ------------------------------------------------------------------ fp16 Gram update (gram_f16.cu)
+ * G (+)= Z^T Z for a mini-batch of fp16 staged rows (ORR; per-record update behind node.receiveTuple,
+ * operators/spoke/FlinkSpoke.scala:101; worker -> hub push network/FlinkNetwork.scala:260-261).
+ * fp16 staged row, pitch `ld` halves (multiple of 64, 128-byte aligned base):
+ *         [ x_0 .. x_{d-1} | 1.0 bias/valid (0 = empty row) | y_hi | y_lo | zero pad ],  target = y_hi + y_lo
+ * n = d + 3 columns take part.  Only 32 x 32 blocks that touch the upper triangle are written.
+ *   peers == NULL : the partial sums are reduce-added into C (n x n fp32, pitch ldc).
+ *   peers != NULL : C is this GPU's delta (zero on entry, zero again on exit); every 128-row half tile is moved by
+ *                   the last CTA that finishes it into the accumulation matrix of the GPU that owns those rows
+ *                   (owner_base[row / rows_per_owner], same pitch ldc; TMA reduce-add over NVLink), and once the whole
+ *                   step is delivered the step number (1, 2, ... kept in scratch) is stored with release semantics in
+ *                   word OMLDM_PAD_GSTEP + rank of every pad.  Nothing waits for another GPU.
+ * scratch: omldm_gram_f16_scratch_words() uint32 words, zero before the first call, private to one (C, peers) pair.
+ * ksplit 0 = automatic (fills the 74 SM pairs). */
+typedef struct omldm_gram_peers {
+  float* owner_base[16];     /* every owner's accumulation matrix (peer mapped), pitch ldc floats */
+  uint32_t* pads[16];        /* every rank's signal pad */
+  int world;
+  int rank;
+  int rows_per_owner;        /* multiple of 32; owner p holds rows [p * rows_per_owner, (p + 1) * rows_per_owner) */
+} omldm_gram_peers;
+size_t omldm_gram_f16_scratch_words(void);
+int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers_host,
+                   uint32_t* scratch, int ksplit, void* stream);
+
+/* ------------------------------------------------------------------ fp16 staged rows (rows_f16.cu)
+ * f16s rows -> fp32 staged rows (target = y_hi + y_lo); for learners without an fp16 path and for scoring.
+ * Conversion behind utils/parsers/dataStream/DataPointParser.scala:16-55. */
+int omldm_expand_rows_f16s(const void* Zh, int ldh, int B, int d, float* Z, int ld, void* stream);
+/* stats[0] += sum over valid rows of (w.x + b - y)^2, stats[2] += #valid, straight from f16s rows;
+ * wt = [w_0..w_{d-1}, b, -1, -1] (d + 3 floats).  Predict-before-fit of ORR, operators/spoke/FlinkSpoke.scala:101. */
+int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats, void* stream);
+
 /* ------------------------------------------------------------------ linear learners (linear_learners.cu)
  * PA / RegressorPA / SVM named in utils/parsers/requestStream/PipelineMap.scala:68. */
 typedef struct omldm_linear_desc {

@@ -189,6 +189,87 @@ def stage_rows_f16(raw: torch.Tensor, d: int, ld: Optional[int] = None, out: Opt
     return Z
 
 
+# ------------------------------------------------------------------------------ fp16 staged rows ("f16s")
+def pad64(n: int) -> int:
+    return (n + 63) // 64 * 64
+
+
+def f16s_pitch(d: int) -> int:
+    """Row pitch (in halves) of fp16 staged rows [x | 1 | y_hi | y_lo | 0-pad]: the layout the fp16 Gram kernel
+    (csrc/gram_f16.cu) reads in place."""
+    return pad64(d + 3)
+
+
+def pack_f16s(Z: torch.Tensor, d: int) -> torch.Tensor:
+    """Staged fp32 rows (or raw [B, d+1] rows) -> fp16 staged rows [B, f16s_pitch(d)].  The target is split into
+    two halves (y = y_hi + y_lo keeps 22 significand bits); empty staged rows stay empty."""
+    B = Z.shape[0]
+    staged = Z.shape[1] >= d + 2
+    y = Z[:, d + 1 if staged else d].float()
+    out = torch.zeros(B, f16s_pitch(d), dtype=torch.float16, device=Z.device)
+    out[:, :d] = Z[:, :d].to(torch.float16)
+    out[:, d] = 1.0
+    yh = y.to(torch.float16)
+    out[:, d + 1] = yh
+    out[:, d + 2] = (y - yh.float()).to(torch.float16)
+    if staged:
+        out[Z[:, d] == 0] = 0
+    return out
+
+
+def expand_rows_f16s(Zh: torch.Tensor, d: int, ld: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp16 staged rows -> fp32 staged rows [B, ld] (csrc/rows_f16.cu::expand_rows_f16s_kernel)."""
+    B = Zh.shape[0]
+    ld = ld or pad32(d + 2)
+    Z = out if out is not None else torch.empty(B, ld, device=Zh.device, dtype=torch.float32)
+    if native(Zh):
+        _lib.check(_k().omldm_expand_rows_f16s(_p(Zh), _i(Zh.stride(0)), _i(B), _i(d), _p(Z), _i(ld),
+                                               _lib.stream_ptr()), "expand_rows_f16s")
+        return Z
+    Z.zero_()
+    Z[:, : d + 1] = Zh[:, : d + 1].float()
+    Z[:, d + 1] = Zh[:, d + 1].float() + Zh[:, d + 2].float()
+    return Z
+
+
+def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor) -> None:
+    """stats[0] += sum over valid rows of (w.x + b - y)^2, stats[2] += #valid; wt = [w, b, -1, -1] (d + 3 floats)."""
+    if native(Zh):
+        _lib.check(_k().omldm_sq_residual_f16s(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(d), _p(wt), _p(stats),
+                                               _lib.stream_ptr()), "sq_residual_f16s")
+        return
+    valid = Zh[:, d] != 0
+    r = Zh[:, : d + 3].float() @ wt[: d + 3]
+    stats[0] += (r[valid].double() ** 2).sum()
+    stats[2] += valid.sum().double()
+
+
+class GramPeers(ctypes.Structure):
+    _fields_ = [("owner_base", ctypes.c_void_p * 16), ("pads", ctypes.c_void_p * 16), ("world", ctypes.c_int),
+                ("rank", ctypes.c_int), ("rows_per_owner", ctypes.c_int)]
+
+
+def gram_f16_scratch(device) -> torch.Tensor:
+    return torch.zeros(512, dtype=torch.int32, device=device)
+
+
+def gram_f16(Zh: torch.Tensor, n: int, C: torch.Tensor, scratch: Optional[torch.Tensor] = None,
+             peers: Optional[GramPeers] = None, ksplit: int = 0) -> None:
+    """C[:n, :n] (upper 32 x 32 blocks) += Zh[:, :n]^T Zh[:, :n] on the tcgen05 CTA-pair kernel (csrc/gram_f16.cu).
+    With `peers`, C is the local delta and the result is delivered to the owners' accumulation matrices."""
+    if native(Zh, C):
+        _lib.check(_k().omldm_gram_f16(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(n), _p(C), _i(C.stride(0)),
+                                       ctypes.byref(peers) if peers is not None else None, _p(scratch), _i(ksplit),
+                                       _lib.stream_ptr()), "gram_f16")
+        return
+    X = Zh[:, :n].float()
+    G = X.t() @ X
+    # the kernel writes the 32 x 32 blocks that touch the upper triangle
+    i = torch.arange(n, device=G.device)
+    keep = (i[None, :] // 32 * 32 + 31) >= (i[:, None] // 32 * 32)
+    C[:n, :n] += G * keep
+
+
 def densify(indptr: torch.Tensor, indices: torch.Tensor, values: torch.Tensor, targets: Optional[torch.Tensor],
             d: int, ld: Optional[int] = None, out: Optional[torch.Tensor] = None,
             sq_out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:

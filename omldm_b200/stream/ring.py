@@ -13,7 +13,7 @@ from typing import Optional, Tuple
 import torch
 
 from ..ops import _lib
-from ..ops.functional import pack_wire_f16, pad32, wire_f16_pitch
+from ..ops.functional import f16s_pitch, pack_f16s, pack_wire_f16, pad32, wire_f16_pitch
 
 KIND_BINARY, KIND_REGRESSION, KIND_CLUSTERS, KIND_MULTICLASS, KIND_SPARSE_MULTICLASS = 0, 1, 2, 3, 4
 MODE_GENERATE, MODE_REPLAY = 0, 1
@@ -46,6 +46,7 @@ def _h():
         h.omldm_producer_start_wire.argtypes = [vp, i, i, i, i, i, u64, i, i64, i, i]
         h.omldm_producer_stop.argtypes = [vp]
         h.omldm_generate_batch_f16.argtypes = [vp, i, i, i, i, u64, u64]
+        h.omldm_generate_batch_f16s.argtypes = [vp, i, i, i, i, u64, u64]
         h.omldm_generate_batch.argtypes = [vp, i, i, i, i, i, u64, u64]
         h.omldm_generate_sparse_batch.argtypes = [vp, i, i, i, i, u64, u64]
         h.omldm_parse_json_records.restype = i
@@ -62,15 +63,17 @@ class Topic:
 
     `wire="f16"` keeps the slots in the compact wire format instead ([fp16 x d | pad | fp32 target],
     `wire_f16_pitch(d)` halves per record): half the bytes per record on the host->device link, expanded to
-    staged fp32 rows on the GPU (`Engine.train_batch_host` recognises the dtype)."""
+    staged fp32 rows on the GPU (`Engine.train_batch_host` recognises the dtype).
+    `wire="f16s"` keeps fp16 STAGED rows ([x | 1 | y_hi | y_lo | 0-pad], `f16s_pitch(d)` halves): the layout the
+    fp16 Gram kernel of ORR reads in place, so the slot is trained on as it lands on the GPU."""
 
     def __init__(self, d: int, batch: int, n_slots: int = 8, pin: Optional[bool] = None, wire: str = "f32"):
-        if wire not in ("f32", "f16"):
-            raise ValueError("wire must be 'f32' or 'f16'")
+        if wire not in ("f32", "f16", "f16s"):
+            raise ValueError("wire must be 'f32', 'f16' or 'f16s'")
         self.d, self.batch, self.n_slots, self.wire = d, batch, n_slots, wire
         self.ld = pad32(d + 2)
-        if wire == "f16":
-            self.wire_ld = wire_f16_pitch(d)
+        if wire in ("f16", "f16s"):
+            self.wire_ld = wire_f16_pitch(d) if wire == "f16" else f16s_pitch(d)
             self.storage = torch.zeros(n_slots, batch, self.wire_ld, dtype=torch.float16)
         else:
             self.wire_ld = self.ld
@@ -89,7 +92,7 @@ class Topic:
     def start_synthetic(self, kind: int, seed: int = 0, n_aux: int = 0, mode: int = MODE_GENERATE,
                         max_batches: int = -1, n_threads: int = 1) -> None:
         self._producer = _h().omldm_producer_start_wire(self._ring, kind, self.d, self.ld, self.batch, n_aux, seed,
-                                                        mode, max_batches, n_threads, 1 if self.wire == "f16" else 0)
+                                                        mode, max_batches, n_threads, {"f32": 0, "f16": 1, "f16s": 2}[self.wire])
         if not self._producer:
             raise RuntimeError("producer start failed")
 
@@ -101,6 +104,8 @@ class Topic:
         n = rows.shape[0]
         if self.wire == "f16" and rows.dtype != torch.float16:
             rows = pack_wire_f16(rows, self.d)
+        elif self.wire == "f16s" and rows.dtype != torch.float16:
+            rows = pack_f16s(rows, self.d)
         self.storage[s, :n].copy_(rows)
         if n < self.batch:
             self.storage[s, n:].zero_()
@@ -191,7 +196,14 @@ def generate_sparse_batch(d: int, batch: int, nnz: int, n_aux: int = 10, seed: i
 
 def generate_batch(kind: int, d: int, batch: int, seed: int = 0, batch_index: int = 0, n_aux: int = 0,
                    pin: bool = False, wire: str = "f32") -> torch.Tensor:
-    """One synthetic staged batch [batch, pad32(d+2)] on the host (`wire="f16"`: compact wire rows)."""
+    """One synthetic staged batch [batch, pad32(d+2)] on the host (`wire="f16"`: compact wire rows, `"f16s"`: fp16
+    staged rows)."""
+    if wire == "f16s":
+        out = torch.empty(batch, f16s_pitch(d), dtype=torch.float16)
+        if pin and torch.cuda.is_available():
+            out = out.pin_memory()
+        _h().omldm_generate_batch_f16s(out.data_ptr(), kind, d, batch, n_aux, seed, batch_index)
+        return out
     if wire == "f16":
         out = torch.empty(batch, wire_f16_pitch(d), dtype=torch.float16)
         if pin and torch.cuda.is_available():

@@ -28,33 +28,3 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
-
-
-PENDING = "first hardware run pending"
-
-
-def _pending_hw(item) -> bool:
-    mk = item.get_closest_marker("xfail")
-    return mk is not None and PENDING in str(mk.kwargs.get("reason", ""))
-
-
-@pytest.hookimpl(tryfirst=True)
-def pytest_pyfunc_call(pyfuncitem):
-    """GPU tests of code that has not run on hardware yet (non-strict xfail, reason "first hardware run pending")
-    execute in a child process: a fault in such a kernel leaves a sticky CUDA error behind, and in this process that
-    would fail every GPU test that follows.  The child runs the one test with --runxfail, so its exit code says
-    whether the test really passed (XPASS here) or failed (xfailed here, with the child's output as the reason)."""
-    if os.environ.get("OMLDM_ISOLATED_CHILD") or "gpu" not in pyfuncitem.keywords or not _pending_hw(pyfuncitem):
-        return None
-    import subprocess
-    env = dict(os.environ, OMLDM_ISOLATED_CHILD="1")
-    cmd = [sys.executable, "-m", "pytest", pyfuncitem.nodeid, "-x", "-q", "--runxfail", "-p", "no:cacheprovider"]
-    try:
-        p = subprocess.run(cmd, cwd=str(pyfuncitem.config.rootpath), env=env, capture_output=True, text=True,
-                           timeout=540)
-    except subprocess.TimeoutExpired as e:
-        raise AssertionError(f"isolated run of {pyfuncitem.nodeid} timed out: {str(e.stdout)[-1500:]}")
-    if p.returncode != 0:
-        raise AssertionError(f"isolated run of {pyfuncitem.nodeid} failed (exit {p.returncode}):\n"
-                             + (p.stdout + p.stderr)[-3000:])
-    return True

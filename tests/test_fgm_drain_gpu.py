@@ -9,7 +9,7 @@ import torch
 from omldm_b200.ops import _lib
 from omldm_b200.parallel.comm import PAD_FGM, PAD_PHI, PipelineComm
 
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(reason="first hardware run pending", strict=False)]
+pytestmark = pytest.mark.gpu
 _i, _f, _u, _sz = ctypes.c_int, ctypes.c_float, ctypes.c_uint32, ctypes.c_size_t
 
 

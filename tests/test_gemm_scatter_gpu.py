@@ -6,7 +6,7 @@ import torch
 
 from omldm_b200.ops import functional as F
 
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(reason="first hardware run pending", strict=False)]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("n_peers,d,K,ks", [(4, 510, 4096, 4), (8, 1022, 2048, 7), (2, 254, 1024, 1)])

@@ -1,0 +1,116 @@
+"""fp16 Gram kernel (csrc/gram_f16.cu: CTA pairs, tcgen05 cta_group::2, TMA, split-K, TMA reduce-add epilogue and the
+in-kernel hub push) against a plain PyTorch reference of the same op: G = X^T X in fp64 from the same fp16 rows."""
+import pytest
+import torch
+
+from omldm_b200.ops import functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rows(K, d, seed=0, empty_every=0):
+    g = torch.Generator().manual_seed(seed)
+    raw = torch.randn(K, d + 1, generator=g)
+    raw[:, d] = raw[:, :d].sum(1) * 0.1 + 0.01 * torch.randn(K, generator=g)
+    Zh = F.pack_f16s(raw, d)
+    if empty_every:
+        Zh[::empty_every] = 0          # empty rows (valid flag 0) contribute nothing
+    return Zh.cuda()
+
+
+def _ref(Zh, n):
+    X = Zh[:, :n].double()
+    return X.t() @ X, X.abs().t() @ X.abs()
+
+
+def _upper_blocks(n, device):
+    i = torch.arange(n, device=device)
+    return (i[None, :] // 32 * 32 + 31) >= (i[:, None] // 32 * 32)
+
+
+@pytest.mark.parametrize("K,d,ksplit", [(4096, 1000, 0), (300, 28, 0), (1000, 200, 1), (777, 509, 3), (64, 5, 0),
+                                        (5000, 253, 0), (8192, 300, 5)])
+def test_gram_matches_fp64_reference(K, d, ksplit):
+    n = d + 3
+    Zh = _rows(K, d, seed=K + d, empty_every=7)
+    ldg = F.pad64(n)
+    C = torch.zeros(ldg, ldg, device="cuda")
+    F.gram_f16(Zh, n, C, ksplit=ksplit)
+    F.gram_f16(Zh, n, C, ksplit=ksplit)                # accumulates
+    torch.cuda.synchronize()
+    ref, bound = _ref(Zh, n)
+    keep = _upper_blocks(n, "cuda")
+    got = C[:n, :n].double()
+    err = (got - 2 * ref).abs()
+    tol = 1e-5 * 2 * bound + 1e-5                      # exact fp16 products; the fp32 accumulation in TMEM truncates
+    assert bool((err[keep] <= tol[keep]).all()), float((err / tol)[keep].max())
+    assert float(got[~keep].abs().max()) == 0.0 if (~keep).any() else True     # blocks below the diagonal are not written
+    if n < ldg:
+        assert float(C[n:, :].abs().max()) == 0.0 and float(C[:, n:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("world,K,d", [(4, 2048, 1000), (2, 1500, 509), (8, 4096, 1000), (3, 640, 200)])
+def test_hub_push_delivers_rows_to_their_owners(world, K, d):
+    """Two-level mode with local buffers standing in for the peers: the split-K partials meet in the local delta, the
+    last CTA of every half tile moves it to the owner of its rows, the delta is zero again, and the step number is
+    published in every pad once the whole step has been delivered."""
+    from omldm_b200.parallel.comm import PAD_GSTEP, PAD_WORDS
+    n = d + 3
+    ldg = F.pad64(n)
+    rows_per_owner = ldg // world // 32 * 32
+    if rows_per_owner * world < n:
+        rows_per_owner += 32
+    owners = [torch.zeros(ldg, ldg, device="cuda") for _ in range(world)]
+    pads = [torch.zeros(PAD_WORDS, dtype=torch.int32, device="cuda") for _ in range(world)]
+    delta = torch.zeros(ldg, ldg, device="cuda")
+    scratch = F.gram_f16_scratch("cuda")
+    peers = F.GramPeers()
+    for p in range(world):
+        peers.owner_base[p] = owners[p].data_ptr()
+        peers.pads[p] = pads[p].data_ptr()
+    peers.world, peers.rank, peers.rows_per_owner = world, 1 % world, rows_per_owner
+    total = torch.zeros(n, n, dtype=torch.float64, device="cuda")
+    bound = torch.zeros_like(total)
+    for step in range(1, 4):
+        Zh = _rows(K, d, seed=step)
+        F.gram_f16(Zh, n, delta, scratch=scratch, peers=peers)
+        torch.cuda.synchronize()
+        r, b = _ref(Zh, n)
+        total += r
+        bound += b
+        assert float(delta.abs().max()) == 0.0, "the local delta must be zero again after the push"
+        for p in range(world):
+            assert int(pads[p][PAD_GSTEP + peers.rank]) == step
+    keep = _upper_blocks(n, "cuda")
+    tol = 1e-5 * bound + 1e-5
+    for p in range(world):
+        lo, hi = p * rows_per_owner, min(n, (p + 1) * rows_per_owner)
+        got = owners[p][:n, :n].double()
+        if lo < hi:
+            err = (got[lo:hi] - total[lo:hi]).abs()
+            assert bool((err[keep[lo:hi]] <= tol[lo:hi][keep[lo:hi]]).all()), (p, float(err.max()))
+        mask = torch.ones(n, dtype=torch.bool, device="cuda")
+        mask[lo:hi] = False
+        assert float(got[mask].abs().max()) == 0.0 if mask.any() else True, f"owner {p} received foreign rows"
+
+
+def test_gram_f16_speed_report():
+    """Not an assertion on speed: prints the device time at the bench shape so a GPU run leaves the number behind."""
+    K, d = 32768, 1000
+    n = d + 3
+    pool = [_rows(K, d, seed=s) for s in range(3)]          # 3 x 64 MB > L2 in total
+    C = torch.zeros(1024, 1024, device="cuda")
+    for Zh in pool:
+        F.gram_f16(Zh, n, C)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    reps = 30
+    for i in range(reps):
+        F.gram_f16(pool[i % 3], n, C)
+    e1.record()
+    torch.cuda.synchronize()
+    us = 1000.0 * e0.elapsed_time(e1) / reps
+    flops = 2.0 * K * 10 * 256 * 256            # 10 upper 256 x 256 tiles
+    print(f"\ngram_f16 K={K} d={d}: {us:.1f} us per call, {flops / us / 1e6:.0f} TFLOP/s executed")
+    assert us > 0

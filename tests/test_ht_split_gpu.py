@@ -7,7 +7,7 @@ from omldm_b200.engine import Engine
 from omldm_b200.stream import ring as R
 from omldm_b200.utils.config import JobParameters
 
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(reason="first hardware run pending", strict=False)]
+pytestmark = pytest.mark.gpu
 
 
 def test_device_grown_tree_matches_host_grown_tree():

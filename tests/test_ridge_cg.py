@@ -8,7 +8,6 @@ from omldm_b200.ops import functional as F
 from omldm_b200.stream import ring as R
 from omldm_b200.utils.config import JobParameters
 
-_first_hw_run = pytest.mark.xfail(reason="first hardware run pending", strict=False)
 
 
 def _system(n, m, seed, device="cpu"):
@@ -88,7 +87,6 @@ def test_orr_cg_falls_back_to_direct_solve():
 
 
 @pytest.mark.gpu
-@_first_hw_run
 def test_ridge_cg_kernel_matches_fp64_solve():
     for n, m in ((7, 100), (129, 3000), (1001, 20000)):
         W = _system(n, m, n + 1, "cuda")
@@ -106,7 +104,6 @@ def test_ridge_cg_kernel_matches_fp64_solve():
 
 
 @pytest.mark.gpu
-@_first_hw_run
 def test_orr_gpu_cg_refresh_matches_cholesky():
     d = 200
     outs = []

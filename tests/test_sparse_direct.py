@@ -11,7 +11,6 @@ from omldm_b200.stream import ring as R
 from omldm_b200.utils.checkpoint import load_checkpoint, save_checkpoint
 from omldm_b200.utils.config import JobParameters
 
-_first_hw_run = pytest.mark.xfail(reason="first hardware run pending", strict=False)
 D, B, NNZ, C = 5000, 64, 16, 6
 
 
@@ -103,7 +102,6 @@ def test_direct_route_checkpoint_roundtrip(tmp_path):
 
 
 @pytest.mark.gpu
-@_first_hw_run
 def test_sparse_kernels_match_reference_route():
     """GPU sparse kernels vs the torch restatement (CPU engine, same sparse semantics incl. duplicates)."""
     ref, gpu = _engine(True, "cpu"), _engine(True, "cuda")
@@ -122,7 +120,6 @@ def test_sparse_kernels_match_reference_route():
 
 
 @pytest.mark.gpu
-@_first_hw_run
 def test_sparse_rows_kernel():
     slot = R.generate_sparse_batch(D, B, NNZ, n_aux=C, seed=3, batch_index=1)
     idx, val, tgt = R.SparseTopic.unpack(slot, B, NNZ)

@@ -13,11 +13,6 @@ from omldm_b200.stream import ring as R
 from omldm_b200.utils.config import JobParameters
 
 
-# Written after this round's GPU budget was spent: until their first hardware run these two must not be able
-# to stop the suite (`-x`), so a failure is reported as xfail and a pass as xpass.
-_first_hw_run = pytest.mark.xfail(reason="first hardware run pending", strict=False)
-
-
 def _bits(t):
     return t.contiguous().view(torch.int16)
 
@@ -111,7 +106,6 @@ def test_engine_e2e_path_accepts_wire_rows():
 
 
 @pytest.mark.gpu
-@_first_hw_run
 def test_stage_rows_f16_kernel_matches_reference():
     """Kernel vs the plain torch restatement of the same op (exact: the conversion is a widening)."""
     for d, B in ((1, 3), (5, 7), (28, 1000), (1000, 4096), (999, 513)):
@@ -129,10 +123,9 @@ def test_stage_rows_f16_kernel_matches_reference():
 
 
 @pytest.mark.gpu
-@_first_hw_run
 def test_engine_e2e_wire_f16_gpu():
     d = 28
-    eng = Engine(JobParameters(parallelism=1, testSetSize=64))
+    eng = Engine(JobParameters(parallelism=1, testSetSize=32))      # same holdout size as the CPU engine of _engine()
     eng.handle_request({"id": 1, "request": "Create", "learner": {"name": "PA", "hyperParameters": {"C": 0.1}},
                         "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": d}})
     ref = _engine(d, {"name": "PA", "hyperParameters": {"C": 0.1}})
