@@ -264,6 +264,20 @@ using namespace omldm;
 
 extern "C" size_t omldm_gram_f16_scratch_words(void) { return 512; }
 
+// The batch-axis split omldm_gram_f16 uses for (K, n, ksplit): records per split (0 if K <= 0).
+extern "C" int omldm_gram_f16_rows_per_split(int K, int n, int ksplit) {
+  if (K <= 0 || n < 1) return 0;
+  const int T = (n + 255) / 256;
+  const int tiles = T * (T + 1) / 2;
+  if (ksplit <= 0) {
+    ksplit = 74 / tiles;
+    if (ksplit < 1) ksplit = 1;
+  }
+  const int max_split = (K + 4 * G_BK - 1) / (4 * G_BK);
+  if (ksplit > max_split) ksplit = max_split;
+  return ((K + ksplit - 1) / ksplit + G_BK - 1) / G_BK * G_BK;
+}
+
 extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers,
                               uint32_t* scratch, int ksplit, void* stream) {
   if (K <= 0) return 0;
@@ -293,13 +307,7 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
     for (int p = peers->world; p < 16; ++p) push.owner[p] = push.owner[0];
   }
   // split the batch axis so that the pairs fill the 74 SM pairs; at least 4 stages of work per CTA
-  if (ksplit <= 0) {
-    ksplit = 74 / tiles;
-    if (ksplit < 1) ksplit = 1;
-  }
-  const int max_split = (K + 4 * G_BK - 1) / (4 * G_BK);
-  if (ksplit > max_split) ksplit = max_split;
-  const int k_per_split = ((K + ksplit - 1) / ksplit + G_BK - 1) / G_BK * G_BK;
+  const int k_per_split = omldm_gram_f16_rows_per_split(K, n, ksplit);
   const int gy = (K + k_per_split - 1) / k_per_split;
   static bool attr_set[16] = {};
   int dev = 0;

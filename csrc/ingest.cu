@@ -7,6 +7,7 @@
 // #(h - cap).  The kernel swaps rows in place, so after it runs the batch rows ARE the training
 // sequence in the original order (an empty row, bias column 0, where nothing was evicted yet).
 #include <cuda_fp16.h>
+#include <cstring>
 #include "ptx.cuh"
 #include "host_common.h"
 #include "omldm_kernels.h"
@@ -24,55 +25,64 @@ __host__ __device__ inline long long holdouts_before(long long c) {
 // shift by one along the chain: ring <- row i_m, row i_j <- row i_{j-1}, row i_0 <- old ring
 // content (or an empty row while the ring is still filling).  Each thread owns a fixed set of
 // columns, walks the chain from the tail and so never needs a barrier.
-__global__ void __launch_bounds__(256)
+// V = the vector a thread moves (float4, or float2 for short rows so that all 256 threads of the CTA have a column:
+// a 2 KB fp16 staged row is 256 float2); MAXC rows are in flight per thread (all loads issued before the shifted stores).
+// `count_dev` (graph-replayable launches): the running record count is read from device memory and advanced by the
+// LAST CTA to finish - every CTA has read the old value by then (`done` is a self-resetting arrival counter).
+template <typename V, int MAXC, bool EVEN_CAP>
+__global__ void __launch_bounds__(256, 2)
 holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restrict__ ring, int cap,
-                    long long count0_arg, const long long* __restrict__ count_dev) {
-  const long long count0 = count_dev ? *count_dev : count0_arg;
+                    long long count0_arg, long long* __restrict__ count_dev, unsigned int* __restrict__ done) {
+  const long long count0 = count_dev ? *reinterpret_cast<volatile long long*>(count_dev) : count0_arg;
   const int slot = blockIdx.x;
-  if (slot >= cap) return;
   const long long h0 = holdouts_before(count0), h1 = holdouts_before(count0 + B);
   const long long hf = h0 + ((slot - (h0 % cap)) % cap + cap) % cap;   // first chain element
-  if (hf >= h1) return;
-  const int m = static_cast<int>((h1 - 1 - hf) / cap);                // chain has m + 1 elements
-  auto row_of = [&](int j) -> float* {
-    const long long h = hf + static_cast<long long>(j) * cap;
-    const long long c = (h / 2) * 10 + 8 + (h & 1);
-    return Z + static_cast<size_t>(c - count0) * ld;
-  };
-  const bool evict = hf >= cap;
-  float* rs = ring + static_cast<size_t>(slot) * ld;
-  const int ld4 = ld >> 2;   // ld is a multiple of 32
-  constexpr int MAXC = 16;
-  for (int c4 = threadIdx.x; c4 < ld4; c4 += blockDim.x) {
-    float4* r4 = reinterpret_cast<float4*>(rs) + c4;
-    const float4 old = evict ? *r4 : make_float4(0.f, 0.f, 0.f, 0.f);
-    if (m < MAXC) {
-      // short chain: issue every load first (independent, pipelined), then the shifted stores
-      float4 v[MAXC];
-#pragma unroll
-      for (int j = 0; j < MAXC; ++j)
-        if (j <= m) v[j] = reinterpret_cast<const float4*>(row_of(j))[c4];
-#pragma unroll
-      for (int j = 0; j < MAXC; ++j) {
-        if (j == m) *r4 = v[j];
-        else if (j < m) reinterpret_cast<float4*>(row_of(j + 1))[c4] = v[j];
-      }
-    } else {
-      // long chain: walk it from the tail in segments of MAXC rows; inside a segment every load is
-      // issued before the shifted stores, so only ceil(m / MAXC) phases are serialised
-      *r4 = reinterpret_cast<float4*>(row_of(m))[c4];
+  if (slot < cap && hf < h1) {
+    const int m = static_cast<int>((h1 - 1 - hf) / cap);                // chain has m + 1 elements
+    // with an even ring size every element of a chain has the parity of the first one, so its rows are equally
+    // spaced (5 cap records apart): one base pointer and a stride instead of a pointer per row
+    const long long c0 = (hf / 2) * 10 + 8 + (hf & 1);
+    V* const r0 = reinterpret_cast<V*>(Z + static_cast<size_t>(c0 - count0) * ld);
+    const size_t rstride = static_cast<size_t>(cap / 2) * 10 * ld / (sizeof(V) / sizeof(float));
+    auto row_of = [&](int j) -> V* {
+      if (EVEN_CAP) return r0 + static_cast<size_t>(j) * rstride;
+      const long long h = hf + static_cast<long long>(j) * cap;
+      const long long c = (h / 2) * 10 + 8 + (h & 1);
+      return reinterpret_cast<V*>(Z + static_cast<size_t>(c - count0) * ld);
+    };
+    const bool evict = hf >= cap;
+    V* rs = reinterpret_cast<V*>(ring + static_cast<size_t>(slot) * ld);
+    const int ldv = ld / static_cast<int>(sizeof(V) / sizeof(float));
+    V zero;
+    memset(&zero, 0, sizeof(V));
+    for (int cv = threadIdx.x; cv < ldv; cv += blockDim.x) {
+      V* rv = rs + cv;
+      const V old = evict ? *rv : zero;
+      // walk the chain from the tail in segments of MAXC rows: row i_j <- row i_{j-1}.  Inside a segment every load is
+      // issued before the shifted stores (independent, pipelined), so only ceil(m / MAXC) phases are serialised.
+      *rv = row_of(m)[cv];
       for (int hi = m; hi >= 1; hi -= MAXC) {
         const int lo = hi - MAXC + 1 > 1 ? hi - MAXC + 1 : 1;   // rows lo..hi receive rows lo-1..hi-1
-        float4 v[MAXC];
+        V v[MAXC];
 #pragma unroll
         for (int t = 0; t < MAXC; ++t)
-          if (lo + t <= hi) v[t] = reinterpret_cast<const float4*>(row_of(lo + t - 1))[c4];
+          if (lo + t <= hi) v[t] = row_of(lo + t - 1)[cv];
 #pragma unroll
         for (int t = 0; t < MAXC; ++t)
-          if (lo + t <= hi) reinterpret_cast<float4*>(row_of(lo + t))[c4] = v[t];
+          if (lo + t <= hi) row_of(lo + t)[cv] = v[t];
+      }
+      row_of(0)[cv] = old;
+    }
+  }
+  if (count_dev != nullptr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int prev = atomicAdd(done, 1u);
+      if (prev == gridDim.x - 1) {              // every CTA has read the old count
+        *done = 0;
+        *count_dev = count0 + B;
       }
     }
-    reinterpret_cast<float4*>(row_of(0))[c4] = old;
   }
 }
 
@@ -152,23 +162,34 @@ __global__ void stage_rows_f16_kernel(const __half* __restrict__ raw, int raw_ld
 
 using namespace omldm;
 
+static int launch_holdout(float* Z, int ld, int B, int d, float* ring, int cap, long long count0, long long* count_dev,
+                          unsigned int* done, cudaStream_t st) {
+  if (ld & 3) return set_error_msg("holdout_swap: ld must be a multiple of 4");
+  const bool even = (cap & 1) == 0;
+  if (ld <= 512) {  // short rows (e.g. 2 KB fp16 staged rows viewed as 512 words): 8 bytes per thread keeps the CTA busy
+    if (even) holdout_swap_kernel<float2, 32, true><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+    else holdout_swap_kernel<float2, 16, false><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+  } else {
+    if (even) holdout_swap_kernel<float4, 16, true><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+    else holdout_swap_kernel<float4, 16, false><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+  }
+  return check_launch("holdout_swap_kernel");
+}
+
 extern "C" int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, int cap, long long count0,
                                   void* stream) {
   if (B <= 0 || cap <= 0) return 0;
   if (holdouts_before(count0 + B) == holdouts_before(count0)) return 0;
-  if (ld & 3) return set_error_msg("holdout_swap: ld must be a multiple of 4");
-  holdout_swap_kernel<<<cap, 256, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, ring, cap, count0, nullptr);
-  return check_launch("holdout_swap_kernel");
+  return launch_holdout(Z, ld, B, d, ring, cap, count0, nullptr, nullptr, static_cast<cudaStream_t>(stream));
 }
 
-// Graph-replayable variant: the running record count lives in device memory and is advanced by
-// `omldm_advance_count` (a separate node, so every block of the swap kernel reads the old value).
+// Graph-replayable variant: the running record count lives in device memory (count_dev[0]) and is advanced by the
+// kernel itself once every CTA has read it; count_dev[1] is the kernel's arrival counter (zero before the first call).
 extern "C" int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* ring, int cap,
-                                      const long long* count_dev, void* stream) {
+                                      long long* count_dev, void* stream) {
   if (B <= 0 || cap <= 0) return 0;
-  if (ld & 3) return set_error_msg("holdout_swap: ld must be a multiple of 4");
-  holdout_swap_kernel<<<cap, 256, 0, static_cast<cudaStream_t>(stream)>>>(Z, ld, B, d, ring, cap, 0, count_dev);
-  return check_launch("holdout_swap_kernel");
+  return launch_holdout(Z, ld, B, d, ring, cap, 0, count_dev, reinterpret_cast<unsigned int*>(count_dev + 1),
+                        static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int omldm_advance_count(long long* count_dev, long long delta, void* stream) {

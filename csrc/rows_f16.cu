@@ -36,11 +36,29 @@ expand_rows_f16s_kernel(const __half* __restrict__ Zh, int ldh, int B, int d, fl
   }
 }
 
-// One warp per row, two rows in flight, 16-byte loads (8 halves).  wt = [w_0..w_{d-1}, b, -1, -1] sits in shared memory
-// as fp32; the row's dot product with it is the residual.
+__device__ __forceinline__ float dot8(const float4& a, const float4& w0, const float4& w1, float acc) {
+  const __half2* h = reinterpret_cast<const __half2*>(&a);
+  float2 t;
+  t = __half22float2(h[0]); acc = fmaf(t.x, w0.x, acc); acc = fmaf(t.y, w0.y, acc);
+  t = __half22float2(h[1]); acc = fmaf(t.x, w0.z, acc); acc = fmaf(t.y, w0.w, acc);
+  t = __half22float2(h[2]); acc = fmaf(t.x, w1.x, acc); acc = fmaf(t.y, w1.y, acc);
+  t = __half22float2(h[3]); acc = fmaf(t.x, w1.z, acc); acc = fmaf(t.y, w1.w, acc);
+  return acc;
+}
+
+// One warp per row, RI rows in flight per warp, 16-byte loads (8 halves): RI x (row bytes / 512) independent loads per
+// lane are issued before any of them is consumed.  wt = [w_0..w_{d-1}, b, -1, -1] sits in shared memory as fp32; the
+// row's dot product with it is the residual.
+constexpr int RI = 4;
+// `rows_per_range` > 0: the batch is swept as ceil(B / rows_per_range) ranges side by side, blockIdx.y = range, each in
+// row order - the order in which the split-K CTAs of the Gram kernel read the same rows, so that whichever kernel is
+// ahead pulls a row from HBM and the other finds it in L2 when the two run concurrently.
 __global__ void __launch_bounds__(256)
-sq_residual_f16s_kernel(const __half* __restrict__ Zh, int ldh, int B, int d, const float* __restrict__ wt,
-                        double* __restrict__ stats) {
+sq_residual_f16s_kernel(const __half* __restrict__ Zh_all, int ldh, int B_all, int d, const float* __restrict__ wt,
+                        double* __restrict__ stats, int rows_per_range) {
+  const int row0 = rows_per_range > 0 ? blockIdx.y * rows_per_range : 0;
+  const int B = rows_per_range > 0 ? min(rows_per_range, B_all - row0) : B_all;
+  const __half* __restrict__ Zh = Zh_all + static_cast<size_t>(row0) * ldh;
   extern __shared__ float s_w[];          // ldh floats, zero beyond d + 3
   const int n = d + 3;
   for (int c = threadIdx.x; c < ldh; c += blockDim.x) s_w[c] = c < n ? wt[c] : 0.f;
@@ -51,31 +69,41 @@ sq_residual_f16s_kernel(const __half* __restrict__ Zh, int ldh, int B, int d, co
   const int n8 = (n + 7) >> 3;
   double acc = 0.0;
   int nv = 0;
-  for (int r = warp; r < B; r += 2 * nwarps) {
-    const int r2 = r + nwarps;
-    const uint4* z0 = reinterpret_cast<const uint4*>(Zh + static_cast<size_t>(r) * ldh);
-    const uint4* z1 = reinterpret_cast<const uint4*>(Zh + static_cast<size_t>(r2 < B ? r2 : r) * ldh);
-    float d0 = 0.f, d1 = 0.f;
-    for (int c = lane; c < n8; c += 32) {
-      const uint4 a = __ldg(z0 + c), b = __ldg(z1 + c);
-      const float4 w0 = *reinterpret_cast<const float4*>(s_w + 8 * c);
-      const float4 w1 = *reinterpret_cast<const float4*>(s_w + 8 * c + 4);
-      const __half2* ah = reinterpret_cast<const __half2*>(&a);
-      const __half2* bh = reinterpret_cast<const __half2*>(&b);
-      float2 t;
-      t = __half22float2(ah[0]); d0 = fmaf(t.x, w0.x, d0); d0 = fmaf(t.y, w0.y, d0);
-      t = __half22float2(ah[1]); d0 = fmaf(t.x, w0.z, d0); d0 = fmaf(t.y, w0.w, d0);
-      t = __half22float2(ah[2]); d0 = fmaf(t.x, w1.x, d0); d0 = fmaf(t.y, w1.y, d0);
-      t = __half22float2(ah[3]); d0 = fmaf(t.x, w1.z, d0); d0 = fmaf(t.y, w1.w, d0);
-      t = __half22float2(bh[0]); d1 = fmaf(t.x, w0.x, d1); d1 = fmaf(t.y, w0.y, d1);
-      t = __half22float2(bh[1]); d1 = fmaf(t.x, w0.z, d1); d1 = fmaf(t.y, w0.w, d1);
-      t = __half22float2(bh[2]); d1 = fmaf(t.x, w1.x, d1); d1 = fmaf(t.y, w1.y, d1);
-      t = __half22float2(bh[3]); d1 = fmaf(t.x, w1.z, d1); d1 = fmaf(t.y, w1.w, d1);
+  if (B <= 0) return;
+  for (int r = warp; r < B; r += RI * nwarps) {
+    const float4* z[RI];
+    float dsum[RI];
+#pragma unroll
+    for (int u = 0; u < RI; ++u) {
+      const int ru = r + u * nwarps;
+      z[u] = reinterpret_cast<const float4*>(Zh + static_cast<size_t>(ru < B ? ru : r) * ldh);
+      dsum[u] = 0.f;
     }
-    d0 = warp_sum(d0);
-    d1 = warp_sum(d1);
-    if (__half2float(Zh[static_cast<size_t>(r) * ldh + d]) != 0.f) { acc += static_cast<double>(d0) * d0; nv += 1; }
-    if (r2 < B && __half2float(Zh[static_cast<size_t>(r2) * ldh + d]) != 0.f) { acc += static_cast<double>(d1) * d1; nv += 1; }
+    for (int c0 = 0; c0 < n8; c0 += 64) {                   // two 16-byte loads per row and lane per trip
+      const int ca = c0 + lane, cb = c0 + 32 + lane;
+      float4 va[RI], vb[RI];
+#pragma unroll
+      for (int u = 0; u < RI; ++u) {
+        va[u] = ca < n8 ? ld_nc_v4(z[u] + ca) : make_float4(0.f, 0.f, 0.f, 0.f);
+        vb[u] = cb < n8 ? ld_nc_v4(z[u] + cb) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      if (ca < n8) {
+        const float4 w0 = *reinterpret_cast<const float4*>(s_w + 8 * ca), w1 = *reinterpret_cast<const float4*>(s_w + 8 * ca + 4);
+#pragma unroll
+        for (int u = 0; u < RI; ++u) dsum[u] = dot8(va[u], w0, w1, dsum[u]);
+      }
+      if (cb < n8) {
+        const float4 w0 = *reinterpret_cast<const float4*>(s_w + 8 * cb), w1 = *reinterpret_cast<const float4*>(s_w + 8 * cb + 4);
+#pragma unroll
+        for (int u = 0; u < RI; ++u) dsum[u] = dot8(vb[u], w0, w1, dsum[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < RI; ++u) {
+      const float du = warp_sum(dsum[u]);
+      const int ru = r + u * nwarps;
+      if (ru < B && __half2float(Zh[static_cast<size_t>(ru) * ldh + d]) != 0.f) { acc += static_cast<double>(du) * du; nv += 1; }
+    }
   }
   __shared__ double s_l[8];
   __shared__ int s_n[8];
@@ -101,7 +129,8 @@ extern "C" int omldm_expand_rows_f16s(const void* Zh, int ldh, int B, int d, flo
   return check_launch("expand_rows_f16s_kernel");
 }
 
-extern "C" int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats, void* stream) {
+extern "C" int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats,
+                                      int rows_per_range, void* stream) {
   if (B <= 0) return 0;
   if ((ldh & 7) || ldh < d + 3) return set_error_msg("sq_residual_f16s: the fp16 pitch must be a multiple of 8 and >= d + 3");
   if (reinterpret_cast<uintptr_t>(Zh) & 15) return set_error_msg("sq_residual_f16s: rows must be 16-byte aligned");
@@ -111,8 +140,15 @@ extern "C" int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, con
     cudaError_t e = cudaFuncSetAttribute(sq_residual_f16s_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(sq_residual_f16s)", e);
   }
-  int blocks = (B + 15) / 16;
-  if (blocks > 148 * 4) blocks = 148 * 4;
-  sq_residual_f16s_kernel<<<blocks, 256, smem, static_cast<cudaStream_t>(stream)>>>(static_cast<const __half*>(Zh), ldh, B, d, wt, stats);
+  int ranges = 1;
+  if (rows_per_range > 0) ranges = (B + rows_per_range - 1) / rows_per_range;
+  if (ranges < 1 || ranges > 1024) return set_error_msg("sq_residual_f16s: bad rows_per_range");
+  const int per = ranges > 1 ? rows_per_range : B;
+  int blocks = (per + 31) / 32;
+  const int cap = (148 * 3 + ranges - 1) / ranges;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  sq_residual_f16s_kernel<<<dim3(blocks, ranges), 256, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __half*>(Zh), ldh, B, d, wt, stats, ranges > 1 ? rows_per_range : 0);
   return check_launch("sq_residual_f16s_kernel");
 }

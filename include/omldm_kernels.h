@@ -59,6 +59,7 @@ typedef struct omldm_gram_peers {
   int rows_per_owner;        /* multiple of 32; owner p holds rows [p * rows_per_owner, (p + 1) * rows_per_owner) */
 } omldm_gram_peers;
 size_t omldm_gram_f16_scratch_words(void);
+int omldm_gram_f16_rows_per_split(int K, int n, int ksplit);   /* records per batch-axis split the kernel will use */
 int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers_host,
                    uint32_t* scratch, int ksplit, void* stream);
 
@@ -67,8 +68,12 @@ int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const
  * Conversion behind utils/parsers/dataStream/DataPointParser.scala:16-55. */
 int omldm_expand_rows_f16s(const void* Zh, int ldh, int B, int d, float* Z, int ld, void* stream);
 /* stats[0] += sum over valid rows of (w.x + b - y)^2, stats[2] += #valid, straight from f16s rows;
- * wt = [w_0..w_{d-1}, b, -1, -1] (d + 3 floats).  Predict-before-fit of ORR, operators/spoke/FlinkSpoke.scala:101. */
-int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats, void* stream);
+ * wt = [w_0..w_{d-1}, b, -1, -1] (d + 3 floats).  Predict-before-fit of ORR, operators/spoke/FlinkSpoke.scala:101.
+ * rows_per_range > 0: sweep the batch as ceil(B / rows_per_range) ranges side by side, each in row order (pass
+ * omldm_gram_f16_rows_per_split so that the pass walks the rows in the order of the concurrent Gram kernel and the two
+ * share them through L2); 0 = one range. */
+int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats, int rows_per_range,
+                           void* stream);
 
 /* ------------------------------------------------------------------ linear learners (linear_learners.cu)
  * PA / RegressorPA / SVM named in utils/parsers/requestStream/PipelineMap.scala:68. */
@@ -118,10 +123,10 @@ int omldm_linear_predict(const float* Z, int ld, int B, const float* w, int d, f
  * `count0` = number of training records seen before this batch; holdout ring = `cap` rows. */
 int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, int cap, long long count0,
                        void* stream);
-/* CUDA-graph friendly variant: the record count is read from device memory; advance it with
- * omldm_advance_count after the swap (separate launch, so all blocks saw the old value) */
+/* CUDA-graph friendly variant: count_dev[0] = running record count in device memory, read by every CTA and advanced
+ * by B by the last CTA to finish; count_dev[1] = arrival counter of the kernel (zero before the first call) */
 int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* ring, int cap,
-                           const long long* count_dev, void* stream);
+                           long long* count_dev, void* stream);
 int omldm_advance_count(long long* count_dev, long long delta, void* stream);
 /* sparse (CSR batch) -> dense staged rows + squared row norms (SparseVector, utils/CommonUtils.scala:23) */
 int omldm_densify(const int* indptr, const int* indices, const float* values, int B, int d,
@@ -256,6 +261,18 @@ int omldm_sync_scatter_push(const omldm_comm* comm_host, float* delta_local, siz
                             void* stream);
 int omldm_sync_scatter_gather(const omldm_comm* comm_host, float* e_local, size_t n, float scale, uint32_t epoch,
                               uint32_t step, int blocks, void* stream);
+/* Sharded-hub Synchronous protocol for the ORR Gram statistics (worker -> hub push network/FlinkNetwork.scala:260-261;
+ * the hub -> worker broadcast :282-291 becomes a pull at weight refreshes).  hubs[p] = GPU p's ld x ld accumulation
+ * matrix, authoritative for rows [p * rows_per_owner, (p + 1) * rows_per_owner).
+ * push  : adds the upper 32 x 32 blocks of the local delta (then cleared) into the owners' rows, then publishes the
+ *         step number (step_words[0], advanced by the call) in every pad.  Never waits.  The fp16 Gram kernel
+ *         (omldm_gram_f16 with peers) performs this step itself; use the same step words for both.
+ * gather: waits until every peer has published the caller's own step, copies the other owners' rows (from their
+ *         diagonal block rightwards) into the local matrix, exit rendezvous.  Collective, same step on all ranks. */
+int omldm_sync_gram_push(const omldm_comm* comm_host, float* delta_local, int ld, int n, int rows_per_owner,
+                         uint32_t* step_words, int blocks, void* stream);
+int omldm_sync_gram_gather(const omldm_comm* comm_host, int ld, int n, int rows_per_owner, const uint32_t* step_words,
+                           uint32_t epoch, int blocks, void* stream);
 /* SingleLearner forwarding (mlworkers.ForwardingWorker -> CentralizedMLServer, MLNodeGenerator.scala:27,56): every
  * rank stores its n-float mini-batch into rank 0's symmetric buffer (2 * world * n floats: slot seq & 1, position =
  * rank); rank 0 returns once all world batches of `seq` have arrived and trains on them.  seq = 1, 2, ... (same on
@@ -341,6 +358,13 @@ size_t omldm_ridge_cg_work_floats(int n);
 size_t omldm_ridge_cg_scalar_bytes(int max_iter);
 int omldm_ridge_cg(const float* A, int ld, int n, float lam, const float* b, int b_stride, float* x, float* work,
                    void* scalars, int max_iter, float tol, float* info, int blocks, void* stream);
+
+/* Direct ridge solve (no counterpart in the reference; replaces the library potrf / potrs pair): blocked Cholesky of
+ * A + lam I with the right-hand side carried as an extra row, one cooperative launch.  W: (n + 1) x (n + 1) leading
+ * block of a FULL symmetric matrix, pitch ld floats, rows / columns 0..n-1 = A, row n = b^T; destroyed.  x <- solution
+ * (n floats, must not alias W); info[0] <- 1 when a pivot was not positive (the caller falls back to fp64), else 0.
+ * blocks 0 = 64 CTAs.  Query-time model read, operators/spoke/FlinkSpoke.scala:163. */
+int omldm_ridge_chol(float* W, int ld, int n, float lam, float* x, float* info, int blocks, void* stream);
 
 /* CUDA IPC plumbing for the symmetric arena (one dedicated, zero-filled cudaMalloc per region) */
 int omldm_dev_malloc(size_t bytes, void** out);

@@ -78,6 +78,7 @@ class Engine:
         self._sparse_nnz: Optional[int] = None
         self._srows: List[Optional[torch.Tensor]] = [None, None]
         self._srows_i = 0
+        self._expand: Dict[Any, torch.Tensor] = {}
         self.forward_peer = str(self.params.extra.get("forwardTransport", "peer")).lower() != "nccl"
         self._fwd_comm = None            # SingleLearner forwarding channel (created on first use, collective)
         self._fwd_n = 0
@@ -150,9 +151,11 @@ class Engine:
         return frags
 
     # ============================================================================ data plane
-    def _ensure_holdout(self, ld: int) -> None:
+    def _ensure_holdout(self, ld: int, dtype=torch.float32) -> None:
         if self.holdout is None:
-            self.holdout = torch.zeros(self.params.testSetSize, ld, device=self.device)
+            self.holdout = torch.zeros(self.params.testSetSize, ld, device=self.device, dtype=dtype)
+        elif self.holdout.dtype != dtype:
+            raise ValueError("one stream, one row format: fp32 and fp16 staged rows cannot be mixed in one engine")
 
     def _holdout_rows(self) -> torch.Tensor:
         if self.holdout is None:
@@ -160,6 +163,8 @@ class Engine:
         n = min(F.holdouts_before(self.count), self.holdout.shape[0])
         if self._sparse_nnz is not None:      # the ring holds sparse rows: score on their dense form
             return F.sparse_rows_to_dense(self.holdout[:n], self._sparse_nnz, self.d)
+        if self.holdout.dtype == torch.float16:     # fp16 staged rows: score on their fp32 form
+            return F.expand_rows_f16s(self.holdout[:n].contiguous(), self.d)
         return self.holdout[:n]
 
     def train_batch(self, Z: torch.Tensor, d: Optional[int] = None, **kw) -> None:
@@ -174,9 +179,13 @@ class Engine:
             d = self.d
         if d is None:
             raise ValueError("feature dimension not known; pass d on the first batch")
-        if Z.dim() != 2 or Z.dtype != torch.float32 or Z.stride(1) != 1 or Z.stride(0) != Z.shape[1]:
-            raise ValueError("train_batch expects a contiguous 2-D fp32 tensor of staged rows")
-        if Z.shape[1] % 32 or Z.shape[1] < d + 2:
+        if Z.dim() != 2 or Z.dtype not in (torch.float32, torch.float16) or Z.stride(1) != 1 or Z.stride(0) != Z.shape[1]:
+            raise ValueError("train_batch expects a contiguous 2-D tensor of staged rows (fp32, or fp16 'f16s' rows)")
+        if Z.dtype == torch.float16:
+            if Z.shape[1] != F.f16s_pitch(d):
+                raise ValueError(f"fp16 staged rows for d = {d} need a pitch of {F.f16s_pitch(d)} halves "
+                                 f"([x | 1 | y_hi | y_lo | pad], omldm_b200.ops.functional.pack_f16s); got {Z.shape[1]}")
+        elif Z.shape[1] % 32 or Z.shape[1] < d + 2:
             raise ValueError(f"staged rows need a pitch that is a multiple of 32 floats and >= d + 2 = {d + 2}; "
                              f"got {Z.shape[1]} (use omldm_b200.ops.functional.stage_rows or stream.ring.Topic)")
         if Z.device.type != self.device.type or (Z.device.index is not None and self.device.index is not None
@@ -198,7 +207,7 @@ class Engine:
         for p in self.pipelines.values():
             if p.protocol != "SingleLearner" or self.rank == 0:
                 self._build(p, d)
-        key = (Z.data_ptr(), B, ld, nnz) + tuple(p.driver.graph_key() for p in self.pipelines.values()
+        key = (Z.data_ptr(), B, ld, nnz, Z.dtype) + tuple(p.driver.graph_key() for p in self.pipelines.values()
                                                  if p.built and hasattr(p.driver, "graph_key"))
         g = None
         if self.use_graphs and not kw and self._graphable(Z):
@@ -272,27 +281,39 @@ class Engine:
         for p in self.pipelines.values():
             if p.built and hasattr(p.driver, "begin_step"):
                 p.driver.begin_step()          # fork: overlapped all-reduce of the previous step's delta
+        half = Z.dtype == torch.float16
         if self.holdout_enabled and self.params.testSetSize > 0:
-            self._ensure_holdout(ld)
+            self._ensure_holdout(ld, Z.dtype)
+            # fp16 staged rows move as raw bytes: the holdout rule is a pure row move, and an all-zero row is empty in
+            # both layouts, so the same kernel serves both with the rows viewed as fp32 words
+            Zv, ring = (Z.view(torch.float32), self.holdout.view(torch.float32)) if half else (Z, self.holdout)
             if F.native(Z):                     # (true for CUDA batches; also under the CPU kernel emulation)
                 if self._count_dev is None:
-                    self._count_dev = torch.tensor([self.count], dtype=torch.int64, device=self.device)
-                F.holdout_swap_dev(Z, self.holdout, d, self._count_dev)   # 2-in-10 holdout, evict-then-train
+                    self._count_dev = torch.tensor([self.count, 0], dtype=torch.int64, device=self.device)
+                F.holdout_swap_dev(Zv, ring, d, self._count_dev)   # 2-in-10 holdout, evict-then-train
             else:
-                F.holdout_swap(Z, self.holdout, d, self.count)
+                F.holdout_swap(Zv, ring, d, self.count)
+        Z32 = None
+        if half and not all(p.f16_capable() for p in self.pipelines.values() if p.built or p.protocol != "SingleLearner"):
+            # some pipeline has no fp16 path: expand once per step (csrc/rows_f16.cu)
+            kx = (B, d)
+            if self._expand.get(kx) is None:
+                self._expand = {kx: torch.empty(B, F.pad32(d + 2), device=self.device)}
+            Z32 = F.expand_rows_f16s(Z, d, out=self._expand[kx])
         n_pipes = len(self.pipelines)
-        batched = self._batched_exact_fit(Z, d) if nnz is None else ()
+        batched = self._batched_exact_fit(Z32 if half else Z, d) if (nnz is None and (not half or Z32 is not None)) else ()
         for p in self.pipelines.values():
             due = p.built and (p.driver._batches % p.driver.sync_every == p.driver.sync_every - 1)
+            Zp = Z if (not half or p.f16_capable()) else Z32
             if p in batched:
-                p.device_train(Z, False, due, skip_fit=True)
+                p.device_train(Zp, False, due, skip_fit=True)
                 continue
             if p.protocol == "SingleLearner":
-                Zs = self._forward_to_rank0(Z)
+                Zs = self._forward_to_rank0(Zp)
                 if self.rank == 0:
                     p.device_train(Zs, True, due, **kw)
                 continue
-            p.device_train(Z, n_pipes > 1, due, **kw)
+            p.device_train(Zp, n_pipes > 1 and not (half and Zp is Z), due, **kw)
 
     def _batched_exact_fit(self, Z: torch.Tensor, d: int):
         """Multi-tenant fast path: all exact-mode linear pipelines without preprocessors advance in ONE
@@ -354,28 +375,52 @@ class Engine:
         return c.buf.view(2, self.world * B, ld)[self._fwd_seq & 1]
 
     # ---- end-to-end path: pinned host slot -> device -> train -> loss back to the host -------------
-    def train_batch_host(self, Z_host: torch.Tensor, d: int, **kw) -> torch.Tensor:
-        """One e2e step from a pinned host slot.  Returns a pinned fp64[4] tensor that will hold
-        (loss_sum, aux, fitted, extra) of the first pipeline once the current stream has drained."""
-        if Z_host.dtype == torch.float16:
-            return self._train_batch_host_f16(Z_host, d, **kw)
-        if self.device.type != "cuda":
-            self.train_batch(Z_host.clone(), d, **kw)
-            return self._read_stats_host()
+    def _stage_slot(self, host: torch.Tensor):
+        """Async H2D copy of a pinned host slot into one of two alternating device buffers.  The copy waits only for
+        the step that last read THAT buffer (two steps ago), so the copy of batch t + 1 overlaps the compute of
+        batch t.  Returns (buffer index, device tensor); call `_stage_done(i)` after enqueueing the step."""
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=self.device)
         i = self._stage_i
         self._stage_i ^= 1
         cur = torch.cuda.current_stream(self.device)
-        if self._stage[i] is None or self._stage[i].shape != Z_host.shape or self._stage[i].dtype != torch.float32:
-            self._stage[i] = torch.empty(Z_host.shape, dtype=torch.float32, device=self.device)
-        self._copy_stream.wait_stream(cur)      # the compute that last used this buffer is ordered before
+        if self._stage[i] is None or self._stage[i].shape != host.shape or self._stage[i].dtype != host.dtype:
+            self._stage[i] = torch.empty(host.shape, dtype=host.dtype, device=self.device)
+            self._stage_evt[i] = None
+            self._copy_stream.wait_stream(cur)
+        if self._stage_evt[i] is not None:
+            self._copy_stream.wait_event(self._stage_evt[i])
         with torch.cuda.stream(self._copy_stream):
-            self._stage[i].copy_(Z_host, non_blocking=True)
+            self._stage[i].copy_(host, non_blocking=True)
             self.last_copy_event = torch.cuda.Event()
             self.last_copy_event.record(self._copy_stream)
-        cur.wait_stream(self._copy_stream)
-        self.train_batch(self._stage[i], d, **kw)
+        cur.wait_event(self.last_copy_event)
+        return i, self._stage[i]
+
+    def _stage_done(self, i: int) -> None:
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._stage_evt[i] = ev
+
+    def train_batch_host(self, Z_host: torch.Tensor, d: int, wire: Optional[str] = None, **kw) -> torch.Tensor:
+        """One e2e step from a pinned host slot.  Returns a pinned fp64[4] tensor that will hold
+        (loss_sum, aux, fitted, extra) of the first pipeline once the current stream has drained.
+        `wire` names the slot's row format ("f32" staged rows, "f16" compact wire rows, "f16s" fp16 staged rows; see
+        stream.ring.Topic); it is inferred from dtype and pitch when it is not given."""
+        if Z_host.dtype == torch.float16:
+            if wire is None:
+                compact, staged = Z_host.shape[1] == F.wire_f16_pitch(d), Z_host.shape[1] == F.f16s_pitch(d)
+                if compact and staged:
+                    raise ValueError(f"for d = {d} the compact and the staged fp16 formats have the same pitch: pass wire=")
+                wire = "f16s" if staged else "f16"
+            if wire == "f16":
+                return self._train_batch_host_f16(Z_host, d, **kw)
+        if self.device.type != "cuda":
+            self.train_batch(Z_host.clone(), d, **kw)
+            return self._read_stats_host()
+        i, Zd = self._stage_slot(Z_host)
+        self.train_batch(Zd, d, **kw)
+        self._stage_done(i)
         return self._read_stats_host()
 
     def _train_batch_host_f16(self, W_host: torch.Tensor, d: int, **kw) -> torch.Tensor:
@@ -388,24 +433,13 @@ class Engine:
         if self.device.type != "cuda":
             self.train_batch(F.stage_rows_f16(W_host, d), d, **kw)
             return self._read_stats_host()
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        i = self._stage_i
-        self._stage_i ^= 1
-        cur = torch.cuda.current_stream(self.device)
-        if self._stage[i] is None or self._stage[i].shape != W_host.shape or self._stage[i].dtype != torch.float16:
-            self._stage[i] = torch.empty(W_host.shape, dtype=torch.float16, device=self.device)
+        i, Wd = self._stage_slot(W_host)
         B, ld = W_host.shape[0], F.pad32(d + 2)
         if self._wire_dense[i] is None or self._wire_dense[i].shape != (B, ld):
             self._wire_dense[i] = torch.empty(B, ld, dtype=torch.float32, device=self.device)
-        self._copy_stream.wait_stream(cur)      # the expansion that last read this buffer is ordered before
-        with torch.cuda.stream(self._copy_stream):
-            self._stage[i].copy_(W_host, non_blocking=True)
-            self.last_copy_event = torch.cuda.Event()
-            self.last_copy_event.record(self._copy_stream)
-        cur.wait_stream(self._copy_stream)
-        F.stage_rows_f16(self._stage[i], d, out=self._wire_dense[i])
+        F.stage_rows_f16(Wd, d, out=self._wire_dense[i])
         self.train_batch(self._wire_dense[i], d, **kw)
+        self._stage_done(i)
         return self._read_stats_host()
 
     # ---- sparse streams (BASELINE config 5: "100k-dim sparse-to-dense stream") ---------------------
@@ -451,20 +485,9 @@ class Engine:
         if self.device.type != "cuda":
             self.train_sparse(slot_host.clone(), batch, nnz, d)
             return self._read_stats_host()
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        i = self._stage_i
-        self._stage_i ^= 1
-        cur = torch.cuda.current_stream(self.device)
-        if self._stage[i] is None or self._stage[i].shape != slot_host.shape or self._stage[i].dtype != slot_host.dtype:
-            self._stage[i] = torch.empty(slot_host.shape, dtype=slot_host.dtype, device=self.device)
-        self._copy_stream.wait_stream(cur)
-        with torch.cuda.stream(self._copy_stream):
-            self._stage[i].copy_(slot_host, non_blocking=True)
-            self.last_copy_event = torch.cuda.Event()
-            self.last_copy_event.record(self._copy_stream)
-        cur.wait_stream(self._copy_stream)
-        self.train_sparse(self._stage[i], batch, nnz, d)
+        i, slot = self._stage_slot(slot_host)
+        self.train_sparse(slot, batch, nnz, d)
+        self._stage_done(i)
         return self._read_stats_host()
 
     def _read_stats_host(self) -> torch.Tensor:

@@ -194,11 +194,17 @@ class GpuSVM(GpuLinear):
 
 # ====================================================================================== ORR
 class GpuORR(GpuLearner):
-    """Online ridge regression on the augmented Gram matrix G = sum [x,1,y]^T [x,1,y].
+    """Online ridge regression on the augmented Gram matrix G = sum z^T z.
 
-    One tcgen05 GEMM per mini-batch (csrc/umma_gemm.cu, MN-major operands straight from the staged
-    rows, upper-triangular tiles only, split-K with red.add epilogue).  A - lambda I, b and y^T y
-    are all blocks of G, so replicas merge by addition.
+    Two data paths, one state.  fp16 staged rows z = [x, 1, y_hi, y_lo] go through the CTA-pair tcgen05 kernel
+    (csrc/gram_f16.cu) exactly as they arrive from the host; fp32 staged rows z = [x, 1, y] through the tf32 GEMM
+    (csrc/umma_gemm.cu).  G is (d + 3) x (d + 3) with pitch ldg = pad64(d + 3): the y_lo row / column is zero on the
+    fp32 path and folded into the y row / column before any solve, so both paths (and a mix) give the same system.
+    A - lambda I, b and y^T y are all blocks of G, so replicas merge by addition.
+
+    The weights are refreshed every `solveEvery` mini-batches on a side stream by warm-started conjugate gradients
+    (csrc/ridge_cg.cu); a refresh that misses its tolerance, and every query, uses the blocked Cholesky of
+    csrc/ridge_chol.cu.  No library solver on this path.
     """
     name, task, merge_mode = "ORR", "regression", "sum"
 
@@ -216,9 +222,9 @@ class GpuORR(GpuLearner):
         self._pending = None
         self._install_at = 0
         self._w_next = None
-        # weight refresh: "cholesky" (cuSOLVER, ~0.6 ms at d = 1000) or "cg" (warm-started preconditioned
-        # conjugate gradients, csrc/ridge_cg.cu; falls back to Cholesky when it does not converge)
-        self.solver = str(_h(hyper, ["solver"], "cholesky")).lower()
+        # weight refresh: "cg" (warm-started preconditioned conjugate gradients, csrc/ridge_cg.cu, Cholesky when it does
+        # not converge) or "cholesky" (csrc/ridge_chol.cu every time)
+        self.solver = str(_h(hyper, ["solver"], "cg")).lower()
         self.cg_iters = int(_h(hyper, ["cgMaxIter"], 32))
         self.cg_tol = float(_h(hyper, ["cgTol"], 1e-5))
         self.cg_failures = 0
@@ -227,30 +233,36 @@ class GpuORR(GpuLearner):
         self._cg_host = None
         self._cg_evt = None
         self._scatter = None
+        self._hub = None                 # ShardedGramDriver when the hub is sharded over the GPUs
+        self._gram_scratch = None
+        self._chol_info = None
+        # "tf32x3": error-compensated Gram on the fp32 path (hi / lo split of the rows, 3 tensor-core passes)
+        self.precision = str(_h(hyper, ["precision"], "default")).lower()
 
     def n_flat(self, d):
-        ld = F.pad32(d + 2)
+        ld = F.pad64(d + 3)
         return ld * ld
 
     def _init(self):
-        ld = self.ld
+        self.ldg = ld = F.pad64(self.d + 3)
         self.dG = self.buf.view(ld, ld)
         self.G = self.e.view(ld, ld)
-        self.wt = torch.zeros(self.d + 2, device=self.device)   # [w, b, -1]
-        self.wt[self.d + 1] = -1.0
+        self.wt = torch.zeros(self.d + 3, device=self.device)   # [w, b, -1, -1]
+        self.wt[self.d + 1:] = -1.0
         self._work = torch.empty(ld, ld, device=self.device)
+        self._chol_info = torch.zeros(2, device=self.device)
         n = self.d + 2
         tiles = sum(1 for mi in range((n + 127) // 128) for nj in range((n + 255) // 256)
                     if not (128 * mi > 256 * nj + 255))
         self.ksplit = max(1, 148 // max(tiles, 1))
         if self.device.type == "cuda":
-            # create the cuSOLVER handle / workspaces now, not inside somebody's timed region
+            self._gram_scratch = F.gram_f16_scratch(self.device)
             self._side = torch.cuda.Stream(device=self.device)
             self._fork = torch.cuda.Stream(device=self.device)
             self._w_next = torch.zeros(self.d + 1, device=self.device)
-            # Run the real refresh path once on both streams now (G = 0, so A = lambda I): creates the
-            # cuSOLVER / cuBLAS handles, workspaces, stream-private allocator blocks and lazily loaded
-            # kernels here instead of inside somebody's timed region (the first refresh costs 10-20 ms).
+            # Run the real refresh path once on both streams now (G = 0, so A = lambda I): lazily loaded kernels,
+            # workspaces and stream-private allocator blocks are created here instead of inside somebody's timed
+            # region.  Not a collective (the sharded hub is attached after bind()).
             lam0, self.lam = self.lam, max(self.lam, 1.0)     # keep the warm-up system non-singular
             self.solve()
             self.solve_async()
@@ -259,22 +271,54 @@ class GpuORR(GpuLearner):
             self.wt[: self.d + 1].zero_()
             self._since = 0
             self.solves = 0
+            self.cg_failures = 0
             torch.cuda.synchronize(self.device)
 
+    # ---- synchronisation variants ---------------------------------------------------------------------
     def use_scatter_gemm(self, driver) -> None:
-        """`syncFusion: "gemm"`: the Gram update reduces straight into the shard owners' rotating copies
+        """`syncFusion: "gemm"`: the tf32 Gram update reduces straight into the shard owners' rotating copies
         (ops.gemm.gemm_outer_scatter) instead of the local delta."""
         k = driver.k
-        if self.ld % k or (self.ld // k) % 32:
-            raise ValueError(f"syncFusion=gemm needs ld / world to be a multiple of 32 (ld = {self.ld}, world = {k})")
+        if self.ldg % k or (self.ldg // k) % 32:
+            raise ValueError(f"syncFusion=gemm needs ld / world to be a multiple of 32 (ld = {self.ldg}, world = {k})")
         self._scatter = driver
 
+    def use_sharded_hub(self, driver) -> None:
+        """`syncFusion: "hub"` (parallel/fused.py::ShardedGramDriver): `G` is this GPU's hub matrix, `dG` the delta of
+        the step in flight, which the Gram kernel itself delivers to the owners of its rows."""
+        self._hub = driver
+
     def _gram(self, Z, ks, n):
+        if Z.dtype == torch.float16:
+            hub = self._hub
+            if hub is not None and Z.is_cuda:
+                F.gram_f16(Z, self.d + 3, self.dG, scratch=hub.scratch, peers=hub.peers)
+            else:
+                F.gram_f16(Z, self.d + 3, self.dG, scratch=self._gram_scratch)
+                if hub is not None:
+                    hub.push_delta(self.dG)
+            return
         if self._scatter is not None and Z.is_cuda:
-            F.gemm_outer_scatter(Z, Z, self._scatter.peer_copy_ptrs(), self.ld // self._scatter.k, self.ld,
+            F.gemm_outer_scatter(Z, Z, self._scatter.peer_copy_ptrs(), self.ldg // self._scatter.k, self.ldg,
                                  ksplit=ks, upper_only=True, m=n, n=n)
+            return
+        if self.precision == "tf32x3" and F.native(Z):
+            # error-compensated products: z = hi + lo with hi = tf32(z); hi^T hi + hi^T lo + lo^T hi (upper part,
+            # so the third product lands in the transposed position and is mirrored by the solve)
+            hi, lo = F.split_tf32(Z)
+            F.gemm_outer(hi, hi, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+            F.gemm_outer(hi, lo, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+            F.gemm_outer(lo, hi, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
         else:
             F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
+        if self._hub is not None:
+            self._hub.push_delta(self.dG)
+
+    def _loss(self, Z):
+        if Z.dtype == torch.float16:
+            F.sq_residual_f16s(Z, self.d, self.wt, self.stats, like_gram=self.overlap)
+        else:
+            F.sq_residual(Z, self.d, self.wt[: self.d + 2], self.stats)   # prequential squared error with current w
 
     def fit_batch(self, Z):
         n = self.d + 2
@@ -286,11 +330,14 @@ class GpuORR(GpuLearner):
             self._fork.wait_stream(main)
             self._gram(Z, ks, n)
             with torch.cuda.stream(self._fork):
-                F.sq_residual(Z, self.d, self.wt, self.stats)
+                self._loss(Z)
             main.wait_stream(self._fork)
             return
-        F.sq_residual(Z, self.d, self.wt, self.stats)    # prequential squared error with current w
+        self._loss(Z)
         self._gram(Z, ks, n)
+
+    def supports_f16(self) -> bool:
+        return True
 
     def host_tick(self):
         self._since += 1
@@ -308,7 +355,7 @@ class GpuORR(GpuLearner):
     # ---- pipelined synchronisation (parallel/fused.py::PipelinedSynchronousDriver) -----------------
     def use_delta_buffers(self, bufs, drain) -> None:
         """Two symmetric delta buffers: updates go to the current one while the other is all-reduced."""
-        ld = self.ld
+        ld = self.ldg
         self._deltas = [b.view(ld, ld) for b in bufs]
         self._drain = drain
         self.dG = self._deltas[0]
@@ -317,7 +364,12 @@ class GpuORR(GpuLearner):
         self.dG = self._deltas[i]
 
     def _snapshot(self) -> None:
-        """_work <- G + (all deltas); must run on the stream that orders the Gram / sync kernels."""
+        """_work <- global statistics as this rank knows them; must run on the stream that orders the Gram / sync
+        kernels.  With the sharded hub this is the collective pull of the other owners' rows."""
+        if self._hub is not None:
+            self._hub.gather()
+            self._work.copy_(self.G)
+            return
         if self._deltas is not None:
             self._drain()                       # in-flight all-reduces update G and clear their delta
             torch.add(self.G, self._deltas[0], out=self._work)
@@ -325,11 +377,21 @@ class GpuORR(GpuLearner):
             return
         torch.add(self.G, self.dG, out=self._work)
 
+    def _complete(self) -> None:
+        """Upper blocks -> full symmetric matrix, then y_lo folded into y (row / column d + 2 into d + 1)."""
+        d = self.d
+        F.mirror_upper(self._work, d + 3)
+        W = self._work
+        W[: d + 3, d + 1] += W[: d + 3, d + 2]
+        W[d + 1, : d + 3] += W[d + 2, : d + 3]
+        W[: d + 3, d + 2] = 0
+        W[d + 2, : d + 3] = 0
+
     def _solve_into(self, out: torch.Tensor, use_cg: bool = False) -> None:
-        """out <- (G_A + lambda I)^-1 G_b from the mirrored upper triangle of _work: Cholesky, or CG started
-        from the current weights."""
+        """out <- (G_A + lambda I)^-1 G_b from the completed _work: CG started from the current weights, or the
+        blocked Cholesky kernel (which destroys _work)."""
         d1 = self.d + 1
-        F.mirror_upper(self._work, self.d + 2)
+        self._complete()
         if use_cg:
             if self._cg is None:
                 self._cg = F.ridge_cg_workspace(d1, self.device, self.cg_iters)
@@ -337,15 +399,11 @@ class GpuORR(GpuLearner):
                 out.copy_(self.wt[:d1])
             F.ridge_cg(self._work, d1, self.lam, out, *self._cg, max_iter=self.cg_iters, tol=self.cg_tol)
             return
-        A = self._work[:d1, :d1].clone()
-        A.diagonal().add_(self.lam)
-        b = self._work[:d1, d1].clone()
-        L, _ = torch.linalg.cholesky_ex(A, check_errors=False)
-        out.copy_(torch.cholesky_solve(b[:, None], L)[:, 0])
+        F.ridge_chol(self._work, d1, self.lam, out, self._chol_info)
 
     def solve_async(self):
-        """Refresh w on a side stream so the ~0.6 ms latency-bound factorisation overlaps the next
-        mini-batches; the result is installed a few steps later (`_install_at`)."""
+        """Refresh w on a side stream so the refresh overlaps the next mini-batches; the result is installed a few
+        steps later (`_install_at`)."""
         if self._pending is not None:
             self._install()
         use_cg = self.solver == "cg"
@@ -383,21 +441,26 @@ class GpuORR(GpuLearner):
         self._pending = None
 
     def solve(self):
-        """Synchronous refresh (queries, checkpoints, CPU)."""
+        """Synchronous refresh (queries, checkpoints, CPU).  Collective with the sharded hub."""
         if self._pending is not None:
             self._install()
         d1 = self.d + 1
         self._snapshot()
+        ok = False
         if self.solver == "cg":
             self._solve_into(self.wt[:d1], True)
             it, rel = self._cg[2].tolist()
             self.cg_last = (int(it), rel)
-            if not rel <= 100.0 * self.cg_tol:            # did not converge (or NaN): direct solve instead
+            ok = rel <= 100.0 * self.cg_tol and bool(torch.isfinite(self.wt).all())
+            if not ok:                                    # did not converge (or NaN): direct solve instead
                 self.cg_failures += 1
-                self._solve_into(self.wt[:d1])
-        else:
-            self._solve_into(self.wt[:d1])
-        if not bool(torch.isfinite(self.wt).all()):      # ill-conditioned in fp32: redo in fp64
+        if not ok:
+            w = torch.empty(d1, device=self.device)
+            self._solve_into(w, False)                    # _work was only read by CG: complete() is idempotent
+            self.wt[:d1].copy_(w)
+            ok = float(self._chol_info[0]) == 0.0 and bool(torch.isfinite(self.wt).all())
+        if not ok:                                        # not positive definite in fp32: redo in fp64
+            self._snapshot_local_again()
             A = self._work[:d1, :d1].double()
             A.diagonal().add_(self.lam)
             try:
@@ -407,11 +470,23 @@ class GpuORR(GpuLearner):
         self._since = 0
         self.solves += 1
 
+    def _snapshot_local_again(self) -> None:
+        """Rebuild the completed _work after the Cholesky kernel destroyed it, WITHOUT another collective."""
+        if self._hub is not None:
+            self._work.copy_(self.G)
+        elif self._deltas is not None:
+            torch.add(self.G, self._deltas[0], out=self._work)
+            self._work.add_(self._deltas[1])
+        else:
+            torch.add(self.G, self.dG, out=self._work)
+        self._complete()
+
     def predict(self, Z):
         return Z[:, : self.d + 1] @ self.wt[: self.d + 1]
 
     def to_oracle(self):
         self.solve()
+        self._snapshot_local_again()
         o = O.ORR(self.hyper)
         o.ensure_init(self.d)
         n = self.d + 2
@@ -436,6 +511,10 @@ class GpuORR(GpuLearner):
             sd = super().state_dict()
             sd["buf"] = (self._deltas[0] + self._deltas[1]).reshape(-1).detach().cpu().clone()
             return sd
+        if self._hub is not None:               # every rank saves the gathered global statistics, the delta is empty
+            self._hub.gather()
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
         return super().state_dict()
 
     def load_state_dict(self, sd):

@@ -77,8 +77,20 @@ class GpuPipeline:
         n = lrn.n_flat(d)
         single = self.protocol == "SingleLearner"
         world = 1 if single else self.world
-        from ..parallel.fused import wants_scatter
+        from ..parallel.fused import ShardedGramDriver, wants_scatter, wants_sharded_hub
         scatter_delta = None
+        if (wants_sharded_hub(self.protocol, lrn.merge_mode, self.request.trainingConfiguration, world, self.impl,
+                              self.device.type) and hasattr(lrn, "use_sharded_hub")):
+            # hub sharded over the GPUs, push inside the producing kernel (ShardedGramDriver): buf = delta of the step
+            # in flight, hub = this GPU's accumulation matrix (authoritative for its own rows)
+            self.comm = PipelineComm(n, self.device, self.rank, world, self.group, emulate=1, with_hub=True)
+            lrn.bind(d, self.comm.buf, self.comm.hub)
+            self.driver = ShardedGramDriver(self.comm, self.comm.hub, lrn.merge_mode, self.request.trainingConfiguration,
+                                            self.impl, self.group, self.max_msg_params, ld=lrn.ldg, n=d + 3)
+            self.driver.counters.protocol = self.protocol
+            lrn.use_sharded_hub(self.driver)
+            self._warm_start(None)
+            return
         if wants_scatter(self.protocol, lrn.merge_mode, self.request.trainingConfiguration, world, self.impl) \
                 and lrn.needs_e() and n % 4 == 0:
             # reduce-scatter moved into the producer: the learner keeps a private delta, the symmetric region holds
@@ -103,6 +115,10 @@ class GpuPipeline:
         if hasattr(self.driver, "on_switch"):
             lrn.use_delta_buffers(self.driver.bufs, self.driver.drain)
             self.driver.on_switch = lrn.switch_delta
+        self._warm_start(e)
+
+    def _warm_start(self, e) -> None:
+        lrn = self.learner
         init = self.request.learner.parameters
         if init and init.get("a") is not None:       # warm start from a serialized model
             o = lrn.to_oracle()
@@ -125,6 +141,12 @@ class GpuPipeline:
         due = self.driver._batches % self.driver.sync_every == self.driver.sync_every - 1
         self.device_train(Z, protect_input, due, **kw)
         self.host_tick()
+
+    def f16_capable(self) -> bool:
+        """Can train straight from fp16 staged rows (no expansion to fp32): no preprocessors, a learner with an fp16
+        path."""
+        return (not self.preprocessors and self.protocol != "SingleLearner"
+                and getattr(self.learner, "supports_f16", lambda: False)())
 
     def sparse_capable(self) -> bool:
         """Can train straight from sparse rows (Engine.train_sparse with `sparseDirect`)."""

@@ -132,12 +132,12 @@ _HOLDOUT_IDX: dict = {}
 
 
 def holdout_swap_dev(Z: torch.Tensor, ring: torch.Tensor, d: int, count_dev: torch.Tensor) -> None:
-    """Graph-replayable holdout: the record count is an int64 device scalar, advanced here."""
+    """Graph-replayable holdout: `count_dev` = int64[2] on the device, [0] the running record count (advanced by the
+    kernel itself), [1] the kernel's arrival counter."""
     B, ld = Z.shape
     cap = ring.shape[0]
     _lib.check(_k().omldm_holdout_swap_dev(_p(Z), _i(ld), _i(B), _i(d), _p(ring), _i(cap), _p(count_dev),
                                            _lib.stream_ptr()), "holdout_swap_dev")
-    _lib.check(_k().omldm_advance_count(_p(count_dev), ctypes.c_longlong(B), _lib.stream_ptr()), "advance_count")
 
 
 def stage_rows(raw: torch.Tensor, d: int, ld: Optional[int] = None) -> torch.Tensor:
@@ -232,11 +232,14 @@ def expand_rows_f16s(Zh: torch.Tensor, d: int, ld: Optional[int] = None, out: Op
     return Z
 
 
-def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor) -> None:
-    """stats[0] += sum over valid rows of (w.x + b - y)^2, stats[2] += #valid; wt = [w, b, -1, -1] (d + 3 floats)."""
+def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor, like_gram: bool = False) -> None:
+    """stats[0] += sum over valid rows of (w.x + b - y)^2, stats[2] += #valid; wt = [w, b, -1, -1] (d + 3 floats).
+    `like_gram`: walk the rows in the order of the concurrent fp16 Gram kernel (its batch-axis splits side by side)."""
     if native(Zh):
+        rpr = int(_k().omldm_gram_f16_rows_per_split(_i(Zh.shape[0]), _i(d + 3), _i(0))) \
+            if (like_gram and not _lib._emulated) else 0
         _lib.check(_k().omldm_sq_residual_f16s(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(d), _p(wt), _p(stats),
-                                               _lib.stream_ptr()), "sq_residual_f16s")
+                                               _i(rpr), _lib.stream_ptr()), "sq_residual_f16s")
         return
     valid = Zh[:, d] != 0
     r = Zh[:, : d + 3].float() @ wt[: d + 3]
@@ -261,6 +264,11 @@ def gram_f16(Zh: torch.Tensor, n: int, C: torch.Tensor, scratch: Optional[torch.
         _lib.check(_k().omldm_gram_f16(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(n), _p(C), _i(C.stride(0)),
                                        ctypes.byref(peers) if peers is not None else None, _p(scratch), _i(ksplit),
                                        _lib.stream_ptr()), "gram_f16")
+        return
+    if Zh.is_cuda:      # PyTorch baseline on the GPU: cuBLAS fp16 GEMM with fp32 output, whole matrix
+        X = Zh[:, :pad32(n)] if pad32(n) <= Zh.shape[1] else Zh
+        G = torch.mm(X.t(), X, out_dtype=torch.float32)
+        C[:n, :n] += G[:n, :n]
         return
     X = Zh[:, :n].float()
     G = X.t() @ X
@@ -509,6 +517,14 @@ def sq_residual(Z: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor) 
     stats[2] += valid.sum()
 
 
+def split_tf32(Z: torch.Tensor):
+    """z = hi + lo with hi = z truncated to tf32 (what the tensor core keeps of an fp32 operand) and lo the exact
+    remainder: hi^T hi + hi^T lo + lo^T hi recovers the fp32 product to ~2^-21 (error-compensated Gram, `precision:
+    "tf32x3"`)."""
+    hi = (Z.view(torch.int32) & -8192).view(torch.float32)
+    return hi, Z - hi
+
+
 def mirror_upper(A: torch.Tensor, n: int) -> None:
     if native(A):
         _lib.check(_k().omldm_mirror_upper(_p(A), _i(A.stride(0)), _i(n), _lib.stream_ptr()), "mirror_upper")
@@ -610,6 +626,28 @@ def ridge_cg(W: torch.Tensor, n: int, lam: float, x: torch.Tensor, work: torch.T
         rz = rz_new
         it += 1
     info[0], info[1] = float(it), (rr / bb) ** 0.5
+
+
+def ridge_chol(W: torch.Tensor, n: int, lam: float, x: torch.Tensor, info: Optional[torch.Tensor] = None,
+               blocks: int = 0) -> torch.Tensor:
+    """Solve (A + lam I) x = b directly: A = W[:n, :n] (symmetric, full storage), b = W[n, :n] (row n).  Blocked
+    Cholesky in one cooperative kernel (csrc/ridge_chol.cu); W is destroyed.  info[0] <- 1 if a pivot was not positive."""
+    if info is None:
+        info = torch.zeros(2, dtype=torch.float32, device=W.device)
+    if native(W):
+        _lib.check(_k().omldm_ridge_chol(_p(W), _i(W.stride(0)), _i(n), _f(lam), _p(x), _p(info), _i(blocks),
+                                         _lib.stream_ptr()), "ridge_chol")
+        return info
+    A = W[:n, :n].double().clone()
+    A.diagonal().add_(lam)
+    L, bad = torch.linalg.cholesky_ex(A)
+    if int(bad) != 0:
+        info[0] = 1.0
+        x[:n] = float("nan")
+        return info
+    x[:n] = torch.cholesky_solve(W[n, :n].double()[:, None], L)[:, 0].float()
+    info[0] = 0.0
+    return info
 
 
 # ------------------------------------------------------------------------------ k-means

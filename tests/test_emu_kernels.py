@@ -378,6 +378,50 @@ def test_ridge_cg_kernel(n, m, blocks):
     assert torch.allclose(x, x2, rtol=1e-3, atol=1e-4)
 
 
+@pytest.mark.parametrize("blocks", [1, 3])
+@pytest.mark.parametrize("n,m", [(1, 10), (5, 40), (32, 200), (33, 300), (97, 700), (130, 900)])
+def test_ridge_chol_kernel(n, m, blocks):
+    """Blocked Cholesky with the right-hand side carried as an extra row (csrc/ridge_chol.cu) against an fp64 solve."""
+    g = torch.Generator().manual_seed(n)
+    X = torch.randn(m, n, generator=g) * (1.0 + 3.0 * torch.rand(n, generator=g))
+    y = X @ torch.randn(n, generator=g) + 0.1 * torch.randn(m, generator=g)
+    ld = F.pad32(n + 2)
+    W = torch.zeros(ld, ld)
+    W[:n, :n] = X.t() @ X
+    W[:n, n] = W[n, :n] = X.t() @ y
+    W[n, n] = y @ y
+    ref = torch.linalg.solve(W[:n, :n].double() + 0.5 * torch.eye(n, dtype=torch.float64), W[:n, n].double()).float()
+    with F.use_impl("emu"):
+        x = torch.zeros(n)
+        info = F.ridge_chol(W.clone(), n, 0.5, x, blocks=blocks)
+        assert float(info[0]) == 0.0
+        assert torch.allclose(x, ref, rtol=2e-3, atol=2e-4), float((x - ref).abs().max())
+        Wbad = W.clone()
+        Wbad[n // 2, n // 2] = -5.0                       # not positive definite: reported, never a hang
+        info = F.ridge_chol(Wbad, n, 0.0, torch.zeros(n), blocks=blocks)
+        assert float(info[0]) == 1.0
+
+
+def test_f16s_row_kernels():
+    """expand_rows_f16s / sq_residual_f16s (csrc/rows_f16.cu) against their PyTorch restatements."""
+    for d, B in ((1, 3), (5, 7), (28, 100), (61, 33), (125, 64)):
+        raw = torch.randn(B, d + 1)
+        Zh = F.pack_f16s(raw, d)
+        Zh[::5] = 0                                       # empty rows
+        wt = torch.randn(d + 3)
+        wt[d + 1:] = -1.0
+        ref_Z = F.expand_rows_f16s(Zh, d)
+        st_ref = torch.zeros(4, dtype=torch.float64)
+        F.sq_residual_f16s(Zh, d, wt, st_ref)
+        with F.use_impl("emu"):
+            out = torch.full((B, F.pad32(d + 2)), float("nan"))
+            F.expand_rows_f16s(Zh, d, out=out)
+            assert torch.equal(out, ref_Z), (d, B)
+            st = torch.zeros(4, dtype=torch.float64)
+            F.sq_residual_f16s(Zh, d, wt, st)
+        assert st[2] == st_ref[2] and abs(float(st[0] - st_ref[0])) <= 1e-4 * max(1.0, float(st_ref[0]))
+
+
 # ---- engine-level: the Python glue of the kernel paths that normally only run on a GPU ---------------------------
 def _mk_engine(learner, tc=None, pre=None, extra=None, d=12):
     from omldm_b200.engine import Engine
@@ -454,7 +498,7 @@ def test_engine_multi_tenant_exact_and_device_count_holdout_on_emulated_kernels(
             for b in batches:
                 e.train_batch(b.clone(), d)
             out.append(([e.pipelines[i].learner.w.clone() for i in (1, 2, 3)], e.holdout.clone(), e.count,
-                        None if e._count_dev is None else int(e._count_dev.item())))
+                        None if e._count_dev is None else int(e._count_dev[0].item())))
     (wt, ht, ct, _), (we, he, ce, cdev) = out
     assert ct == ce == cdev == 4 * B and torch.equal(ht, he)
     for a, b in zip(wt, we):

@@ -114,3 +114,21 @@ def test_gram_f16_speed_report():
     flops = 2.0 * K * 10 * 256 * 256            # 10 upper 256 x 256 tiles
     print(f"\ngram_f16 K={K} d={d}: {us:.1f} us per call, {flops / us / 1e6:.0f} TFLOP/s executed")
     assert us > 0
+
+
+@pytest.mark.parametrize("B,d", [(4096, 1000), (300, 28), (5000, 253), (32768, 1000)])
+def test_loss_pass_in_gram_order_matches_reference(B, d):
+    """sq_residual_f16s with the rows walked in the order of the Gram kernel's batch-axis splits (the layout used when the
+    two run side by side) gives the same sums as the plain pass and as PyTorch."""
+    Zh = _rows(B, d, seed=B, empty_every=9)
+    wt = torch.randn(d + 3, device="cuda") * 0.1
+    wt[d + 1:] = -1.0
+    valid = Zh[:, d] != 0
+    r = (Zh[:, : d + 3].double() @ wt.double())[valid]
+    ref = float((r ** 2).sum())
+    for like_gram in (False, True):
+        st = torch.zeros(4, dtype=torch.float64, device="cuda")
+        F.sq_residual_f16s(Zh, d, wt, st, like_gram=like_gram)
+        torch.cuda.synchronize()
+        assert int(st[2]) == int(valid.sum())
+        assert abs(float(st[0]) - ref) <= 1e-5 * max(1.0, ref), (like_gram, float(st[0]), ref)

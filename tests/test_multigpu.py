@@ -19,5 +19,5 @@ def test_fused_protocols_over_nvlink_match_nccl():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(root, "scripts", "multigpu_check.py")]
-    p = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=420)
     assert "MULTIGPU_OK" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]

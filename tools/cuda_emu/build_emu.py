@@ -25,7 +25,7 @@ OUT = ROOT / "build" / "emu"
 # kernel files whose PTX lives behind ptx.cuh helpers that have a host meaning (sys-scope loads / stores / atomics
 # become host atomics); umma_gemm.cu (tcgen05 / TMA) is hardware only
 SOURCES = ["ingest.cu", "sparse_mcpa.cu", "cluster.cu", "linear_learners.cu", "preprocess.cu", "tree.cu",
-           "fused_pipeline.cu", "ridge_cg.cu", "sync.cu", "nn.cu"]
+           "fused_pipeline.cu", "ridge_cg.cu", "ridge_chol.cu", "rows_f16.cu", "sync.cu", "nn.cu"]
 
 _LAUNCH = re.compile(r"([A-Za-z_][\w:]*(?:<[^<>;(){}]*>)?)\s*<<<(.+?)>>>", re.S)
 _DYN_SMEM = re.compile(r"extern\s+__shared__\s+([\w:]+)\s+(\w+)\s*\[\s*\]\s*;")
