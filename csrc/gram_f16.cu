@@ -19,11 +19,13 @@
 //     accumulators live in TMEM (128 lanes x 256 columns per CTA); tcgen05.commit (multicast to both CTAs) frees the
 //     smem stages and publishes the accumulator.
 //   * epilogue: tcgen05.ld -> registers -> swizzled smem -> TMA reduce-add (fp32 adds at L2), upper 32 x 32 blocks only.
-//   * hub push (world > 1): the split-K partials are first reduced in the local L2-resident delta; the LAST CTA to
-//     finish a 128-row half tile moves it, 32 x 32 block by block, with TMA (load -> reduce-add into the owner GPU's
-//     shard over NVLink -> zero the local block), so every element crosses NVLink once.  When every half tile of
-//     the step has been pushed, the last pusher publishes the step number in all peers' signal pads
-//     (st.release.sys after __threadfence_system).  No CTA ever waits for another CTA or GPU.
+//   * hub push (world > 1): the split-K partials meet in this GPU's own L2-resident running sum; the LAST CTA to
+//     finish a 128-row half tile then copies the updated rows, 32 x 32 block by block, with TMA (load from L2 ->
+//     plain store over NVLink) into THIS worker's slot at the GPU that owns those rows.  Every slot has a single
+//     writer, so the transfer needs no remote atomics, no flags and no zeroing, every element crosses NVLink once,
+//     and the CTA only waits until the stores have read its shared memory.  The owners sum their slots when the
+//     workers pull the global statistics (csrc/sync.cu::sync_gram_gather_kernel).  No CTA ever waits for another
+//     CTA or GPU.
 #include <cuda_fp16.h>
 #include <cstring>
 #include "ptx.cuh"
@@ -40,11 +42,10 @@ constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int G_TMEM_COLS = 256;
 constexpr int G_ZERO_SLOT = 32;                   // epilogue slots 0..31 (4 KB each), slot 32 = zeros for the reset
-enum { GS_STEP = 0, GS_PUSHED = 1, GS_TILE0 = 8 }; // scratch words: step counter, pushers done, per half-tile arrivals
+enum { GS_TILE0 = 8 };                            // scratch words: per half-tile arrival counters from word 8 on
 
 struct GramPush {
-  CUtensorMap owner[16];     // every owner's full-size accumulation matrix (peer mapped), 32 x 32 fp32 boxes
-  uint32_t* pads[16];
+  CUtensorMap owner[16];     // this worker's slot matrix at every owner (peer mapped), 32 x 32 fp32 boxes
   int world, rank, rows_per_owner, enabled;
 };
 
@@ -186,10 +187,6 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       named_bar_sync(1, 128);
       if (*s_flag) {
         __threadfence();
-        float4* z4 = reinterpret_cast<float4*>(smem + G_ZERO_SLOT * 4096);
-        for (int i = threadIdx.x - 64; i < 256; i += 128) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        fence_proxy_async();
-        named_bar_sync(1, 128);
         if (r == 0 && row0 < n) {
           int nblk = 0;
           for (int c = 0; c < 8; ++c) {
@@ -209,23 +206,10 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
             for (int c = 0; c < 8; ++c) {
               const int col0 = n0 + c * 32;
               if (col0 >= n || col0 + 31 < row0) continue;
-              tma_reduce_add_2d(om, smem + (q * 8 + c) * 4096, col0, row0);       // to the owner's shard (NVLink)
-              tma_store_2d(&tmC, smem + G_ZERO_SLOT * 4096, col0, row0);          // local delta block back to zero
+              tma_store_2d(om, smem + (q * 8 + c) * 4096, col0, row0);    // into this worker's slot at the owner (NVLink)
             }
             tma_commit_group();
-            tma_wait_group0();
-          }
-          __threadfence_system();
-        }
-        named_bar_sync(1, 128);
-        if (threadIdx.x == 64) {
-          const uint32_t done = atomicAdd(scratch + GS_PUSHED, 1u);
-          if (done == gridDim.x - 1) {             // every half tile of this step has reached its owner
-            scratch[GS_PUSHED] = 0;
-            const uint32_t step = scratch[GS_STEP] + 1u;
-            scratch[GS_STEP] = step;
-            __threadfence_system();
-            for (int p = 0; p < push.world; ++p) st_release_sys(push.pads[p] + OMLDM_PAD_GSTEP + push.rank, step);
+            tma_wait_group_read0();                // the stores have read smem; their arrival is ordered by the kernel end
           }
         }
       }
@@ -300,10 +284,8 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
         static_cast<long long>(peers->rows_per_owner) * peers->world < n)
       return set_error_msg("gram_f16: rows_per_owner must be a multiple of 32 and cover n");
     push.world = peers->world; push.rank = peers->rank; push.rows_per_owner = peers->rows_per_owner; push.enabled = 1;
-    for (int p = 0; p < peers->world; ++p) {
+    for (int p = 0; p < peers->world; ++p)
       if (encode_g(&push.owner[p], peers->owner_base[p], n, n, ldc)) return -1;
-      push.pads[p] = peers->pads[p];
-    }
     for (int p = peers->world; p < 16; ++p) push.owner[p] = push.owner[0];
   }
   // split the batch axis so that the pairs fill the 74 SM pairs; at least 4 stages of work per CTA

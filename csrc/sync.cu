@@ -309,20 +309,20 @@ sync_scatter_gather_kernel(Comm c, float* e_base, size_t e_stride, size_t n, flo
 // ------------------------------------------------------------------------------------------
 // Sharded-hub Synchronous protocol for the ORR Gram statistics (additive; C1 of network/FlinkNetwork.scala:260-261 with
 // the hub->worker broadcast, :282-291, turned into a pull).  GPU p is the hub shard of rows [p * rpo, (p + 1) * rpo) of
-// the ld x ld Gram matrix and accumulates every worker's contribution there (hubs[p]).  Workers only need the global
-// statistics when they refresh their weights, so nothing is broadcast per step:
-//   push   : every step, each worker adds its delta rows into the owners' shards.  The fp16 Gram kernel does this in
-//            its own epilogue (gram_f16.cu); sync_gram_push_kernel is the same step for deltas produced by another
-//            kernel (the tf32 path).  Upper 32 x 32 blocks only; the local delta is cleared; when the whole delta has
-//            been delivered the step number is published in every pad (GSTEP words).  No waiting.
-//   gather : at a weight refresh / query.  Waits until every peer has delivered the same step, copies the other
-//            owners' shards into the non-owned rows of the local matrix, exit rendezvous (nobody starts the next push
-//            before everybody has read).  `step_ptr` = the worker's own step counter (scratch word 0 of the push).
+// the ld x ld Gram matrix.  hubs[p] holds k SLOT matrices (ld x ld each): slot r is written by worker r only and
+// carries worker r's running sum of those rows, so a push is a plain peer store - no remote atomics, no flags, and a
+// newer value simply replaces the older one.  Workers need the global statistics only when they refresh their
+// weights, so nothing is broadcast per step:
+//   push   : every step, each worker copies the rows its update touched (upper 32 x 32 blocks of its running sum)
+//            into its slot at the owners.  The fp16 Gram kernel does this in its own epilogue (gram_f16.cu);
+//            sync_gram_push_kernel is the same step for running sums maintained by another kernel (the tf32 path).
+//   gather : at a weight refresh / query.  Entry rendezvous (everybody's stores of the step have landed), every owner
+//            sums its k slots and stores the result into every worker's global matrix (bufs[p]), exit rendezvous.
 __global__ void __launch_bounds__(256)
-sync_gram_push_kernel(Comm c, float* delta_base, size_t delta_stride, int ld, int n, int rpo, uint32_t* step_ptr) {
+sync_gram_push_kernel(Comm c, const float* acc_base, size_t acc_stride, int ld, int n, int rpo) {
   const int me = my_rank(c);
-  uint32_t* loc = my_local(c);
-  float* delta = delta_base + delta_stride * (c.emulate > 1 ? me : 0);
+  const float* acc = acc_base + acc_stride * (c.emulate > 1 ? me : 0);
+  const size_t slot = static_cast<size_t>(me) * ld * ld;
   const int nb = (n + 31) / 32;                        // 32 x 32 blocks per dimension; block (bi, bj) kept if bj >= bi
   const int items = nb * nb * 32 * 8;                  // (block, row in block, float4 in row)
   for (int it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
@@ -331,45 +331,39 @@ sync_gram_push_kernel(Comm c, float* delta_base, size_t delta_stride, int ld, in
     if (bj < bi) continue;
     const int row = bi * 32 + r, col = bj * 32 + 4 * q;
     if (row >= n || col >= ld) continue;
-    float4* src = reinterpret_cast<float4*>(delta + static_cast<size_t>(row) * ld + col);
-    const float4 v = *src;
-    if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) {
-      red_add_sys_v4(c.hubs[row / rpo] + static_cast<size_t>(row) * ld + col, v);
-      *src = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  }
-  if (grid_done(loc + L_DONE4)) {                      // includes __threadfence_system(): the additions before the flag
-    uint32_t* sp = step_ptr + (c.emulate > 1 ? 16 * me : 0);
-    const uint32_t step = *reinterpret_cast<volatile uint32_t*>(sp) + 1u;
-    __syncthreads();
-    if (threadIdx.x == 0) *sp = step;
-    signal_all(c, me, OMLDM_PAD_GSTEP, step);
+    const size_t off = static_cast<size_t>(row) * ld + col;
+    st_peer_v4(reinterpret_cast<float4*>(c.hubs[row / rpo] + slot + off), *reinterpret_cast<const float4*>(acc + off));
   }
 }
 
 __global__ void __launch_bounds__(256)
-sync_gram_gather_kernel(Comm c, int ld, int n, int rpo, const uint32_t* step_ptr, uint32_t epoch_arg) {
+sync_gram_gather_kernel(Comm c, int ld, int n, int rpo, uint32_t epoch_arg) {
   const int me = my_rank(c);
   uint32_t* loc = my_local(c);
   const uint32_t epoch = resolve_seq(epoch_arg, loc + L_GEPOCH);
-  const uint32_t step = *reinterpret_cast<const volatile uint32_t*>(step_ptr + (c.emulate > 1 ? 16 * me : 0));
-  wait_all(c, me, OMLDM_PAD_GSTEP, step);              // every peer has delivered step `step` completely
-  float* mine = c.hubs[me];
+  if (blockIdx.x == 0) {
+    __threadfence_system();                            // this worker's pushes (earlier kernels on the stream) before its flag
+    signal_all(c, me, OMLDM_PAD_GENTRY, 2 * epoch + 1);
+  }
+  wait_all(c, me, OMLDM_PAD_GENTRY, 2 * epoch + 1);
+  const int lo = me * rpo, hi = min(n, lo + rpo);
   const int row4 = ld / 4;
-  const size_t total = static_cast<size_t>(n) * row4;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int row = static_cast<int>(i / row4), q = static_cast<int>(i % row4);
-    const int owner = row / rpo;
-    if (owner == me || 4 * q + 3 < (row & ~31)) continue;            // own rows are in place; left of the diagonal block
+  const size_t mat = static_cast<size_t>(ld) * ld;
+  const long long total = hi > lo ? static_cast<long long>(hi - lo) * row4 : 0;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int row = lo + static_cast<int>(i / row4), q = static_cast<int>(i % row4);
+    if (4 * q + 3 < (row & ~31)) continue;             // left of the diagonal block: never written
     const size_t off = static_cast<size_t>(row) * ld + 4 * q;
-    *reinterpret_cast<float4*>(mine + off) = ld_peer_v4(reinterpret_cast<const float4*>(c.hubs[owner] + off));
+    float4 acc = ld_peer_v4(reinterpret_cast<const float4*>(c.hubs[me] + off));
+    for (int r = 1; r < c.world; ++r) acc = f4_add(acc, ld_peer_v4(reinterpret_cast<const float4*>(c.hubs[me] + r * mat + off)));
+    for (int p = 0; p < c.world; ++p) st_peer_v4(reinterpret_cast<float4*>(c.bufs[p] + off), acc);
   }
-  if (grid_done(loc + L_DONE4)) {
+  if (grid_done(loc + L_DONE4)) {                      // includes __threadfence_system(): the rows before the flag
     if (threadIdx.x == 0) loc[L_GEPOCH] = epoch;
-    signal_all(c, me, OMLDM_PAD_GEXIT, epoch);
+    signal_all(c, me, OMLDM_PAD_GEXIT, 2 * epoch + 2);
   }
-  wait_all(c, me, OMLDM_PAD_GEXIT, epoch);
+  wait_all(c, me, OMLDM_PAD_GEXIT, 2 * epoch + 2);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -734,11 +728,11 @@ extern "C" int omldm_sync_scatter_gather(const omldm_comm* h, float* e_local, si
                      "sync_scatter_gather_kernel", c, e_local, n, n, scale, epoch, step);
 }
 
-// Sharded-hub Gram protocol.  hubs[p] = owner p's ld x ld accumulation matrix; rpo = rows per owner (multiple of 32).
-extern "C" int omldm_sync_gram_push(const omldm_comm* h, float* delta_local, int ld, int n, int rows_per_owner,
-                                    uint32_t* step_words, int blocks, void* stream) {
+// Sharded-hub Gram protocol.  hubs[p] = k slot matrices (ld x ld each) at owner p; rpo = rows per owner (multiple of 32).
+extern "C" int omldm_sync_gram_push(const omldm_comm* h, const float* acc_local, int ld, int n, int rows_per_owner,
+                                    int blocks, void* stream) {
   if (h->world < 1 || h->world > 16) return set_error_msg("comm: world must be in [1,16]");
-  if (!delta_local || !step_words) return set_error_msg("sync_gram_push: the delta and the step word are required");
+  if (!acc_local) return set_error_msg("sync_gram_push: the running sum is required");
   if ((ld & 3) || n > ld || rows_per_owner < 32 || (rows_per_owner & 31) ||
       static_cast<long long>(rows_per_owner) * h->world < n)
     return set_error_msg("sync_gram_push: ld % 4 == 0, n <= ld, rows_per_owner a multiple of 32 that covers n");
@@ -746,19 +740,18 @@ extern "C" int omldm_sync_gram_push(const omldm_comm* h, float* delta_local, int
   blocks = clamp_blocks(blocks, static_cast<size_t>(n) * ld / 2, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_gram_push_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream), "sync_gram_push_kernel",
-                     c, delta_local, static_cast<size_t>(ld) * ld, ld, n, rows_per_owner, step_words);
+                     c, acc_local, static_cast<size_t>(ld) * ld, ld, n, rows_per_owner);
 }
-extern "C" int omldm_sync_gram_gather(const omldm_comm* h, int ld, int n, int rows_per_owner, const uint32_t* step_words,
-                                      uint32_t epoch, int blocks, void* stream) {
+extern "C" int omldm_sync_gram_gather(const omldm_comm* h, int ld, int n, int rows_per_owner, uint32_t epoch, int blocks,
+                                      void* stream) {
   if (h->world < 1 || h->world > 16) return set_error_msg("comm: world must be in [1,16]");
-  if (!step_words) return set_error_msg("sync_gram_gather: the step word is required");
   if ((ld & 3) || n > ld || rows_per_owner < 32 || (rows_per_owner & 31))
     return set_error_msg("sync_gram_gather: ld % 4 == 0, n <= ld, rows_per_owner a multiple of 32");
   Comm c = to_comm(h);
-  blocks = clamp_blocks(blocks, static_cast<size_t>(n) * ld, h->emulate);
+  blocks = clamp_blocks(blocks, static_cast<size_t>(rows_per_owner) * ld, h->emulate);
   dim3 grid(blocks, h->emulate > 1 ? h->emulate : 1);
   return launch_coop(sync_gram_gather_kernel, grid, dim3(256), static_cast<cudaStream_t>(stream),
-                     "sync_gram_gather_kernel", c, ld, n, rows_per_owner, step_words, epoch);
+                     "sync_gram_gather_kernel", c, ld, n, rows_per_owner, epoch);
 }
 
 // n floats per rank and batch (multiple of 4); rank 0's symmetric buffer holds 2 * world * n floats; seq = 1, 2, ...

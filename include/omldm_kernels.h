@@ -43,17 +43,16 @@ int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb, float* C,
  * fp16 staged row, pitch `ld` halves (multiple of 64, 128-byte aligned base):
  *         [ x_0 .. x_{d-1} | 1.0 bias/valid (0 = empty row) | y_hi | y_lo | zero pad ],  target = y_hi + y_lo
  * n = d + 3 columns take part.  Only 32 x 32 blocks that touch the upper triangle are written.
- *   peers == NULL : the partial sums are reduce-added into C (n x n fp32, pitch ldc).
- *   peers != NULL : C is this GPU's delta (zero on entry, zero again on exit); every 128-row half tile is moved by
- *                   the last CTA that finishes it into the accumulation matrix of the GPU that owns those rows
- *                   (owner_base[row / rows_per_owner], same pitch ldc; TMA reduce-add over NVLink), and once the whole
- *                   step is delivered the step number (1, 2, ... kept in scratch) is stored with release semantics in
- *                   word OMLDM_PAD_GSTEP + rank of every pad.  Nothing waits for another GPU.
+ * The partial sums are reduce-added into C (n x n fp32, pitch ldc): this worker's running sum.
+ *   peers != NULL : additionally, the last CTA to finish a 128-row half tile copies the updated rows of C into this
+ *                   worker's slot at the GPU that owns those rows (owner_base[row / rows_per_owner] = base of the slot
+ *                   matrix, same pitch ldc; plain TMA stores over NVLink, single writer per slot: no remote atomics,
+ *                   no flags).  The copy is complete when the kernel is; owners sum their slots in
+ *                   omldm_sync_gram_gather.  Nothing waits for another GPU.
  * scratch: omldm_gram_f16_scratch_words() uint32 words, zero before the first call, private to one (C, peers) pair.
  * ksplit 0 = automatic (fills the 74 SM pairs). */
 typedef struct omldm_gram_peers {
-  float* owner_base[16];     /* every owner's accumulation matrix (peer mapped), pitch ldc floats */
-  uint32_t* pads[16];        /* every rank's signal pad */
+  float* owner_base[16];     /* this worker's slot matrix at every owner (peer mapped), pitch ldc floats */
   int world;
   int rank;
   int rows_per_owner;        /* multiple of 32; owner p holds rows [p * rows_per_owner, (p + 1) * rows_per_owner) */
@@ -233,7 +232,7 @@ enum {
   OMLDM_PAD_QENTRY = 256,  /* [256,272) entry arrivals of the query / termination barrier (own words and own
                               sequence counter: an FGM round or an all-reduce never shares a flag with a query) */
   OMLDM_PAD_QEXIT = 272,   /* [272,288) exit arrivals of the query / termination barrier */
-  OMLDM_PAD_GSTEP = 288,   /* [288,304) sharded-Gram protocol: last step each peer has pushed completely */
+  OMLDM_PAD_GSTEP = 288,   /* [288,304) reserved */
   OMLDM_PAD_GENTRY = 304,  /* [304,320) sharded-Gram gather: entry arrivals */
   OMLDM_PAD_GEXIT = 320,   /* [320,336) sharded-Gram gather: exit arrivals  */
   OMLDM_PAD_WORDS = 512
@@ -262,17 +261,17 @@ int omldm_sync_scatter_push(const omldm_comm* comm_host, float* delta_local, siz
 int omldm_sync_scatter_gather(const omldm_comm* comm_host, float* e_local, size_t n, float scale, uint32_t epoch,
                               uint32_t step, int blocks, void* stream);
 /* Sharded-hub Synchronous protocol for the ORR Gram statistics (worker -> hub push network/FlinkNetwork.scala:260-261;
- * the hub -> worker broadcast :282-291 becomes a pull at weight refreshes).  hubs[p] = GPU p's ld x ld accumulation
- * matrix, authoritative for rows [p * rows_per_owner, (p + 1) * rows_per_owner).
- * push  : adds the upper 32 x 32 blocks of the local delta (then cleared) into the owners' rows, then publishes the
- *         step number (step_words[0], advanced by the call) in every pad.  Never waits.  The fp16 Gram kernel
- *         (omldm_gram_f16 with peers) performs this step itself; use the same step words for both.
- * gather: waits until every peer has published the caller's own step, copies the other owners' rows (from their
- *         diagonal block rightwards) into the local matrix, exit rendezvous.  Collective, same step on all ranks. */
-int omldm_sync_gram_push(const omldm_comm* comm_host, float* delta_local, int ld, int n, int rows_per_owner,
-                         uint32_t* step_words, int blocks, void* stream);
-int omldm_sync_gram_gather(const omldm_comm* comm_host, int ld, int n, int rows_per_owner, const uint32_t* step_words,
-                           uint32_t epoch, int blocks, void* stream);
+ * the hub -> worker broadcast :282-291 becomes a pull at weight refreshes).  GPU p is the hub shard of rows
+ * [p * rows_per_owner, (p + 1) * rows_per_owner).  hubs[p] = k slot matrices (ld x ld each, slot r written by worker r
+ * only) holding every worker's RUNNING SUM of those rows; bufs[p] = worker p's copy of the global matrix.
+ * push  : copies the upper 32 x 32 blocks of the worker's running sum `acc_local` into its slot at every owner (plain
+ *         peer stores).  Never waits.  The fp16 Gram kernel (omldm_gram_f16 with peers) does this itself.
+ * gather: entry rendezvous (every worker's stores of the current step have landed), each owner sums its k slots and
+ *         stores the result into every worker's global matrix, exit rendezvous.  Collective. */
+int omldm_sync_gram_push(const omldm_comm* comm_host, const float* acc_local, int ld, int n, int rows_per_owner,
+                         int blocks, void* stream);
+int omldm_sync_gram_gather(const omldm_comm* comm_host, int ld, int n, int rows_per_owner, uint32_t epoch, int blocks,
+                           void* stream);
 /* SingleLearner forwarding (mlworkers.ForwardingWorker -> CentralizedMLServer, MLNodeGenerator.scala:27,56): every
  * rank stores its n-float mini-batch into rank 0's symmetric buffer (2 * world * n floats: slot seq & 1, position =
  * rank); rank 0 returns once all world batches of `seq` have arrived and trains on them.  seq = 1, 2, ... (same on

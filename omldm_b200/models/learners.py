@@ -284,8 +284,9 @@ class GpuORR(GpuLearner):
         self._scatter = driver
 
     def use_sharded_hub(self, driver) -> None:
-        """`syncFusion: "hub"` (parallel/fused.py::ShardedGramDriver): `G` is this GPU's hub matrix, `dG` the delta of
-        the step in flight, which the Gram kernel itself delivers to the owners of its rows."""
+        """`syncFusion: "hub"` (parallel/fused.py::ShardedGramDriver): `dG` is this worker's private running sum, whose
+        touched rows the Gram kernel itself copies into the worker's slots at the owners; `G` is the worker's copy of
+        the global statistics, valid after a `gather()`."""
         self._hub = driver
 
     def _gram(self, Z, ks, n):
@@ -296,7 +297,7 @@ class GpuORR(GpuLearner):
             else:
                 F.gram_f16(Z, self.d + 3, self.dG, scratch=self._gram_scratch)
                 if hub is not None:
-                    hub.push_delta(self.dG)
+                    hub.push()
             return
         if self._scatter is not None and Z.is_cuda:
             F.gemm_outer_scatter(Z, Z, self._scatter.peer_copy_ptrs(), self.ldg // self._scatter.k, self.ldg,
@@ -312,7 +313,7 @@ class GpuORR(GpuLearner):
         else:
             F.gemm_outer(Z, Z, self.dG, accumulate=True, ksplit=ks, upper_only=True, m=n, n=n)
         if self._hub is not None:
-            self._hub.push_delta(self.dG)
+            self._hub.push()
 
     def _loss(self, Z):
         if Z.dtype == torch.float16:
@@ -500,7 +501,13 @@ class GpuORR(GpuLearner):
         n = self.d + 2
         self.G.zero_()
         self.dG.zero_()
-        self.G[:n, :n] = torch.from_numpy(o.G.astype(np.float32)).to(self.device)
+        Gt = torch.from_numpy(o.G.astype(np.float32)).to(self.device)
+        if self._hub is not None:               # running sums add up to the global matrix: rank 0 carries the warm start
+            if self._hub.comm.rank == 0:
+                self.dG[:n, :n] = Gt
+            self._hub.push()
+        else:
+            self.G[:n, :n] = Gt
         self.solve()
 
     def state_dict(self):
@@ -511,7 +518,7 @@ class GpuORR(GpuLearner):
             sd = super().state_dict()
             sd["buf"] = (self._deltas[0] + self._deltas[1]).reshape(-1).detach().cpu().clone()
             return sd
-        if self._hub is not None:               # every rank saves the gathered global statistics, the delta is empty
+        if self._hub is not None:               # buf = this worker's running sum, e = the gathered global statistics
             self._hub.gather()
             if self.device.type == "cuda":
                 torch.cuda.synchronize(self.device)

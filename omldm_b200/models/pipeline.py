@@ -81,12 +81,16 @@ class GpuPipeline:
         scatter_delta = None
         if (wants_sharded_hub(self.protocol, lrn.merge_mode, self.request.trainingConfiguration, world, self.impl,
                               self.device.type) and hasattr(lrn, "use_sharded_hub")):
-            # hub sharded over the GPUs, push inside the producing kernel (ShardedGramDriver): buf = delta of the step
-            # in flight, hub = this GPU's accumulation matrix (authoritative for its own rows)
-            self.comm = PipelineComm(n, self.device, self.rank, world, self.group, emulate=1, with_hub=True)
-            lrn.bind(d, self.comm.buf, self.comm.hub)
-            self.driver = ShardedGramDriver(self.comm, self.comm.hub, lrn.merge_mode, self.request.trainingConfiguration,
-                                            self.impl, self.group, self.max_msg_params, ld=lrn.ldg, n=d + 3)
+            # hub sharded over the GPUs, push inside the producing kernel (ShardedGramDriver): buf = this worker's copy of
+            # the global statistics, hub = k slot matrices (every worker's running sum of the rows this GPU owns); the
+            # worker's own running sum is private to the driver
+            ld = int(round(n ** 0.5))                    # n_flat of these learners is ld * ld
+            nb, nh = ShardedGramDriver.region_floats(ld, world)
+            self.comm = PipelineComm(nb, self.device, self.rank, world, self.group, emulate=1, with_hub=True,
+                                     hub_floats=nh)
+            self.driver = ShardedGramDriver(self.comm, self.comm.buf, lrn.merge_mode, self.request.trainingConfiguration,
+                                            self.impl, self.group, self.max_msg_params, ld=ld, n=d + 3)
+            lrn.bind(d, self.driver.acc, self.comm.buf)
             self.driver.counters.protocol = self.protocol
             lrn.use_sharded_hub(self.driver)
             self._warm_start(None)

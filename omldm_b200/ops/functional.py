@@ -248,8 +248,8 @@ def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Te
 
 
 class GramPeers(ctypes.Structure):
-    _fields_ = [("owner_base", ctypes.c_void_p * 16), ("pads", ctypes.c_void_p * 16), ("world", ctypes.c_int),
-                ("rank", ctypes.c_int), ("rows_per_owner", ctypes.c_int)]
+    _fields_ = [("owner_base", ctypes.c_void_p * 16), ("world", ctypes.c_int), ("rank", ctypes.c_int),
+                ("rows_per_owner", ctypes.c_int)]
 
 
 def gram_f16_scratch(device) -> torch.Tensor:
@@ -259,7 +259,8 @@ def gram_f16_scratch(device) -> torch.Tensor:
 def gram_f16(Zh: torch.Tensor, n: int, C: torch.Tensor, scratch: Optional[torch.Tensor] = None,
              peers: Optional[GramPeers] = None, ksplit: int = 0) -> None:
     """C[:n, :n] (upper 32 x 32 blocks) += Zh[:, :n]^T Zh[:, :n] on the tcgen05 CTA-pair kernel (csrc/gram_f16.cu).
-    With `peers`, C is the local delta and the result is delivered to the owners' accumulation matrices."""
+    With `peers`, the updated rows of C (this worker's running sum) are also copied into the worker's slot at the GPU
+    that owns them."""
     if native(Zh, C):
         _lib.check(_k().omldm_gram_f16(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(n), _p(C), _i(C.stride(0)),
                                        ctypes.byref(peers) if peers is not None else None, _p(scratch), _i(ksplit),

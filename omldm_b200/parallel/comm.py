@@ -134,7 +134,7 @@ class PipelineComm:
     """pad | buf[n] | hub[n] for one pipeline, plus the pointer tables the kernels take."""
 
     def __init__(self, n_floats: int, device, rank: int = 0, world: int = 1, group=None, emulate: int = 1,
-                 with_hub: bool = True):
+                 with_hub: bool = True, hub_floats: Optional[int] = None):
         self.device = torch.device(device)
         self.rank, self.world, self.emulate = rank, world, emulate
         self.k = emulate if emulate > 1 else world
@@ -142,14 +142,16 @@ class PipelineComm:
         pad_bytes = _align(PAD_WORDS * 4)
         buf_bytes = _align(self.n * 4)
         self.with_hub = with_hub
-        nbytes = pad_bytes + buf_bytes * (2 if with_hub else 1)
+        self.hub_n = self.n if hub_floats is None else (hub_floats + 3) // 4 * 4     # the hub region may be larger
+        hub_bytes = _align(self.hub_n * 4)
+        nbytes = pad_bytes + buf_bytes + (hub_bytes if with_hub else 0)
         self.region = Region(nbytes, self.device, rank, world, group, emulate)
         self._off_buf, self._off_hub = pad_bytes, pad_bytes + buf_bytes
         nl = len(self.region.locals)
         self.pads = [self.region.locals[i][:PAD_WORDS * 4].view(torch.int32) for i in range(nl)]
         self.bufs = [self.region.locals[i][self._off_buf:self._off_buf + self.n * 4].view(torch.float32)
                      for i in range(nl)]
-        self.hubs = [self.region.locals[i][self._off_hub:self._off_hub + self.n * 4].view(torch.float32)
+        self.hubs = [self.region.locals[i][self._off_hub:self._off_hub + self.hub_n * 4].view(torch.float32)
                      for i in range(nl)] if with_hub else [None] * nl
         # private (non-symmetric) words
         self.local = torch.zeros(LOCAL_WORDS * max(self.k, 1), dtype=torch.int32, device=self.device)

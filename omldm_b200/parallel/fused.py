@@ -276,32 +276,39 @@ class ScatterSynchronousDriver(SyncDriver):
 
 class ShardedGramDriver(SyncDriver):
     """Synchronous protocol for the ORR Gram statistics with the hub SHARDED over the GPUs and the worker -> hub push
-    performed by the kernel that computes the update (csrc/gram_f16.cu; csrc/sync.cu::sync_gram_push_kernel for deltas
-    produced by the tf32 path).  GPU p accumulates rows [p * rpo, (p + 1) * rpo) of the global Gram matrix in its
-    `hub` buffer; `buf` is the local delta of the step in flight (zero between steps).  Workers need the global
-    statistics only when they refresh their weights (`solveEvery`) or answer a query, so the hub -> worker broadcast of
-    FlinkNetwork.scala:282-291 becomes a pull: `gather()` (one rendezvous, peer loads of the other owners' rows).
-    Per step nothing waits for another GPU.  Default for Synchronous ORR on the fused path (`syncFusion: "hub"`)."""
+    performed by the kernel that computes the update (csrc/gram_f16.cu; csrc/sync.cu::sync_gram_push_kernel for the
+    tf32 path).  Every worker keeps its own running sum `acc` (private) and, each step, copies the rows it touched into
+    ITS slot at the GPU that owns them (`hub` region = k slot matrices; single writer per slot, so plain stores over
+    NVLink: no remote atomics, no flags, nothing waits).  Workers need the global statistics only when they refresh
+    their weights (`solveEvery`) or answer a query, so the hub -> worker broadcast of FlinkNetwork.scala:282-291
+    becomes a pull: `gather()` - entry rendezvous, every owner sums its k slots and stores the result into every
+    worker's global matrix (`buf` region), exit rendezvous.  Default for Synchronous ORR on the fused path
+    (`syncFusion: "hub"`)."""
     protocol = "Synchronous"
+
+    @staticmethod
+    def region_floats(ld: int, k: int):
+        """(buf floats, hub floats) of the symmetric region: the global matrix and k slot matrices."""
+        return ld * ld, max(k, 1) * ld * ld
 
     def __init__(self, comm, e, merge_mode, tc, impl="fused", group=None, max_msg_params=2000, ld: int = 0, n: int = 0):
         super().__init__(comm, e, merge_mode, tc, impl, group, max_msg_params)
-        if self.mode != 1 or ld * ld != comm.n or not comm.with_hub:
-            raise ValueError("the sharded hub needs additive statistics and an ld x ld symmetric region with a hub buffer")
-        from ..ops.functional import GramPeers, gram_f16_scratch
         k = max(comm.k, 1)
+        if self.mode != 1 or ld * ld != comm.n or not comm.with_hub or comm.hub_n < k * ld * ld:
+            raise ValueError("the sharded hub needs additive statistics, an ld x ld global matrix and k slot matrices")
+        from ..ops.functional import GramPeers, gram_f16_scratch
         self.ld, self.n_rows = ld, n
         rpo = (ld // k) // 32 * 32
         while rpo * k < n:
             rpo += 32
         self.rows_per_owner = rpo
-        self.scratch = gram_f16_scratch(comm.device) if comm.emulate <= 1 else \
-            torch.zeros(16 * k, dtype=torch.int32, device=comm.device)
+        self.scratch = gram_f16_scratch(comm.device)
+        # this worker's running sum; under emulation one private matrix per emulated rank
+        self.acc = torch.zeros(max(comm.emulate, 1) * ld * ld, device=comm.device)
         self.peers = GramPeers()
         bases = comm.region.bases
         for p_ in range(k if comm.emulate <= 1 else 0):
-            self.peers.owner_base[p_] = int(bases[p_]) + comm._off_hub
-            self.peers.pads[p_] = int(bases[p_])
+            self.peers.owner_base[p_] = int(bases[p_]) + comm._off_hub + 4 * comm.rank * ld * ld
         self.peers.world, self.peers.rank, self.peers.rows_per_owner = k, comm.rank, rpo
         self.gathers = 0
 
@@ -311,26 +318,30 @@ class ShardedGramDriver(SyncDriver):
     def step(self) -> bool:
         return False                   # the push happened in the producer; derived state follows the learner's cadence
 
-    def push_delta(self, delta: torch.Tensor) -> None:
-        """Deliver a delta produced by another kernel (tf32 path) to the owners."""
+    def push(self) -> None:
+        """Copy the running sum's upper blocks into this worker's slots (for running sums kept by the tf32 path)."""
         c = self.comm
-        _lib.check(_lib.kernels().omldm_sync_gram_push(c.struct_ptr(), _lib.ptr(delta), _i(self.ld), _i(self.n_rows),
-                                                       _i(self.rows_per_owner), _lib.ptr(self.scratch), _i(self.blocks),
-                                                       _lib.stream_ptr()), "sync_gram_push")
+        _lib.check(_lib.kernels().omldm_sync_gram_push(c.struct_ptr(), _lib.ptr(self.acc), _i(self.ld), _i(self.n_rows),
+                                                       _i(self.rows_per_owner), _i(self.blocks), _lib.stream_ptr()),
+                   "sync_gram_push")
 
     def gather(self) -> None:
-        """Collective: after it, the local `hub` matrix holds every owner's rows (global statistics)."""
+        """Collective: after it, `comm.buf` holds the global statistics (the sum of every worker's running sum)."""
         c = self.comm
         self.gathers += 1
         _lib.check(_lib.kernels().omldm_sync_gram_gather(c.struct_ptr(), _i(self.ld), _i(self.n_rows),
-                                                         _i(self.rows_per_owner), _lib.ptr(self.scratch), _u(0),
-                                                         _i(self.blocks), _lib.stream_ptr()), "sync_gram_gather")
+                                                         _i(self.rows_per_owner), _u(0), _i(self.blocks),
+                                                         _lib.stream_ptr()), "sync_gram_gather")
+
+
+def hub_mode(tc) -> str:
+    return str(cfg(tc, ["syncFusion"], "hub")).lower()
 
 
 def wants_sharded_hub(protocol: str, merge_mode: str, tc, world: int, impl: str, device_type: str) -> bool:
     """`syncFusion: "hub"` (the default for additive learners that support it): Synchronous on more than one GPU."""
     return (protocol == "Synchronous" and merge_mode == "sum" and world > 1 and impl == "fused" and device_type == "cuda"
-            and str(cfg(tc, ["syncFusion"], "hub")).lower() == "hub"
+            and hub_mode(tc) == "hub"
             and int(cfg(tc, ["syncEvery", "syncPeriod"], 1)) == 1)
 
 

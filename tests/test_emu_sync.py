@@ -271,15 +271,17 @@ def test_scatter_push_gather_three_rotating_copies(k, blocks):
 @pytest.mark.parametrize("k,blocks,n", [(2, 1, 61), (4, 2, 100), (3, 1, 128)])
 def test_sharded_hub_push_and_gather(k, blocks, n):
     """Sharded-hub protocol of the ORR Gram statistics (sync_gram_push_kernel / sync_gram_gather_kernel, driver class
-    parallel/fused.py::ShardedGramDriver) with k emulated ranks: every rank adds its delta into the owners' rows without
-    waiting, the pull at a refresh waits for everybody's step flag and leaves the same global matrix (upper 32 x 32
-    blocks) on every rank; a query barrier and extra steps in between must not disturb the step flags."""
+    parallel/fused.py::ShardedGramDriver) with k emulated ranks: every rank copies its running sum into its own slot at
+    the owners without waiting; the pull at a refresh sums the slots at the owners and leaves the same global matrix
+    (upper 32 x 32 blocks) on every rank.  Several pushes between two pulls (newer values replace older ones) and a
+    query barrier in between must not disturb it."""
     from omldm_b200.parallel.fused import ShardedGramDriver
     ld = F.pad64(n)
-    comm = PipelineComm(ld * ld, DEV, 0, 1, None, emulate=k)
-    drv = ShardedGramDriver(comm, comm.hub, "sum", {"syncBlocks": blocks}, impl="fused", ld=ld, n=n)
+    nb, nh = ShardedGramDriver.region_floats(ld, k)
+    comm = PipelineComm(nb, DEV, 0, 1, None, emulate=k, hub_floats=nh)
+    drv = ShardedGramDriver(comm, comm.buf, "sum", {"syncBlocks": blocks}, impl="fused", ld=ld, n=n)
     assert drv.rows_per_owner % 32 == 0 and drv.rows_per_owner * k >= n
-    delta = torch.zeros(k, ld * ld)
+    acc = drv.acc.view(k, ld, ld)
     total = torch.zeros(ld, ld)
     g = torch.Generator().manual_seed(k + n)
     i = torch.arange(ld)
@@ -287,13 +289,12 @@ def test_sharded_hub_push_and_gather(k, blocks, n):
     for rnd in range(3):
         for step in range(1 + rnd):
             dlt = torch.randint(-3, 4, (k, ld, ld), generator=g).float() * keep        # integers: exact sums
-            delta.copy_(dlt.view(k, -1))
+            acc += dlt
             total += dlt.sum(0)
-            drv.push_delta(delta)
-            assert float(delta.abs().max()) == 0.0                                  # the push clears the local delta
+            drv.push()
         drv.gather()
         for r in range(k):
-            got = comm.hubs[r].view(ld, ld)
+            got = comm.bufs[r].view(ld, ld)
             assert torch.equal(got * keep, total), f"round {rnd}, rank {r}"
         if rnd == 1:
             _lib.check(K().omldm_device_barrier(comm.struct_ptr(), _u(0), sp()), "barrier")
