@@ -54,7 +54,7 @@ CONFIGS = {
     "kmeans": dict(model="K-means", d=128, batch=16384, protocol="SSP", kind=2, n_aux=256,
                    hyper={"k": 256}, tc={"staleness": 3}, pre=[],
                    name="Online k-means k=256 on 128-dim synthetic stream, SSP protocol"),
-    "mcpa": dict(model="MultiClassPA", d=100000, batch=256, protocol="Synchronous", kind=4, n_aux=10, nnz=128,
+    "mcpa": dict(model="MultiClassPA", d=100000, batch=16384, protocol="Synchronous", kind=4, n_aux=10, nnz=128,
                  hyper={"nClasses": 10, "C": 0.1}, tc={}, pre=[],
                  name="Multiclass PA 100k-dim sparse-to-dense stream, hub sharded over all GPUs"),
 }
@@ -281,7 +281,7 @@ def main() -> None:
             try:
                 if sparse:
                     topic = R.SparseTopic(d, B, nnz, n_slots=8)
-                    topic.start_synthetic(seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_GENERATE, n_threads=2)
+                    topic.start_synthetic(seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_REPLAY, n_threads=2)
                 else:
                     topic = R.Topic(d, B, n_slots=max(4, min(n_rot, 8)), wire=wire)
                     topic.start_synthetic(cfg["kind"], seed=99 + rank, n_aux=cfg["n_aux"], mode=R.MODE_REPLAY,
@@ -301,6 +301,25 @@ def main() -> None:
                 for _ in range(max(8, args.warmup)):   # includes graph capture for the two staging buffers
                     step_e2e()
                 eng.flush()
+                # the box's own ceiling for this path: every rank copies a pinned slot to its GPU at the same time,
+                # nothing else running (one cudaMemcpyAsync per slot, like the engine)
+                ceiling = None
+                if not dry:
+                    src, dst = topic.storage[0], torch.empty_like(topic.storage[0], device=dev)
+                    dst.copy_(src, non_blocking=True)
+                    sync_all()
+                    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    n_cp = max(10, int(1.5e9 // topic.slot_bytes))       # ~1.5 GB: long enough to measure bandwidth
+                    c0.record()
+                    for _ in range(n_cp):
+                        dst.copy_(src, non_blocking=True)
+                    c1.record()
+                    dev_sync()
+                    cms = torch.tensor([c0.elapsed_time(c1)], device=dev)
+                    if world > 1:
+                        dist.all_reduce(cms, op=dist.ReduceOp.MAX)
+                    ceiling = n_cp * topic.slot_bytes / (float(cms.item()) / 1e3) / 1e9
+                    del dst
                 e_windows = []
                 for _ in range(1 if dry else 5):
                     sync_all()
@@ -320,6 +339,10 @@ def main() -> None:
                               "wire": "sparse ELL (int32 index + fp32 value)" if sparse else wire,
                               "windows_s": [round(w, 5) for w in e_windows],
                               "h2d_gbs_per_gpu": h2d * args.steps / e_med / 1e9,
+                              "h2d_ceiling_gbs_per_gpu": ceiling,
+                              "fraction_of_h2d_ceiling": (h2d * args.steps / e_med / 1e9 / ceiling) if ceiling else None,
+                              "h2d_ceiling_note": "pinned -> device cudaMemcpyAsync of one slot, all ranks copying at "
+                                                  "once, nothing else running (max over ranks)",
                               "last_loss_sum": float(loss_host[0])}
                 topic.stop()
             except Exception as ex:      # the device-timed line above stays valid; report why e2e is missing
