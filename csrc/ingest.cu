@@ -88,6 +88,18 @@ holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restri
 
 __global__ void advance_count_kernel(long long* c, long long delta) { *c += delta; }
 
+// Learning curve of the test mode (operators/hub/FlinkHub.scala:101-113: the hub records (loss, #fitted) per
+// mini-batch): one sample of the learner's cumulative (loss sum, records fitted) per step into a device ring, so a
+// default run keeps its curve without any host synchronisation.  counter = samples written so far.
+__global__ void curve_sample_kernel(const double* __restrict__ stats, double* __restrict__ ring, int cap,
+                                    long long* __restrict__ counter) {
+  const long long i = *counter;
+  double* slot = ring + 2 * (i % cap);
+  slot[0] = stats[0];
+  slot[1] = stats[2];
+  *counter = i + 1;
+}
+
 __global__ void densify_kernel(const int* __restrict__ indptr, const int* __restrict__ indices,
                                const float* __restrict__ values, int d, const float* __restrict__ targets,
                                float* __restrict__ Z, int ld, float* __restrict__ sqnorm) {
@@ -195,6 +207,12 @@ extern "C" int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* rin
 extern "C" int omldm_advance_count(long long* count_dev, long long delta, void* stream) {
   advance_count_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(count_dev, delta);
   return check_launch("advance_count_kernel");
+}
+
+extern "C" int omldm_curve_sample(const double* stats, double* ring, int cap, long long* counter, void* stream) {
+  if (cap <= 0) return set_error_msg("curve_sample: the ring needs at least one slot");
+  curve_sample_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(stats, ring, cap, counter);
+  return check_launch("curve_sample_kernel");
 }
 
 extern "C" int omldm_densify(const int* indptr, const int* indices, const float* values, int B, int d,

@@ -26,7 +26,11 @@ struct Comm {
   uint32_t* local;
   float* mc_buf;
   int rank, world, emulate;
+  int nhub;            // hub shards (HubParallelism): ranks 0 .. nhub-1 own a shard; 0 = every rank does
 };
+
+// number of hub shards the model vector is cut into (FlinkSpoke.scala:181-190, key net_hub FlinkLearning.scala:91-94)
+__device__ __forceinline__ int hub_count(const Comm& c) { return c.nhub > 0 && c.nhub < c.world ? c.nhub : c.world; }
 
 constexpr int LOCAL_WORDS = 64;  // private scratch words per (emulated) rank
 // local scratch word indices
@@ -72,8 +76,8 @@ __device__ __forceinline__ float4 f4_scale(float4 a, float s) { return make_floa
 // Phase: owner-side reduce of this rank's shard over all peers and write-back to all peers.
 // n4 = number of float4 elements.  Shards are contiguous: shard r = [r*per, min(n4,(r+1)*per)).
 __device__ __forceinline__ void reduce_and_broadcast_shard(const Comm& c, int me, size_t n4, float scale) {
-  const size_t per = (n4 + c.world - 1) / c.world;
-  const size_t lo = per * me, hi = lo + per < n4 ? lo + per : n4;
+  const size_t per = (n4 + hub_count(c) - 1) / hub_count(c);
+  const size_t lo = per * me < n4 ? per * me : n4, hi = lo + per < n4 ? lo + per : n4;   // ranks >= hub_count: empty shard
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   if (c.mc_buf != nullptr && c.emulate <= 1) {
     for (size_t i = lo + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
@@ -265,7 +269,7 @@ sync_scatter_push_kernel(Comm c, float* delta_base, size_t delta_stride, size_t 
   const size_t cur = step % 3u;
   float4* d4 = reinterpret_cast<float4*>(delta_base + delta_stride * (c.emulate > 1 ? me : 0));
   const size_t n4 = n / 4;
-  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t per = (n4 + hub_count(c) - 1) / hub_count(c);
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
     const float4 v = d4[i];
@@ -286,7 +290,7 @@ sync_scatter_gather_kernel(Comm c, float* e_base, size_t e_stride, size_t n, flo
   const size_t cur = step % 3u, clr = (step + 2u) % 3u;
   float4* e4 = reinterpret_cast<float4*>(e_base + e_stride * (c.emulate > 1 ? me : 0));
   const size_t n4 = n / 4;
-  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t per = (n4 + hub_count(c) - 1) / hub_count(c);
   const size_t lo = per * me, hi = lo + per < n4 ? lo + per : n4;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   const uint32_t seq_entry = 2 * epoch + 1;
@@ -411,7 +415,7 @@ sync_async_kernel(Comm c, float* e_base, size_t e_stride, size_t n, float scale,
   float4* b4 = reinterpret_cast<float4*>(c.bufs[me]);
   float4* e4 = reinterpret_cast<float4*>(e_base + e_stride * (c.emulate > 1 ? me : 0));
   const size_t n4 = n / 4;
-  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t per = (n4 + hub_count(c) - 1) / hub_count(c);
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
     const int owner = static_cast<int>(i / per);
@@ -446,7 +450,7 @@ __global__ void __launch_bounds__(256) sync_easgd_kernel(Comm c, size_t n, float
   const int me = my_rank(c);
   float4* b4 = reinterpret_cast<float4*>(c.bufs[me]);
   const size_t n4 = n / 4;
-  const size_t per = (n4 + c.world - 1) / c.world;
+  const size_t per = (n4 + hub_count(c) - 1) / hub_count(c);
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
     const int owner = static_cast<int>(i / per);
@@ -643,7 +647,7 @@ __global__ void query_reduce_kernel(Comm c, const float* vals_base, float* out_b
 static Comm to_comm(const omldm_comm* h) {
   Comm c;
   c.bufs = h->bufs; c.hubs = h->hubs; c.pads = h->pads; c.local = h->local; c.mc_buf = h->mc_buf;
-  c.rank = h->rank; c.world = h->world; c.emulate = h->emulate;
+  c.rank = h->rank; c.world = h->world; c.emulate = h->emulate; c.nhub = h->nhub;
   return c;
 }
 static int clamp_blocks(int blocks, size_t n, int emulate) {

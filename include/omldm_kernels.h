@@ -127,6 +127,8 @@ int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, int cap, lon
 int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* ring, int cap,
                            long long* count_dev, void* stream);
 int omldm_advance_count(long long* count_dev, long long delta, void* stream);
+/* learning curve sample (operators/hub/FlinkHub.scala:101-113): ring[2 * (*counter % cap)] = (stats[0], stats[2]), ++*counter */
+int omldm_curve_sample(const double* stats, double* ring, int cap, long long* counter, void* stream);
 /* sparse (CSR batch) -> dense staged rows + squared row norms (SparseVector, utils/CommonUtils.scala:23) */
 int omldm_densify(const int* indptr, const int* indices, const float* values, int B, int d,
                   const float* targets, float* Z, int ld, float* sqnorm, void* stream);
@@ -213,6 +215,7 @@ typedef struct omldm_comm {
   int rank;
   int world;
   int emulate;               /* >1: one launch plays `emulate` ranks (single-GPU tests)  */
+  int nhub;                  /* hub shards (HubParallelism, FlinkSpoke.scala:181-190): ranks 0..nhub-1 own one; 0 = all */
 } omldm_comm;
 
 /* Sequence numbers (`epoch`, `clock`, `step`) passed as 0 are device managed: the kernel keeps the

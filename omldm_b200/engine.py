@@ -27,7 +27,7 @@ from .ops import functional as F
 from .ops import _lib
 from .parallel.fused import device_barrier, join_count, query_reduce, split_count
 from .stream.parsers import parse_request
-from .utils.config import JobParameters
+from .utils.config import RECORD_BUFFER_CAP, REQUEST_BUFFER_CAP, JobParameters
 
 
 class Engine:
@@ -42,7 +42,17 @@ class Engine:
             self.device = torch.device("cuda", torch.cuda.current_device())
         self.pipeline_map = PipelineMap(world, self.params.distributedKMeans)
         self.pipelines: Dict[int, GpuPipeline] = {}
+        # Creates that arrive before every expected worker is present are parked and replayed once the observed
+        # parallelism matches (FlinkSpoke.scala:145-156, requestBuffer cap SpokeLogic.scala:35); `observe_parallelism`
+        # is the launcher's hook (torch.distributed gives the final world size at start-up, so by default nothing waits)
         self.pending_requests: List[Request] = []
+        self.observed_parallelism = world
+        self.expected_parallelism = int(self.params.extra.get("expectedParallelism", world))
+        # training records that arrive before the first pipeline exists wait here (recordBuffer, cap 100 000 records,
+        # SpokeLogic.scala:32) and are trained on - oldest first - as soon as one does (FlinkSpoke.scala:69-80)
+        self._record_buffer: List[torch.Tensor] = []
+        self._buffered_rows = 0
+        self.dropped_records = 0
         self.holdout: Optional[torch.Tensor] = None   # [cap, ld] staged rows
         self.count = 0                                # training records seen by this worker
         self.d: Optional[int] = None
@@ -101,9 +111,14 @@ class Engine:
             self._graph_launches.clear()
             self._seen.clear()
         if kind == "Create":
+            if self.observed_parallelism != self.expected_parallelism:
+                if len(self.pending_requests) < REQUEST_BUFFER_CAP:
+                    self.pending_requests.append(r)     # parked until every expected worker is present
+                return []
             self.pipelines[r.id] = GpuPipeline(
                 r, self.device, self.rank, self.world, impl=self.impl, group=self.group,
-                distributed_kmeans=self.params.distributedKMeans, max_msg_params=self.params.maxMsgParams)
+                distributed_kmeans=self.params.distributedKMeans, max_msg_params=self.params.maxMsgParams,
+                test_mode=bool(self.params.test))
             d = (r.trainingConfiguration or {}).get("nFeatures") or (r.learner.hyperParameters or {}).get("nFeatures")
             if d is not None:
                 self._build(self.pipelines[r.id], int(d))
@@ -115,11 +130,37 @@ class Engine:
         if kind == "Delete":
             p = self.pipelines.pop(r.id, None)
             if p is not None:
-                p.close()
+                self._retire(p)
             return []
         if kind == "Query":
             return self.query(r.id, r.requestId)
         return []
+
+    def _retire(self, p: GpuPipeline) -> None:
+        """Collective end of a pipeline.  Peers push into this rank's hub shard without a rendezvous under the
+        asynchronous protocols, so the symmetric region may only be freed once every rank has stopped using it:
+        settle the protocol, device barrier, wait for the stream, then release."""
+        if p.built and p.protocol != "SingleLearner":
+            p.driver.flush()
+            device_barrier(p.comm)
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            elif self.world > 1:
+                import torch.distributed as dist
+                if dist.is_available() and dist.is_initialized():
+                    dist.barrier(group=self.group)
+        p.close()
+
+    def observe_parallelism(self, n: int) -> List[str]:
+        """The launcher reports how many workers are present (FlinkSpoke.checkParallelism, :345-348).  Once the
+        number matches the expected parallelism the parked Create requests are replayed in arrival order."""
+        self.observed_parallelism = int(n)
+        out: List[str] = []
+        if self.observed_parallelism == self.expected_parallelism and self.pending_requests:
+            parked, self.pending_requests = self.pending_requests, []
+            for r in parked:
+                out += self._process_control(r)
+        return out
 
     def _build(self, p: GpuPipeline, d: int) -> None:
         if not p.built and not (p.protocol == "SingleLearner" and self.rank != 0):
@@ -200,6 +241,33 @@ class Engine:
     def _train_rows(self, Z: torch.Tensor, d: int, nnz: Optional[int], **kw) -> None:
         """One step on validated rows: staged dense rows, or sparse rows when `nnz` is given."""
         self.d = d
+        if not self.pipelines:
+            self._buffer_records(Z, nnz)           # no pipeline yet: the records wait (FlinkSpoke.scala:79-80)
+            return
+        if self._record_buffer:
+            pending, self._record_buffer, self._buffered_rows = self._record_buffer, [], 0
+            for Zb, nb in pending:                 # drain the buffer first, oldest first (FlinkSpoke.scala:72-78)
+                self._train_rows_now(Zb, d, nb, **kw)
+        self._train_rows_now(Z, d, nnz, **kw)
+
+    def _buffer_records(self, Z: torch.Tensor, nnz: Optional[int]) -> None:
+        """Bounded FIFO of whole batches, RECORD_BUFFER_CAP records in total; when it is full the oldest records
+        are dropped (DataSet.append evicts the oldest element)."""
+        self._record_buffer.append((Z.clone(), nnz))
+        self._buffered_rows += Z.shape[0]
+        while self._buffered_rows > RECORD_BUFFER_CAP and self._record_buffer:
+            Zo, no = self._record_buffer[0]
+            excess = self._buffered_rows - RECORD_BUFFER_CAP
+            if Zo.shape[0] <= excess:
+                self._record_buffer.pop(0)
+                self._buffered_rows -= Zo.shape[0]
+                self.dropped_records += Zo.shape[0]
+            else:
+                self._record_buffer[0] = (Zo[excess:].clone(), no)
+                self._buffered_rows -= excess
+                self.dropped_records += excess
+
+    def _train_rows_now(self, Z: torch.Tensor, d: int, nnz: Optional[int], **kw) -> None:
         now = time.monotonic()
         if self.t_first is None:
             self.t_first = now
@@ -535,7 +603,8 @@ class Engine:
             k = p.driver.counters
             out.append(Statistics(pipeline=pid, protocol=k.protocol, models=k.models, bytes=k.bytes, blocks=k.blocks,
                                   fitted=c["fitted"], score=p.score(ring),
-                                  learningCurve=[x[0] for x in p.curve], lcx=[x[1] for x in p.curve]))
+                                  learningCurve=[x[0] for x in p.learning_curve()],
+                                  lcx=[x[1] for x in p.learning_curve()]))
         return out
 
     def terminate(self) -> Optional[JobStatistics]:

@@ -40,6 +40,36 @@ class GpuLearner:
         self.stats = torch.zeros(4, dtype=torch.float64, device=self.device)  # loss, aux, fitted, extra
         self.buf: Optional[torch.Tensor] = None
         self.e: Optional[torch.Tensor] = None
+        self.curve_ring: Optional[torch.Tensor] = None      # [cap, 2] fp64 (cumulative loss sum, fitted) per mini-batch
+        self.curve_count: Optional[torch.Tensor] = None
+        self._curve_sampled = False
+
+    def enable_curve(self, cap: int = 1024) -> None:
+        """Test mode: keep a device ring of per-mini-batch (loss sum, fitted) samples (FlinkHub.scala:101-113)."""
+        self.curve_ring = torch.zeros(cap, 2, dtype=torch.float64, device=self.device)
+        self.curve_count = torch.zeros(1, dtype=torch.int64, device=self.device)
+
+    def sample_curve(self) -> None:
+        """One sample on the current stream; learners that run their loss pass on a side stream call it there."""
+        if self.curve_ring is not None:
+            F.curve_sample(self.stats, self.curve_ring, self.curve_count)
+            self._curve_sampled = True
+
+    def learning_curve(self):
+        """[(mean loss of the mini-batch, records fitted so far)] in time order, from the device ring."""
+        if self.curve_ring is None:
+            return []
+        n = int(self.curve_count.item())
+        cap = self.curve_ring.shape[0]
+        ring = self.curve_ring.cpu()
+        idx = [i % cap for i in range(max(0, n - cap), n)]
+        out, prev = [], (0.0, 0.0) if n <= cap else None
+        for i in idx:
+            L, m = float(ring[i, 0]), float(ring[i, 1])
+            if prev is not None and m > prev[1]:
+                out.append(((L - prev[0]) / (m - prev[1]), int(m)))
+            prev = (L, m)
+        return out
 
     # ---- sizing / binding -------------------------------------------------------------
     def n_flat(self, d: int) -> int:
@@ -320,6 +350,7 @@ class GpuORR(GpuLearner):
             F.sq_residual_f16s(Z, self.d, self.wt, self.stats, like_gram=self.overlap)
         else:
             F.sq_residual(Z, self.d, self.wt[: self.d + 2], self.stats)   # prequential squared error with current w
+        self.sample_curve()          # on the loss pass's stream: beside the Gram kernel, not after it
 
     def fit_batch(self, Z):
         n = self.d + 2

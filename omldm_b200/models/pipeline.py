@@ -36,7 +36,8 @@ def effective_protocol(request: Request, world: int, distributed_kmeans: bool) -
 
 class GpuPipeline:
     def __init__(self, request: Request, device, rank: int, world: int, *, impl: str = "fused", group=None,
-                 distributed_kmeans: bool = True, max_msg_params: int = 2000, emulate: int = 1):
+                 distributed_kmeans: bool = True, max_msg_params: int = 2000, emulate: int = 1,
+                 test_mode: bool = False):
         self.request = request
         self.device = torch.device(device)
         self.rank, self.world, self.impl, self.group, self.emulate = rank, world, impl, group, emulate
@@ -58,6 +59,7 @@ class GpuPipeline:
         self._win_n = 0
         self._inplace = any(p.name != "PolynomialFeatures" for p in self.preprocessors[:1])
         self._fused = None
+        self.test_mode = test_mode
         self._curve_every = int(cfg(tc, ["curveEvery", "learningCurveEvery"], 0))
         self._curve_loss, self._curve_n = 0.0, 0
 
@@ -77,6 +79,10 @@ class GpuPipeline:
         n = lrn.n_flat(d)
         single = self.protocol == "SingleLearner"
         world = 1 if single else self.world
+        # HubParallelism (FlinkSpoke.scala:181-190, FlinkHub.scala:176-177): how many parameter-server shards the model
+        # is cut into.  The reference defaults to 1; here every GPU is a shard unless the request says otherwise.
+        n_hubs = int(cfg(self.request.trainingConfiguration, ["HubParallelism", "hubParallelism"], 0) or 0)
+        self.n_hubs = n_hubs if 0 < n_hubs < world else world
         from ..parallel.fused import ShardedGramDriver, wants_scatter, wants_sharded_hub
         scatter_delta = None
         if (wants_sharded_hub(self.protocol, lrn.merge_mode, self.request.trainingConfiguration, world, self.impl,
@@ -87,7 +93,7 @@ class GpuPipeline:
             ld = int(round(n ** 0.5))                    # n_flat of these learners is ld * ld
             nb, nh = ShardedGramDriver.region_floats(ld, world)
             self.comm = PipelineComm(nb, self.device, self.rank, world, self.group, emulate=1, with_hub=True,
-                                     hub_floats=nh)
+                                     hub_floats=nh, n_hubs=self.n_hubs)
             self.driver = ShardedGramDriver(self.comm, self.comm.buf, lrn.merge_mode, self.request.trainingConfiguration,
                                             self.impl, self.group, self.max_msg_params, ld=ld, n=d + 3)
             lrn.bind(d, self.driver.acc, self.comm.buf)
@@ -99,13 +105,14 @@ class GpuPipeline:
                 and lrn.needs_e() and n % 4 == 0:
             # reduce-scatter moved into the producer: the learner keeps a private delta, the symmetric region holds
             # three rotating copies of it (parallel/fused.py::ScatterSynchronousDriver)
-            self.comm = PipelineComm(3 * n, self.device, self.rank, world, self.group, emulate=1, with_hub=False)
+            self.comm = PipelineComm(3 * n, self.device, self.rank, world, self.group, emulate=1, with_hub=False,
+                                     n_hubs=self.n_hubs)
             scatter_delta = torch.zeros(n, device=self.device)
             e = torch.zeros(n, device=self.device)
             lrn.bind(d, scatter_delta, e)
         else:
             self.comm = PipelineComm(n, self.device, self.rank if not single else 0, world, self.group,
-                                     emulate=1, with_hub=True)
+                                     emulate=1, with_hub=True, n_hubs=self.n_hubs)
             e = torch.zeros(self.comm.n, device=self.device) if lrn.needs_e() else None
             lrn.bind(d, self.comm.buf, e)
         self.driver = make_driver(self.protocol, self.comm, e, lrn.merge_mode,
@@ -123,6 +130,8 @@ class GpuPipeline:
 
     def _warm_start(self, e) -> None:
         lrn = self.learner
+        if self.test_mode and lrn.curve_ring is None and not self._curve_every:
+            lrn.enable_curve()           # default test mode: per-mini-batch learning curve kept on the device
         init = self.request.learner.parameters
         if init and init.get("a") is not None:       # warm start from a serialized model
             o = lrn.to_oracle()
@@ -173,6 +182,11 @@ class GpuPipeline:
         elif not skip_fit:
             Zp = self.preprocess(Z, True, protect_input)
             self.learner.fit_batch(Zp, **kw)
+        lrn = self.learner
+        if lrn.curve_ring is not None:
+            if not lrn._curve_sampled:
+                lrn.sample_curve()
+            lrn._curve_sampled = False
         if sync_due and self.driver.step():
             self.learner.after_sync()
 
@@ -199,6 +213,12 @@ class GpuPipeline:
             n = c["fitted"] - self._curve_n
             self.curve.append(((c["loss_sum"] - self._curve_loss) / n if n > 0 else 0.0, c["fitted"]))
             self._curve_loss, self._curve_n = c["loss_sum"], c["fitted"]
+
+    def learning_curve(self):
+        """Per-mini-batch curve from the device ring (test mode), else the host-side samples (queries, `curveEvery`)."""
+        if self.built and self.learner.curve_ring is not None:
+            return self.learner.learning_curve()
+        return list(self.curve)
 
     def graph_safe(self) -> bool:
         return (self.built and self.protocol != "SingleLearner" and self.driver.graph_safe

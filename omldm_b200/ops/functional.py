@@ -74,7 +74,7 @@ class LinearDesc(ctypes.Structure):
 class CommStruct(ctypes.Structure):
     _fields_ = [("bufs", ctypes.c_void_p), ("hubs", ctypes.c_void_p), ("pads", ctypes.c_void_p),
                 ("local", ctypes.c_void_p), ("mc_buf", ctypes.c_void_p), ("rank", ctypes.c_int),
-                ("world", ctypes.c_int), ("emulate", ctypes.c_int)]
+                ("world", ctypes.c_int), ("emulate", ctypes.c_int), ("nhub", ctypes.c_int)]
 
 
 KIND_PA, KIND_PA_REG, KIND_SVM = 0, 1, 2
@@ -138,6 +138,19 @@ def holdout_swap_dev(Z: torch.Tensor, ring: torch.Tensor, d: int, count_dev: tor
     cap = ring.shape[0]
     _lib.check(_k().omldm_holdout_swap_dev(_p(Z), _i(ld), _i(B), _i(d), _p(ring), _i(cap), _p(count_dev),
                                            _lib.stream_ptr()), "holdout_swap_dev")
+
+
+def curve_sample(stats: torch.Tensor, ring: torch.Tensor, counter: torch.Tensor) -> None:
+    """One learning-curve sample (cumulative loss sum, records fitted) into the device ring [cap, 2] (fp64);
+    `counter` = int64[1] samples written so far.  Device work only (graph-capturable)."""
+    cap = ring.shape[0]
+    if native(stats):
+        _lib.check(_k().omldm_curve_sample(_p(stats), _p(ring), _i(cap), _p(counter), _lib.stream_ptr()), "curve_sample")
+        return
+    i = int(counter[0])
+    ring[i % cap, 0] = stats[0]
+    ring[i % cap, 1] = stats[2]
+    counter[0] = i + 1
 
 
 def stage_rows(raw: torch.Tensor, d: int, ld: Optional[int] = None) -> torch.Tensor:

@@ -134,7 +134,7 @@ class PipelineComm:
     """pad | buf[n] | hub[n] for one pipeline, plus the pointer tables the kernels take."""
 
     def __init__(self, n_floats: int, device, rank: int = 0, world: int = 1, group=None, emulate: int = 1,
-                 with_hub: bool = True, hub_floats: Optional[int] = None):
+                 with_hub: bool = True, hub_floats: Optional[int] = None, n_hubs: int = 0):
         self.device = torch.device(device)
         self.rank, self.world, self.emulate = rank, world, emulate
         self.k = emulate if emulate > 1 else world
@@ -166,7 +166,9 @@ class PipelineComm:
         self.struct = CommStruct(
             self.tables[0].data_ptr(), self.tables[1].data_ptr(), self.tables[2].data_ptr(),
             self.local.data_ptr(), (self.region.mc_base + self._off_buf) if self.region.mc_base else 0,
-            rank if emulate <= 1 else 0, self.k, emulate if emulate > 1 else 0)
+            rank if emulate <= 1 else 0, self.k, emulate if emulate > 1 else 0,
+            n_hubs if 0 < n_hubs < self.k else 0)
+        self.n_hubs = n_hubs if 0 < n_hubs < self.k else self.k
         self.multicast = bool(self.region.mc_base)
 
     # local views of this rank (rank 0 in emulate mode)
@@ -206,8 +208,9 @@ class PipelineComm:
         return [int(v) & 0xFFFFFFFF for v in self.pad[PAD_HEART:PAD_HEART + self.k].tolist()]
 
     def shard_bounds(self, r: int):
+        """Float range of hub shard r (empty for ranks that own none, r >= n_hubs)."""
         n4 = self.n // 4
-        per = (n4 + self.k - 1) // self.k
+        per = (n4 + self.n_hubs - 1) // self.n_hubs
         return min(self.n, 4 * per * r), min(self.n, 4 * per * (r + 1))
 
     def close(self) -> None:

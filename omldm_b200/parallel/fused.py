@@ -161,7 +161,7 @@ class PipelinedSynchronousDriver(SyncDriver):
         from ..ops.functional import CommStruct
         # second view of the region: the kernels' "buf" table points at the hub buffers
         self._struct_b = CommStruct(c.tables[1].data_ptr(), c.tables[0].data_ptr(), c.tables[2].data_ptr(),
-                                    c.local.data_ptr(), 0, c.struct.rank, c.struct.world, c.struct.emulate)
+                                    c.local.data_ptr(), 0, c.struct.rank, c.struct.world, c.struct.emulate, c.struct.nhub)
         self.on_switch = None          # learner callback: (index) -> use that delta buffer from now on
         if self.blocks == 0:
             self.blocks = 48           # leave the SMs to the tensor-core kernel it overlaps with
@@ -298,8 +298,9 @@ class ShardedGramDriver(SyncDriver):
             raise ValueError("the sharded hub needs additive statistics, an ld x ld global matrix and k slot matrices")
         from ..ops.functional import GramPeers, gram_f16_scratch
         self.ld, self.n_rows = ld, n
-        rpo = (ld // k) // 32 * 32
-        while rpo * k < n:
+        h = comm.n_hubs                      # HubParallelism: only ranks 0 .. h-1 own rows
+        rpo = (ld // h) // 32 * 32
+        while rpo * h < n:
             rpo += 32
         self.rows_per_owner = rpo
         self.scratch = gram_f16_scratch(comm.device)

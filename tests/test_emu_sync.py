@@ -268,6 +268,38 @@ def test_scatter_push_gather_three_rotating_copies(k, blocks):
         assert int((copies.abs().sum(1) > 0).sum()) <= 1
 
 
+@pytest.mark.parametrize("k,h", [(4, 1), (4, 2), (3, 2)])
+def test_hub_parallelism_fewer_shards_than_workers(k, h):
+    """HubParallelism = h < k (FlinkSpoke.scala:181-190): only ranks 0 .. h-1 own a hub shard.  The all-reduce still
+    yields the exact mean on every rank, and the asynchronous push lands in the h owners' shards only."""
+    n = 1000
+    comm = PipelineComm(n, DEV, 0, 1, None, emulate=k, n_hubs=h)
+    assert comm.n_hubs == h and comm.shard_bounds(h - 1)[1] == comm.n and comm.shard_bounds(k - 1)[0] == comm.n or h == k
+    e = torch.zeros(k, comm.n)
+    xs = [torch.randn(comm.n) for _ in range(k)]
+    for r in range(k):
+        comm.bufs[r].copy_(xs[r])
+    _lib.check(K().omldm_sync_allreduce(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0 / k), _i(0), _u(0), _i(2), sp()),
+               "allreduce")
+    ref = torch.stack(xs).mean(0)
+    for r in range(k):
+        assert torch.allclose(comm.bufs[r], ref, rtol=1e-5, atol=1e-6)
+    # asynchronous pushes: hub shards live on the first h ranks only
+    for r in range(k):
+        comm.hubs[r].zero_()
+        comm.bufs[r].fill_(float(r + 1))
+    e.zero_()
+    _lib.check(K().omldm_sync_async(comm.struct_ptr(), _lib.ptr(e), _sz(comm.n), _f(1.0), _i(0), _i(2), sp()), "async")
+    tot = float(sum(range(1, k + 1)))
+    for r in range(k):
+        lo, hi = comm.shard_bounds(r)
+        if r < h:
+            assert torch.allclose(comm.hubs[r][lo:hi], torch.full((hi - lo,), tot))
+        assert float(comm.hubs[r][:lo].abs().max() if lo else 0.0) == 0.0
+        assert float(comm.hubs[r][hi:].abs().max() if hi < comm.n else 0.0) == 0.0
+    assert comm.status() == 0
+
+
 @pytest.mark.parametrize("k,blocks,n", [(2, 1, 61), (4, 2, 100), (3, 1, 128)])
 def test_sharded_hub_push_and_gather(k, blocks, n):
     """Sharded-hub protocol of the ORR Gram statistics (sync_gram_push_kernel / sync_gram_gather_kernel, driver class

@@ -151,3 +151,75 @@ def test_hoeffding_tree_device_statistics_path_learns():
     eng2.load_state_dict(sd)
     r2 = json.loads(eng2.handle_request({"id": 1, "request": "Query", "requestId": 2})[0])
     assert r2["learner"]["dataStructure"]["feature"] == ds["feature"]
+
+
+def test_records_before_the_first_create_are_buffered_and_trained_on():
+    """FlinkSpoke.scala:69-80 / SpokeLogic.scala:32: without a pipeline, training records wait in a bounded FIFO
+    (100 000 records) and are trained on, oldest first, as soon as a pipeline exists."""
+    import torch
+    from omldm_b200.engine import Engine
+    from omldm_b200.stream import ring as R
+    from omldm_b200.utils.config import RECORD_BUFFER_CAP, JobParameters
+    d = 6
+    a = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")
+    b = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")
+    create = {"id": 1, "request": "Create", "learner": {"name": "PA", "hyperParameters": {"C": 0.1}},
+              "trainingConfiguration": {"protocol": "Synchronous"}}
+    batches = [R.generate_batch(R.KIND_BINARY, d, 100, seed=2, batch_index=i) for i in range(6)]
+    b.handle_request(create)                            # b: pipeline first, then the whole stream
+    for i, Z in enumerate(batches):
+        if i == 3:
+            assert a._buffered_rows == 300 and a.count == 0 and not a.pipelines
+            a.handle_request(create)                    # a: three batches arrive before the Create
+        a.train_batch(Z.clone(), d)
+        b.train_batch(Z.clone(), d)
+    assert a._buffered_rows == 0 and a.count == b.count == 600
+    assert torch.equal(a.pipelines[1].learner.w, b.pipelines[1].learner.w)          # same records, same order
+    # the buffer is bounded: the oldest records are dropped
+    c = Engine(JobParameters(parallelism=1), device="cpu")
+    big = torch.zeros(60000, 32)
+    big[:, d] = 1.0
+    c.train_batch(big.clone(), d)
+    c.train_batch(big.clone(), d)
+    assert c._buffered_rows == RECORD_BUFFER_CAP and c.dropped_records == 20000
+
+
+def test_create_is_parked_until_every_expected_worker_is_present():
+    """FlinkSpoke.scala:145-156: a Create that arrives before the observed parallelism matches the expected one is
+    parked (requestBuffer) and replayed when it does; records keep being buffered meanwhile."""
+    from omldm_b200.engine import Engine
+    from omldm_b200.stream import ring as R
+    from omldm_b200.utils.config import JobParameters
+    jp = JobParameters(parallelism=1, testSetSize=16)
+    jp.extra["expectedParallelism"] = "2"
+    e = Engine(jp, device="cpu")
+    e.handle_request({"id": 1, "request": "Create", "learner": {"name": "PA"}, "trainingConfiguration": {"protocol": "Synchronous"}})
+    assert not e.pipelines and len(e.pending_requests) == 1
+    e.train_batch(R.generate_batch(R.KIND_BINARY, 5, 64, seed=1), 5)
+    assert e._buffered_rows == 64
+    e.observe_parallelism(2)
+    assert list(e.pipelines) == [1] and not e.pending_requests
+    e.train_batch(R.generate_batch(R.KIND_BINARY, 5, 64, seed=1, batch_index=1), 5)
+    assert e._buffered_rows == 0 and e.count == 128
+
+
+def test_default_test_mode_keeps_a_per_mini_batch_learning_curve():
+    """FlinkHub.scala:101-113: in test mode (the default) the hub records (loss, #fitted) per mini-batch; the engine
+    keeps those samples in a device ring, no host synchronisation per step."""
+    from omldm_b200.engine import Engine
+    from omldm_b200.stream import ring as R
+    from omldm_b200.utils.config import JobParameters
+    d = 8
+    e = Engine(JobParameters(parallelism=1, testSetSize=16), device="cpu")          # test=True is the default
+    e.handle_request({"id": 1, "request": "Create", "learner": {"name": "ORR", "hyperParameters": {"solveEvery": 1}},
+                      "trainingConfiguration": {"protocol": "Synchronous"}})
+    for i in range(12):
+        e.train_batch(R.generate_batch(R.KIND_REGRESSION, d, 50, seed=4, batch_index=i), d)
+    js = e.terminate()
+    st = js.statistics[0]
+    assert len(st.learningCurve) == len(st.lcx) >= 11 and st.lcx == sorted(st.lcx) and st.lcx[-1] == st.fitted
+    assert st.learningCurve[-1] < st.learningCurve[1]            # the loss of a learnable stream goes down
+    e2 = Engine(JobParameters(parallelism=1, testSetSize=16, test=False), device="cpu")
+    e2.handle_request({"id": 1, "request": "Create", "learner": {"name": "PA"}, "trainingConfiguration": {"protocol": "Synchronous"}})
+    e2.train_batch(R.generate_batch(R.KIND_BINARY, d, 50, seed=4), d)
+    assert e2.pipelines[1].learner.curve_ring is None
