@@ -233,6 +233,25 @@ extern "C" omldm_producer* omldm_producer_start_wire(omldm_ring* r, int kind, in
   return p;
 }
 
+// Same, resuming a stream: the first batch produced has index `first_batch` (the stream position stored in a
+// checkpoint), max_batches still counts from 0.
+extern "C" omldm_producer* omldm_producer_start_from(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
+                                                     uint64_t seed, int mode, int64_t max_batches, int n_threads,
+                                                     int wire, int64_t first_batch) {
+  if (!r || d <= 0 || batch <= 0 || (kind != 4 && ld < d + 2) || (kind == 4 && ld <= 0)) return nullptr;
+  if (wire != 0 && ((wire != 1 && wire != 2) || kind == 4)) return nullptr;
+  auto* p = new omldm_producer(kind, d, n_aux, seed);
+  p->ring = r; p->kind = kind; p->d = d; p->ld = ld; p->batch = batch; p->n_aux = n_aux; p->mode = mode;
+  p->wire = wire;
+  p->seed = seed; p->max_batches = max_batches;
+  p->next_batch.store(first_batch < 0 ? 0 : first_batch);
+  p->n_threads = n_threads < 1 ? 1 : n_threads;
+  p->filled.assign(1 << 16, 0);
+  p->live.store(p->n_threads);
+  for (int i = 0; i < p->n_threads; ++i) p->threads.emplace_back(producer_loop, p);
+  return p;
+}
+
 extern "C" omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
                                                 uint64_t seed, int mode, int64_t max_batches, int n_threads) {
   return omldm_producer_start_wire(r, kind, d, ld, batch, n_aux, seed, mode, max_batches, n_threads, 0);

@@ -43,6 +43,11 @@ omldm_producer* omldm_producer_start(omldm_ring* r, int kind, int d, int ld, int
  * place by the fp16 Gram kernel.  Neither is available for kind 4. */
 omldm_producer* omldm_producer_start_wire(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
                                           uint64_t seed, int mode, int64_t max_batches, int n_threads, int wire);
+/* Same, resuming at a stream position: the first batch produced has index first_batch (batches first_batch ..
+ * max_batches - 1 are produced). */
+omldm_producer* omldm_producer_start_from(omldm_ring* r, int kind, int d, int ld, int batch, int n_aux,
+                                          uint64_t seed, int mode, int64_t max_batches, int n_threads, int wire,
+                                          int64_t first_batch);
 void omldm_producer_stop(omldm_producer* p);
 
 /* kind 4 = sparse multiclass stream (BASELINE.json config 5): pass the non-zeros per record as `ld`;

@@ -44,6 +44,8 @@ def _h():
         h.omldm_producer_start.argtypes = [vp, i, i, i, i, i, u64, i, i64, i]
         h.omldm_producer_start_wire.restype = vp
         h.omldm_producer_start_wire.argtypes = [vp, i, i, i, i, i, u64, i, i64, i, i]
+        h.omldm_producer_start_from.restype = vp
+        h.omldm_producer_start_from.argtypes = [vp, i, i, i, i, i, u64, i, i64, i, i, i64]
         h.omldm_producer_stop.argtypes = [vp]
         h.omldm_generate_batch_f16.argtypes = [vp, i, i, i, i, u64, u64]
         h.omldm_generate_batch_f16s.argtypes = [vp, i, i, i, i, u64, u64]
@@ -90,9 +92,11 @@ class Topic:
 
     # ---- producer side -------------------------------------------------------------------------
     def start_synthetic(self, kind: int, seed: int = 0, n_aux: int = 0, mode: int = MODE_GENERATE,
-                        max_batches: int = -1, n_threads: int = 1) -> None:
-        self._producer = _h().omldm_producer_start_wire(self._ring, kind, self.d, self.ld, self.batch, n_aux, seed,
-                                                        mode, max_batches, n_threads, {"f32": 0, "f16": 1, "f16s": 2}[self.wire])
+                        max_batches: int = -1, n_threads: int = 1, first_batch: int = 0) -> None:
+        """`first_batch` > 0 resumes the stream at that position (batches first_batch .. max_batches - 1)."""
+        self._producer = _h().omldm_producer_start_from(self._ring, kind, self.d, self.ld, self.batch, n_aux, seed,
+                                                        mode, max_batches, n_threads,
+                                                        {"f32": 0, "f16": 1, "f16s": 2}[self.wire], first_batch)
         if not self._producer:
             raise RuntimeError("producer start failed")
 

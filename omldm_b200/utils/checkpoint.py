@@ -22,14 +22,28 @@ def _rank_file(directory: str, rank: int) -> str:
     return os.path.join(directory, f"rank{rank:03d}.pt")
 
 
+def _barrier(engine) -> None:
+    if engine.world > 1:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.barrier(group=engine.group)
+
+
 def save_checkpoint(engine, directory: str, step: int = 0) -> str:
+    """One consistent snapshot.  COLLECTIVE when world > 1: every rank calls it at the SAME step (the reference's
+    checkpoints are barrier aligned).  The protocols are settled first (`engine.flush()`), the ranks meet, every rank
+    writes its file, they meet again, and only then does rank 0 write the manifest - a manifest therefore always
+    describes a complete set of rank files of one step.  `step` is the stream position to resume from."""
     os.makedirs(directory, exist_ok=True)
+    engine.flush()
     if engine.device.type == "cuda":
         torch.cuda.synchronize(engine.device)
+    _barrier(engine)
     path = _rank_file(directory, engine.rank)
     tmp = path + ".tmp"
     torch.save({"step": step, "time": time.time(), "engine": engine.state_dict()}, tmp)
     os.replace(tmp, path)                      # atomic: a crash never leaves a torn checkpoint
+    _barrier(engine)
     if engine.rank == 0:
         man = {"world": engine.world, "step": step, "time": time.time(), "job": engine.params.jobName,
                "pipelines": sorted(engine.pipelines)}
@@ -194,18 +208,31 @@ def load_checkpoint(engine, directory: str) -> Optional[int]:
 
 
 class PeriodicCheckpointer:
-    """`--checkInterval` milliseconds between snapshots (Checkpointing.scala:15)."""
+    """`--checkInterval` milliseconds between snapshots (Checkpointing.scala:15).  With several ranks the decision is
+    rank 0's: every `agree_every` steps it tells the others whether the interval has elapsed (one tiny broadcast), so
+    every rank snapshots at the same step."""
 
-    def __init__(self, engine, directory: str, interval_ms: int = 5000):
+    def __init__(self, engine, directory: str, interval_ms: int = 5000, agree_every: int = 8):
         self.engine, self.directory, self.interval = engine, directory, interval_ms / 1000.0
         self.last = time.monotonic()
         self.saved = 0
+        self.agree_every = max(1, agree_every)
 
     def maybe_save(self, step: int) -> bool:
-        now = time.monotonic()
-        if now - self.last < self.interval:
+        eng = self.engine
+        if eng.world > 1:
+            if step % self.agree_every:
+                return False
+            import torch.distributed as dist
+            dev = eng.device if eng.device.type == "cuda" else torch.device("cpu")
+            flag = torch.tensor([1 if (eng.rank == 0 and time.monotonic() - self.last >= self.interval) else 0], device=dev)
+            dist.broadcast(flag, 0, group=eng.group)
+            due = bool(int(flag.item()))
+        else:
+            due = time.monotonic() - self.last >= self.interval
+        if not due:
             return False
-        save_checkpoint(self.engine, self.directory, step)
-        self.last = now
+        save_checkpoint(eng, self.directory, step)
+        self.last = time.monotonic()
         self.saved += 1
         return True

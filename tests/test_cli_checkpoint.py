@@ -152,3 +152,39 @@ def test_restore_averaged_model_and_more_ranks(tmp_path):
     assert torch.allclose(g.pipelines[1].learner.w, wb, atol=1e-7)
     assert g.pipelines[1].learner.counters()["fitted"] == 0 and g.count == 0
     assert g._holdout_rows().shape[0] == 0
+
+
+def test_cli_resume_starts_at_the_stream_position_and_requests_apply_in_mid_stream(tmp_path):
+    """A run cut in two by a checkpoint + `--resume true` trains every record exactly once (the topic restarts at the
+    checkpointed step), and a request with "atBatch" takes effect at that step boundary, not before the stream."""
+    req = tmp_path / "req.jsonl"
+    with open(req, "w") as f:
+        f.write(json.dumps({"id": 1, "request": "Create", "learner": {"name": "PA", "hyperParameters": {"C": 0.1}},
+                            "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": 12}}) + "\n")
+        f.write(json.dumps({"id": 2, "request": "Create", "atBatch": 6, "learner": {"name": "RegressorPA"},
+                            "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": 12}}) + "\n")
+        f.write(json.dumps({"id": 1, "request": "Query", "requestId": 5}) + "\n")
+        f.write(json.dumps({"id": 2, "request": "Query", "requestId": 6}) + "\n")
+    common = ["--engine", "gpu", "--requests", str(req), "--trainingData", "synthetic:binary:12", "--batch", "100",
+              "--testSetSize", "20", "--test", "false"]
+    # one uninterrupted run of 10 batches
+    out_a = tmp_path / "a"
+    assert cli.main(common + ["--batches", "10", "--outDir", str(out_a)]) == 0
+    ra = {json.loads(l)["mlpId"]: json.loads(l) for l in open(out_a / "responses.jsonl")}
+    assert ra[1]["dataFitted"] == 10 * 100 - 20
+    assert ra[2]["dataFitted"] == 4 * 100           # created at the boundary before step 6: sees batches 6..9 only
+    # the same stream cut in two: 4 batches with a checkpoint at the end, then resume
+    ck = tmp_path / "ck"
+    out_b = tmp_path / "b"
+    assert cli.main(common + ["--batches", "4", "--outDir", str(out_b), "--checkpointing", "true", "--checkInterval", "0",
+                              "--stateBackend", str(ck)]) == 0
+    assert json.load(open(ck / "manifest.json"))["step"] == 4
+    out_c = tmp_path / "c"
+    assert cli.main(common + ["--batches", "10", "--outDir", str(out_c), "--checkpointing", "true", "--checkInterval",
+                              "100000000", "--stateBackend", str(ck), "--resume", "true"]) == 0
+    rc = {json.loads(l)["mlpId"]: json.loads(l) for l in open(out_c / "responses.jsonl")}
+    assert rc[1]["dataFitted"] == ra[1]["dataFitted"]          # nothing trained twice, nothing skipped
+    assert rc[2]["dataFitted"] == ra[2]["dataFitted"]
+    wa = ra[1]["learner"]["parameters"]["a"]
+    wc = rc[1]["learner"]["parameters"]["a"]
+    assert np.allclose(np.asarray(wa, dtype=float), np.asarray(wc, dtype=float), rtol=1e-5, atol=1e-6)
