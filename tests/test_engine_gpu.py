@@ -130,7 +130,7 @@ def test_multi_pipeline_exact_batched_launch_matches_separate_pipelines():
     d, B = 28, 256
     specs = [("PA", {"C": 0.1}), ("PA", {"C": 1.0, "updateType": "PA-II"}), ("SVM", {"lambda": 0.01}),
              ("RegressorPA", {"C": 0.5, "epsilon": 0.05})]
-    eng = Engine(JobParameters(parallelism=1, testSetSize=0), device="cuda")
+    eng = Engine(JobParameters(parallelism=1, testSetSize=0, test=False), device="cuda")   # no curve samples: count launches
     for i, (name, hyper) in enumerate(specs):
         eng.handle_request({"id": i + 1, "request": "Create",
                             "learner": {"name": name, "hyperParameters": dict(hyper, trainingMode="exact")},
