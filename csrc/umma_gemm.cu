@@ -9,6 +9,8 @@
 //               Z^T Z Gram for ridge regression, T^T X for MultiClassPA / k-means / NN updates;
 //               K is the mini-batch axis so records are consumed exactly as they sit in the
 //               staged ring slot, no transpose pass)
+//   gemm_nn   : C[M,N] (+)= A[M,K] * B[K,N]        (A K-major, B MN-major, both row-major in memory:
+//               the back-propagated gradient dL/dA = G W of the NN learner)
 //
 // Replaces the per-record Breeze `Double` arithmetic behind `node.receiveTuple`
 // (reference call site: src/main/scala/omldm/operators/spoke/FlinkSpoke.scala:101); the
@@ -46,10 +48,23 @@ struct PeerMaps {
   int rows_per_owner;
 };
 
-template <int BN, bool MN_MAJOR, bool PEER>
+// K-means assignment as the epilogue of the distance GEMM S = X C^T (SURVEY K-L5): the scores never leave the SM.
+// Each epilogue thread owns one record (one TMEM lane): pass 1 walks the accumulator columns and keeps
+// argmin_j (||c_j||^2 - 2 S_ij); pass 2 writes the one-hot row of T in 32 x 32 blocks through shared memory and TMA
+// (tmC maps T), which the update GEMM sums += T^T Z consumes.  stats += {inertia, -, #records}.
+struct KMeansEpi {
+  const float* cnorm;   // ||c_j||^2, +inf for empty centroids
+  const float* Z;       // the staged rows (valid flags; exact distance to the chosen centroid), pitch ldz
+  const float* Cm;      // centroids, pitch ldcm
+  int ldz, ldcm, d;
+  int* assign;          // optional
+  double* stats;
+};
+
+template <int BN, bool A_MN, bool B_MN, bool PEER>
 __device__ __forceinline__ void umma_gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                                const PeerMaps* pm, float* __restrict__ C, int ldc, int M, int N, int K,
-                                               int k_per_split, int flags) {
+                                               int k_per_split, int flags, const KMeansEpi* km = nullptr) {
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * BN;
   if ((flags & GEMM_UPPER_ONLY) && m0 > n0 + BN - 1) return;  // tile strictly below the diagonal
@@ -87,6 +102,7 @@ __device__ __forceinline__ void umma_gemm_body(const CUtensorMap& tmA, const CUt
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  constexpr bool MN_MAJOR = A_MN && B_MN;
   if (warp == 0 && MN_MAJOR && (flags & GEMM_MN_SLAB2D)) {
     // ------------------------------------------------------------ TMA producer, one 2-D box per
     // 32-float slab (lane l loads slab l): A has BM/32 slabs, B has BN/32.
@@ -120,19 +136,16 @@ __device__ __forceinline__ void umma_gemm_body(const CUtensorMap& tmA, const CUt
         uint8_t* sb = sa + S::A_BYTES;
         mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
         const int k0 = k_begin + kb * BK;
-        if constexpr (MN_MAJOR) {
-          tma_load_3d(sa, &tmA, &full_bar[stage], 0, k0, m0 / 32);
-          tma_load_3d(sb, &tmB, &full_bar[stage], 0, k0, n0 / 32);
-        } else {
-          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
-          tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
-        }
+        if constexpr (A_MN) tma_load_3d(sa, &tmA, &full_bar[stage], 0, k0, m0 / 32);
+        else tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+        if constexpr (B_MN) tma_load_3d(sb, &tmB, &full_bar[stage], 0, k0, n0 / 32);
+        else tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = make_idesc_tf32(BM, BN, MN_MAJOR, MN_MAJOR);
+    constexpr uint32_t idesc = make_idesc_tf32(BM, BN, A_MN, B_MN);
     int stage = 0;
     uint32_t phase = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
@@ -143,17 +156,13 @@ __device__ __forceinline__ void umma_gemm_body(const CUtensorMap& tmA, const CUt
         const uint32_t sb = sa + S::A_BYTES;
 #pragma unroll
         for (int kk = 0; kk < BK / 8; ++kk) {
-          uint64_t da, db;
-          if constexpr (MN_MAJOR) {
-            // K advance = 8 rows of 128 B; MN atoms (32 floats) are BK*128 B apart.
-            // 32-byte-atom swizzle: K groups are 4 rows (512 B) apart.
-            da = make_smem_desc_sw128(sa + kk * 1024, BK * 128, 512, 1);
-            db = make_smem_desc_sw128(sb + kk * 1024, BK * 128, 512, 1);
-          } else {
-            // K advance = 8 tf32 = 32 B inside the 128-B swizzle row; 8-row groups 1024 B apart.
-            da = make_smem_desc_sw128(sa + kk * 32, 16, 1024);
-            db = make_smem_desc_sw128(sb + kk * 32, 16, 1024);
-          }
+          // MN-major: K advance = 8 rows of 128 B; MN atoms (32 floats) are BK*128 B apart; 32-byte-atom
+          //           swizzle: K groups are 4 rows (512 B) apart.
+          // K-major : K advance = 8 tf32 = 32 B inside the 128-B swizzle row; 8-row groups 1024 B apart.
+          const uint64_t da = A_MN ? make_smem_desc_sw128(sa + kk * 1024, BK * 128, 512, 1)
+                                   : make_smem_desc_sw128(sa + kk * 32, 16, 1024);
+          const uint64_t db = B_MN ? make_smem_desc_sw128(sb + kk * 1024, BK * 128, 512, 1)
+                                   : make_smem_desc_sw128(sb + kk * 32, 16, 1024);
           umma_tf32(tmem_base, da, db, idesc, (kb | kk) != 0);
         }
         umma_commit(&empty_bar[stage]);                 // frees this smem stage when MMAs retire
@@ -169,7 +178,79 @@ __device__ __forceinline__ void umma_gemm_body(const CUtensorMap& tmA, const CUt
     tc_fence_after();
     const int row = m0 + q * 32 + static_cast<int>(lane_id());
     const bool accumulate = (flags & GEMM_ACCUMULATE) != 0;
-    if (flags & GEMM_TMA_EPILOGUE) {
+    if (km != nullptr) {
+      // ---- fused k-means assignment (N <= BN: one tile holds every centroid of a record)
+      const uint32_t r = lane_id();
+      const bool in_range = row < M;
+      const float* zr = km->Z + static_cast<size_t>(in_range ? row : 0) * km->ldz;
+      const bool valid = in_range && zr[km->d] != 0.f;
+      float best = INFINITY;
+      int bj = 0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        if (c * 32 >= N) break;                      // warp-uniform
+        float v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int col = c * 32 + j;
+          if (col < N) {
+            const float dist = __ldg(km->cnorm + col) - 2.f * v[j];
+            if (dist < best) { best = dist; bj = col; }
+          }
+        }
+      }
+      double inertia = 0.0;
+      if (valid) {
+        // the tf32 scores decide the argmin; the reported distance to the chosen centroid is recomputed in fp32
+        // (||x||^2 - 2 x.c + ||c||^2 cancels, and tf32 truncation would bias the sum)
+        const float4* z4 = reinterpret_cast<const float4*>(zr);
+        const float4* c4 = reinterpret_cast<const float4*>(km->Cm + static_cast<size_t>(bj) * km->ldcm);
+        const int d4 = km->d >> 2;
+        float acc = 0.f;
+        for (int i = 0; i < d4; ++i) {
+          const float4 t = z4[i], u = __ldg(c4 + i);
+          const float a0 = t.x - u.x, a1 = t.y - u.y, a2 = t.z - u.z, a3 = t.w - u.w;
+          acc = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, acc))));
+        }
+        for (int i = d4 << 2; i < km->d; ++i) {
+          const float a0 = zr[i] - km->Cm[static_cast<size_t>(bj) * km->ldcm + i];
+          acc = fmaf(a0, a0, acc);
+        }
+        inertia = static_cast<double>(acc);
+      }
+      if (in_range && km->assign) km->assign[row] = valid ? bj : -1;
+      // one-hot rows of T, 32 x 32 blocks through swizzled shared memory and TMA (full 128-byte lines)
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        if (c * 32 >= ldc || m0 + q * 32 >= M) break;   // ldc = pitch of T: pad columns are written as zeros too
+        uint8_t* slot = smem + (q * (BN / 32) + c) * 4096;
+        const int hot = (valid && (bj >> 5) == c) ? (bj & 31) : -1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(slot + r * 128 + ((j ^ (r & 7)) << 4)) =
+              make_float4(hot == 4 * j ? 1.f : 0.f, hot == 4 * j + 1 ? 1.f : 0.f, hot == 4 * j + 2 ? 1.f : 0.f,
+                          hot == 4 * j + 3 ? 1.f : 0.f);
+        fence_proxy_async();
+        __syncwarp();
+        if (r == 0) {
+          tma_store_2d(&tmC, slot, c * 32, m0 + q * 32);
+          tma_commit_group();
+        }
+      }
+      if (r == 0) tma_wait_group0();
+      __syncwarp();
+      // statistics: one pair of atomics per warp
+      double w_in = inertia;
+      int w_n = valid ? 1 : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        w_in += __shfl_xor_sync(0xffffffffu, w_in, o);
+        w_n += __shfl_xor_sync(0xffffffffu, w_n, o);
+      }
+      if (r == 0 && w_n) { atomicAdd(&km->stats[0], w_in); atomicAdd(&km->stats[2], static_cast<double>(w_n)); }
+    } else if (flags & GEMM_TMA_EPILOGUE) {
       // TMEM -> registers -> swizzled smem tile (32 rows x 128 B per warp and 32-column chunk) ->
       // TMA store / TMA reduce-add: the TMA unit writes full 128-B lines and performs the fp32
       // adds at L2 (the vector red.global is lowered to scalar REDGs on sm_100a).  The operand
@@ -246,7 +327,25 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, int ldc, int M, int N, int K,
                  int k_per_split, int flags) {
-  umma_gemm_body<BN, MN_MAJOR, false>(tmA, tmB, tmC, nullptr, C, ldc, M, N, K, k_per_split, flags);
+  umma_gemm_body<BN, MN_MAJOR, MN_MAJOR, false>(tmA, tmB, tmC, nullptr, C, ldc, M, N, K, k_per_split, flags);
+}
+
+// distance GEMM with the k-means assignment as its epilogue (tmC maps the one-hot matrix T)
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+umma_kmeans_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                   const __grid_constant__ CUtensorMap tmT, const __grid_constant__ KMeansEpi km, int ldt, int M, int N,
+                   int K) {
+  umma_gemm_body<BN, false, false, false>(tmA, tmB, tmT, nullptr, nullptr, ldt, M, N, K, (K + BK - 1) / BK * BK, 0, &km);
+}
+
+// A K-major, B MN-major (both row-major in memory): C = A B
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+umma_gemm_nn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, int ldc, int M, int N, int K,
+                    int k_per_split, int flags) {
+  umma_gemm_body<BN, false, true, false>(tmA, tmB, tmC, nullptr, C, ldc, M, N, K, k_per_split, flags);
 }
 
 // Gram / outer-product GEMM whose epilogue IS the reduce-scatter: every output strip is TMA-reduce-added into the
@@ -255,7 +354,7 @@ template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 umma_gemm_scatter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ PeerMaps pm, int M, int N, int K, int k_per_split, int flags) {
-  umma_gemm_body<BN, true, true>(tmA, tmB, pm.tm[0], &pm, nullptr, 0, M, N, K, k_per_split,
+  umma_gemm_body<BN, true, true, true>(tmA, tmB, pm.tm[0], &pm, nullptr, 0, M, N, K, k_per_split,
                                  flags | GEMM_ACCUMULATE | GEMM_TMA_EPILOGUE);
 }
 
@@ -374,6 +473,90 @@ extern "C" int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb
   }
   return dispatch_bn<true>(tmA, tmB, bn, C, ldc, M, N, K, ksplit, flags,
                            static_cast<cudaStream_t>(stream));
+}
+
+// Fused k-means assignment: T[B, ldt] <- one-hot(argmin_j ||x_i - c_j||^2), stats += {inertia, -, #valid}; centroids
+// Cm[Kc, ldc] (K-major rows of d floats), cnorm[Kc].  Kc <= 256, ldt % 32 == 0 and >= Kc.
+extern "C" int omldm_kmeans_assign_fused(const float* Z, int ld, int d, int B, const float* Cm, int ldcm, const float* cnorm,
+                                         int Kc, float* T, int ldt, int* assign, double* stats, void* stream) {
+  if (B <= 0) return 0;
+  if (Kc < 1 || Kc > 256) return set_error_msg("kmeans_assign_fused: 1 <= K <= 256 (one tile holds all centroids)");
+  if ((ld & 3) || (ldcm & 3) || (ldt & 31) || ldt < Kc) return set_error_msg("kmeans_assign_fused: bad pitches");
+  if ((reinterpret_cast<uintptr_t>(Z) & 15) || (reinterpret_cast<uintptr_t>(Cm) & 15) || (reinterpret_cast<uintptr_t>(T) & 15))
+    return set_error_msg("kmeans_assign_fused: operands must be 16-byte aligned");
+  const int bn = pick_bn(ldt < 256 ? ldt : 256);       // covers the pad columns of T as well (written as zeros)
+  CUtensorMap tmA, tmB, tmT;
+  if (encode_kmajor(&tmA, Z, B, d, ld, BM)) return -1;
+  if (encode_kmajor(&tmB, Cm, Kc, d, ldcm, bn)) return -1;
+  if (encode_c(&tmT, T, B, ldt, ldt)) return -1;
+  KMeansEpi km;
+  km.cnorm = cnorm; km.Z = Z; km.Cm = Cm; km.ldz = ld; km.ldcm = ldcm; km.d = d; km.assign = assign; km.stats = stats;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static bool attr_set[16][4] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto go = [&](auto kern, int smem, int BNv) -> int {
+    bool& done = attr_set[dev & 15][BNv == 32 ? 0 : BNv == 64 ? 1 : BNv == 128 ? 2 : 3];
+    if (!done) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(kmeans)", e);
+      done = true;
+    }
+    dim3 grid((B + BM - 1) / BM, 1, 1);
+    kern<<<grid, GEMM_THREADS, smem, st>>>(tmA, tmB, tmT, km, ldt, B, Kc, d);
+    return check_launch("umma_kmeans_kernel");
+  };
+  switch (bn) {
+    case 32: return go(umma_kmeans_kernel<32>, GemmSmem<32>::TOTAL, 32);
+    case 64: return go(umma_kmeans_kernel<64>, GemmSmem<64>::TOTAL, 64);
+    case 128: return go(umma_kmeans_kernel<128>, GemmSmem<128>::TOTAL, 128);
+    default: return go(umma_kmeans_kernel<256>, GemmSmem<256>::TOTAL, 256);
+  }
+}
+
+// C[M,N] (+)= A[M,K] B[K,N]: A row-major (pitch lda, multiple of 4 floats), B row-major (pitch ldb, multiple of 32
+// floats, 128-byte aligned, N <= ldb).
+extern "C" int omldm_gemm_nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
+                             int ksplit, int flags, void* stream) {
+  if (lda & 3) return set_error_msg("gemm_nn: lda must be a multiple of 4 floats");
+  if (ldb & 31) return set_error_msg("gemm_nn: ldb must be a multiple of 32 floats (padded rows)");
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 127))
+    return set_error_msg("gemm_nn: A must be 16-byte and B 128-byte aligned");
+  if (N > ldb) return set_error_msg("gemm_nn: N exceeds the row pitch of B");
+  if (ksplit > 1 && !(flags & GEMM_ACCUMULATE)) return set_error_msg("gemm_nn: split-K requires the accumulate flag");
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB, tmC;
+  if (encode_kmajor(&tmA, A, M, K, lda, BM)) return -1;
+  if (encode_mnmajor(&tmB, B, K, ldb, bn / 32)) return -1;
+  memset(&tmC, 0, sizeof(tmC));
+  flags &= ~GEMM_MN_SLAB2D;
+  if (!(flags & GEMM_NO_TMA_EPILOGUE) && (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0) {
+    if (encode_c(&tmC, C, M, N, ldc)) return -1;
+    flags |= GEMM_TMA_EPILOGUE;
+  }
+  if (ksplit < 1) ksplit = 1;
+  const int k_per_split = ((K + ksplit - 1) / ksplit + BK - 1) / BK * BK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static bool attr_set[16][4] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto go = [&](auto kern, int smem, int BNv) -> int {
+    bool& done = attr_set[dev & 15][BNv == 32 ? 0 : BNv == 64 ? 1 : BNv == 128 ? 2 : 3];
+    if (!done) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm_nn)", e);
+      done = true;
+    }
+    dim3 grid((M + BM - 1) / BM, (N + BNv - 1) / BNv, (K + k_per_split - 1) / k_per_split);
+    kern<<<grid, GEMM_THREADS, smem, st>>>(tmA, tmB, tmC, C, ldc, M, N, K, k_per_split, flags);
+    return check_launch("umma_gemm_nn_kernel");
+  };
+  switch (bn) {
+    case 32: return go(umma_gemm_nn_kernel<32>, GemmSmem<32>::TOTAL, 32);
+    case 64: return go(umma_gemm_nn_kernel<64>, GemmSmem<64>::TOTAL, 64);
+    case 128: return go(umma_gemm_nn_kernel<128>, GemmSmem<128>::TOTAL, 128);
+    default: return go(umma_gemm_nn_kernel<256>, GemmSmem<256>::TOTAL, 256);
+  }
 }
 
 // C_peers[p] = base of GPU p's accumulation matrix (M x N, pitch ldc, peer-mapped; the caller picks the rotating

@@ -36,6 +36,10 @@ int omldm_gemm_tn(const float* A, int lda, const float* B, int ldb, float* C, in
                   int M, int N, int K, int ksplit, int flags, void* stream);
 int omldm_gemm_outer(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                      int M, int N, int K, int ksplit, int flags, void* stream);
+/* C[M,N] (+)= A[M,K] B[K,N], both row-major (A K-major, B MN-major: ldb % 32 == 0, 128-byte aligned): the
+ * back-propagated gradient G W of the NN learner. */
+int omldm_gemm_nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                  int M, int N, int K, int ksplit, int flags, void* stream);
 
 /* ------------------------------------------------------------------ fp16 Gram update (gram_f16.cu)
  * G (+)= Z^T Z for a mini-batch of fp16 staged rows (ORR; per-record update behind node.receiveTuple,
@@ -165,6 +169,11 @@ int omldm_fused_poly_scaler_linear(const float* Z, int ld, int d_in, int B, cons
 int omldm_kmeans_assign(const float* Z, int ld, int d, int B, const float* S, int lds,
                         const float* cnorm, int K, float* T, int ldt, int* assign, double* stats,
                         void* stream);
+/* the same assignment as the EPILOGUE of the tcgen05 distance GEMM X C^T (umma_gemm.cu): argmin straight from the TMEM
+ * accumulator, the scores never reach global memory.  centroids Cm[K, ldcm] (rows of d floats), K <= 256,
+ * ldt % 32 == 0 and >= K (pad columns of T are written as zeros). */
+int omldm_kmeans_assign_fused(const float* Z, int ld, int d, int B, const float* Cm, int ldcm, const float* cnorm,
+                              int K, float* T, int ldt, int* assign, double* stats, void* stream);
 /* centroids = (sums + sums2) / counts (count column = d; sums2 may be NULL), refreshes ||c||^2 */
 int omldm_kmeans_finalize(const float* sums, const float* sums2, int lds, int K, int d, float* centroids,
                           int ldc, float* cnorm, void* stream);

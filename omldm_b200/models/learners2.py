@@ -70,8 +70,10 @@ class GpuKMeans(GpuLearner):
             self.refresh()
             return
         T, Sc = self._bufs(Zb.shape[0])
-        F.gemm_tn(Zb[:, : self.d], self.centroids[:, : self.d], Sc[:, : self.k])
-        F.kmeans_assign(Zb, self.d, Sc, self.cnorm, self.k, T, self.stats)
+        # distances, argmin and the one-hot rows in one tcgen05 kernel (argmin read from TMEM); two kernels otherwise
+        if not F.kmeans_assign_fused(Zb, self.d, self.centroids, self.cnorm, self.k, T, self.stats):
+            F.gemm_tn(Zb[:, : self.d], self.centroids[:, : self.d], Sc[:, : self.k])
+            F.kmeans_assign(Zb, self.d, Sc, self.cnorm, self.k, T, self.stats)
         F.gemm_outer(T, Zb, self.dS, accumulate=True, m=self.k, n=self.d + 1,
                      ksplit=max(1, min(32, Zb.shape[0] // 256)))
         self.refresh()
@@ -294,8 +296,8 @@ class GpuNN(GpuLearner):
             fan_in, od = self.sizes[i], self.sizes[i + 1]
             W, G = self.layers[i], Gs[i]
             if i > 0:
-                # gradient w.r.t. the previous activations, through the relu (library GEMM: G and W are both K-major here)
-                torch.mm(G[:, :od], W[:, :fan_in], out=Gs[i - 1][:, :fan_in])
+                # gradient w.r.t. the previous activations, through the relu: G (K-major) times W (rows = K, MN-major)
+                F.gemm_nn(G[:, :od], W, Gs[i - 1][:, :fan_in])
                 F.nn_relu_mask(Gs[i - 1], acts[i], fan_in)
             gW = gWs[i]
             gW.zero_()

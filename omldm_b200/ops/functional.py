@@ -20,7 +20,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
-from .gemm import gemm_outer, gemm_outer_scatter, gemm_tn  # noqa: F401  (re-exported)
+from .gemm import gemm_nn, gemm_outer, gemm_outer_scatter, gemm_tn  # noqa: F401  (re-exported)
 
 _IMPL = "auto"
 
@@ -683,6 +683,17 @@ def kmeans_assign(Z, d, S, cnorm, K, T, stats, assign=None) -> None:
     stats[2] += int(valid.sum().item())
     if assign is not None:
         assign.copy_(torch.where(valid, bj, torch.full_like(bj, -1)).int())
+
+
+def kmeans_assign_fused(Z, d, centroids, cnorm, K, T, stats, assign=None) -> bool:
+    """Distance GEMM + argmin + one-hot rows in one tcgen05 kernel (csrc/umma_gemm.cu::umma_kmeans_kernel).  Returns
+    False when the fused kernel does not apply (CPU tensors, K > 256): use gemm_tn + kmeans_assign then."""
+    if not (native(Z) and Z.is_cuda) or K > 256 or _IMPL == "emu":
+        return False
+    _lib.check(_k().omldm_kmeans_assign_fused(_p(Z), _i(Z.stride(0)), _i(d), _i(Z.shape[0]), _p(centroids),
+                                              _i(centroids.stride(0)), _p(cnorm), _i(K), _p(T), _i(T.stride(0)),
+                                              _p(assign), _p(stats), _lib.stream_ptr()), "kmeans_assign_fused")
+    return True
 
 
 def kmeans_finalize(sums, sums2, K, d, centroids, cnorm) -> None:

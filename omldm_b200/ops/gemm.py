@@ -57,6 +57,26 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None, *
     return out
 
 
+def gemm_nn(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, accumulate: bool = False) -> torch.Tensor:
+    """out[M,N] (+)= a[M,K] @ b[K,N], both row-major; b needs a pitch that is a multiple of 32 floats."""
+    _check2d(a, "a"); _check2d(b, "b"); _check2d(out, "out")
+    M, K = a.shape
+    N = out.shape[1]
+    if b.shape[0] != K or b.shape[1] < N:
+        raise ValueError("inner dimensions differ")
+    if not _lib.use_native(a, b, out):
+        r = a @ b[:, :N]
+        out.add_(r) if accumulate else out.copy_(r)
+        return out
+    rc = _lib.kernels().omldm_gemm_nn(
+        _lib.ptr(a), ctypes.c_int(a.stride(0)), _lib.ptr(b), ctypes.c_int(b.stride(0)),
+        _lib.ptr(out), ctypes.c_int(out.stride(0)), ctypes.c_int(M), ctypes.c_int(N),
+        ctypes.c_int(K), ctypes.c_int(1), ctypes.c_int((ACCUMULATE if accumulate else 0) | (_ENV_FLAGS & NO_TMA_EPILOGUE)),
+        _lib.stream_ptr())
+    _lib.check(rc, "omldm_gemm_nn")
+    return out
+
+
 def gemm_outer(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None, *,
                accumulate: bool = False, ksplit: int = 1, upper_only: bool = False,
                m: int | None = None, n: int | None = None) -> torch.Tensor:
