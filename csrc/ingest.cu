@@ -34,10 +34,16 @@ __global__ void __launch_bounds__(256, 2)
 holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restrict__ ring, int cap,
                     long long count0_arg, long long* __restrict__ count_dev, unsigned int* __restrict__ done) {
   const long long count0 = count_dev ? *reinterpret_cast<volatile long long*>(count_dev) : count0_arg;
-  const int slot = blockIdx.x;
+  // narrow rows: several ring slots share a CTA so that every thread has a column (a 128-byte row is 16 float2)
+  const int ldv_all = ld / static_cast<int>(sizeof(V) / sizeof(float));
+  const int spc = ldv_all < static_cast<int>(blockDim.x) ? static_cast<int>(blockDim.x) / ldv_all : 1;
+  const int slot = blockIdx.x * spc + (spc > 1 ? static_cast<int>(threadIdx.x) / ldv_all : 0);
+  const int cv_first = spc > 1 ? static_cast<int>(threadIdx.x) % ldv_all : static_cast<int>(threadIdx.x);
+  const int cv_step = spc > 1 ? ldv_all : static_cast<int>(blockDim.x);
+  const bool lane_on = spc == 1 || static_cast<int>(threadIdx.x) < spc * ldv_all;
   const long long h0 = holdouts_before(count0), h1 = holdouts_before(count0 + B);
   const long long hf = h0 + ((slot - (h0 % cap)) % cap + cap) % cap;   // first chain element
-  if (slot < cap && hf < h1) {
+  if (lane_on && slot < cap && hf < h1) {
     const int m = static_cast<int>((h1 - 1 - hf) / cap);                // chain has m + 1 elements
     // with an even ring size every element of a chain has the parity of the first one, so its rows are equally
     // spaced (5 cap records apart): one base pointer and a stride instead of a pointer per row
@@ -55,7 +61,7 @@ holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restri
     const int ldv = ld / static_cast<int>(sizeof(V) / sizeof(float));
     V zero;
     memset(&zero, 0, sizeof(V));
-    for (int cv = threadIdx.x; cv < ldv; cv += blockDim.x) {
+    for (int cv = cv_first; cv < ldv; cv += cv_step) {
       V* rv = rs + cv;
       const V old = evict ? *rv : zero;
       // walk the chain from the tail in segments of MAXC rows: row i_j <- row i_{j-1}.  Inside a segment every load is
@@ -178,12 +184,15 @@ static int launch_holdout(float* Z, int ld, int B, int d, float* ring, int cap, 
                           unsigned int* done, cudaStream_t st) {
   if (ld & 3) return set_error_msg("holdout_swap: ld must be a multiple of 4");
   const bool even = (cap & 1) == 0;
+  const int ldv = ld <= 512 ? ld / 2 : ld / 4;
+  const int spc = ldv < 256 ? 256 / ldv : 1;           // ring slots per CTA (narrow rows)
+  const int grid = (cap + spc - 1) / spc;
   if (ld <= 512) {  // short rows (e.g. 2 KB fp16 staged rows viewed as 512 words): 8 bytes per thread keeps the CTA busy
-    if (even) holdout_swap_kernel<float2, 32, true><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
-    else holdout_swap_kernel<float2, 16, false><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+    if (even) holdout_swap_kernel<float2, 32, true><<<grid, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+    else holdout_swap_kernel<float2, 16, false><<<grid, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
   } else {
-    if (even) holdout_swap_kernel<float4, 16, true><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
-    else holdout_swap_kernel<float4, 16, false><<<cap, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+    if (even) holdout_swap_kernel<float4, 16, true><<<grid, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
+    else holdout_swap_kernel<float4, 16, false><<<grid, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done);
   }
   return check_launch("holdout_swap_kernel");
 }

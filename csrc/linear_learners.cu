@@ -13,6 +13,7 @@
 //
 // Formulas are the literature ones (Crammer et al. 2006; Shalev-Shwartz et al. 2007); the
 // reference tree contains only the learner names (PipelineMap.scala:68).
+#include <atomic>
 #include "ptx.cuh"
 #include "host_common.h"
 #include "omldm_kernels.h"
@@ -99,46 +100,16 @@ linear_exact_kernel(const float* __restrict__ Z, int ld, int B, const omldm_line
 // scratch layout (floats): [0, dw) delta accumulators | dw: active count | dw+1: blocks done (as u32)
 constexpr int MB_WARPS = 8;
 
-__global__ void __launch_bounds__(MB_WARPS * 32)
-linear_minibatch_kernel(const float* __restrict__ Z, int ld, int B, omldm_linear_desc D,
-                        float* __restrict__ scratch, int mean_update) {
-  extern __shared__ float s_delta[];  // dw floats
+// Block epilogue shared by the mini-batch kernels: per-warp statistics and the block's delta go to the global
+// accumulator; the last block applies the averaged (or summed) update and clears the scratch for the next call.
+__device__ __forceinline__ void minibatch_finish(const omldm_linear_desc& D, float* __restrict__ scratch, int B,
+                                                 int mean_update, float svm_eta, float* s_delta, double loss_sum,
+                                                 double aux_sum, int fitted, int active) {
   __shared__ double s_loss[MB_WARPS], s_aux[MB_WARPS];
   __shared__ int s_fit[MB_WARPS], s_act[MB_WARPS];
   __shared__ bool s_last;
   const int dw = D.d + 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int c = threadIdx.x; c < dw; c += blockDim.x) s_delta[c] = 0.f;
-  __syncthreads();
-  double loss_sum = 0.0, aux_sum = 0.0;
-  int fitted = 0, active = 0;
-  const float svm_eta = (D.kind == 2) ? 1.f / (D.lambda * static_cast<float>(D.stats[3] + 1.0)) : 0.f;
-  for (int r = blockIdx.x * MB_WARPS + warp; r < B; r += gridDim.x * MB_WARPS) {
-    const float* zr = Z + static_cast<size_t>(r) * ld;
-    if (zr[D.d] == 0.f) continue;
-    float dot = 0.f, nrm = 0.f;
-    for (int c = lane; c < dw; c += 32) {
-      const float xv = zr[c];
-      dot = fmaf(D.w[c], xv, dot);
-      nrm = fmaf(xv, xv, nrm);
-    }
-    dot = warp_sum(dot);
-    nrm = warp_sum(nrm);
-    const float y = zr[D.d + 1];
-    float loss, aux;
-    float c = linear_coef(D.kind, D.variant, D.C, D.eps, dot, y, nrm, loss, aux);
-    if (D.kind == 2) {
-      const float yy = y > 0.f ? 1.f : -1.f;
-      c = (yy * dot < 1.f) ? svm_eta * yy : 0.f;
-    }
-    if (c != 0.f) {
-      for (int col = lane; col < dw; col += 32) atomicAdd(&s_delta[col], c * zr[col]);
-      active += 1;
-    }
-    loss_sum += loss;
-    aux_sum += aux;
-    fitted += 1;
-  }
   if (lane == 0) { s_loss[warp] = loss_sum; s_aux[warp] = aux_sum; s_fit[warp] = fitted; s_act[warp] = active; }
   __syncthreads();
   for (int c = threadIdx.x; c < dw; c += blockDim.x) {
@@ -185,6 +156,121 @@ linear_minibatch_kernel(const float* __restrict__ Z, int ld, int B, omldm_linear
     __syncthreads();
     if (threadIdx.x == 0) { scratch[dw] = 0.f; scratch[dw + 1] = 0.f; }
   }
+}
+
+__global__ void __launch_bounds__(MB_WARPS * 32)
+linear_minibatch_kernel(const float* __restrict__ Z, int ld, int B, omldm_linear_desc D,
+                        float* __restrict__ scratch, int mean_update) {
+  extern __shared__ float s_delta[];  // dw floats
+  const int dw = D.d + 1;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int c = threadIdx.x; c < dw; c += blockDim.x) s_delta[c] = 0.f;
+  __syncthreads();
+  double loss_sum = 0.0, aux_sum = 0.0;
+  int fitted = 0, active = 0;
+  const float svm_eta = (D.kind == 2) ? 1.f / (D.lambda * static_cast<float>(D.stats[3] + 1.0)) : 0.f;
+  for (int r = blockIdx.x * MB_WARPS + warp; r < B; r += gridDim.x * MB_WARPS) {
+    const float* zr = Z + static_cast<size_t>(r) * ld;
+    if (zr[D.d] == 0.f) continue;
+    float dot = 0.f, nrm = 0.f;
+    for (int c = lane; c < dw; c += 32) {
+      const float xv = zr[c];
+      dot = fmaf(D.w[c], xv, dot);
+      nrm = fmaf(xv, xv, nrm);
+    }
+    dot = warp_sum(dot);
+    nrm = warp_sum(nrm);
+    const float y = zr[D.d + 1];
+    float loss, aux;
+    float c = linear_coef(D.kind, D.variant, D.C, D.eps, dot, y, nrm, loss, aux);
+    if (D.kind == 2) {
+      const float yy = y > 0.f ? 1.f : -1.f;
+      c = (yy * dot < 1.f) ? svm_eta * yy : 0.f;
+    }
+    if (c != 0.f) {
+      for (int col = lane; col < dw; col += 32) atomicAdd(&s_delta[col], c * zr[col]);
+      active += 1;
+    }
+    loss_sum += loss;
+    aux_sum += aux;
+    fitted += 1;
+  }
+  minibatch_finish(D, scratch, B, mean_update, svm_eta, s_delta, loss_sum, aux_sum, fitted, active);
+}
+
+// Thin rows (pitch 32 floats, d <= 30; BASELINE config 1 is d = 28): one LANE per record instead of one warp.  A lane
+// holds its whole 128-byte row in registers (consecutive lanes = consecutive rows, so a warp reads 4 KB contiguous),
+// needs no shuffle for the margin, and accumulates its share of the update in registers; the 32 partial sums are
+// warp-reduced once at the end.  Same arithmetic and the same block epilogue as the general kernel.
+__global__ void __launch_bounds__(MB_WARPS * 32)
+linear_minibatch_thin_kernel(const float* __restrict__ Z, int B, omldm_linear_desc D, float* __restrict__ scratch,
+                             int mean_update) {
+  __shared__ float s_delta[32];
+  __shared__ float s_w[32];
+  const int dw = D.d + 1;
+  if (threadIdx.x < 32) {
+    s_delta[threadIdx.x] = 0.f;
+    s_w[threadIdx.x] = threadIdx.x < dw ? D.w[threadIdx.x] : 0.f;
+  }
+  __syncthreads();
+  double loss_sum = 0.0, aux_sum = 0.0;
+  int fitted = 0, active = 0;
+  const float svm_eta = (D.kind == 2) ? 1.f / (D.lambda * static_cast<float>(D.stats[3] + 1.0)) : 0.f;
+  float acc[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < B; r += gridDim.x * blockDim.x) {
+    const float4* z4 = reinterpret_cast<const float4*>(Z + static_cast<size_t>(r) * 32);
+    float x[32];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 t = ld_nc_v4(z4 + j);
+      x[4 * j] = t.x; x[4 * j + 1] = t.y; x[4 * j + 2] = t.z; x[4 * j + 3] = t.w;
+    }
+    float valid = 0.f, y = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {          // row[d] = valid flag, row[d + 1] = target; columns beyond the bias do not
+      if (j == D.d) valid = x[j];           // take part in the margin
+      if (j == D.d + 1) y = x[j];
+      if (j >= dw) x[j] = 0.f;
+    }
+    if (valid == 0.f) continue;
+    float dot = 0.f, nrm = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      dot = fmaf(s_w[j], x[j], dot);
+      nrm = fmaf(x[j], x[j], nrm);
+    }
+    float loss, aux;
+    float c = linear_coef(D.kind, D.variant, D.C, D.eps, dot, y, nrm, loss, aux);
+    if (D.kind == 2) {
+      const float yy = y > 0.f ? 1.f : -1.f;
+      c = (yy * dot < 1.f) ? svm_eta * yy : 0.f;
+    }
+    if (c != 0.f) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc[j] = fmaf(c, x[j], acc[j]);
+      active += 1;
+    }
+    loss_sum += loss;
+    aux_sum += aux;
+    fitted += 1;
+  }
+  // per-warp totals (the epilogue expects them in lane 0) and the warp's share of the update
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    loss_sum += __shfl_xor_sync(0xffffffffu, loss_sum, o);
+    aux_sum += __shfl_xor_sync(0xffffffffu, aux_sum, o);
+    fitted += __shfl_xor_sync(0xffffffffu, fitted, o);
+    active += __shfl_xor_sync(0xffffffffu, active, o);
+  }
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float t = warp_sum(acc[j]);
+    if (lane == 0 && j < dw && t != 0.f) atomicAdd(&s_delta[j], t);
+  }
+  minibatch_finish(D, scratch, B, mean_update, svm_eta, s_delta, loss_sum, aux_sum, fitted, active);
 }
 
 // Predictions f = w . [x, 1] for a batch (forecast path, FlinkSpoke.scala:105).
@@ -237,6 +323,12 @@ extern "C" int omldm_linear_minibatch(const float* Z, int ld, int B, const omldm
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, dw * 4);
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(linear_minibatch)", e);
   }
+  if (ld == 32 && dw + 1 <= 32 && (reinterpret_cast<uintptr_t>(Z) & 15) == 0) {      // thin rows: one lane per record
+    int tb = (B + MB_WARPS * 32 - 1) / (MB_WARPS * 32);
+    if (tb > 148 * 2) tb = 148 * 2;
+    linear_minibatch_thin_kernel<<<tb, MB_WARPS * 32, 0, st>>>(Z, B, *desc_host, scratch, mean_update);
+    return check_launch("linear_minibatch_thin_kernel");
+  }
   linear_minibatch_kernel<<<blocks, MB_WARPS * 32, dw * 4, st>>>(Z, ld, B, *desc_host, scratch, mean_update);
   return check_launch("linear_minibatch_kernel");
 }
@@ -265,8 +357,10 @@ namespace {
 constexpr int kMaxDevices = 64;
 // Device address of g_static_scratch per device.  In host code the symbol name is only a
 // stand-in, not an address a kernel can use, so it is resolved once per device with
-// cudaGetSymbolAddress (with that device current) and cached.
-float* g_static_scratch_ptr[kMaxDevices] = {};
+// cudaGetSymbolAddress (with that device current) and cached.  Host threads may make their first call on a
+// device at the same time: the slots are atomics (release store / acquire load), and two threads that both find
+// a slot empty resolve the same address.
+std::atomic<float*> g_static_scratch_ptr[kMaxDevices];
 }  // namespace
 
 extern "C" int omldm_linear_minibatch_static(const float* Z, int ld, int B, const omldm_linear_desc* desc_host,
@@ -280,14 +374,13 @@ extern "C" int omldm_linear_minibatch_static(const float* Z, int ld, int B, cons
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return set_error("cudaGetDevice", e);
   if (dev < 0 || dev >= kMaxDevices) return set_error_msg("linear_minibatch_static: device ordinal out of range");
-  if (g_static_scratch_ptr[dev] == nullptr) {
+  float* scratch = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {
     // one-time set-up for this device (the current one): resolve the symbol's device address
-    float* p = nullptr;
-    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch);
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_static_scratch);
     if (e != cudaSuccess) return set_error("cudaGetSymbolAddress(g_static_scratch)", e);
-    g_static_scratch_ptr[dev] = p;
+    g_static_scratch_ptr[dev].store(scratch, std::memory_order_release);
   }
-  float* scratch = g_static_scratch_ptr[dev];
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // The array is shared by every call and keeps whatever the last call left behind; the
   // accumulators, the active count and the block counter must start at zero.

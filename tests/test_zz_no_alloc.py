@@ -4,8 +4,8 @@
 (an ingest loop that cannot afford cudaMalloc's device-wide synchronisation, or a host process
 whose HBM was fully handed out at start-up).  It keeps its accumulator in a fixed array inside
 the library, so the checks here are: same result as `omldm_linear_minibatch` with caller-owned
-scratch, twice in a row (the shared array must be clean for the second call), and a clear
-refusal beyond the documented size limit.
+scratch and as a plain PyTorch fp32 restatement of the update, twice in a row (the shared array
+must be clean for the second call), and a clear refusal beyond the documented size limit.
 
 Collected last on purpose (file name): if it fails under `-x`, every other test has already run.
 """
@@ -49,8 +49,13 @@ def test_static_scratch_matches_regular_entry_point(kind, d, B):
     st_ref = torch.zeros(4, dtype=torch.float64, device="cuda")
     st_new = torch.zeros(4, dtype=torch.float64, device="cuda")
     scratch = torch.zeros(d + 3, device="cuda")          # the regular entry point wants caller scratch
+    from omldm_b200.ops import functional as F
+    w_pt = torch.zeros(d + 1)                            # the same update in plain PyTorch (fp32, CPU)
+    st_pt = torch.zeros(4, dtype=torch.float64)
     for call in range(2):                                # two calls in a row share the built-in array
         Z, ld = _batch(d, B, seed=100 + call)
+        with F.use_impl("torch"):
+            F.linear_minibatch(Z.cpu(), d, w_pt, st_pt, torch.zeros(d + 3), kind, 1, 0.5, 0.05, 0.01, True)
         ref = Desc(w_ref.data_ptr(), st_ref.data_ptr(), d, kind, 1, 0.5, 0.05, 0.01)
         new = Desc(w_new.data_ptr(), st_new.data_ptr(), d, kind, 1, 0.5, 0.05, 0.01)
         rc = lib.omldm_linear_minibatch(ctypes.c_void_p(Z.data_ptr()), ld, B, ctypes.byref(ref),
@@ -61,6 +66,8 @@ def test_static_scratch_matches_regular_entry_point(kind, d, B):
         torch.cuda.synchronize()
         assert torch.allclose(w_new, w_ref, rtol=1e-3, atol=1e-5), f"weights differ after call {call}"
         assert torch.allclose(st_new, st_ref, rtol=1e-4), f"statistics differ after call {call}"
+        assert torch.allclose(w_new.cpu(), w_pt, rtol=1e-3, atol=1e-5), f"differs from the PyTorch reference after call {call}"
+        assert torch.allclose(st_new.cpu()[:3], st_pt[:3], rtol=1e-4), f"statistics differ from PyTorch after call {call}"
     assert float(w_ref.abs().sum()) > 0                  # the update actually happened
 
 
