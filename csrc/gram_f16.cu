@@ -34,14 +34,19 @@
 
 namespace omldm {
 
-constexpr int G_BK = 64;                          // records per stage
-constexpr int G_STAGES = 6;
+#ifndef OMLDM_GRAM_BK
+#define OMLDM_GRAM_BK 64
+#endif
+#ifndef OMLDM_GRAM_STAGES
+#define OMLDM_GRAM_STAGES 6
+#endif
+constexpr int G_BK = OMLDM_GRAM_BK;               // records per stage
+constexpr int G_STAGES = OMLDM_GRAM_STAGES;
 constexpr int G_THREADS = 192;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2..5 epilogue
 constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 64 halves x 64 records = 16 KB
 constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int G_TMEM_COLS = 256;
-constexpr int G_ZERO_SLOT = 32;                   // epilogue slots 0..31 (4 KB each), slot 32 = zeros for the reset
 enum { GS_TILE0 = 8 };                            // scratch words: per half-tile arrival counters from word 8 on
 
 struct GramPush {

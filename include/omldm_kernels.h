@@ -130,6 +130,11 @@ int omldm_holdout_swap(float* Z, int ld, int B, int d, float* ring, int cap, lon
  * by B by the last CTA to finish; count_dev[1] = arrival counter of the kernel (zero before the first call) */
 int omldm_holdout_swap_dev(float* Z, int ld, int B, int d, float* ring, int cap,
                            long long* count_dev, void* stream);
+/* same contract, for consumers that only SUM over the batch (every mini-batch learner): one exchange per ring slot
+ * (ring <- last holdout of the slot's chain, that row <- evicted occupant) instead of the shift along the chain: the
+ * same records are trained on and the same records stay in the ring, at a fraction of the rows moved */
+int omldm_holdout_exchange_dev(float* Z, int ld, int B, int d, float* ring, int cap,
+                               long long* count_dev, void* stream);
 int omldm_advance_count(long long* count_dev, long long delta, void* stream);
 /* learning curve sample (operators/hub/FlinkHub.scala:101-113): ring[2 * (*counter % cap)] = (stats[0], stats[2]), ++*counter */
 int omldm_curve_sample(const double* stats, double* ring, int cap, long long* counter, void* stream);

@@ -358,7 +358,10 @@ class Engine:
             if F.native(Z):                     # (true for CUDA batches; also under the CPU kernel emulation)
                 if self._count_dev is None:
                     self._count_dev = torch.tensor([self.count, 0], dtype=torch.int64, device=self.device)
-                F.holdout_swap_dev(Zv, ring, d, self._count_dev)   # 2-in-10 holdout, evict-then-train
+                # 2-in-10 holdout, evict-then-train; per-record learners need the sequential positions, mini-batch
+                # learners only the set (one exchange per ring slot)
+                ordered = any(getattr(p.learner, "mode", "") == "exact" for p in self.pipelines.values())
+                F.holdout_swap_dev(Zv, ring, d, self._count_dev, ordered=ordered)
             else:
                 F.holdout_swap(Zv, ring, d, self.count)
         Z32 = None

@@ -39,6 +39,8 @@ def kernels() -> ctypes.CDLL:
     global _kernels
     if _kernels is None:
         path = _LIBDIR / "libomldm_kernels.so"
+        if os.environ.get("OMLDM_KERNELS_LIB"):          # kernel-tuning experiments: an alternative build of the library
+            path = Path(os.environ["OMLDM_KERNELS_LIB"])
         if not path.exists():
             _try_build()
         if not path.exists():

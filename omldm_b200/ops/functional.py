@@ -131,13 +131,14 @@ def holdout_swap(Z: torch.Tensor, ring: torch.Tensor, d: int, count0: int) -> No
 _HOLDOUT_IDX: dict = {}
 
 
-def holdout_swap_dev(Z: torch.Tensor, ring: torch.Tensor, d: int, count_dev: torch.Tensor) -> None:
+def holdout_swap_dev(Z: torch.Tensor, ring: torch.Tensor, d: int, count_dev: torch.Tensor, ordered: bool = True) -> None:
     """Graph-replayable holdout: `count_dev` = int64[2] on the device, [0] the running record count (advanced by the
-    kernel itself), [1] the kernel's arrival counter."""
+    kernel itself), [1] the kernel's arrival counter.  `ordered=False`: one exchange per ring slot instead of the shift
+    along the chain - same trained set, same ring, for learners that only sum over the batch."""
     B, ld = Z.shape
     cap = ring.shape[0]
-    _lib.check(_k().omldm_holdout_swap_dev(_p(Z), _i(ld), _i(B), _i(d), _p(ring), _i(cap), _p(count_dev),
-                                           _lib.stream_ptr()), "holdout_swap_dev")
+    fn = _k().omldm_holdout_swap_dev if ordered else _k().omldm_holdout_exchange_dev
+    _lib.check(fn(_p(Z), _i(ld), _i(B), _i(d), _p(ring), _i(cap), _p(count_dev), _lib.stream_ptr()), "holdout_swap_dev")
 
 
 def curve_sample(stats: torch.Tensor, ring: torch.Tensor, counter: torch.Tensor) -> None:

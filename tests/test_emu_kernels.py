@@ -55,6 +55,32 @@ def test_holdout_swap(B, count0, cap):
     assert torch.equal(Zr, Zn) and torch.equal(rr, rn)
 
 
+@pytest.mark.parametrize("B,count0,cap,ld", [(100, 0, 16, 32), (300, 12345, 16, 32), (37, 8, 4, 64), (700, 777, 8, 512),
+                                             (2000, 4321, 16, 1024), (50, 3, 256, 32)])
+def test_holdout_exchange_keeps_the_trained_set_and_the_ring(B, count0, cap, ld):
+    """The exchange form of the holdout (one swap per ring slot, for learners that only sum over the batch) against the
+    ordered shift: the ring ends up identical, the batch holds the same MULTISET of rows, the device-resident record
+    count advances by B - for narrow rows (several slots per CTA), 2 KB rows (8-byte lanes) and wide rows."""
+    g = torch.Generator().manual_seed(B + cap)
+    Z0 = torch.randn(B, ld, generator=g)
+    ring0 = torch.randn(cap, ld, generator=g)
+    out = []
+    with F.use_impl("emu"):
+        for ordered in (True, False):
+            Z, ring = Z0.clone(), ring0.clone()
+            cnt = torch.tensor([count0, 0], dtype=torch.int64)
+            F.holdout_swap_dev(Z, ring, ld - 2, cnt, ordered=ordered)
+            assert int(cnt[0]) == count0 + B and int(cnt[1]) == 0
+            out.append((Z, ring))
+    (Zo, ro), (Zx, rx) = out
+    Zref, rref = Z0.clone(), ring0.clone()
+    F.holdout_swap(Zref, rref, ld - 2, count0)                      # PyTorch restatement of the sequential rule
+    assert torch.equal(Zo, Zref) and torch.equal(ro, rref)
+    assert torch.equal(rx, ro)
+    key = lambda t: sorted(map(tuple, t.tolist()))
+    assert key(Zx) == key(Zo)
+
+
 @pytest.mark.parametrize("kind,variant", [(F.KIND_PA, 1), (F.KIND_PA_REG, 1), (F.KIND_SVM, 0)])
 @pytest.mark.parametrize("d", [28, 70])
 def test_linear_exact(kind, variant, d):
