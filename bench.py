@@ -223,7 +223,11 @@ def main() -> None:
             F.set_impl("auto")
         params = JobParameters(parallelism=world, jobName="bench_" + args.config)
         params.extra["sparseDirect"] = "true" if sparse_direct else "false"
-        eng = Engine(params, rank, world, dev, impl=impl)
+        if impl == "nccl":      # the in-repo baseline: torch.distributed collectives + stock PyTorch ops
+            from omldm_b200 import baseline
+            eng = baseline.make_engine(params, rank, world, dev)
+        else:
+            eng = Engine(params, rank, world, dev, impl=impl)
         eng.handle_request({"id": 1, "request": "Create",
                             "learner": {"name": cfg["model"], "hyperParameters": cfg["hyper"]},
                             "preProcessors": cfg["pre"], "trainingConfiguration": tc})
@@ -249,10 +253,13 @@ def main() -> None:
         sampler = ClockSampler(local) if (sample_clocks and rank == 0 and not dry) else None
         mk = (lambda: _WallEvent()) if dry else (lambda: torch.cuda.Event(enable_timing=True))
         windows, launches, it = [], 0, args.warmup
+        prof_window = (not dry) and impl != "nccl" and os.environ.get("OMLDM_PROFILE_WINDOW") == "1"
         total_ms, max_windows = 0.0, 4000
         while True:
             sync_all()
             _lib.reset_launch_count()
+            if prof_window:      # `ncu --profile-from-start off`: capture exactly this window (never a bench value)
+                torch.cuda.cudart().cudaProfilerStart()
             e0, e1 = mk(), mk()
             e0.record()
             for i in range(args.steps):
@@ -260,6 +267,8 @@ def main() -> None:
             eng.flush()          # inside the timed region: the protocol's end-of-stream settlement is part of the work
             e1.record()
             dev_sync()
+            if prof_window:
+                torch.cuda.cudart().cudaProfilerStop()
             it += args.steps
             launches = _lib.launch_count()
             ms = torch.tensor([e0.elapsed_time(e1)], device=dev)

@@ -22,6 +22,8 @@ import math
 from dataclasses import dataclass, field
 from typing import Any, Dict, List, Optional
 
+from .compat import CountableSerial
+
 REQUEST_TYPES = ("Create", "Update", "Query", "Delete")
 LEARNERS = ("PA", "RegressorPA", "ORR", "SVM", "MultiClassPA", "K-means", "NN", "HT")
 PREPROCESSORS = ("PolynomialFeatures", "StandardScaler", "MinMaxScaler")
@@ -63,7 +65,7 @@ def _sizeof(o: Any) -> int:
         return sum(_sizeof(v) for v in o)
     if hasattr(o, "nbytes"):
         return int(o.nbytes)
-    if hasattr(o, "get_size"):
+    if isinstance(o, CountableSerial):      # anything with get_size(): POJOs, messages, parameter containers
         return int(o.get_size())
     return 8
 

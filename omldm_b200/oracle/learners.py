@@ -17,6 +17,8 @@ from typing import Any, Dict, List, Optional
 
 import numpy as np
 
+from ..api.compat import VectorBias
+
 
 def _h(hyper: Optional[dict], keys, default):
     """Hyper-parameter lookup accepting several spellings ('accept common spellings')."""
@@ -160,12 +162,12 @@ class PAClassifier(OracleLearner):
         self.w = np.array(v, dtype=np.float64)
 
     def to_parameters(self):
-        return {"a": self.w[:-1].tolist(), "b": float(self.w[-1])}
+        return VectorBias.from_flat(self.w).to_parameters()
 
     def from_parameters(self, p):
-        a = np.atleast_1d(np.asarray(p["a"], dtype=np.float64))
-        self.d = len(a)
-        self.w = np.concatenate([a, [float(p.get("b", 0.0))]])
+        vb = VectorBias.from_parameters(p)       # (weights, bias) <-> the flat [w | b] layout
+        self.d = len(vb.weights)
+        self.w = vb.flat()
 
 
 class PARegressor(PAClassifier):

@@ -20,7 +20,7 @@ import torch
 
 from ..ops import _lib
 from .comm import PipelineComm
-from .host_protocols import cfg
+from .host_protocols import cfg, cfg_float, cfg_int
 
 _i, _f, _u = ctypes.c_int, ctypes.c_float, ctypes.c_uint32
 _sz = ctypes.c_size_t
@@ -60,8 +60,8 @@ class SyncDriver:
         # (tools/cuda_emu), which is how these driver classes are tested without GPUs
         self.impl = impl if (comm.device.type == "cuda" or (_lib._emulated and comm.emulate > 1)) else "nccl"
         self.group = group
-        self.sync_every = int(cfg(tc, ["syncEvery", "syncPeriod"], 1))
-        self.blocks = int(cfg(tc, ["syncBlocks"], 0))
+        self.sync_every = cfg_int(tc, ["syncEvery", "syncPeriod"], 1)
+        self.blocks = cfg_int(tc, ["syncBlocks"], 0)
         self.counters = ProtocolCounters(self.protocol, max_msg_params)
         self._batches = 0
         self.synced_last_step = False
@@ -343,14 +343,14 @@ def wants_sharded_hub(protocol: str, merge_mode: str, tc, world: int, impl: str,
     """`syncFusion: "hub"` (the default for additive learners that support it): Synchronous on more than one GPU."""
     return (protocol == "Synchronous" and merge_mode == "sum" and world > 1 and impl == "fused" and device_type == "cuda"
             and hub_mode(tc) == "hub"
-            and int(cfg(tc, ["syncEvery", "syncPeriod"], 1)) == 1)
+            and cfg_int(tc, ["syncEvery", "syncPeriod"], 1) == 1)
 
 
 def wants_scatter(protocol: str, merge_mode: str, tc, world: int, impl: str) -> bool:
     """`syncFusion: "scatter"` / `"gemm"` apply to Synchronous pipelines of additive learners on more than one GPU."""
     return (protocol == "Synchronous" and merge_mode == "sum" and world > 1
             and str(cfg(tc, ["syncFusion"], "none")).lower() in ("scatter", "gemm")
-            and int(cfg(tc, ["syncEvery", "syncPeriod"], 1)) == 1)
+            and cfg_int(tc, ["syncEvery", "syncPeriod"], 1) == 1)
 
 
 class AsynchronousDriver(SyncDriver):
@@ -406,7 +406,7 @@ class SSPDriver(AsynchronousDriver):
 
     def __init__(self, *a, **kw):
         super().__init__(*a, **kw)
-        self.staleness = int(cfg(self.tc, ["staleness", "s", "stalenessBound"], 3))
+        self.staleness = cfg_int(self.tc, ["staleness", "s", "stalenessBound"], 3)
 
     def step(self) -> bool:
         if self.impl == "fused":
@@ -421,8 +421,8 @@ class EASGDDriver(SyncDriver):
 
     def __init__(self, *a, **kw):
         super().__init__(*a, **kw)
-        self.alpha = float(cfg(self.tc, ["alpha", "elasticity", "rho"], 0.1))
-        self.sync_every = int(cfg(self.tc, ["tau", "commPeriod", "syncEvery"], 1))
+        self.alpha = cfg_float(self.tc, ["alpha", "elasticity", "rho"], 0.1)
+        self.sync_every = cfg_int(self.tc, ["tau", "commPeriod", "syncEvery"], 1)
         if self.mode == 1:
             raise ValueError("EASGD needs an averaged model (merge mode 'mean')")
         for h in self.comm.hubs:
@@ -453,7 +453,7 @@ class GMDriver(SyncDriver):
 
     def __init__(self, *a, **kw):
         super().__init__(*a, **kw)
-        self.threshold = float(cfg(self.tc, ["threshold", "T", "gmThreshold"], 0.5))
+        self.threshold = cfg_float(self.tc, ["threshold", "T", "gmThreshold"], 0.5)
         self.rounds = 0
         if self.e is None:
             raise ValueError("GM needs the estimate vector e")
@@ -483,8 +483,8 @@ class FGMDriver(SyncDriver):
 
     def __init__(self, *a, **kw):
         super().__init__(*a, **kw)
-        self.threshold = float(cfg(self.tc, ["threshold", "T", "fgmThreshold"], 0.5))
-        self.eps_psi = float(cfg(self.tc, ["epsPsi", "eps_psi"], 0.01))
+        self.threshold = cfg_float(self.tc, ["threshold", "T", "fgmThreshold"], 0.5)
+        self.eps_psi = cfg_float(self.tc, ["epsPsi", "eps_psi"], 0.01)
         if self.e is None:
             raise ValueError("FGM needs the estimate vector e")
         n_state = 8 * max(self.comm.emulate, 1)
@@ -492,7 +492,7 @@ class FGMDriver(SyncDriver):
         self.state[1::8] = -1.0   # force re-anchoring on the first step
         self.rounds = 0
         self.flush_mode = str(cfg(self.tc, ["fgmFlush"], "drain")).lower()
-        self.flush_timeout_s = float(cfg(self.tc, ["fgmFlushTimeout"], 5.0))
+        self.flush_timeout_s = cfg_float(self.tc, ["fgmFlushTimeout"], 5.0)
         self.flush_timeouts = 0
         self._drain_gen = 0
         if self.impl == "fused":
@@ -589,7 +589,7 @@ def make_driver(protocol: str, comm: PipelineComm, e, merge_mode: str, tc, impl:
         cls = LocalDriver
     overlap = str(cfg(tc, ["overlapSync"], "false")).lower() in ("1", "true", "yes")   # opt-in: measured slower at 2 GPUs
     if (cls is SynchronousDriver and merge_mode == "sum" and overlap and impl == "fused" and comm.k > 1
-            and comm.device.type == "cuda" and comm.emulate <= 1 and int(cfg(tc, ["syncEvery", "syncPeriod"], 1)) == 1
+            and comm.device.type == "cuda" and comm.emulate <= 1 and cfg_int(tc, ["syncEvery", "syncPeriod"], 1) == 1
             and pipelined_ok):
         cls = PipelinedSynchronousDriver
     if cls is EASGDDriver and merge_mode == "sum":

@@ -23,6 +23,7 @@ from typing import Any, Dict, List, Optional, Tuple
 
 import numpy as np
 
+from ..api.compat import double_parsing, integer_parsing
 from ..api.pojos import Prediction, Request
 from ..messages import NodeId, NodeType, RemoteCallIdentifier
 from ..oracle.pipeline import OraclePipeline
@@ -36,6 +37,15 @@ def cfg(tc: Optional[dict], keys, default):
             if k in tc and tc[k] is not None:
                 return tc[k]
     return default
+
+
+def cfg_int(tc: Optional[dict], keys, default: int) -> int:
+    """Typed lookup with the reference's `Parsing.IntegerParsing` rule: absent or malformed -> the default."""
+    return integer_parsing({"v": cfg(tc, keys, None)}, "v", default)
+
+
+def cfg_float(tc: Optional[dict], keys, default: float) -> float:
+    return double_parsing({"v": cfg(tc, keys, None)}, "v", default)
 
 
 def shard_bounds(n: int, H: int) -> List[Tuple[int, int]]:
@@ -78,8 +88,8 @@ class WorkerNode:
         self.request = request
         self.pipeline = OraclePipeline(request)
         tc = request.trainingConfiguration
-        self.mini_batch = int(cfg(tc, ["miniBatchSize", "mini_batch_size", "batchSize"], 64))
-        self.H = int(cfg(tc, ["HubParallelism", "hubParallelism"], 1))
+        self.mini_batch = cfg_int(tc, ["miniBatchSize", "mini_batch_size", "batchSize"], 64)
+        self.H = cfg_int(tc, ["HubParallelism", "hubParallelism"], 1)
         self.tc = tc or {}
         return self
 
@@ -235,7 +245,7 @@ class SSPWorker(AsynchronousWorker):
     def configure_worker(self, request):
         super().configure_worker(request)
         self.clock = 0
-        self.staleness = int(cfg(self.tc, ["staleness", "s", "stalenessBound"], 3))
+        self.staleness = cfg_int(self.tc, ["staleness", "s", "stalenessBound"], 3)
         return self
 
     def _extra(self):
@@ -248,8 +258,8 @@ class EASGDWorker(WorkerNode):
 
     def configure_worker(self, request):
         super().configure_worker(request)
-        self.alpha = float(cfg(self.tc, ["alpha", "elasticity", "rho"], 0.1))
-        self.tau = int(cfg(self.tc, ["tau", "commPeriod"], 1))
+        self.alpha = cfg_float(self.tc, ["alpha", "elasticity", "rho"], 0.1)
+        self.tau = cfg_int(self.tc, ["tau", "commPeriod"], 1)
         self._mb = 0
         return self
 
@@ -280,7 +290,7 @@ class GMWorker(WorkerNode):
 
     def configure_worker(self, request):
         super().configure_worker(request)
-        self.threshold = float(cfg(self.tc, ["threshold", "T", "gmThreshold"], 0.5))
+        self.threshold = cfg_float(self.tc, ["threshold", "T", "gmThreshold"], 0.5)
         return self
 
     def on_mini_batch(self):
@@ -313,7 +323,7 @@ class FGMWorker(WorkerNode):
 
     def configure_worker(self, request):
         super().configure_worker(request)
-        self.threshold = float(cfg(self.tc, ["threshold", "T", "fgmThreshold"], 0.5))
+        self.threshold = cfg_float(self.tc, ["threshold", "T", "fgmThreshold"], 0.5)
         self.theta = math.sqrt(self.threshold) / 2.0
         self.zeta = -math.sqrt(self.threshold)
         self.sent = 0
@@ -379,8 +389,8 @@ class ParameterServerNode:
     def configure_parameter_server(self, request: Request) -> "ParameterServerNode":
         self.request = request
         self.tc = request.trainingConfiguration or {}
-        self.mini_batch = int(cfg(self.tc, ["miniBatchSize", "mini_batch_size", "batchSize"], 64))
-        self.max_msg_params = int(cfg(self.tc, ["maxMsgParams"], 2000))
+        self.mini_batch = cfg_int(self.tc, ["miniBatchSize", "mini_batch_size", "batchSize"], 64)
+        self.max_msg_params = cfg_int(self.tc, ["maxMsgParams"], 2000)
         self.stats = ProtocolStatistics(self.protocol)
         return self
 
@@ -505,7 +515,7 @@ class SSPParameterServer(AsynchronousParameterServer):
 
     def configure_parameter_server(self, request):
         super().configure_parameter_server(request)
-        self.staleness = int(cfg(self.tc, ["staleness", "s", "stalenessBound"], 3))
+        self.staleness = cfg_int(self.tc, ["staleness", "s", "stalenessBound"], 3)
         self.clocks: Dict[int, int] = {}
         self.deferred: List[Tuple[NodeId, int, int]] = []
         return self
@@ -537,7 +547,7 @@ class EASGDParameterServer(ParameterServerNode):
 
     def configure_parameter_server(self, request):
         super().configure_parameter_server(request)
-        self.alpha = float(cfg(self.tc, ["alpha", "elasticity", "rho"], 0.1))
+        self.alpha = cfg_float(self.tc, ["alpha", "elasticity", "rho"], 0.1)
         return self
 
     def rpc_elastic(self, source, data):
@@ -599,8 +609,8 @@ class FGMParameterServer(GMParameterServer):
 
     def configure_parameter_server(self, request):
         super().configure_parameter_server(request)
-        self.threshold = float(cfg(self.tc, ["threshold", "T", "fgmThreshold"], 0.5))
-        self.eps_psi = float(cfg(self.tc, ["epsPsi", "eps_psi"], 0.01))
+        self.threshold = cfg_float(self.tc, ["threshold", "T", "fgmThreshold"], 0.5)
+        self.eps_psi = cfg_float(self.tc, ["epsPsi", "eps_psi"], 0.01)
         self.counter = 0
         self.polling = False
         self._phis: Dict[int, float] = {}

@@ -140,6 +140,10 @@ def test_compat_api_surface():
     req = Request.from_dict({"id": 1, "request": "Create", "learner": {"name": "PA"}})
     assert isinstance(req, CountableSerial) and isinstance(vb, CountableSerial)
     assert isinstance(DataSet(4), Mergeable)
+    # the protocols read their configuration through the same rule: a malformed value falls back to the default
+    from omldm_b200.parallel.host_protocols import cfg_float, cfg_int
+    assert cfg_int({"staleness": "4"}, ["staleness", "s"], 3) == 4 and cfg_int({"s": "many"}, ["staleness", "s"], 3) == 3
+    assert cfg_float({"threshold": None, "T": "0.25"}, ["threshold", "T"], 0.5) == 0.25 and cfg_float(None, ["T"], 0.5) == 0.5
 
 
 def test_math_vector_and_point_types():
