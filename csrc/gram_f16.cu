@@ -47,7 +47,14 @@ constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 6
 constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int G_TMEM_COLS = 256;
-enum { GS_TILE0 = 8 };                            // scratch words: per half-tile arrival counters from word 8 on
+enum { GS_TILE0 = 8 };
+#ifdef OMLDM_GRAM_TIMING        // tuning builds only (scripts/build_variant.sh): per-CTA phase stamps in SM cycles, read back by
+                                // tests/test_gram_f16_gpu.py::test_gram_f16_speed_report
+__device__ long long g_gram_stamp[160 * 8];
+#define GRAM_STAMP(i) do { if ((threadIdx.x & 31) == 0) g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 8 + (i)] = clock64(); } while (0)
+#else
+#define GRAM_STAMP(i) do { } while (0)
+#endif                            // scratch words: per half-tile arrival counters from word 8 on
 
 struct GramPush {
   CUtensorMap owner[16];     // this worker's slot matrix at every owner (peer mapped), 32 x 32 fp32 boxes
@@ -88,6 +95,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
   uint32_t* s_flag = tmem_slot + 1;
 
   const int warp = threadIdx.x >> 5;
+  if (warp == 0) GRAM_STAMP(0);
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmZ);
     tma_prefetch_desc(&tmC);
@@ -104,6 +112,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
   cluster_sync_all();                 // barrier inits of both CTAs are visible before any remote arrival
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (warp == 0) GRAM_STAMP(1);
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
@@ -130,6 +139,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       uint32_t phase = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
+        if (kb == 0) GRAM_STAMP(2);
         tc_fence_after();
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * G_STAGE_BYTES);
@@ -155,6 +165,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     const uint32_t r = lane_id();
     const int row0 = m0 + q * 32;
     mbar_wait(accum_bar, 0);
+    if (warp == 2) GRAM_STAMP(3);
     tc_fence_after();
 #pragma unroll 1
     for (int c = 0; c < 8; ++c) {
@@ -175,8 +186,10 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
         tma_commit_group();
       }
     }
+    if (warp == 2) GRAM_STAMP(4);
     if (r == 0) tma_wait_group0();
     __syncwarp();
+    if (warp == 2) GRAM_STAMP(5);
 
     if (push.enabled) {
       // -------------------------------------------------------- hub push by the last CTA of this half tile
@@ -226,6 +239,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_pair<G_TMEM_COLS>(tmem_base);
+    GRAM_STAMP(6);
   }
 }
 
@@ -252,6 +266,12 @@ static int encode_g(CUtensorMap* tm, float* C, int rows, int cols, int ldc) {
 using namespace omldm;
 
 extern "C" size_t omldm_gram_f16_scratch_words(void) { return 512; }
+
+#ifdef OMLDM_GRAM_TIMING
+extern "C" int omldm_gram_f16_stamps(long long* out_host) {
+  return cudaMemcpyFromSymbol(out_host, g_gram_stamp, sizeof(long long) * 160 * 8) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 // The batch-axis split omldm_gram_f16 uses for (K, n, ksplit): records per split (0 if K <= 0).
 extern "C" int omldm_gram_f16_rows_per_split(int K, int n, int ksplit) {

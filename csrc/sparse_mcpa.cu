@@ -8,7 +8,9 @@
 //   conventions hold):  [ index bits x nnz | value x nnz | valid (1.0, 0 = empty row) | target | 0-pad ]
 //
 //   coef   : one warp per record - scores s_c = sum_j W[c, idx_j] v_j + W[c, d] (bias), rival class, hinge
-//            loss, PA step size tau (same rule and statistics as cluster.cu::mcpa_coef_kernel)
+//            loss, PA step size tau (same rule and statistics as cluster.cu::mcpa_coef_kernel).  With up to 16
+//            classes the scores are gathered from a class-minor copy Wt[col][16] made by a small transpose kernel
+//            in front: one non-zero then costs two 32-byte sectors of L2 traffic instead of one per class
 //   update : one warp per record - W[y, idx_j] += s tau v_j, W[rival, idx_j] -= s tau v_j (+ bias column),
 //            s = 1 / (#active records) for the averaged mini-batch update; red.global.add
 //
@@ -42,7 +44,21 @@ __global__ void sparse_rows_kernel(const int* __restrict__ idx, const float* __r
   }
 }
 
-// coef[r] = (tau, y, rival, 0)
+// Wt[col][16] <- W[c][col], col in [0, d] (bias column included), classes beyond C zero
+__global__ void __launch_bounds__(256)
+mcpa_transpose_kernel(const float* __restrict__ W, int ldw, int d, int C, float* __restrict__ Wt) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col > d) return;
+  float v[16];
+#pragma unroll
+  for (int c = 0; c < 16; ++c) v[c] = c < C ? W[static_cast<size_t>(c) * ldw + col] : 0.f;
+  float4* out = reinterpret_cast<float4*>(Wt + static_cast<size_t>(col) * 16);
+#pragma unroll
+  for (int g = 0; g < 4; ++g) out[g] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+}
+
+// coef[r] = (tau, y, rival, 0).  WT: scores from the class-minor copy (C <= 16), else from W[c][col]
+template <bool WT>
 __global__ void __launch_bounds__(256)
 mcpa_sparse_coef_kernel(const float* __restrict__ rows, int ld, int B, int nnz, const float* __restrict__ W, int ldw,
                         int d, int C, int variant, float Creg, float4* __restrict__ coef, double* __restrict__ stats) {
@@ -66,15 +82,28 @@ mcpa_sparse_coef_kernel(const float* __restrict__ rows, int ld, int B, int nnz, 
         const float v = row[nnz + j];
         if (col >= 0 && col < d) {
           n2 = fmaf(v, v, n2);
+          if (WT) {
+            const float4* wt = reinterpret_cast<const float4*>(W + static_cast<size_t>(col) * 16);
 #pragma unroll
-          for (int c = 0; c < SP_MAXC; ++c)
-            if (c < C) acc[c] = fmaf(W[static_cast<size_t>(c) * ldw + col], v, acc[c]);
+            for (int g = 0; g < 4; ++g)
+              if (4 * g < C) {
+                const float4 w4 = wt[g];
+                acc[4 * g] = fmaf(w4.x, v, acc[4 * g]);
+                acc[4 * g + 1] = fmaf(w4.y, v, acc[4 * g + 1]);
+                acc[4 * g + 2] = fmaf(w4.z, v, acc[4 * g + 2]);
+                acc[4 * g + 3] = fmaf(w4.w, v, acc[4 * g + 3]);
+              }
+          } else {
+#pragma unroll
+            for (int c = 0; c < SP_MAXC; ++c)
+              if (c < C) acc[c] = fmaf(W[static_cast<size_t>(c) * ldw + col], v, acc[c]);
+          }
         }
       }
       n2 = warp_sum(n2) + 1.f;              // the bias feature contributes 1
 #pragma unroll
       for (int c = 0; c < SP_MAXC; ++c)
-        if (c < C) acc[c] = warp_sum(acc[c]) + W[static_cast<size_t>(c) * ldw + d];
+        if (c < C) acc[c] = warp_sum(acc[c]) + (WT ? W[static_cast<size_t>(d) * 16 + c] : W[static_cast<size_t>(c) * ldw + d]);
       y = static_cast<int>(row[2 * nnz + 1] + 0.5f);
       float best = -CUDART_INF_F;
 #pragma unroll
@@ -156,9 +185,18 @@ extern "C" int omldm_sparse_rows(const int* idx, const float* val, const float* 
   return check_launch("sparse_rows_kernel");
 }
 
+extern "C" size_t omldm_mcpa_sparse_wt_floats(int d) { return static_cast<size_t>(d + 1) * 16; }
+
 extern "C" int omldm_mcpa_sparse_step(const float* rows, int ld, int B, int nnz, float* W, int ldw, int d, int C,
                                       int variant, float Creg, float* coef, double* stats,
                                       const double* active_before, int mean_update, void* stream) {
+  return omldm_mcpa_sparse_step_wt(rows, ld, B, nnz, W, ldw, d, C, variant, Creg, coef, stats, active_before,
+                                   mean_update, nullptr, stream);
+}
+
+extern "C" int omldm_mcpa_sparse_step_wt(const float* rows, int ld, int B, int nnz, float* W, int ldw, int d, int C,
+                                         int variant, float Creg, float* coef, double* stats,
+                                         const double* active_before, int mean_update, float* wt, void* stream) {
   if (B <= 0) return 0;
   if (C < 2 || C > SP_MAXC) return set_error_msg("mcpa_sparse_step: 2 <= classes <= 32");
   if (nnz <= 0 || ld < 2 * nnz + 2 || ldw < d + 1) return set_error_msg("mcpa_sparse_step: bad row pitch");
@@ -166,8 +204,16 @@ extern "C" int omldm_mcpa_sparse_step(const float* rows, int ld, int B, int nnz,
   if (mean_update && !active_before) return set_error_msg("mcpa_sparse_step: averaged update needs active_before");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int blocks = (B + 7) / 8;
-  mcpa_sparse_coef_kernel<<<blocks, 256, 0, st>>>(rows, ld, B, nnz, W, ldw, d, C, variant, Creg,
-                                                  reinterpret_cast<float4*>(coef), stats);
+  if (wt && C <= 16) {
+    if (reinterpret_cast<uintptr_t>(wt) & 15) return set_error_msg("mcpa_sparse_step: wt must be 16-byte aligned");
+    mcpa_transpose_kernel<<<(d + 1 + 255) / 256, 256, 0, st>>>(W, ldw, d, C, wt);
+    if (int rc = check_launch("mcpa_transpose_kernel")) return rc;
+    mcpa_sparse_coef_kernel<true><<<blocks, 256, 0, st>>>(rows, ld, B, nnz, wt, 16, d, C, variant, Creg,
+                                                          reinterpret_cast<float4*>(coef), stats);
+  } else {
+    mcpa_sparse_coef_kernel<false><<<blocks, 256, 0, st>>>(rows, ld, B, nnz, W, ldw, d, C, variant, Creg,
+                                                           reinterpret_cast<float4*>(coef), stats);
+  }
   if (int rc = check_launch("mcpa_sparse_coef_kernel")) return rc;
   mcpa_sparse_update_kernel<<<blocks, 256, 0, st>>>(rows, ld, B, nnz, reinterpret_cast<const float4*>(coef), W, ldw, d,
                                                     C, stats, active_before, mean_update);

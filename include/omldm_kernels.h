@@ -349,6 +349,13 @@ int omldm_sparse_rows(const int* idx, const float* val, const float* targets, in
 int omldm_mcpa_sparse_step(const float* rows, int ld, int B, int nnz, float* W, int ldw, int d, int C, int variant,
                            float Creg, float* coef, double* stats, const double* active_before, int mean_update,
                            void* stream);
+/* Same step with a scratch of omldm_mcpa_sparse_wt_floats(d) floats (16-byte aligned): for C <= 16 the scores are
+ * gathered from a class-minor copy Wt[col][16] rebuilt in front of the step (one 64-byte line per non-zero instead of
+ * one 32-byte sector per class); wt == NULL or C > 16 = the plain step. */
+size_t omldm_mcpa_sparse_wt_floats(int d);
+int omldm_mcpa_sparse_step_wt(const float* rows, int ld, int B, int nnz, float* W, int ldw, int d, int C, int variant,
+                              float Creg, float* coef, double* stats, const double* active_before, int mean_update,
+                              float* wt, void* stream);
 
 /* ------------------------------------------------------------------ neural network glue (nn.cu)
  * Element-wise steps between the GEMMs of the small MLP learner "NN" (whitelist PipelineMap.scala:68).

@@ -133,6 +133,7 @@ class GpuMultiClassPA(GpuLearner):
         self.W = self.buf.view(self.n_classes, self.ld)
         self._T = None
         self._coef = None
+        self._wt = None
         self._act = torch.zeros(1, device=self.device)
 
     def _bufs(self, B):
@@ -169,9 +170,11 @@ class GpuMultiClassPA(GpuLearner):
             B = rows.shape[0]
             if self._coef is None or self._coef.shape[0] < B:
                 self._coef = torch.empty(B, 4, device=self.device)
+            if self._wt is None and self.n_classes <= 16:
+                self._wt = torch.empty((self.d + 1) * 16, device=self.device)
             prev = self.stats[3].clone()
             F.mcpa_sparse_step(rows, nnz, self.W, self.d, self.n_classes, self.variant, self.C, self._coef,
-                               self.stats, prev, self.mean_update)
+                               self.stats, prev, self.mean_update, self._wt)
             return
         Z = F.sparse_rows_to_dense(rows, nnz, self.d)
         col = rows[:, :nnz].contiguous().view(torch.int32)

@@ -591,13 +591,16 @@ def sparse_rows_to_dense(rows: torch.Tensor, nnz: int, d: int) -> torch.Tensor:
 
 
 def mcpa_sparse_step(rows: torch.Tensor, nnz: int, W: torch.Tensor, d: int, C: int, variant: int, Creg: float,
-                     coef: torch.Tensor, stats: torch.Tensor, active_before: torch.Tensor, mean_update: bool) -> None:
+                     coef: torch.Tensor, stats: torch.Tensor, active_before: torch.Tensor, mean_update: bool,
+                     wt: Optional[torch.Tensor] = None) -> None:
     """One mini-batch MultiClassPA step from sparse rows against the dense model W[C, ldw]
-    (csrc/sparse_mcpa.cu).  CUDA only; callers on CPU densify and use the dense step."""
+    (csrc/sparse_mcpa.cu).  CUDA only; callers on CPU densify and use the dense step.  `wt`: (d + 1) * 16 floats of
+    scratch for the class-minor copy of W the scores are gathered from (C <= 16)."""
     B = rows.shape[0]
-    _lib.check(_k().omldm_mcpa_sparse_step(_p(rows), _i(rows.stride(0)), _i(B), _i(nnz), _p(W), _i(W.stride(0)), _i(d),
-                                           _i(C), _i(variant), _f(Creg), _p(coef), _p(stats), _p(active_before),
-                                           _i(1 if mean_update else 0), _lib.stream_ptr()), "mcpa_sparse_step")
+    _lib.check(_k().omldm_mcpa_sparse_step_wt(_p(rows), _i(rows.stride(0)), _i(B), _i(nnz), _p(W), _i(W.stride(0)),
+                                              _i(d), _i(C), _i(variant), _f(Creg), _p(coef), _p(stats),
+                                              _p(active_before), _i(1 if mean_update else 0), _p(wt),
+                                              _lib.stream_ptr()), "mcpa_sparse_step")
 
 
 def ridge_cg_workspace(n: int, device, max_iter: int = 32):

@@ -332,8 +332,10 @@ def _sparse_slot(i, d, B, nnz, C, unique):
 
 @pytest.mark.parametrize("unique", [True, False])
 @pytest.mark.parametrize("mean", [True, False])
-def test_sparse_mcpa_step(unique, mean):
+@pytest.mark.parametrize("class_minor", [False, True])
+def test_sparse_mcpa_step(unique, mean, class_minor):
     d, B, nnz, C = 500, 50, 12, 6
+    wt = torch.empty((d + 1) * 16) if class_minor else None     # scores gathered from the class-minor copy of W
     ldw = F.pad32(d + 2)
     W0 = 0.05 * torch.randn(C, ldw)
     W0[:, d + 1:] = 0.0
@@ -347,7 +349,7 @@ def test_sparse_mcpa_step(unique, mean):
             rows = F.sparse_rows(idx, val, y, B, nnz)
             rows[4] = 0.0                                    # an empty row is skipped
             prev = st[3].clone()
-            F.mcpa_sparse_step(rows, nnz, W, d, C, 1, 0.5, coef, st, prev, mean)
+            F.mcpa_sparse_step(rows, nnz, W, d, C, 1, 0.5, coef, st, prev, mean, wt)
         return W, st
 
     def run_ref():

@@ -110,6 +110,24 @@ def test_gram_f16_speed_report():
     us = 1000.0 * e0.elapsed_time(e1) / reps
     flops = 2.0 * K * 10 * 256 * 256            # 10 upper 256 x 256 tiles
     print(f"\ngram_f16 K={K} d={d}: {us:.1f} us per call, {flops / us / 1e6:.0f} TFLOP/s executed")
+    from omldm_b200.ops import _lib
+    lib = _lib.kernels()
+    if hasattr(lib, "omldm_gram_f16_stamps"):        # a tuning build (-DOMLDM_GRAM_TIMING): per-CTA phase durations in SM cycles
+        import ctypes
+        import numpy as np
+        buf = np.zeros(160 * 8, dtype=np.int64)
+        assert lib.omldm_gram_f16_stamps(buf.ctypes.data_as(ctypes.c_void_p)) == 0
+        st = buf.reshape(160, 8)[:140]
+        names = ["prologue", "first stage landed", "main loop", "epilogue issue", "reduce drain", "teardown"]
+        for i, nm in enumerate(names):
+            dt = st[:, i + 1] - st[:, i]
+            ok = (st[:, i + 1] > 0) & (st[:, i] > 0)
+            if ok.any():
+                print(f"  {nm:20s} cycles: median {int(np.median(dt[ok]))}  min {int(dt[ok].min())}  max {int(dt[ok].max())}")
+        tot = st[:, 6] - st[:, 0]
+        ok = st[:, 6] > 0
+        if ok.any():
+            print(f"  leader CTAs start..teardown: median {int(np.median(tot[ok]))} max {int(tot[ok].max())}")
     assert us > 0
 
 
