@@ -48,10 +48,17 @@ constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int G_TMEM_COLS = 256;
 enum { GS_TILE0 = 8 };
+#ifdef OMLDM_GRAM_TIMING
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#endif
 #ifdef OMLDM_GRAM_TIMING        // tuning builds only (scripts/build_variant.sh): per-CTA phase stamps in SM cycles, read back by
                                 // tests/test_gram_f16_gpu.py::test_gram_f16_speed_report
-__device__ long long g_gram_stamp[160 * 8];
-#define GRAM_STAMP(i) do { if ((threadIdx.x & 31) == 0) g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 8 + (i)] = clock64(); } while (0)
+__device__ long long g_gram_stamp[160 * 16];   // 0..6 SM cycles per phase, 8 / 9 globaltimer ns at start / end
+#define GRAM_STAMP(i) do { if ((threadIdx.x & 31) == 0) g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 16 + (i)] = (i) >= 8 ? static_cast<long long>(globaltimer_ns()) : clock64(); } while (0)
 #else
 #define GRAM_STAMP(i) do { } while (0)
 #endif                            // scratch words: per half-tile arrival counters from word 8 on
@@ -76,7 +83,11 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       t -= len;
     }
   }
+#ifdef OMLDM_GRAM_FORCE_DIAG     // traffic experiment only (wrong results): every tile loads one operand, like a diagonal tile
+  const bool diag = true;
+#else
   const bool diag = ti == tj;
+#endif
   const int m0 = ti * 256 + static_cast<int>(rank) * 128;    // A-side columns of this CTA = its accumulator rows
   const int b0 = tj * 256 + static_cast<int>(rank) * 128;    // B-side columns this CTA feeds
   const int n0 = tj * 256;                                   // accumulator columns (all 256 in each CTA)
@@ -95,7 +106,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
   uint32_t* s_flag = tmem_slot + 1;
 
   const int warp = threadIdx.x >> 5;
-  if (warp == 0) GRAM_STAMP(0);
+  if (warp == 0) { GRAM_STAMP(0); GRAM_STAMP(8); }
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmZ);
     tma_prefetch_desc(&tmC);
@@ -240,6 +251,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     tc_fence_after();
     tmem_dealloc_pair<G_TMEM_COLS>(tmem_base);
     GRAM_STAMP(6);
+    GRAM_STAMP(9);
   }
 }
 
@@ -269,7 +281,7 @@ extern "C" size_t omldm_gram_f16_scratch_words(void) { return 512; }
 
 #ifdef OMLDM_GRAM_TIMING
 extern "C" int omldm_gram_f16_stamps(long long* out_host) {
-  return cudaMemcpyFromSymbol(out_host, g_gram_stamp, sizeof(long long) * 160 * 8) == cudaSuccess ? 0 : -1;
+  return cudaMemcpyFromSymbol(out_host, g_gram_stamp, sizeof(long long) * 160 * 16) == cudaSuccess ? 0 : -1;
 }
 #endif
 
@@ -322,6 +334,8 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
   if (!attr_set[dev & 15]) {                       // once per device, never inside a graph capture
     cudaError_t e = cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gram_f16)", e);
+    // leave the SM at its largest shared-memory carve-out so that blocks of the loss pass fit beside a Gram CTA
+    cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_set[dev & 15] = true;
   }
   dim3 grid(2 * tiles, gy);

@@ -12,6 +12,8 @@
 #include "host_common.h"
 #include "omldm_kernels.h"
 
+OMLDM_TL_DECLARE(holdout)
+
 namespace omldm {
 
 __host__ __device__ inline long long holdouts_before(long long c) {
@@ -39,6 +41,7 @@ __global__ void __launch_bounds__(256, 2)
 holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restrict__ ring, int cap,
                     long long count0_arg, long long* __restrict__ count_dev, unsigned int* __restrict__ done,
                     int ordered) {
+  OMLDM_TL_BEGIN(holdout);
   const long long count0 = count_dev ? *reinterpret_cast<volatile long long*>(count_dev) : count0_arg;
   // narrow rows: several ring slots share a CTA so that every thread has a column (a 128-byte row is 16 float2)
   const int ldv_all = ld / static_cast<int>(sizeof(V) / sizeof(float));
@@ -102,6 +105,7 @@ holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restri
       }
     }
   }
+  OMLDM_TL_END(holdout);
 }
 
 __global__ void advance_count_kernel(long long* c, long long delta) { *c += delta; }

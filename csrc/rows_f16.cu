@@ -14,6 +14,8 @@
 #include "host_common.h"
 #include "omldm_kernels.h"
 
+OMLDM_TL_DECLARE(loss)
+
 namespace omldm {
 
 __global__ void __launch_bounds__(128)
@@ -53,9 +55,19 @@ constexpr int RI = 4;
 // `rows_per_range` > 0: the batch is swept as ceil(B / rows_per_range) ranges side by side, blockIdx.y = range, each in
 // row order - the order in which the split-K CTAs of the Gram kernel read the same rows, so that whichever kernel is
 // ahead pulls a row from HBM and the other finds it in L2 when the two run concurrently.
+// Optional tail of the pass: the last block to finish writes one learning-curve sample (cumulative loss sum, records
+// fitted) into the device ring - the work of ingest.cu::curve_sample_kernel without a launch of its own.
+struct CurveTail {
+  double* ring;            // [cap][2], null = no sample
+  long long* counter;      // samples written so far
+  unsigned int* done;      // blocks finished (self-resetting)
+  int cap;
+};
+
 __global__ void __launch_bounds__(256)
 sq_residual_f16s_kernel(const __half* __restrict__ Zh_all, int ldh, int B_all, int d, const float* __restrict__ wt,
-                        double* __restrict__ stats, int rows_per_range) {
+                        double* __restrict__ stats, int rows_per_range, const CurveTail tail) {
+  OMLDM_TL_BEGIN(loss);
   const int row0 = rows_per_range > 0 ? blockIdx.y * rows_per_range : 0;
   const int B = rows_per_range > 0 ? min(rows_per_range, B_all - row0) : B_all;
   const __half* __restrict__ Zh = Zh_all + static_cast<size_t>(row0) * ldh;
@@ -69,7 +81,6 @@ sq_residual_f16s_kernel(const __half* __restrict__ Zh_all, int ldh, int B_all, i
   const int n8 = (n + 7) >> 3;
   double acc = 0.0;
   int nv = 0;
-  if (B <= 0) return;
   for (int r = warp; r < B; r += RI * nwarps) {
     const float4* z[RI];
     float dsum[RI];
@@ -114,7 +125,20 @@ sq_residual_f16s_kernel(const __half* __restrict__ Zh_all, int ldh, int B_all, i
     double l = 0; int c = 0;
     for (int i = 0; i < (blockDim.x >> 5); ++i) { l += s_l[i]; c += s_n[i]; }
     if (c) { atomicAdd(&stats[0], l); atomicAdd(&stats[2], static_cast<double>(c)); }
+    if (tail.ring) {
+      __threadfence();                                         // this block's sums before its arrival
+      if (atomicAdd(tail.done, 1u) == gridDim.x * gridDim.y - 1) {
+        __threadfence();
+        *tail.done = 0;
+        const long long i = *tail.counter;
+        double* slot = tail.ring + 2 * (i % tail.cap);
+        slot[0] = __ldcg(&stats[0]);                           // the other blocks' atomics live in L2
+        slot[1] = __ldcg(&stats[2]);
+        *tail.counter = i + 1;
+      }
+    }
   }
+  OMLDM_TL_END(loss);
 }
 
 }  // namespace omldm
@@ -131,9 +155,17 @@ extern "C" int omldm_expand_rows_f16s(const void* Zh, int ldh, int B, int d, flo
 
 extern "C" int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats,
                                       int rows_per_range, void* stream) {
+  return omldm_sq_residual_f16s_tail(Zh, ldh, B, d, wt, stats, rows_per_range, 0, nullptr, 0, nullptr, nullptr, stream);
+}
+
+extern "C" int omldm_sq_residual_f16s_tail(const void* Zh, int ldh, int B, int d, const float* wt, double* stats,
+                                           int rows_per_range, int max_blocks, double* curve_ring, int curve_cap,
+                                           long long* curve_counter, unsigned int* done_word, void* stream) {
   if (B <= 0) return 0;
   if ((ldh & 7) || ldh < d + 3) return set_error_msg("sq_residual_f16s: the fp16 pitch must be a multiple of 8 and >= d + 3");
   if (reinterpret_cast<uintptr_t>(Zh) & 15) return set_error_msg("sq_residual_f16s: rows must be 16-byte aligned");
+  if (curve_ring && (curve_cap <= 0 || !curve_counter || !done_word))
+    return set_error_msg("sq_residual_f16s: the curve sample needs a ring, its counter and a completion word");
   const size_t smem = static_cast<size_t>(ldh) * sizeof(float);
   if (smem > 200 * 1024) return set_error_msg("sq_residual_f16s: row pitch too large for the smem weight copy");
   if (smem > 48 * 1024) {
@@ -145,10 +177,14 @@ extern "C" int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, con
   if (ranges < 1 || ranges > 1024) return set_error_msg("sq_residual_f16s: bad rows_per_range");
   const int per = ranges > 1 ? rows_per_range : B;
   int blocks = (per + 31) / 32;
-  const int cap = (148 * 3 + ranges - 1) / ranges;
+  // three blocks fit an SM alone; beside a kernel that holds registers on every SM the caller asks for fewer, so that
+  // the pass stays one wave (max_blocks = blocks in total, 0 = 3 per SM)
+  const int total = max_blocks > 0 ? max_blocks : 148 * 3;
+  const int cap = (total + ranges - 1) / ranges;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
+  CurveTail tail{curve_ring, curve_counter, done_word, curve_cap};
   sq_residual_f16s_kernel<<<dim3(blocks, ranges), 256, smem, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __half*>(Zh), ldh, B, d, wt, stats, ranges > 1 ? rows_per_range : 0);
+      static_cast<const __half*>(Zh), ldh, B, d, wt, stats, ranges > 1 ? rows_per_range : 0, tail);
   return check_launch("sq_residual_f16s_kernel");
 }

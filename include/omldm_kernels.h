@@ -77,6 +77,13 @@ int omldm_expand_rows_f16s(const void* Zh, int ldh, int B, int d, float* Z, int 
  * share them through L2); 0 = one range. */
 int omldm_sq_residual_f16s(const void* Zh, int ldh, int B, int d, const float* wt, double* stats, int rows_per_range,
                            void* stream);
+/* The same pass with (a) max_blocks > 0: at most that many blocks in total (the pass is a grid-stride loop; beside a
+ * kernel that holds registers on every SM, e.g. omldm_gram_f16, 2 x 148 keeps it one wave), (b) curve_ring != NULL: the
+ * last block to finish writes one learning-curve sample (stats[0], stats[2]) into ring[(counter % cap)] and advances
+ * the counter - omldm_curve_sample without a launch of its own; done_word = one zero-initialised word of scratch. */
+int omldm_sq_residual_f16s_tail(const void* Zh, int ldh, int B, int d, const float* wt, double* stats,
+                                int rows_per_range, int max_blocks, double* curve_ring, int curve_cap,
+                                long long* curve_counter, unsigned int* done_word, void* stream);
 
 /* ------------------------------------------------------------------ linear learners (linear_learners.cu)
  * PA / RegressorPA / SVM named in utils/parsers/requestStream/PipelineMap.scala:68. */

@@ -47,7 +47,7 @@ class GpuLearner:
     def enable_curve(self, cap: int = 1024) -> None:
         """Test mode: keep a device ring of per-mini-batch (loss sum, fitted) samples (FlinkHub.scala:101-113)."""
         self.curve_ring = torch.zeros(cap, 2, dtype=torch.float64, device=self.device)
-        self.curve_count = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.curve_count = torch.zeros(2, dtype=torch.int64, device=self.device)   # [samples written, completion word of a fused sample]
 
     def sample_curve(self) -> None:
         """One sample on the current stream; learners that run their loss pass on a side stream call it there."""
@@ -59,7 +59,7 @@ class GpuLearner:
         """[(mean loss of the mini-batch, records fitted so far)] in time order, from the device ring."""
         if self.curve_ring is None:
             return []
-        n = int(self.curve_count.item())
+        n = int(self.curve_count[0].item())
         cap = self.curve_ring.shape[0]
         ring = self.curve_ring.cpu()
         idx = [i % cap for i in range(max(0, n - cap), n)]
@@ -346,10 +346,12 @@ class GpuORR(GpuLearner):
             self._hub.push()
 
     def _loss(self, Z):
-        if Z.dtype == torch.float16:
-            F.sq_residual_f16s(Z, self.d, self.wt, self.stats, like_gram=self.overlap)
-        else:
-            F.sq_residual(Z, self.d, self.wt[: self.d + 2], self.stats)   # prequential squared error with current w
+        if Z.dtype == torch.float16:     # the learning-curve sample rides in the pass's last block
+            F.sq_residual_f16s(Z, self.d, self.wt, self.stats, like_gram=self.overlap and Z.is_cuda,
+                               curve_ring=self.curve_ring, curve_counter=self.curve_count)
+            self._curve_sampled = self.curve_ring is not None
+            return
+        F.sq_residual(Z, self.d, self.wt[: self.d + 2], self.stats)   # prequential squared error with current w
         self.sample_curve()          # on the loss pass's stream: beside the Gram kernel, not after it
 
     def fit_batch(self, Z):

@@ -246,19 +246,29 @@ def expand_rows_f16s(Zh: torch.Tensor, d: int, ld: Optional[int] = None, out: Op
     return Z
 
 
-def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor, like_gram: bool = False) -> None:
+def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Tensor, like_gram: bool = False,
+                     curve_ring: Optional[torch.Tensor] = None, curve_counter: Optional[torch.Tensor] = None) -> None:
     """stats[0] += sum over valid rows of (w.x + b - y)^2, stats[2] += #valid; wt = [w, b, -1, -1] (d + 3 floats).
-    `like_gram`: walk the rows in the order of the concurrent fp16 Gram kernel (its batch-axis splits side by side)."""
+    `like_gram`: the pass runs beside the fp16 Gram kernel - walk the rows in the order of its batch-axis splits and
+    use two blocks per SM (what fits next to a Gram CTA) so that it stays one wave.
+    `curve_ring` [cap, 2] fp64 + `curve_counter` int64[2] (samples written, completion word): the last block also
+    writes the learning-curve sample of `curve_sample`."""
     if native(Zh):
         rpr = int(_k().omldm_gram_f16_rows_per_split(_i(Zh.shape[0]), _i(d + 3), _i(0))) \
             if (like_gram and not _lib._emulated) else 0
-        _lib.check(_k().omldm_sq_residual_f16s(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(d), _p(wt), _p(stats),
-                                               _i(rpr), _lib.stream_ptr()), "sq_residual_f16s")
+        cap = curve_ring.shape[0] if curve_ring is not None else 0
+        done = ctypes.c_void_p(curve_counter.data_ptr() + 8) if curve_ring is not None else None
+        _lib.check(_k().omldm_sq_residual_f16s_tail(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(d), _p(wt), _p(stats),
+                                                    _i(rpr), _i(2 * 148 if like_gram else 0), _p(curve_ring), _i(cap),
+                                                    _p(curve_counter) if curve_ring is not None else None, done,
+                                                    _lib.stream_ptr()), "sq_residual_f16s")
         return
     valid = Zh[:, d] != 0
     r = Zh[:, : d + 3].float() @ wt[: d + 3]
     stats[0] += (r[valid].double() ** 2).sum()
     stats[2] += valid.sum().double()
+    if curve_ring is not None:
+        curve_sample(stats, curve_ring, curve_counter)
 
 
 class GramPeers(ctypes.Structure):

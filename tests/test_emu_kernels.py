@@ -448,6 +448,14 @@ def test_f16s_row_kernels():
             st = torch.zeros(4, dtype=torch.float64)
             F.sq_residual_f16s(Zh, d, wt, st)
         assert st[2] == st_ref[2] and abs(float(st[0] - st_ref[0])) <= 1e-4 * max(1.0, float(st_ref[0]))
+        # the learning-curve sample written by the pass's last block: same ring content as curve_sample after the pass
+        with F.use_impl("emu"):
+            st2 = torch.zeros(4, dtype=torch.float64)
+            ring, cnt = torch.zeros(3, 2, dtype=torch.float64), torch.zeros(2, dtype=torch.int64)
+            for k in range(4):                                # wraps around the 3-slot ring
+                F.sq_residual_f16s(Zh, d, wt, st2, curve_ring=ring, curve_counter=cnt)
+                assert int(cnt[0]) == k + 1 and int(cnt[1]) == 0        # sample taken, completion word reset
+                assert ring[k % 3, 0] == st2[0] and ring[k % 3, 1] == st2[2]
 
 
 # ---- engine-level: the Python glue of the kernel paths that normally only run on a GPU ---------------------------

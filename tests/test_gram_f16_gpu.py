@@ -110,25 +110,36 @@ def test_gram_f16_speed_report():
     us = 1000.0 * e0.elapsed_time(e1) / reps
     flops = 2.0 * K * 10 * 256 * 256            # 10 upper 256 x 256 tiles
     print(f"\ngram_f16 K={K} d={d}: {us:.1f} us per call, {flops / us / 1e6:.0f} TFLOP/s executed")
+    for line in gram_phase_report():
+        print(line)
+
+
+def gram_phase_report():
+    """Per-CTA phase durations of the LAST gram_f16 launch; empty unless the loaded library is a tuning build
+    (scripts/build_variant.sh timing csrc/gram_f16.cu -DOMLDM_GRAM_TIMING)."""
     from omldm_b200.ops import _lib
     lib = _lib.kernels()
-    if hasattr(lib, "omldm_gram_f16_stamps"):        # a tuning build (-DOMLDM_GRAM_TIMING): per-CTA phase durations in SM cycles
-        import ctypes
-        import numpy as np
-        buf = np.zeros(160 * 8, dtype=np.int64)
-        assert lib.omldm_gram_f16_stamps(buf.ctypes.data_as(ctypes.c_void_p)) == 0
-        st = buf.reshape(160, 8)[:140]
-        names = ["prologue", "first stage landed", "main loop", "epilogue issue", "reduce drain", "teardown"]
-        for i, nm in enumerate(names):
-            dt = st[:, i + 1] - st[:, i]
-            ok = (st[:, i + 1] > 0) & (st[:, i] > 0)
-            if ok.any():
-                print(f"  {nm:20s} cycles: median {int(np.median(dt[ok]))}  min {int(dt[ok].min())}  max {int(dt[ok].max())}")
-        tot = st[:, 6] - st[:, 0]
-        ok = st[:, 6] > 0
+    if not hasattr(lib, "omldm_gram_f16_stamps"):
+        return []
+    import ctypes
+    import numpy as np
+    torch.cuda.synchronize()
+    buf = np.zeros(160 * 16, dtype=np.int64)
+    assert lib.omldm_gram_f16_stamps(buf.ctypes.data_as(ctypes.c_void_p)) == 0
+    st = buf.reshape(160, 16)[:140]
+    out = []
+    names = ["prologue", "first stage landed", "main loop", "epilogue issue", "reduce drain", "teardown"]
+    for i, nm in enumerate(names):
+        dt = st[:, i + 1] - st[:, i]
+        ok = (st[:, i + 1] > 0) & (st[:, i] > 0)
         if ok.any():
-            print(f"  leader CTAs start..teardown: median {int(np.median(tot[ok]))} max {int(tot[ok].max())}")
-    assert us > 0
+            out.append(f"  {nm:20s} cycles: median {int(np.median(dt[ok]))}  min {int(dt[ok].min())}  max {int(dt[ok].max())}")
+    ok = st[:, 6] > 0
+    if ok.any():
+        tot, ns = (st[:, 6] - st[:, 0])[ok], (st[:, 9] - st[:, 8])[ok]
+        out.append(f"  leader CTAs start..teardown: median {int(np.median(tot))} cycles = {np.median(ns) / 1e3:.1f} us "
+                   f"-> {np.median(tot / np.maximum(ns, 1)):.3f} GHz; first start .. last end {(st[:, 9][ok].max() - st[:, 8][st[:, 8] > 0].min()) / 1e3:.1f} us")
+    return out
 
 
 @pytest.mark.parametrize("B,d", [(4096, 1000), (300, 28), (5000, 253), (32768, 1000)])
