@@ -177,6 +177,13 @@ extern "C" int omldm_ridge_cg(const float* A, int ld, int n, float lam, const fl
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  // the refresh runs on a side stream while the Gram kernel (198 KB of shared memory per CTA) owns the SMs: keep every SM
+  // it touches at the largest shared-memory carve-out, or a Gram CTA waits until the refresh blocks have left that SM
+  static bool carveout_set[16] = {};
+  if (!carveout_set[dev & 15]) {
+    cudaFuncSetAttribute(ridge_pcg_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    carveout_set[dev & 15] = true;
+  }
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ridge_pcg_kernel, CG_THREADS, 0);
   int grid = blocks > 0 ? blocks : 32;
   if (grid > sms * per_sm) grid = sms * per_sm;

@@ -170,6 +170,11 @@ extern "C" int omldm_ridge_chol(float* W, int ld, int n, float lam, float* x, fl
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  static bool carveout_set[16] = {};     // same reason as in ridge_cg.cu: never make a Gram CTA wait for an SM to drain
+  if (!carveout_set[dev & 15]) {
+    cudaFuncSetAttribute(ridge_chol_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    carveout_set[dev & 15] = true;
+  }
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ridge_chol_kernel, CH_THREADS, 0);
   int grid = blocks > 0 ? blocks : 64;
   if (grid > sms * per_sm) grid = sms * per_sm;
