@@ -140,6 +140,12 @@ def main() -> None:
                           "no JVM/Maven/Kafka in this image and it is not pip-installable (no setup.py/pyproject)"}))
         return
 
+    # stdout carries the ONE JSON line and nothing else: whatever a library prints to file descriptor 1 meanwhile (NCCL's
+    # version banner does) goes to stderr; the line itself is written to the saved descriptor at the end
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from omldm_b200.engine import Engine
@@ -154,7 +160,7 @@ def main() -> None:
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dry = args.dry_run_cpu
     if not dry and not torch.cuda.is_available():
-        print(json.dumps({"error": "no CUDA device", "metric": "records/sec"}))
+        print(json.dumps({"error": "no CUDA device", "metric": "records/sec"}), file=real_stdout, flush=True)
         return
     if dry:
         dev, numa = torch.device("cpu"), None
@@ -487,7 +493,7 @@ def main() -> None:
                 "value": base["value"], "ms_per_step": base["ms_per_step"], "windows": base["windows"],
                 "e2e_value": (base["e2e"] or {}).get("value")}),
         }
-        print(json.dumps(out))
+        print(json.dumps(out), file=real_stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

@@ -19,7 +19,13 @@
 //     accumulators live in TMEM (128 lanes x 256 columns per CTA); tcgen05.commit (multicast to both CTAs) frees the
 //     smem stages and publishes the accumulator.
 //   * epilogue: tcgen05.ld -> registers -> swizzled smem -> TMA reduce-add (fp32 adds at L2), upper 32 x 32 blocks only.
-//   * hub push (world > 1): the split-K partials meet in this GPU's own L2-resident running sum; the LAST CTA to
+//   * hub push, lead mode (world > 1, default): while the MMAs of this launch run, the otherwise idle epilogue warps
+//     copy the running sum AS IT WAS WHEN THE KERNEL STARTED (the result of the previous mini-batch), 32 x 32 block by
+//     block, with TMA (load from L2 -> plain store over NVLink) into THIS worker's slot at the GPU that owns those rows;
+//     the blocks of a half tile are dealt out over its batch-axis splits.  The transfer hides completely behind the main
+//     loop; the slots trail the running sum by one mini-batch and are brought up to date by
+//     csrc/sync.cu::sync_gram_push_kernel right before anybody reads them (the gather at a weight refresh or a query).
+//   * hub push, tail mode: the split-K partials meet in this GPU's own L2-resident running sum; the LAST CTA to
 //     finish a 128-row half tile then copies the updated rows, 32 x 32 block by block, with TMA (load from L2 ->
 //     plain store over NVLink) into THIS worker's slot at the GPU that owns those rows.  Every slot has a single
 //     writer, so the transfer needs no remote atomics, no flags and no zeroing, every element crosses NVLink once,
@@ -46,6 +52,7 @@ constexpr int G_THREADS = 192;                    // warp 0 TMA, warp 1 TMEM + M
 constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 64 halves x 64 records = 16 KB
 constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int G_LEAD_BYTES = 4 * 4096 + 768;      // lead-mode push: one 32 x 32 fp32 staging block per epilogue warp, 1024-aligned behind the barriers
 constexpr int G_TMEM_COLS = 256;
 enum { GS_TILE0 = 8 };
 #ifdef OMLDM_GRAM_TIMING
@@ -65,7 +72,7 @@ __device__ long long g_gram_stamp[160 * 16];   // 0..6 SM cycles per phase, 8 / 
 
 struct GramPush {
   CUtensorMap owner[16];     // this worker's slot matrix at every owner (peer mapped), 32 x 32 fp32 boxes
-  int world, rank, rows_per_owner, enabled;
+  int world, rank, rows_per_owner, enabled;   // enabled: 0 off, 1 tail (exact at kernel end), 2 lead (during the main loop)
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G_THREADS, 1)
@@ -175,6 +182,25 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     const int q = warp & 3;                        // TMEM lane quadrant this warp may read
     const uint32_t r = lane_id();
     const int row0 = m0 + q * 32;
+    if (push.enabled == 2 && r == 0 && row0 < n) {
+      // ---------------------------------------------------------- hub push, lead mode: hidden behind the main loop
+      uint8_t* stage_blk = smem + G_STAGES * G_STAGE_BYTES + 1024 + q * 4096;
+      const CUtensorMap* om = &push.owner[row0 / push.rows_per_owner];
+      uint32_t ph = 0;
+      for (int c = 0; c < 8; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= n || col0 + 31 < row0) continue;
+        if ((q * 8 + c) % static_cast<int>(gridDim.y) != static_cast<int>(blockIdx.y)) continue;   // another split's block
+        mbar_expect_tx(&push_bar[q], 4096);
+        tma_load_2d(stage_blk, &tmC, &push_bar[q], col0, row0);
+        mbar_wait(&push_bar[q], ph);
+        ph ^= 1;
+        tma_store_2d(om, stage_blk, col0, row0);   // into this worker's slot at the owner (NVLink)
+        tma_commit_group();
+        tma_wait_group_read0();                    // the staging block is free again
+      }
+    }
+    __syncwarp();
     mbar_wait(accum_bar, 0);
     if (warp == 2) GRAM_STAMP(3);
     tc_fence_after();
@@ -202,8 +228,8 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     __syncwarp();
     if (warp == 2) GRAM_STAMP(5);
 
-    if (push.enabled) {
-      // -------------------------------------------------------- hub push by the last CTA of this half tile
+    if (push.enabled == 1) {
+      // -------------------------------------------------------- hub push, tail mode: by the last CTA of this half tile
       named_bar_sync(1, 128);                      // the reductions of all four epilogue warps are complete
       if (threadIdx.x == 64) {
         __threadfence();
@@ -320,7 +346,8 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
     if (peers->rows_per_owner < 32 || (peers->rows_per_owner & 31) ||
         static_cast<long long>(peers->rows_per_owner) * peers->world < n)
       return set_error_msg("gram_f16: rows_per_owner must be a multiple of 32 and cover n");
-    push.world = peers->world; push.rank = peers->rank; push.rows_per_owner = peers->rows_per_owner; push.enabled = 1;
+    push.world = peers->world; push.rank = peers->rank; push.rows_per_owner = peers->rows_per_owner;
+    push.enabled = peers->lead ? 2 : 1;
     for (int p = 0; p < peers->world; ++p)
       if (encode_g(&push.owner[p], peers->owner_base[p], n, n, ldc)) return -1;
     for (int p = peers->world; p < 16; ++p) push.owner[p] = push.owner[0];
@@ -332,14 +359,15 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 15]) {                       // once per device, never inside a graph capture
-    cudaError_t e = cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM + G_LEAD_BYTES);
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gram_f16)", e);
     // leave the SM at its largest shared-memory carve-out so that blocks of the loss pass fit beside a Gram CTA
     cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_set[dev & 15] = true;
   }
   dim3 grid(2 * tiles, gy);
-  gram_f16_kernel<<<grid, G_THREADS, G_SMEM, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, n, K, k_per_split, T,
-                                                                                scratch);
+  const int smem_bytes = G_SMEM + (push.enabled == 2 ? G_LEAD_BYTES : 0);
+  gram_f16_kernel<<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, n, K, k_per_split,
+                                                                                    T, scratch);
   return check_launch("gram_f16_kernel");
 }

@@ -60,6 +60,9 @@ typedef struct omldm_gram_peers {
   int world;
   int rank;
   int rows_per_owner;        /* multiple of 32; owner p holds rows [p * rows_per_owner, (p + 1) * rows_per_owner) */
+  int lead;                  /* 0: tail push - after the call the slots hold this call's result (last CTA of a half tile
+                                copies it).  1: lead push - the slots receive C as it was BEFORE this call, copied while
+                                the MMAs run (free); run omldm_sync_gram_push before the slots are read. */
 } omldm_gram_peers;
 size_t omldm_gram_f16_scratch_words(void);
 int omldm_gram_f16_rows_per_split(int K, int n, int ksplit);   /* records per batch-axis split the kernel will use */

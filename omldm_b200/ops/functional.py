@@ -273,7 +273,7 @@ def sq_residual_f16s(Zh: torch.Tensor, d: int, wt: torch.Tensor, stats: torch.Te
 
 class GramPeers(ctypes.Structure):
     _fields_ = [("owner_base", ctypes.c_void_p * 16), ("world", ctypes.c_int), ("rank", ctypes.c_int),
-                ("rows_per_owner", ctypes.c_int)]
+                ("rows_per_owner", ctypes.c_int), ("lead", ctypes.c_int)]
 
 
 def gram_f16_scratch(device) -> torch.Tensor:

@@ -277,9 +277,12 @@ class ScatterSynchronousDriver(SyncDriver):
 class ShardedGramDriver(SyncDriver):
     """Synchronous protocol for the ORR Gram statistics with the hub SHARDED over the GPUs and the worker -> hub push
     performed by the kernel that computes the update (csrc/gram_f16.cu; csrc/sync.cu::sync_gram_push_kernel for the
-    tf32 path).  Every worker keeps its own running sum `acc` (private) and, each step, copies the rows it touched into
+    tf32 path).  Every worker keeps its own running sum `acc` (private) and, each step, copies its rows into
     ITS slot at the GPU that owns them (`hub` region = k slot matrices; single writer per slot, so plain stores over
-    NVLink: no remote atomics, no flags, nothing waits).  Workers need the global statistics only when they refresh
+    NVLink: no remote atomics, no flags, nothing waits).  `hubPush: "lead"` (default): the Gram kernel ships the
+    running sum as it was before the step while its MMAs run - the transfer costs nothing, the slots trail by one
+    mini-batch and `gather()` first brings them up to date; `hubPush: "tail"`: the last CTA of every half tile ships the
+    step's result, the slots are exact after every step (measured + 6 us per step at 2 GPUs).  Workers need the global statistics only when they refresh
     their weights (`solveEvery`) or answer a query, so the hub -> worker broadcast of FlinkNetwork.scala:282-291
     becomes a pull: `gather()` - entry rendezvous, every owner sums its k slots and stores the result into every
     worker's global matrix (`buf` region), exit rendezvous.  Default for Synchronous ORR on the fused path
@@ -311,6 +314,8 @@ class ShardedGramDriver(SyncDriver):
         for p_ in range(k if comm.emulate <= 1 else 0):
             self.peers.owner_base[p_] = int(bases[p_]) + comm._off_hub + 4 * comm.rank * ld * ld
         self.peers.world, self.peers.rank, self.peers.rows_per_owner = k, comm.rank, rpo
+        self.lead = str(cfg(tc, ["hubPush"], "lead")).lower() != "tail"
+        self.peers.lead = 1 if self.lead else 0
         self.gathers = 0
 
     def account(self):
@@ -330,6 +335,8 @@ class ShardedGramDriver(SyncDriver):
         """Collective: after it, `comm.buf` holds the global statistics (the sum of every worker's running sum)."""
         c = self.comm
         self.gathers += 1
+        if self.lead and c.emulate <= 1:
+            self.push()                # the slots trail the running sum by one mini-batch: bring them up to date
         _lib.check(_lib.kernels().omldm_sync_gram_gather(c.struct_ptr(), _i(self.ld), _i(self.n_rows),
                                                          _i(self.rows_per_owner), _u(0), _i(self.blocks),
                                                          _lib.stream_ptr()), "sync_gram_gather")

@@ -26,8 +26,11 @@ pool = [R.generate_batch(R.KIND_REGRESSION, d, K, seed=1, batch_index=i, wire="f
 acc = torch.zeros(ldg, ldg, device="cuda:0")           # this worker's running sum
 slot0 = torch.zeros(ldg, ldg, device="cuda:0")         # this worker's slot at owner 0 (itself)
 slot1 = torch.zeros(ldg, ldg, device="cuda:1")         # this worker's slot at owner 1: the other GPU
-torch.zeros(1, device="cuda:1").to("cuda:0")           # a cross-device copy makes torch enable peer access both ways
 assert torch.cuda.can_device_access_peer(0, 1)
+import ctypes
+rt = ctypes.CDLL("libcudart.so.12")                     # kernels on GPU 0 store into GPU 1's memory: explicit peer access
+rc = rt.cudaDeviceEnablePeerAccess(ctypes.c_int(1), ctypes.c_uint(0))
+assert rc in (0, 704), f"cudaDeviceEnablePeerAccess -> {rc}"      # 704 = already enabled
 peers = F.GramPeers()
 peers.world, peers.rank, peers.rows_per_owner = 2, 0, rpo
 peers.owner_base[0] = slot0.data_ptr()

@@ -91,6 +91,49 @@ def test_hub_push_copies_rows_into_the_owners_slots(world, K, d):
                 assert float(got[mask].abs().max()) == 0.0, f"owner {p} received foreign rows"
 
 
+@pytest.mark.parametrize("world,K,d", [(4, 16384, 1000), (2, 1500, 509), (8, 32768, 1000), (3, 640, 200)])
+def test_hub_push_lead_mode_ships_the_previous_result(world, K, d):
+    """Lead mode: while the MMAs of call t run, the kernel copies the running sum as it was before the call.  With a main
+    loop much longer than the copy (the bench shape) the slots hold exactly the result of call t - 1 after call t; with
+    short loops a copy may overlap another CTA's epilogue, which is why readers always run the catch-up push first
+    (parallel/fused.py::ShardedGramDriver.gather) - there only the placement and the running sum are checked."""
+    exact = K >= 16384 and d >= 1000
+    n = d + 3
+    ldg = F.pad64(n)
+    rows_per_owner = ldg // world // 32 * 32
+    if rows_per_owner * world < n:
+        rows_per_owner += 32
+    slots = [torch.zeros(ldg, ldg, device="cuda") for _ in range(world)]
+    C = torch.zeros(ldg, ldg, device="cuda")
+    scratch = F.gram_f16_scratch("cuda")
+    peers = F.GramPeers()
+    for p in range(world):
+        peers.owner_base[p] = slots[p].data_ptr()
+    peers.world, peers.rank, peers.rows_per_owner, peers.lead = world, 1 % world, rows_per_owner, 1
+    keep = _upper_blocks(n, "cuda")
+    before = C.clone()
+    for step in range(1, 4):
+        Zh = _rows(K, d, seed=step)
+        F.gram_f16(Zh, n, C, scratch=scratch, peers=peers)
+        torch.cuda.synchronize()
+        for p in range(world):
+            lo, hi = p * rows_per_owner, min(n, (p + 1) * rows_per_owner)
+            got = slots[p][:n, :n]
+            if lo < hi and exact:
+                assert torch.equal(got[lo:hi][keep[lo:hi]], before[:n, :n][lo:hi][keep[lo:hi]]), (step, p)
+            mask = torch.ones(n, dtype=torch.bool, device="cuda")
+            mask[lo:hi] = False
+            if mask.any():
+                assert float(got[mask].abs().max()) == 0.0, f"owner {p} received foreign rows"
+        before = C.clone()
+    # same running sum as without any push
+    C2 = torch.zeros(ldg, ldg, device="cuda")
+    for step in range(1, 4):
+        F.gram_f16(_rows(K, d, seed=step), n, C2)
+    torch.cuda.synchronize()
+    assert torch.allclose(C, C2, rtol=1e-5, atol=1e-3)
+
+
 def test_gram_f16_speed_report():
     """Not an assertion on speed: prints the device time at the bench shape so a GPU run leaves the number behind."""
     K, d = 32768, 1000
