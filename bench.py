@@ -117,6 +117,9 @@ def main() -> None:
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-baseline", action="store_true",
                     help="skip the in-repo PyTorch + NCCL baseline arm (then vs_baseline is null)")
+    ap.add_argument("--pipelined-holdout", action="store_true",
+                    help="run the holdout exchange of the next batch on its own stream behind the current training "
+                         "kernels (Engine option `pipelinedHoldout`) instead of inside the step's own graph")
     ap.add_argument("--min-timed-ms", type=float, default=400.0,
                     help="repeat the --steps window until this much device time has been measured")
     ap.add_argument("--wire", default="auto", choices=["auto", "f32", "f16", "f16s"],
@@ -229,6 +232,11 @@ def main() -> None:
             F.set_impl("auto")
         params = JobParameters(parallelism=world, jobName="bench_" + args.config)
         params.extra["sparseDirect"] = "true" if sparse_direct else "false"
+        if impl != "nccl" and args.pipelined_holdout:
+            # the holdout exchange of the next batch runs behind the current training kernels (Engine option; measured
+            # on a B200: 41.2 against 43.0 us per ORR step with 3 rotating batches, 50.3 against 48.5 us with the 4 of
+            # this script - no clear gain, so it stays off)
+            params.extra["pipelinedHoldout"] = "true"
         if impl == "nccl":      # the in-repo baseline: torch.distributed collectives + stock PyTorch ops
             from omldm_b200 import baseline
             eng = baseline.make_engine(params, rank, world, dev)

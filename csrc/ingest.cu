@@ -108,6 +108,48 @@ holdout_swap_kernel(float* __restrict__ Z, int ld, int B, int d, float* __restri
   OMLDM_TL_END(holdout);
 }
 
+// The exchange rule (`ordered` = 0) on its own: no chain walk, hence few registers - small enough to be placed on an SM
+// that is already full of a GEMM CTA and two loss-pass blocks, which is where it runs when the engine pipelines the
+// holdout of the next batch behind the current training step (Engine `pipelinedHoldout`).
+template <typename V>
+__global__ void __launch_bounds__(256)
+holdout_exchange_kernel(float* __restrict__ Z, int ld, int B, float* __restrict__ ring, int cap,
+                        long long* __restrict__ count_dev, unsigned int* __restrict__ done) {
+  OMLDM_TL_BEGIN(holdout);
+  const long long count0 = *reinterpret_cast<volatile long long*>(count_dev);
+  const int ldv = ld / static_cast<int>(sizeof(V) / sizeof(float));
+  const int spc = ldv < static_cast<int>(blockDim.x) ? static_cast<int>(blockDim.x) / ldv : 1;
+  const int slot = blockIdx.x * spc + (spc > 1 ? static_cast<int>(threadIdx.x) / ldv : 0);
+  const int cv_first = spc > 1 ? static_cast<int>(threadIdx.x) % ldv : static_cast<int>(threadIdx.x);
+  const int cv_step = spc > 1 ? ldv : static_cast<int>(blockDim.x);
+  const bool lane_on = spc == 1 || static_cast<int>(threadIdx.x) < spc * ldv;
+  const long long h0 = holdouts_before(count0), h1 = holdouts_before(count0 + B);
+  const long long hf = h0 + ((slot - (h0 % cap)) % cap + cap) % cap;   // first holdout of this batch that maps to the slot
+  if (lane_on && slot < cap && hf < h1) {
+    const long long hl = hf + (h1 - 1 - hf) / cap * cap;               // last one: it stays in the ring
+    const long long c = (hl / 2) * 10 + 8 + (hl & 1);                  // its record index
+    V* last = reinterpret_cast<V*>(Z + static_cast<size_t>(c - count0) * ld);
+    V* rs = reinterpret_cast<V*>(ring + static_cast<size_t>(slot) * ld);
+    const bool evict = hf >= cap;
+    V zero;
+    memset(&zero, 0, sizeof(V));
+    for (int cv = cv_first; cv < ldv; cv += cv_step) {
+      const V old = evict ? rs[cv] : zero;
+      rs[cv] = last[cv];
+      last[cv] = old;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(done, 1u);
+    if (prev == gridDim.x - 1) {              // every CTA has read the old count
+      *done = 0;
+      *count_dev = count0 + B;
+    }
+  }
+  OMLDM_TL_END(holdout);
+}
+
 __global__ void advance_count_kernel(long long* c, long long delta) { *c += delta; }
 
 // Learning curve of the test mode (operators/hub/FlinkHub.scala:101-113: the hub records (loss, #fitted) per
@@ -203,6 +245,11 @@ static int launch_holdout(float* Z, int ld, int B, int d, float* ring, int cap, 
   const int ldv = ld <= 512 ? ld / 2 : ld / 4;
   const int spc = ldv < 256 ? 256 / ldv : 1;           // ring slots per CTA (narrow rows)
   const int grid = (cap + spc - 1) / spc;
+  if (!ordered && count_dev != nullptr) {
+    if (ld <= 512) holdout_exchange_kernel<float2><<<grid, 256, 0, st>>>(Z, ld, B, ring, cap, count_dev, done);
+    else holdout_exchange_kernel<float4><<<grid, 256, 0, st>>>(Z, ld, B, ring, cap, count_dev, done);
+    return check_launch("holdout_exchange_kernel");
+  }
   if (ld <= 512) {  // short rows (e.g. 2 KB fp16 staged rows viewed as 512 words): 8 bytes per thread keeps the CTA busy
     if (even) holdout_swap_kernel<float2, 32, true><<<grid, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done, ordered);
     else holdout_swap_kernel<float2, 16, false><<<grid, 256, 0, st>>>(Z, ld, B, d, ring, cap, count0, count_dev, done, ordered);

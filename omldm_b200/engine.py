@@ -14,6 +14,8 @@ this; requests are broadcast exactly like PipelineMap.scala:54-57 does).
 """
 from __future__ import annotations
 
+import contextlib
+import os
 import time
 from typing import Any, Dict, List, Optional, Union
 
@@ -82,6 +84,22 @@ class Engine:
         self.use_priority_stream = str(self.params.extra.get("priorityStream", "false")).lower() in ("1", "true", "yes")
         self._multi_key = None
         self._multi_desc = None
+        # `pipelinedHoldout`: the holdout exchange of batch i + 1 runs on its own stream behind the training kernels of
+        # batch i (it only touches batch i + 1 and the ring), so it leaves the critical path of the step.  The caller's
+        # stream is then ordered after the engine's work only at the engine's own API boundaries (requests, queries,
+        # flush, forecasts, ...), not after every step: a batch tensor handed to train_batch must not be rewritten
+        # before the next of those, or before it is handed in again.  Off by default for that reason.
+        self.pipelined_holdout = str(self.params.extra.get("pipelinedHoldout", "false")).lower() in ("1", "true", "yes")
+        self._hold_stream = None
+        self._train_stream = None
+        self._pipe_evt: Dict[Any, Any] = {}       # per batch buffer: (inputs ready, holdout done, training done)
+        self._user_stream = None
+        # steady-state fast path of `_train_rows_now`: batch buffer -> (signature, graph, launches, pipelines to tick);
+        # `_epoch` moves whenever a request is processed, which retires every entry
+        self._fast: Dict[int, Any] = {}
+        self._epoch = 0
+        self._nvtx = os.environ.get("OMLDM_NVTX", "0") == "1"     # NVTX ranges around every step (2 us per step)
+        self._unsettled = None                    # last training event the caller's stream has not waited for yet
         # sparse streams: train straight from the sparse rows when every pipeline can (csrc/sparse_mcpa.cu)
         # instead of rebuilding the dense batch each step; opt-in until measured on hardware
         self.sparse_direct = str(self.params.extra.get("sparseDirect", "false")).lower() in ("1", "true", "yes")
@@ -95,10 +113,19 @@ class Engine:
         self._fwd_seq = 0
 
     # ============================================================================ control plane
+    def _settle(self) -> None:
+        """Order the caller's stream after everything the engine has in flight (pipelined holdout mode)."""
+        if self._unsettled is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._unsettled)
+            self._unsettled = None
+
     def handle_request(self, req: Union[str, bytes, dict, Request]) -> List[str]:
         r = parse_request(req)
         if r is None:
             return []
+        self._settle()
+        self._epoch += 1                  # pipelines may change: every captured step is looked at again
+        self._fast.clear()
         out: List[str] = []
         for cm in self.pipeline_map.flat_map(r)[:1]:   # every worker gets the same message; we are one worker
             out += self._process_control(cm.request)
@@ -106,6 +133,8 @@ class Engine:
 
     def _process_control(self, r: Request) -> List[str]:
         kind = r.request
+        self._epoch += 1
+        self._fast.clear()
         if kind in ("Create", "Delete"):
             self._graphs.clear()      # captured steps reference the old set of pipelines
             self._graph_launches.clear()
@@ -167,6 +196,7 @@ class Engine:
             p.build(d)
 
     def query(self, pipeline_id: int, response_id: int) -> List[str]:
+        self._settle()
         p = self.pipelines.get(pipeline_id)
         if p is None:
             return []
@@ -272,11 +302,36 @@ class Engine:
         if self.t_first is None:
             self.t_first = now
         B, ld = Z.shape
+        # ---- steady state: this buffer's step is captured and nothing changed since - replay without re-deriving
+        # anything (the host side of a step is what bounds small models: ~25 us per step before this path existed)
+        fast = self._fast.get(Z.data_ptr()) if not kw else None
+        if fast is not None and fast[0] == (B, ld, nnz, Z.dtype, self._epoch):
+            g, launches, tickers = fast[1], fast[2], fast[3]
+            if isinstance(g, tuple):
+                self._replay_pipelined(g, Z)
+                torch.cuda.set_stream(self._train_stream)      # cadence work is ordered after this step's kernels
+                try:
+                    for p in tickers:
+                        p.host_tick()
+                finally:
+                    torch.cuda.set_stream(self._user_stream)
+            else:
+                if self._nvtx:
+                    torch.cuda.nvtx.range_push("omldm.step.replay")
+                g.replay()
+                if self._nvtx:
+                    torch.cuda.nvtx.range_pop()
+                for p in tickers:
+                    p.host_tick()
+            _lib.add_launch_count(launches)
+            self.count += B
+            self.t_last = now
+            return
         for p in self.pipelines.values():
             if p.protocol != "SingleLearner" or self.rank == 0:
                 self._build(p, d)
-        key = (Z.data_ptr(), B, ld, nnz, Z.dtype) + tuple(p.driver.graph_key() for p in self.pipelines.values()
-                                                 if p.built and hasattr(p.driver, "graph_key"))
+        keyed = [p for p in self.pipelines.values() if p.built and hasattr(p.driver, "graph_key")]
+        key = (Z.data_ptr(), B, ld, nnz, Z.dtype) + tuple(p.driver.graph_key() for p in keyed)
         g = None
         if self.use_graphs and not kw and self._graphable(Z):
             g = self._graphs.get(key)
@@ -288,10 +343,10 @@ class Engine:
                     warnings.warn(f"CUDA graph capture failed ({e}); continuing with eager launches")
                     self.use_graphs = False
                     g = None
-        nvtx = self.device.type == "cuda"
-        if nvtx:
+        cuda = self.device.type == "cuda"
+        if cuda and self._nvtx:
             torch.cuda.nvtx.range_push("omldm.step.replay" if g is not None else "omldm.step.eager")
-        hp = self._step_stream() if nvtx else None
+        hp = self._step_stream() if cuda else None
         if hp is not None:
             # the step runs on a high-priority stream so that background work on ordinary streams (the
             # ORR weight refresh, a checkpoint copy) cannot push the hot kernels out of the SMs
@@ -299,23 +354,35 @@ class Engine:
             hp.wait_stream(user)
             ctx = torch.cuda.stream(hp)
             ctx.__enter__()
+        pipelined = isinstance(g, tuple)
         try:
-            if g is not None:
+            if pipelined:
+                self._replay_pipelined(g, Z)
+                _lib.add_launch_count(self._graph_launches[key])
+            elif g is not None:
                 g.replay()
                 _lib.add_launch_count(self._graph_launches[key])
             else:
+                self._settle()
                 self._seen[key] = self._seen.get(key, 0) + 1
                 self._device_step(Z, d, nnz, **kw)
         finally:
             if hp is not None:
                 ctx.__exit__(None, None, None)
                 user.wait_stream(hp)
-        if nvtx:
+        if cuda and self._nvtx:
             torch.cuda.nvtx.range_pop()
         self.count += B
-        for p in self.pipelines.values():
-            if p.built and (p.protocol != "SingleLearner" or self.rank == 0):
+        # cadence work of the learners / drivers (weight refresh, FGM rounds): ordered after this step's kernels, so in
+        # pipelined mode it is issued on the training stream
+        tickers = [p for p in self.pipelines.values() if p.built and (p.protocol != "SingleLearner" or self.rank == 0)]
+        tick_ctx = torch.cuda.stream(self._train_stream) if pipelined else contextlib.nullcontext()
+        with tick_ctx:
+            for p in tickers:
                 p.host_tick()
+        if g is not None and not keyed and hp is None:
+            # from now on this buffer takes the fast path, until a request changes the set of pipelines (`_epoch`)
+            self._fast[Z.data_ptr()] = ((B, ld, nnz, Z.dtype, self._epoch), g, self._graph_launches[key], tickers)
         self.t_last = time.monotonic()
 
     def _step_stream(self):
@@ -332,17 +399,79 @@ class Engine:
 
     def _capture(self, key, Z: torch.Tensor, d: int, nnz: Optional[int] = None):
         torch.cuda.synchronize(self.device)
-        g = torch.cuda.CUDAGraph()
         before = _lib.launch_count()
-        with torch.cuda.graph(g):
-            self._device_step(Z, d, nnz)
+        if self.pipelined_holdout and self.holdout_enabled and self.params.testSetSize > 0:
+            # two graphs: the holdout exchange (replayed on the holdout stream, behind the previous batch's training
+            # kernels) and the training step proper
+            gh, g = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gh):
+                self._holdout_step(Z, d)
+            with torch.cuda.graph(g):
+                self._device_step(Z, d, nnz, skip_holdout=True)
+            g = (gh, g)
+        else:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._device_step(Z, d, nnz)
         self._graph_launches[key] = _lib.launch_count() - before
         _lib.add_launch_count(-self._graph_launches[key])   # capture does not execute anything
         self._graphs[key] = g
         return g
 
-    def _device_step(self, Z: torch.Tensor, d: int, nnz: Optional[int] = None, **kw) -> None:
-        """All device work of one training step, in stream order."""
+    def _replay_pipelined(self, g, Z: torch.Tensor) -> None:
+        """Holdout graph on the holdout stream, training graph on the training stream; see `pipelinedHoldout`.
+        (set_stream instead of stream contexts: 1 us against 7 us each on the host.)"""
+        gh, gt = g
+        if self._hold_stream is None:
+            self._hold_stream = torch.cuda.Stream(device=self.device)
+            self._train_stream = torch.cuda.Stream(device=self.device)
+        ev = self._pipe_evt.get(Z.data_ptr())
+        if ev is None:
+            ev = self._pipe_evt[Z.data_ptr()] = (torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event(), [False])
+        e_in, e_hold, e_train, used = ev
+        user = self._user_stream = torch.cuda.current_stream(self.device)
+        sh, st = self._hold_stream, self._train_stream
+        if used[0]:
+            sh.wait_event(e_train)            # the previous training step on THIS buffer has finished reading it
+        e_in.record(user)                     # whatever the caller enqueued before this call (its input, a request)
+        sh.wait_event(e_in)
+        st.wait_event(e_in)
+        try:
+            torch.cuda.set_stream(sh)
+            gh.replay()
+            e_hold.record(sh)
+            st.wait_event(e_hold)
+            torch.cuda.set_stream(st)
+            gt.replay()
+            e_train.record(st)
+        finally:
+            torch.cuda.set_stream(user)
+        used[0] = True
+        self._unsettled = e_train
+
+    def _holdout_step(self, Z: torch.Tensor, d: int) -> None:
+        """The 2-in-10 holdout rule on one batch, in place (FlinkSpoke.scala:92-107)."""
+        if not (self.holdout_enabled and self.params.testSetSize > 0):
+            return
+        ld = Z.shape[1]
+        half = Z.dtype == torch.float16
+        self._ensure_holdout(ld, Z.dtype)
+        # fp16 staged rows move as raw bytes: the holdout rule is a pure row move, and an all-zero row is empty in
+        # both layouts, so the same kernel serves both with the rows viewed as fp32 words
+        Zv, ring = (Z.view(torch.float32), self.holdout.view(torch.float32)) if half else (Z, self.holdout)
+        if F.native(Z):                     # (true for CUDA batches; also under the CPU kernel emulation)
+            if self._count_dev is None:
+                self._count_dev = torch.tensor([self.count, 0], dtype=torch.int64, device=self.device)
+            # 2-in-10 holdout, evict-then-train; per-record learners need the sequential positions, mini-batch
+            # learners only the set (one exchange per ring slot)
+            ordered = any(getattr(p.learner, "mode", "") == "exact" for p in self.pipelines.values())
+            F.holdout_swap_dev(Zv, ring, d, self._count_dev, ordered=ordered)
+        else:
+            F.holdout_swap(Zv, ring, d, self.count)
+
+    def _device_step(self, Z: torch.Tensor, d: int, nnz: Optional[int] = None, skip_holdout: bool = False, **kw) -> None:
+        """All device work of one training step, in stream order (`skip_holdout`: the holdout rule has already been
+        applied to this batch on the holdout stream)."""
         B, ld = Z.shape
         if nnz is not None:
             kw = dict(kw, nnz=nnz)
@@ -350,20 +479,8 @@ class Engine:
             if p.built and hasattr(p.driver, "begin_step"):
                 p.driver.begin_step()          # fork: overlapped all-reduce of the previous step's delta
         half = Z.dtype == torch.float16
-        if self.holdout_enabled and self.params.testSetSize > 0:
-            self._ensure_holdout(ld, Z.dtype)
-            # fp16 staged rows move as raw bytes: the holdout rule is a pure row move, and an all-zero row is empty in
-            # both layouts, so the same kernel serves both with the rows viewed as fp32 words
-            Zv, ring = (Z.view(torch.float32), self.holdout.view(torch.float32)) if half else (Z, self.holdout)
-            if F.native(Z):                     # (true for CUDA batches; also under the CPU kernel emulation)
-                if self._count_dev is None:
-                    self._count_dev = torch.tensor([self.count, 0], dtype=torch.int64, device=self.device)
-                # 2-in-10 holdout, evict-then-train; per-record learners need the sequential positions, mini-batch
-                # learners only the set (one exchange per ring slot)
-                ordered = any(getattr(p.learner, "mode", "") == "exact" for p in self.pipelines.values())
-                F.holdout_swap_dev(Zv, ring, d, self._count_dev, ordered=ordered)
-            else:
-                F.holdout_swap(Zv, ring, d, self.count)
+        if not skip_holdout:
+            self._holdout_step(Z, d)
         Z32 = None
         if half and not all(p.f16_capable() for p in self.pipelines.values() if p.built or p.protocol != "SingleLearner"):
             # some pipeline has no fp16 path: expand once per step (csrc/rows_f16.cu)
@@ -468,7 +585,15 @@ class Engine:
         cur.wait_event(self.last_copy_event)
         return i, self._stage[i]
 
+    def _buffer_free(self, t: torch.Tensor) -> None:
+        """The current stream may rewrite an engine-owned batch buffer once the last training step that read it has
+        finished (pipelined holdout mode; otherwise stream order already says so)."""
+        ev = self._pipe_evt.get(t.data_ptr())
+        if ev is not None and ev[3][0]:
+            torch.cuda.current_stream(self.device).wait_event(ev[2])
+
     def _stage_done(self, i: int) -> None:
+        self._settle()
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
         self._stage_evt[i] = ev
@@ -508,6 +633,7 @@ class Engine:
         B, ld = W_host.shape[0], F.pad32(d + 2)
         if self._wire_dense[i] is None or self._wire_dense[i].shape != (B, ld):
             self._wire_dense[i] = torch.empty(B, ld, dtype=torch.float32, device=self.device)
+        self._buffer_free(self._wire_dense[i])
         F.stage_rows_f16(Wd, d, out=self._wire_dense[i])
         self.train_batch(self._wire_dense[i], d, **kw)
         self._stage_done(i)
@@ -530,6 +656,7 @@ class Engine:
             if self._srows[i] is None or self._srows[i].shape != shape:
                 self._srows[i] = torch.empty(shape, dtype=torch.float32, device=self.device)
             self._sparse_nnz = nnz
+            self._buffer_free(self._srows[i])
             F.sparse_rows(idx, val, tgt, batch, nnz, out=self._srows[i])
             self._train_rows(self._srows[i], d, nnz)
             return
@@ -542,6 +669,7 @@ class Engine:
             self._dense_i = 0
         Z = self._dense[self._dense_i]
         self._dense_i ^= 1
+        self._buffer_free(Z)
         F.densify(self._indptr, idx, val, tgt, d, out=Z, sq_out=self._sqn)
         self.train_batch(Z, d)
 
@@ -562,6 +690,7 @@ class Engine:
         return self._read_stats_host()
 
     def _read_stats_host(self) -> torch.Tensor:
+        self._settle()
         if self._loss_host is None:
             self._loss_host = torch.zeros(4, dtype=torch.float64)
             if self.device.type == "cuda":
@@ -577,6 +706,7 @@ class Engine:
         delta, resolve an FGM round that only some ranks have entered).  Call it on every rank before
         a host-side barrier, otherwise a rank may sit in a device-side rendezvous that its peers will
         never join."""
+        self._settle()
         for p in self.pipelines.values():
             if p.built and p.protocol != "SingleLearner":
                 p.driver.flush()
@@ -584,6 +714,7 @@ class Engine:
     def forecast_batch(self, Z: torch.Tensor, instances: Optional[List[DataInstance]] = None) -> List[str]:
         """Every pipeline predicts every forecasting record with its local replica
         (FlinkSpoke.scala:105, FlinkNetwork.scala:250)."""
+        self._settle()
         out: List[str] = []
         for pid, p in self.pipelines.items():
             if not p.built:
@@ -597,6 +728,7 @@ class Engine:
 
     # ============================================================================ termination / stats
     def statistics(self) -> List[Statistics]:
+        self._settle()
         out = []
         ring = self._holdout_rows()
         for pid, p in self.pipelines.items():
@@ -613,6 +745,7 @@ class Engine:
     def terminate(self) -> Optional[JobStatistics]:
         """Termination probe: device barrier, final holdout evaluation, JobStatistics on rank 0
         (StatisticsOperator.scala:93-142)."""
+        self._settle()
         for p in self.pipelines.values():
             if p.built and p.protocol != "SingleLearner":
                 p.driver.flush()
@@ -671,6 +804,7 @@ class Engine:
 
     # ============================================================================ checkpoint
     def state_dict(self) -> dict:
+        self._settle()
         return {"rank": self.rank, "world": self.world, "count": self.count, "d": self.d,
                 "registry": self.pipeline_map.state_dict(),
                 "holdout": None if self.holdout is None else self.holdout.cpu().clone(),
@@ -682,6 +816,8 @@ class Engine:
         self._sparse_nnz = sd.get("sparse_nnz")
         self._count_dev = None
         self._graphs, self._seen = {}, {}
+        self._fast.clear()
+        self._epoch += 1
         self.pipeline_map.load_state_dict(sd["registry"])
         if sd["holdout"] is not None:
             self.holdout = sd["holdout"].to(self.device)
@@ -692,6 +828,7 @@ class Engine:
             self.pipelines[pid].load_state_dict(ps)
 
     def close(self) -> None:
+        self._settle()
         if getattr(self, "watchdog", None) is not None:
             self.watchdog.stop()
             self.watchdog = None

@@ -120,19 +120,26 @@ def ptr(t: torch.Tensor | None) -> ctypes.c_void_p:
     return ctypes.c_void_p(0 if t is None else t.data_ptr())
 
 
+_replayed = 0        # kernels launched through graph replays, kept on the Python side (no native call per step)
+
+
 def launch_count() -> int:
-    """Number of kernels this library has launched since the last reset (0 on CPU-only hosts)."""
+    """Number of kernels this library has launched since the last reset (0 on CPU-only hosts): direct launches
+    counted by the library plus the kernels of replayed CUDA graphs."""
     if not have_cuda():
         return 0
-    return int(kernels().omldm_launch_count())
+    return int(kernels().omldm_launch_count()) + _replayed
 
 
 def add_launch_count(n: int) -> None:
-    """Account for kernels launched by replaying a captured CUDA graph (n per replay)."""
-    if have_cuda() and n:
-        kernels().omldm_add_launch_count(ctypes.c_longlong(n))
+    """Account for kernels launched by replaying a captured CUDA graph (n per replay; negative to take back the
+    launches counted while capturing)."""
+    global _replayed
+    _replayed += n
 
 
 def reset_launch_count() -> None:
+    global _replayed
+    _replayed = 0
     if have_cuda():
         kernels().omldm_reset_launch_count()

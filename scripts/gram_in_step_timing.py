@@ -43,8 +43,10 @@ def timeline():
 dev = torch.device("cuda", 0)
 B, d = 32768, 1000
 pool = [R.generate_batch(R.KIND_REGRESSION, d, B, seed=5, batch_index=i, wire="f16s").to(dev) for i in range(3)]
-for overlap in ("true", "false"):
-    eng = Engine(JobParameters(parallelism=1, jobName="t"), 0, 1, dev, impl="fused")
+for overlap, piped in (("true", "false"), ("true", "true"), ("false", "false")):
+    jp = JobParameters(parallelism=1, jobName="t")
+    jp.extra["pipelinedHoldout"] = piped
+    eng = Engine(jp, 0, 1, dev, impl="fused")
     eng.handle_request({"id": 1, "request": "Create", "learner": {"name": "ORR", "hyperParameters": {"lambda": 1.0, "solveEvery": 1000000, "overlapLoss": overlap}},
                         "preProcessors": [], "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": d}})
     for i in range(30):
@@ -55,9 +57,12 @@ for overlap in ("true", "false"):
     e0.record()
     for i in range(40):
         eng.train_batch(pool[i % 3], d)
+    eng.flush()
     e1.record()
     torch.cuda.synchronize()
-    print(f"overlapLoss={overlap}: {1000 * e0.elapsed_time(e1) / 40:.1f} us per step")
+    eng.flush()
+    torch.cuda.synchronize()
+    print(f"overlapLoss={overlap} pipelinedHoldout={piped}: {1000 * e0.elapsed_time(e1) / 40:.1f} us per step")
     for line in gram_phase_report():
         print(line)
     timeline()

@@ -150,3 +150,45 @@ def test_multi_pipeline_exact_batched_launch_matches_separate_pipelines():
         assert np.allclose(resp["learner"]["parameters"]["a"], o.w[:-1], rtol=2e-3, atol=2e-4), name
         assert resp["dataFitted"] == B * len(batches)
     eng.close()
+
+
+@pytest.mark.parametrize("name,hyper,kind,wire,n_bufs", [
+    ("ORR", {"lambda": 1.0, "solveEvery": 4}, R.KIND_REGRESSION, "f16s", 3),
+    ("ORR", {"lambda": 1.0, "solveEvery": 4}, R.KIND_REGRESSION, "f16s", 1),
+    ("PA", {"C": 0.1, "trainingMode": "minibatch"}, R.KIND_BINARY, "f32", 2),
+])
+def test_pipelined_holdout_gives_the_same_model_and_ring(name, hyper, kind, wire, n_bufs):
+    """`pipelinedHoldout`: the holdout exchange of batch i + 1 runs on its own stream behind the training kernels of
+    batch i.  Same weights, statistics, holdout ring and record count as the default in-graph order - with distinct
+    buffers per step and with ONE buffer refilled for every step (the exchange must then wait for the previous step)."""
+    d, B, steps = 60, 4096, 14
+
+    def run(pipelined):
+        jp = JobParameters(parallelism=1, testSetSize=64)
+        jp.extra["pipelinedHoldout"] = "true" if pipelined else "false"
+        eng = Engine(jp, device="cuda")
+        eng.handle_request({"id": 1, "request": "Create", "learner": {"name": name, "hyperParameters": hyper},
+                            "preProcessors": [], "trainingConfiguration": {"protocol": "Synchronous", "nFeatures": d}})
+        bufs = [None] * n_bufs
+        for i in range(steps):
+            src = R.generate_batch(kind, d, B, seed=3, batch_index=i, wire=wire).cuda()
+            k = i % n_bufs
+            if bufs[k] is None:
+                bufs[k] = torch.empty_like(src)
+            eng._buffer_free(bufs[k])        # what an owner of a reused buffer does in pipelined mode
+            bufs[k].copy_(src)
+            eng.train_batch(bufs[k], d)
+        out = [json.loads(o) for o in eng.handle_request({"id": 1, "request": "Query", "requestId": 5})]
+        lrn = eng.pipelines[1].learner
+        torch.cuda.synchronize()
+        res = (lrn.stats.clone(), eng.holdout.clone(), eng.count, out, any(isinstance(g, tuple) for g in eng._graphs.values()))
+        eng.close()
+        return res
+
+    s0, h0, c0, o0, piped0 = run(False)
+    s1, h1, c1, o1, piped1 = run(True)
+    assert piped1 and not piped0                      # the pipelined run really replayed split graphs
+    assert c0 == c1 and torch.equal(h0, h1)
+    assert torch.allclose(s0, s1, rtol=1e-6)
+    p0, p1 = o0[0]["learner"]["parameters"], o1[0]["learner"]["parameters"]
+    assert np.allclose(np.asarray(p0["a"]), np.asarray(p1["a"]), rtol=1e-4, atol=1e-6)
