@@ -48,7 +48,10 @@ namespace omldm {
 #endif
 constexpr int G_BK = OMLDM_GRAM_BK;               // records per stage
 constexpr int G_STAGES = OMLDM_GRAM_STAGES;
-constexpr int G_THREADS = 192;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2..5 epilogue
+#ifndef OMLDM_GRAM_THREADS
+#define OMLDM_GRAM_THREADS 384
+#endif
+constexpr int G_THREADS = OMLDM_GRAM_THREADS;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2, 3, 6..11 loss (two groups), warps 4..7 epilogue, warp 4 relay, warp 5 lead push
 constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 64 halves x 64 records = 16 KB
 constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -65,9 +68,12 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 #ifdef OMLDM_GRAM_TIMING        // tuning builds only (scripts/build_variant.sh): per-CTA phase stamps in SM cycles, read back by
                                 // tests/test_gram_f16_gpu.py::test_gram_f16_speed_report
 __device__ long long g_gram_stamp[160 * 16];   // 0..6 SM cycles per phase, 8 / 9 globaltimer ns at start / end
+__device__ long long g_gram_trace[2][5][24];   // tile 0, slice 0, both ranks: per stage use 30..53 the cycle of five events
+#define GRAM_TRACE(ev, kb) do { if (blockIdx.x < 2 && blockIdx.y == 0 && (kb) >= 30 && (kb) < 54) g_gram_trace[blockIdx.x][ev][(kb) - 30] = clock64(); } while (0)
 #define GRAM_STAMP(i) do { if ((threadIdx.x & 31) == 0) g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 16 + (i)] = (i) >= 8 ? static_cast<long long>(globaltimer_ns()) : clock64(); } while (0)
 #else
 #define GRAM_STAMP(i) do { } while (0)
+#define GRAM_TRACE(ev, kb) do { } while (0)
 #endif                            // scratch words: per half-tile arrival counters from word 8 on
 
 struct GramPush {
@@ -75,9 +81,33 @@ struct GramPush {
   int world, rank, rows_per_owner, enabled;   // enabled: 0 off, 1 tail (exact at kernel end), 2 lead (during the main loop)
 };
 
+// Prequential loss of the batch from inside the Gram kernel (optional).  The CTAs of the DIAGONAL tiles see every column
+// block of every record exactly once; while the tensor cores work on a stage, the four (otherwise idle) epilogue warps
+// of those CTAs read the same shared-memory stage, form the partial dot products z_r . w over the CTA's 128 columns
+// and add them into dots[r] (fp32 red at L2, 8 partials per record at d = 1000).  The last CTA half to finish a batch
+// slice squares and sums that slice's dots into stats[0], counts its valid rows into stats[2] and clears them; the last
+// slice writes the learning-curve sample.  No second pass over the batch, no second kernel.
+// Measured on a B200 (32 768 x 1003): correct to 1e-9 relative, but the kernel takes 48.8 us per launch against 35.6 us
+// without it - the diagonal CTAs' loss warps need 16 KB of shared-memory reads per stage on top of the 96 B/clk the MMAs
+// take of the 128 B/clk an SM delivers, so their stages are released late (main loop 56 k instead of 38 k cycles).  The
+// separate loss pass beside the kernel is faster end to end (47.6 against ~50 us per step) and stays the default;
+// this path is `lossInGram: true`.  Sharing the loss work of a column block among ALL pairs that hold it (T per block)
+// would cut the per-CTA reads four-fold; not done.
+struct GramLoss {
+  const float* wt;           // [w_0 .. w_{d-1}, b, -1, -1]: residual of a record = z . wt
+  float* dots;               // K floats, zero between launches
+  unsigned int* words;       // 3 * 128 words, zero between launches: valid rows per slice | arrivals per slice | slices done
+  double* stats;             // stats[0] += sum of squared residuals, stats[2] += valid rows
+  double* curve_ring;        // optional learning-curve ring [cap][2]
+  long long* curve_counter;
+  int curve_cap, d, enabled;
+};
+
+template <bool LOSS>     // LOSS = false: the loss code is compiled out (72 registers instead of 142, which is what lets two
+                         // blocks of the separate loss pass fit beside a CTA of this kernel)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G_THREADS, 1)
 gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ CUtensorMap tmC,
-                const __grid_constant__ GramPush push, int n, int K, int k_per_split, int T,
+                const __grid_constant__ GramPush push, const GramLoss loss, int n, int K, int k_per_split, int T,
                 uint32_t* __restrict__ scratch) {
   const uint32_t rank = cluster_ctarank();        // 0 = leader of the pair
   const int tile = blockIdx.x >> 1;
@@ -109,8 +139,11 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
   uint64_t* empty_bar = full_bar + G_STAGES;
   uint64_t* accum_bar = empty_bar + G_STAGES;
   uint64_t* push_bar = accum_bar + 1;                        // 4, one per epilogue warp
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(push_bar + 4);
+  uint64_t* ready_bar = push_bar + 4;                        // G_STAGES: "stage landed" for the loss warps of the non-leader
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ready_bar + G_STAGES);
   uint32_t* s_flag = tmem_slot + 1;
+  static_assert((3 * G_STAGES + 5) * 8 + 8 <= 256, "barrier area");
+  const bool loss_on = LOSS && loss.enabled && ti == tj;     // this CTA also forms the residual dots of its columns
 
   const int warp = threadIdx.x >> 5;
   if (warp == 0) { GRAM_STAMP(0); GRAM_STAMP(8); }
@@ -119,7 +152,8 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     tma_prefetch_desc(&tmC);
     for (int s = 0; s < G_STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], loss_on ? 5 : 1);             // the MMA commit (+ one arrival per loss warp)
+      mbar_init(&ready_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
     for (int q = 0; q < 4; ++q) mbar_init(&push_bar[q], 1);
@@ -137,8 +171,19 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+#ifdef OMLDM_GRAM_TIMING
+      long long t_empty = 0;
+#endif
       for (int kb = 0; kb < num_kb; ++kb) {
+#ifdef OMLDM_GRAM_TIMING
+        const long long te0 = clock64();
+#endif
         mbar_wait(&empty_bar[stage], phase ^ 1);
+#ifdef OMLDM_GRAM_TIMING
+        t_empty += clock64() - te0;
+        if (kb == num_kb - 1) g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 16 + 12] = t_empty;
+#endif
+        GRAM_TRACE(0, kb);
         uint8_t* sa = smem + stage * G_STAGE_BYTES;
         uint8_t* sb = sa + G_HALF_BYTES;
         // the leader's barrier counts the bytes of both CTAs
@@ -149,14 +194,78 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
         if (++stage == G_STAGES) { stage = 0; phase ^= 1; }
       }
     }
+    __syncwarp();
+    if (loss_on) {
+      // ---------------------------------------------------------- loss: close this batch slice if we are its last CTA half
+      named_bar_sync(2, 288);                      // the eight loss warps of this CTA have added their dots
+      const uint32_t lane = lane_id();
+      unsigned int last = 0;
+      if (lane == 0) {
+        __threadfence();
+        unsigned int* cnt = loss.words + 128 + blockIdx.y;
+        last = atomicAdd(cnt, 1u) == 2u * static_cast<unsigned int>(T) - 1u;   // 2 CTA halves per diagonal tile
+        if (last) *cnt = 0;
+      }
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (last) {
+        __threadfence();
+        double sq = 0.0;
+        const int k4 = (k_end - k_begin) >> 2;
+        float4* d4 = reinterpret_cast<float4*>(loss.dots + k_begin);            // k_begin is a multiple of 64
+        for (int i = static_cast<int>(lane); i < k4; i += 32) {
+          const float4 v = __ldcg(d4 + i);
+          d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          sq += static_cast<double>(v.x) * v.x + static_cast<double>(v.y) * v.y + static_cast<double>(v.z) * v.z +
+                static_cast<double>(v.w) * v.w;
+        }
+        for (int i = k_begin + 4 * k4 + static_cast<int>(lane); i < k_end; i += 32) {
+          const float v = __ldcg(loss.dots + i);
+          loss.dots[i] = 0.f;
+          sq += static_cast<double>(v) * v;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        if (lane == 0) {
+          const unsigned int nv = __ldcg(loss.words + blockIdx.y);
+          loss.words[blockIdx.y] = 0;
+          if (nv) {
+            atomicAdd(loss.stats + 0, sq);
+            atomicAdd(loss.stats + 2, static_cast<double>(nv));
+          }
+          __threadfence();
+          if (atomicAdd(loss.words + 256, 1u) == gridDim.y - 1) {               // the last slice of this launch
+            loss.words[256] = 0;
+            __threadfence();
+            if (loss.curve_ring) {
+              const long long i = *loss.curve_counter;
+              double* slot = loss.curve_ring + 2 * (i % loss.curve_cap);
+              slot[0] = __ldcg(loss.stats + 0);
+              slot[1] = __ldcg(loss.stats + 2);
+              *loss.curve_counter = i + 1;
+            }
+          }
+        }
+      }
+    }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (leader CTA only)
     if (rank == 0) {
       constexpr uint32_t idesc = make_idesc_f16(256, 256, true, true);
       int stage = 0;
       uint32_t phase = 0;
+#ifdef OMLDM_GRAM_TIMING
+      long long t_full = 0;
+#endif
       for (int kb = 0; kb < num_kb; ++kb) {
+#ifdef OMLDM_GRAM_TIMING
+        const long long tf0 = clock64();
+#endif
         mbar_wait(&full_bar[stage], phase);
+#ifdef OMLDM_GRAM_TIMING
+        t_full += clock64() - tf0;
+        if (kb == num_kb - 1 && lane_id() == 0) g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 16 + 13] = t_full;
+        if (lane_id() == 0) GRAM_TRACE(2, kb);
+#endif
         if (kb == 0) GRAM_STAMP(2);
         tc_fence_after();
         if (elect_one()) {
@@ -178,31 +287,150 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       }
     }
   } else {
-    // ------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
-    const int q = warp & 3;                        // TMEM lane quadrant this warp may read
-    const uint32_t r = lane_id();
-    const int row0 = m0 + q * 32;
-    if (push.enabled == 2 && r == 0 && row0 < n) {
-      // ---------------------------------------------------------- hub push, lead mode: hidden behind the main loop
-      uint8_t* stage_blk = smem + G_STAGES * G_STAGE_BYTES + 1024 + q * 4096;
-      const CUtensorMap* om = &push.owner[row0 / push.rows_per_owner];
+   // Warps 2..7.  Loss work (ALU heavy) runs on warps 2, 3, 6, 7 = schedulers 2 and 3 only: on the schedulers of the
+   // TMA producer (warp 0) and the MMA issuer (warp 1) it delayed their few but urgent instructions and the main loop
+   // of the diagonal tiles took 88 k instead of 38 k cycles.  Warps 4 and 5 (schedulers 0 and 1) only relay / push,
+   // i.e. mostly sleep.  The epilogue needs one warp per TMEM lane quadrant (warp & 3): warps 4..7.
+   if (warp == 4) {
+    // ------------------------------------------------------------ relay (leader CTA, loss inside): tells the peer's loss
+    // warps that a stage has landed.  The peer's TMA loads signal the LEADER's barrier, and putting this arrive into
+    // the MMA-issuing thread's loop slowed the main loop from 38 k to 58 k cycles even when it was never executed.
+    if (loss_on && rank == 0) {
+      // one lane per stage: the release at cluster scope in front of the remote arrive takes ~1 000 cycles, so a single
+      // relaying thread would pace the pipeline at one stage per 1 000 cycles (measured: main loop 88 k instead of 38 k)
+      const int l = static_cast<int>(lane_id());
+      if (l < G_STAGES) {
+        uint32_t ph = 0;
+        for (int kb = l; kb < num_kb; kb += G_STAGES) {
+          mbar_wait(&full_bar[l], ph);
+          mbar_arrive_remote_relaxed(&ready_bar[l], 1);
+          ph ^= 1;
+        }
+      }
+      __syncwarp();
+    }
+   } else if (warp == 5) {
+    // ------------------------------------------------------------ hub push, lead mode: hidden behind the main loop
+    if (push.enabled == 2 && elect_one()) {
+      uint8_t* stage_blk = smem + G_STAGES * G_STAGE_BYTES + 1024;
       uint32_t ph = 0;
-      for (int c = 0; c < 8; ++c) {
-        const int col0 = n0 + c * 32;
-        if (col0 >= n || col0 + 31 < row0) continue;
-        if ((q * 8 + c) % static_cast<int>(gridDim.y) != static_cast<int>(blockIdx.y)) continue;   // another split's block
-        mbar_expect_tx(&push_bar[q], 4096);
-        tma_load_2d(stage_blk, &tmC, &push_bar[q], col0, row0);
-        mbar_wait(&push_bar[q], ph);
+      for (int b = static_cast<int>(blockIdx.y); b < 32; b += static_cast<int>(gridDim.y)) {   // this split's share of the half tile
+        const int row0 = m0 + (b >> 3) * 32, col0 = n0 + (b & 7) * 32;
+        if (row0 >= n || col0 >= n || col0 + 31 < row0) continue;
+        mbar_expect_tx(&push_bar[0], 4096);
+        tma_load_2d(stage_blk, &tmC, &push_bar[0], col0, row0);
+        mbar_wait(&push_bar[0], ph);
         ph ^= 1;
-        tma_store_2d(om, stage_blk, col0, row0);   // into this worker's slot at the owner (NVLink)
+        tma_store_2d(&push.owner[row0 / push.rows_per_owner], stage_blk, col0, row0);   // this worker's slot at the owner (NVLink)
         tma_commit_group();
         tma_wait_group_read0();                    // the staging block is free again
       }
     }
     __syncwarp();
+   }
+   {
+    // ------------------------------------------------------------ loss warps (2, 3, 6, 7) / epilogue (4..7), both CTAs
+    const int q = warp & 3;                        // TMEM lane quadrant this warp may read
+    const uint32_t r = lane_id();
+    const int row0 = m0 + q * 32;
+    // eight loss warps in two groups: group 0 (warps 2, 3, 6, 7) takes the even stages, group 1 (warps 8..11) the odd
+    // ones - a warp needs ~950 cycles per stage (370 of them for the barrier hand-over), the MMAs 512
+    const bool loss_warp = warp == 2 || warp == 3 || warp >= 6;
+    const int lgroup = warp >= 8 ? 1 : 0;
+    static_assert(G_STAGES % 2 == 0, "the loss groups alternate over the stages");
+    if (loss_on && loss_warp) {
+      // Residual dots of this CTA's 128 columns, stage by stage, from the shared-memory tile the MMAs are reading.
+      // A lane owns one record of the stage and one 64-column chunk of it (warp w: records 16 w .. 16 w + 15; lanes
+      // 0-15 chunk 0, lanes 16-31 chunk 1): eight 16-byte loads and 64 FMAs against weights held in registers, no
+      // shuffles inside the record (a first version that spread a record over 16 lanes was latency bound: 3 260 cycles
+      // per stage against the 512 the MMAs take).
+      const int lw = warp < 4 ? warp - 2 : warp < 8 ? warp - 4 : warp - 8, ch = static_cast<int>(r) >> 4, kr = lw * (G_BK / 4) + (static_cast<int>(r) & 15);
+      float w64[64];
+#pragma unroll
+      for (int j = 0; j < 64; ++j) {
+        const int col = m0 + ch * 64 + j;
+        w64[j] = col < n ? __ldg(loss.wt + col) : 0.f;
+      }
+      const int cd = loss.d - m0;                  // the bias / valid column, if this CTA holds it
+      const bool has_valid = cd >= 0 && cd < 128 && (cd >> 6) == ch;
+      const int uv = (cd & 63) >> 3, jv = cd & 7;
+      unsigned int nvalid = 0;
+      int stage = lgroup;
+      uint32_t phase = 0;
+      const uint32_t row_off = static_cast<uint32_t>(ch * (G_BK * 128) + kr * 128), sw = static_cast<uint32_t>(kr & 7);
+#ifdef OMLDM_GRAM_TIMING
+      long long t_wait = 0, t_work = 0;
+#endif
+      for (int kb = lgroup; kb < num_kb; kb += 2) {
+#ifdef OMLDM_GRAM_TIMING
+        const long long t0 = clock64();
+#endif
+        if (r == 0) {                               // one lane polls
+          if (rank == 0) mbar_wait(&full_bar[stage], phase);
+          else mbar_wait(&ready_bar[stage], phase);      // (an acquire at cluster scope here cost ~700 cycles per stage)
+        }
+        __syncwarp();
+#ifdef OMLDM_GRAM_TIMING
+        const long long t1 = clock64();
+        t_wait += t1 - t0;
+        if (warp == 2 && r == 0) GRAM_TRACE(3, kb);
+#endif
+        const uint8_t* rowp = smem + stage * G_STAGE_BYTES + row_off;
+        uint4 raw[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) raw[u] = *reinterpret_cast<const uint4*>(rowp + ((static_cast<uint32_t>(u) ^ sw) << 4));
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const __half2* hp = reinterpret_cast<const __half2*>(&raw[u]);
+          const float2 f0 = __half22float2(hp[0]), f1 = __half22float2(hp[1]), f2 = __half22float2(hp[2]),
+                       f3 = __half22float2(hp[3]);
+          a0 = fmaf(f0.x, w64[8 * u], a0);
+          a1 = fmaf(f0.y, w64[8 * u + 1], a1);
+          a2 = fmaf(f1.x, w64[8 * u + 2], a2);
+          a3 = fmaf(f1.y, w64[8 * u + 3], a3);
+          a0 = fmaf(f2.x, w64[8 * u + 4], a0);
+          a1 = fmaf(f2.y, w64[8 * u + 5], a1);
+          a2 = fmaf(f3.x, w64[8 * u + 6], a2);
+          a3 = fmaf(f3.y, w64[8 * u + 7], a3);
+        }
+        if (has_valid) {                            // bias half != +-0: the record is not an empty row
+          uint32_t wv = 0;
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            if (u == uv) wv = jv < 2 ? raw[u].x : jv < 4 ? raw[u].y : jv < 6 ? raw[u].z : raw[u].w;
+          nvalid += (((jv & 1) ? wv >> 16 : wv) & 0x7fffu) ? 1u : 0u;
+        }
+        float acc = (a0 + a1) + (a2 + a3);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 16);                      // the record's other chunk
+        const int kg = k_begin + kb * G_BK + kr;
+        if (ch == 0 && kg < k_end) atomicAdd(loss.dots + kg, acc);
+        __syncwarp();
+        if (r == 0) mbar_arrive(&empty_bar[stage]);                        // this warp is done with the stage
+#ifdef OMLDM_GRAM_TIMING
+        t_work += clock64() - t1;
+        if (warp == 2 && r == 0) GRAM_TRACE(4, kb);
+#endif
+        stage += 2;
+        if (stage >= G_STAGES) { stage -= G_STAGES; phase ^= 1; }
+      }
+#ifdef OMLDM_GRAM_TIMING
+      if (warp == 2 && r == 0) {
+        g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 16 + 10] = t_wait;
+        g_gram_stamp[(blockIdx.y * gridDim.x + blockIdx.x) % 160 * 16 + 11] = t_work;
+      }
+#endif
+      nvalid = __reduce_add_sync(0xffffffffu, nvalid);
+      if (r == 0 && nvalid) atomicAdd(loss.words + blockIdx.y, nvalid);
+      __threadfence();                              // this warp's adds before the CTA's arrival below
+      named_bar_arrive(2, 288);                     // warp 0 collects the eight loss warps
+    }
+    if (loss_on) named_bar_sync(3, 320);            // warps 2..11: the epilogue below reuses the stage memory - not before
+                                                    // the slowest loss warp has read its last stage
+    if (warp >= 4 && warp < 8) {
+    __syncwarp();
     mbar_wait(accum_bar, 0);
-    if (warp == 2) GRAM_STAMP(3);
+    if (warp == 4) GRAM_STAMP(3);
     tc_fence_after();
 #pragma unroll 1
     for (int c = 0; c < 8; ++c) {
@@ -223,15 +451,15 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
         tma_commit_group();
       }
     }
-    if (warp == 2) GRAM_STAMP(4);
+    if (warp == 4) GRAM_STAMP(4);
     if (r == 0) tma_wait_group0();
     __syncwarp();
-    if (warp == 2) GRAM_STAMP(5);
+    if (warp == 4) GRAM_STAMP(5);
 
     if (push.enabled == 1) {
       // -------------------------------------------------------- hub push, tail mode: by the last CTA of this half tile
       named_bar_sync(1, 128);                      // the reductions of all four epilogue warps are complete
-      if (threadIdx.x == 64) {
+      if (threadIdx.x == 128) {
         __threadfence();
         uint32_t* cnt = scratch + GS_TILE0 + 2 * tile + rank;
         const uint32_t prev = atomicAdd(cnt, 1u);
@@ -269,6 +497,8 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
         }
       }
     }
+    }   // epilogue warps
+   }
   }
 
   tc_fence_before();
@@ -306,6 +536,9 @@ using namespace omldm;
 extern "C" size_t omldm_gram_f16_scratch_words(void) { return 512; }
 
 #ifdef OMLDM_GRAM_TIMING
+extern "C" int omldm_gram_f16_trace(long long* out_host) {
+  return cudaMemcpyFromSymbol(out_host, g_gram_trace, sizeof(long long) * 2 * 5 * 24) == cudaSuccess ? 0 : -1;
+}
 extern "C" int omldm_gram_f16_stamps(long long* out_host) {
   return cudaMemcpyFromSymbol(out_host, g_gram_stamp, sizeof(long long) * 160 * 16) == cudaSuccess ? 0 : -1;
 }
@@ -325,8 +558,15 @@ extern "C" int omldm_gram_f16_rows_per_split(int K, int n, int ksplit) {
   return ((K + ksplit - 1) / ksplit + G_BK - 1) / G_BK * G_BK;
 }
 
+extern "C" size_t omldm_gram_f16_loss_words(void) { return 3 * 128; }
+
 extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers,
                               uint32_t* scratch, int ksplit, void* stream) {
+  return omldm_gram_f16_loss(Z, ld, K, n, C, ldc, peers, scratch, ksplit, nullptr, stream);
+}
+
+extern "C" int omldm_gram_f16_loss(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers,
+                                   uint32_t* scratch, int ksplit, const omldm_gram_loss* lossd, void* stream) {
   if (K <= 0) return 0;
   if (ld < 64 || (ld & 63)) return set_error_msg("gram_f16: the row pitch must be a multiple of 64 halves");
   if (reinterpret_cast<uintptr_t>(Z) & 127) return set_error_msg("gram_f16: rows must be 128-byte aligned");
@@ -352,6 +592,17 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
       if (encode_g(&push.owner[p], peers->owner_base[p], n, n, ldc)) return -1;
     for (int p = peers->world; p < 16; ++p) push.owner[p] = push.owner[0];
   }
+  GramLoss loss;
+  memset(&loss, 0, sizeof(loss));
+  if (lossd) {
+    if (!lossd->wt || !lossd->dots || !lossd->words || !lossd->stats) return set_error_msg("gram_f16: incomplete loss descriptor");
+    if (lossd->d < 0 || lossd->d + 3 > n) return set_error_msg("gram_f16: loss needs n >= d + 3");
+    if (reinterpret_cast<uintptr_t>(lossd->dots) & 15) return set_error_msg("gram_f16: dots must be 16-byte aligned");
+    if (lossd->curve_ring && (lossd->curve_cap <= 0 || !lossd->curve_counter)) return set_error_msg("gram_f16: curve ring without counter");
+    loss.wt = lossd->wt; loss.dots = lossd->dots; loss.words = lossd->words; loss.stats = lossd->stats;
+    loss.curve_ring = lossd->curve_ring; loss.curve_counter = lossd->curve_counter; loss.curve_cap = lossd->curve_cap;
+    loss.d = lossd->d; loss.enabled = 1;
+  }
   // split the batch axis so that the pairs fill the 74 SM pairs; at least 4 stages of work per CTA
   const int k_per_split = omldm_gram_f16_rows_per_split(K, n, ksplit);
   const int gy = (K + k_per_split - 1) / k_per_split;
@@ -359,15 +610,25 @@ extern "C" int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 15]) {                       // once per device, never inside a graph capture
-    cudaError_t e = cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM + G_LEAD_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gram_f16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM + G_LEAD_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gram_f16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM + G_LEAD_BYTES);
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gram_f16)", e);
     // leave the SM at its largest shared-memory carve-out so that blocks of the loss pass fit beside a Gram CTA
-    cudaFuncSetAttribute(gram_f16_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(gram_f16_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(gram_f16_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_set[dev & 15] = true;
   }
   dim3 grid(2 * tiles, gy);
   const int smem_bytes = G_SMEM + (push.enabled == 2 ? G_LEAD_BYTES : 0);
-  gram_f16_kernel<<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, n, K, k_per_split,
-                                                                                    T, scratch);
+  if (loss.enabled && gy > 128) return set_error_msg("gram_f16: more than 128 batch slices with the loss inside");
+  // without the loss inside, warps 8..11 have no role: 256 threads, so that two blocks of the separate loss pass still
+  // fit beside a CTA (71 x 256 + 2 x 80 x 256 registers)
+  if (loss.enabled)
+    gram_f16_kernel<true><<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
+                                                                                            k_per_split, T, scratch);
+  else
+    gram_f16_kernel<false><<<grid, 256, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
+                                                                                       k_per_split, T, scratch);
   return check_launch("gram_f16_kernel");
 }

@@ -64,6 +64,24 @@ typedef struct omldm_gram_peers {
                                 copies it).  1: lead push - the slots receive C as it was BEFORE this call, copied while
                                 the MMAs run (free); run omldm_sync_gram_push before the slots are read. */
 } omldm_gram_peers;
+/* Optional: the prequential loss of the batch from inside the same kernel (the CTAs of the diagonal tiles form the
+ * residual dots z . wt from the shared-memory stages the MMAs are reading; no second pass over the batch).
+ * stats[0] += sum over valid rows of (z . wt)^2, stats[2] += #valid rows; with curve_ring, one learning-curve sample
+ * (stats[0], stats[2]) per call like omldm_curve_sample.  dots: K floats, words: omldm_gram_f16_loss_words() uint32 -
+ * both zero before the first call (the kernel leaves them zero), private to one stream of calls. */
+typedef struct omldm_gram_loss {
+  const float* wt;           /* d + 3 floats: [w_0 .. w_{d-1}, b, -1, -1] */
+  float* dots;
+  unsigned int* words;
+  double* stats;
+  double* curve_ring;        /* [curve_cap][2] or NULL */
+  long long* curve_counter;
+  int curve_cap;
+  int d;
+} omldm_gram_loss;
+size_t omldm_gram_f16_loss_words(void);
+int omldm_gram_f16_loss(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers_host,
+                        uint32_t* scratch, int ksplit, const omldm_gram_loss* loss_host, void* stream);
 size_t omldm_gram_f16_scratch_words(void);
 int omldm_gram_f16_rows_per_split(int K, int n, int ksplit);   /* records per batch-axis split the kernel will use */
 int omldm_gram_f16(const void* Z, int ld, int K, int n, float* C, int ldc, const omldm_gram_peers* peers_host,

@@ -249,6 +249,11 @@ class GpuORR(GpuLearner):
         self._drain = None
         self._fork = None
         self.overlap = str(_h(hyper, ["overlapLoss"], "true")).lower() in ("1", "true", "yes")
+        # fp16 rows on a GPU: form the prequential loss inside the Gram kernel (csrc/gram_f16.cu) instead of a pass
+        # of its own beside it
+        self.loss_in_gram = str(_h(hyper, ["lossInGram"], "false")).lower() in ("1", "true", "yes")
+        self._gl_ws = None
+        self._gl_desc = None
         self._pending = None
         self._install_at = 0
         self._w_next = None
@@ -319,15 +324,29 @@ class GpuORR(GpuLearner):
         the global statistics, valid after a `gather()`."""
         self._hub = driver
 
-    def _gram(self, Z, ks, n):
+    def _loss_desc(self, B: int):
+        """Descriptor of the in-kernel loss (workspace sized for the largest batch seen; rebuilt when the learning-curve
+        ring appears or the batch grows)."""
+        key = (B, None if self.curve_ring is None else self.curve_ring.data_ptr(), self.wt.data_ptr())
+        if self._gl_desc is None or self._gl_desc[0][0] < B or self._gl_desc[0][1:] != key[1:]:
+            if self._gl_ws is None or self._gl_ws[0].numel() < B + 64:
+                self._gl_ws = F.gram_loss_workspace(B, self.device)
+            self._gl_desc = (key, F.make_gram_loss(self.wt, self.d, self.stats, self._gl_ws[0], self._gl_ws[1],
+                                                   self.curve_ring, self.curve_count))
+        return self._gl_desc[1]
+
+    def _gram(self, Z, ks, n, with_loss: bool = False):
         if Z.dtype == torch.float16:
             hub = self._hub
+            loss = self._loss_desc(Z.shape[0]) if with_loss else None
             if hub is not None and Z.is_cuda:
-                F.gram_f16(Z, self.d + 3, self.dG, scratch=hub.scratch, peers=hub.peers)
+                F.gram_f16(Z, self.d + 3, self.dG, scratch=hub.scratch, peers=hub.peers, loss=loss)
             else:
-                F.gram_f16(Z, self.d + 3, self.dG, scratch=self._gram_scratch)
+                F.gram_f16(Z, self.d + 3, self.dG, scratch=self._gram_scratch, loss=loss)
                 if hub is not None:
                     hub.push()
+            if with_loss:
+                self._curve_sampled = self.curve_ring is not None
             return
         if self._scatter is not None and Z.is_cuda:
             F.gemm_outer_scatter(Z, Z, self._scatter.peer_copy_ptrs(), self.ldg // self._scatter.k, self.ldg,
@@ -357,6 +376,9 @@ class GpuORR(GpuLearner):
     def fit_batch(self, Z):
         n = self.d + 2
         ks = max(1, min(self.ksplit, Z.shape[0] // 64))
+        if Z.is_cuda and Z.dtype == torch.float16 and self.loss_in_gram and F.native(Z) and not F._lib._emulated:
+            self._gram(Z, ks, n, with_loss=True)     # one kernel: Gram update, hub push and prequential loss
+            return
         if Z.is_cuda and self.overlap:
             # fork: the prequential-loss pass (HBM-bound) runs beside the Gram GEMM (tensor-bound);
             # they touch disjoint outputs and both only read Z

@@ -276,20 +276,48 @@ class GramPeers(ctypes.Structure):
                 ("rows_per_owner", ctypes.c_int), ("lead", ctypes.c_int)]
 
 
+class GramLoss(ctypes.Structure):
+    """omldm_gram_loss: the prequential loss formed inside the Gram kernel (csrc/gram_f16.cu)."""
+    _fields_ = [("wt", ctypes.c_void_p), ("dots", ctypes.c_void_p), ("words", ctypes.c_void_p), ("stats", ctypes.c_void_p),
+                ("curve_ring", ctypes.c_void_p), ("curve_counter", ctypes.c_void_p), ("curve_cap", ctypes.c_int),
+                ("d", ctypes.c_int)]
+
+
+def gram_loss_workspace(max_batch: int, device):
+    """(dots, words) for `gram_f16(..., loss=)`: zero before the first call, left zero by every call."""
+    return (torch.zeros(max_batch + 64, dtype=torch.float32, device=device),
+            torch.zeros(3 * 128, dtype=torch.int32, device=device))
+
+
+def make_gram_loss(wt: torch.Tensor, d: int, stats: torch.Tensor, dots: torch.Tensor, words: torch.Tensor,
+                   curve_ring: Optional[torch.Tensor] = None, curve_counter: Optional[torch.Tensor] = None) -> GramLoss:
+    g = GramLoss()
+    g.wt, g.dots, g.words, g.stats = wt.data_ptr(), dots.data_ptr(), words.data_ptr(), stats.data_ptr()
+    g.curve_ring = curve_ring.data_ptr() if curve_ring is not None else None
+    g.curve_counter = curve_counter.data_ptr() if curve_ring is not None else None
+    g.curve_cap = curve_ring.shape[0] if curve_ring is not None else 0
+    g.d = d
+    return g
+
+
 def gram_f16_scratch(device) -> torch.Tensor:
     return torch.zeros(512, dtype=torch.int32, device=device)
 
 
 def gram_f16(Zh: torch.Tensor, n: int, C: torch.Tensor, scratch: Optional[torch.Tensor] = None,
-             peers: Optional[GramPeers] = None, ksplit: int = 0) -> None:
+             peers: Optional[GramPeers] = None, ksplit: int = 0, loss: Optional[GramLoss] = None) -> None:
     """C[:n, :n] (upper 32 x 32 blocks) += Zh[:, :n]^T Zh[:, :n] on the tcgen05 CTA-pair kernel (csrc/gram_f16.cu).
-    With `peers`, the updated rows of C (this worker's running sum) are also copied into the worker's slot at the GPU
-    that owns them."""
+    With `peers`, the rows of C (this worker's running sum) are also copied into the worker's slot at the GPU
+    that owns them.  With `loss` (native path only), the same kernel adds the batch's squared residuals and valid-row
+    count to the statistics the descriptor names - what `sq_residual_f16s` does in a pass of its own."""
     if native(Zh, C):
-        _lib.check(_k().omldm_gram_f16(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(n), _p(C), _i(C.stride(0)),
-                                       ctypes.byref(peers) if peers is not None else None, _p(scratch), _i(ksplit),
-                                       _lib.stream_ptr()), "gram_f16")
+        _lib.check(_k().omldm_gram_f16_loss(_p(Zh), _i(Zh.stride(0)), _i(Zh.shape[0]), _i(n), _p(C), _i(C.stride(0)),
+                                            ctypes.byref(peers) if peers is not None else None, _p(scratch), _i(ksplit),
+                                            ctypes.byref(loss) if loss is not None else None,
+                                            _lib.stream_ptr()), "gram_f16")
         return
+    if loss is not None:
+        raise ValueError("gram_f16: the in-kernel loss exists on the native path only")
     if Zh.is_cuda:      # PyTorch baseline on the GPU: cuBLAS fp16 GEMM with fp32 output, whole matrix
         X = Zh[:, :pad32(n)] if pad32(n) <= Zh.shape[1] else Zh
         G = torch.mm(X.t(), X, out_dtype=torch.float32)

@@ -177,6 +177,18 @@ def gram_phase_report():
         ok = (st[:, i + 1] > 0) & (st[:, i] > 0)
         if ok.any():
             out.append(f"  {nm:20s} cycles: median {int(np.median(dt[ok]))}  min {int(dt[ok].min())}  max {int(dt[ok].max())}")
+    full = buf.reshape(160, 16)[:140]
+    for rk in (0, 1):                                   # loss warps of the diagonal-tile CTAs, by rank in the pair
+        sel = (full[:, 11] > 0) & ((np.arange(140) % 20) % 2 == rk)
+        if sel.any():
+            out.append(f"  loss warp, rank {rk}: waiting {int(np.median(full[sel, 10]))} cycles, working {int(np.median(full[sel, 11]))} cycles (median of {int(sel.sum())} CTAs)")
+    diag_tiles = {0, 4, 7, 9}
+    for name, sel_fn in (("diagonal", lambda t: t in diag_tiles), ("off-diagonal", lambda t: t not in diag_tiles)):
+        idx = np.array([i for i in range(140) if sel_fn((i % 20) // 2)])
+        lead, both = idx[idx % 2 == 0], idx
+        if full[both, 12].any():
+            out.append(f"  {name} tiles: producer waited for a free stage {int(np.median(full[both, 12]))} cycles, "
+                       f"MMA warp waited for data {int(np.median(full[lead, 13]))} cycles (totals over the main loop, median)")
     ok = st[:, 6] > 0
     if ok.any():
         tot, ns = (st[:, 6] - st[:, 0])[ok], (st[:, 9] - st[:, 8])[ok]
@@ -201,3 +213,41 @@ def test_loss_pass_in_gram_order_matches_reference(B, d):
         torch.cuda.synchronize()
         assert int(st[2]) == int(valid.sum())
         assert abs(float(st[0]) - ref) <= 1e-5 * max(1.0, ref), (like_gram, float(st[0]), ref)
+
+
+@pytest.mark.parametrize("K,d,empty_every", [(32768, 1000, 0), (4096, 1000, 7), (1500, 509, 5), (640, 200, 3), (300, 28, 4),
+                                             (20000, 125, 0)])
+def test_loss_inside_the_gram_kernel_matches_the_separate_pass(K, d, empty_every):
+    """`gram_f16(..., loss=)`: the diagonal-tile CTAs form the residual dots from the shared-memory stages while the MMAs
+    run.  Same squared-residual sum and valid-row count as sq_residual_f16s and as PyTorch in fp64, the same Gram matrix
+    as without it, the learning-curve sample written, and the workspace left zero - three calls in a row."""
+    n = d + 3
+    ldg = F.pad64(n)
+    C = torch.zeros(ldg, ldg, device="cuda")
+    C2 = torch.zeros(ldg, ldg, device="cuda")
+    wt = (torch.randn(n, device="cuda") * 0.1)
+    wt[d + 1:] = -1.0
+    st = torch.zeros(4, dtype=torch.float64, device="cuda")
+    st_ref = torch.zeros(4, dtype=torch.float64, device="cuda")
+    dots, words = F.gram_loss_workspace(K, "cuda")
+    ring = torch.zeros(8, 2, dtype=torch.float64, device="cuda")
+    cnt = torch.zeros(2, dtype=torch.int64, device="cuda")
+    desc = F.make_gram_loss(wt, d, st, dots, words, ring, cnt)
+    exact = 0.0
+    nvalid = 0
+    for step in range(3):
+        Zh = _rows(K, d, seed=10 + step, empty_every=empty_every)
+        F.gram_f16(Zh, n, C, loss=desc)
+        F.gram_f16(Zh, n, C2)
+        F.sq_residual_f16s(Zh, d, wt, st_ref)
+        torch.cuda.synchronize()
+        valid = Zh[:, d] != 0
+        r = (Zh[:, :n].double() @ wt.double())[valid]
+        exact += float((r * r).sum())
+        nvalid += int(valid.sum())
+        assert float(st[2]) == nvalid == float(st_ref[2]), (step, float(st[2]), nvalid)
+        assert abs(float(st[0]) - exact) <= 1e-4 * max(exact, 1.0), (step, float(st[0]), exact)
+        assert abs(float(st[0]) - float(st_ref[0])) <= 1e-4 * max(exact, 1.0)
+        assert int(cnt[0]) == step + 1 and float(ring[step, 0]) == float(st[0]) and float(ring[step, 1]) == nvalid
+        assert float(dots.abs().max()) == 0.0 and int(words.abs().max()) == 0          # workspace clean for the next call
+    assert torch.allclose(C, C2, rtol=1e-5, atol=1e-3)         # split-K partials meet in a different order
