@@ -49,9 +49,9 @@ namespace omldm {
 constexpr int G_BK = OMLDM_GRAM_BK;               // records per stage
 constexpr int G_STAGES = OMLDM_GRAM_STAGES;
 #ifndef OMLDM_GRAM_THREADS
-#define OMLDM_GRAM_THREADS 384
+#define OMLDM_GRAM_THREADS 256
 #endif
-constexpr int G_THREADS = OMLDM_GRAM_THREADS;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2, 3, 6..11 loss (two groups), warps 4..7 epilogue, warp 4 relay, warp 5 lead push
+constexpr int G_THREADS = OMLDM_GRAM_THREADS;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2, 3, 6, 7 loss (two groups), warps 4..7 epilogue, warp 4 relay, warp 5 lead push
 constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 64 halves x 64 records = 16 KB
 constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -81,18 +81,21 @@ struct GramPush {
   int world, rank, rows_per_owner, enabled;   // enabled: 0 off, 1 tail (exact at kernel end), 2 lead (during the main loop)
 };
 
-// Prequential loss of the batch from inside the Gram kernel (optional).  The CTAs of the DIAGONAL tiles see every column
-// block of every record exactly once; while the tensor cores work on a stage, the four (otherwise idle) epilogue warps
-// of those CTAs read the same shared-memory stage, form the partial dot products z_r . w over the CTA's 128 columns
-// and add them into dots[r] (fp32 red at L2, 8 partials per record at d = 1000).  The last CTA half to finish a batch
-// slice squares and sums that slice's dots into stats[0], counts its valid rows into stats[2] and clears them; the last
-// slice writes the learning-curve sample.  No second pass over the batch, no second kernel.
-// Measured on a B200 (32 768 x 1003): correct to 1e-9 relative, but the kernel takes 48.8 us per launch against 35.6 us
-// without it - the diagonal CTAs' loss warps need 16 KB of shared-memory reads per stage on top of the 96 B/clk the MMAs
-// take of the 128 B/clk an SM delivers, so their stages are released late (main loop 56 k instead of 38 k cycles).  The
-// separate loss pass beside the kernel is faster end to end (47.6 against ~50 us per step) and stays the default;
-// this path is `lossInGram: true`.  Sharing the loss work of a column block among ALL pairs that hold it (T per block)
-// would cut the per-CTA reads four-fold; not done.
+// Prequential loss of the batch from inside the Gram kernel (optional).  A 256-column block of the records sits in the
+// shared memory of every pair whose tile touches it - as the A side of tiles (c, j >= c), as the B side of tiles
+// (i < c, c): T pairs per block.  Each of them takes one T-th of the records of a stage: while the tensor cores work on the
+// stage, two loss warps per CTA (one per operand side) read those records' 128 columns, form the partial dot products
+// z_r . w and add them into dots[r] (fp32 red at L2; 2 T partials per record).  The last CTA to finish a batch slice
+// squares and sums that slice's dots into stats[0], counts its valid rows into stats[2] and clears them; the last slice
+// writes the learning-curve sample.  No second pass over the batch, no second kernel.
+// Measured (B200, 32 768 x 1003): correct to 1e-9 relative, but 47.6 us per launch against 35.5 us without the loss, and
+// 53.5 against 47.2 us per engine step - a loss warp needs ~700 cycles of work plus ~650 cycles of barrier hand-over per
+// stage it owns (two groups: 1 024 available), so stages are released late and the main loop takes 51 k instead of 38 k
+// cycles.  The separate loss pass beside the kernel therefore stays the default; this path is `lossInGram: true`.
+// Things that were tried on the way (each measured): the loss on the diagonal tiles' CTAs only (48.8 us, those CTAs
+// then pace the kernel); the remote "stage landed" arrive issued by the MMA thread (the mere presence of that branch in
+// its loop: main loop 58 k cycles) or by one relay thread with a release at cluster scope (~1 000 cycles each); every
+// T-th record per holder (16-way bank conflicts); generic instead of shared-space loads.
 struct GramLoss {
   const float* wt;           // [w_0 .. w_{d-1}, b, -1, -1]: residual of a record = z . wt
   float* dots;               // K floats, zero between launches
@@ -143,7 +146,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ready_bar + G_STAGES);
   uint32_t* s_flag = tmem_slot + 1;
   static_assert((3 * G_STAGES + 5) * 8 + 8 <= 256, "barrier area");
-  const bool loss_on = LOSS && loss.enabled && ti == tj;     // this CTA also forms the residual dots of its columns
+  const bool loss_on = LOSS && loss.enabled;                 // this CTA also forms residual dots (its share of the records)
 
   const int warp = threadIdx.x >> 5;
   if (warp == 0) { GRAM_STAMP(0); GRAM_STAMP(8); }
@@ -152,7 +155,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     tma_prefetch_desc(&tmC);
     for (int s = 0; s < G_STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], loss_on ? 5 : 1);             // the MMA commit (+ one arrival per loss warp)
+      mbar_init(&empty_bar[s], loss_on ? (diag ? 2 : 3) : 1);  // the MMA commit (+ one arrival per loss warp of the stage's group)
       mbar_init(&ready_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
@@ -197,13 +200,13 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     __syncwarp();
     if (loss_on) {
       // ---------------------------------------------------------- loss: close this batch slice if we are its last CTA half
-      named_bar_sync(2, 288);                      // the eight loss warps of this CTA have added their dots
+      named_bar_sync(2, 160);                      // the four loss warps of this CTA have added their dots
       const uint32_t lane = lane_id();
       unsigned int last = 0;
       if (lane == 0) {
         __threadfence();
         unsigned int* cnt = loss.words + 128 + blockIdx.y;
-        last = atomicAdd(cnt, 1u) == 2u * static_cast<unsigned int>(T) - 1u;   // 2 CTA halves per diagonal tile
+        last = atomicAdd(cnt, 1u) == gridDim.x - 1u;             // every CTA of the slice contributes
         if (last) *cnt = 0;
       }
       last = __shfl_sync(0xffffffffu, last, 0);
@@ -333,31 +336,32 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     const int q = warp & 3;                        // TMEM lane quadrant this warp may read
     const uint32_t r = lane_id();
     const int row0 = m0 + q * 32;
-    // eight loss warps in two groups: group 0 (warps 2, 3, 6, 7) takes the even stages, group 1 (warps 8..11) the odd
-    // ones - a warp needs ~950 cycles per stage (370 of them for the barrier hand-over), the MMAs 512
+    // four loss warps: warps 2 / 3 (A side / B side) take the even stages, warps 6 / 7 the odd ones - a warp needs most
+    // of two stage periods per stage (~370 cycles of it for the barrier hand-over), the MMAs 512 cycles
     const bool loss_warp = warp == 2 || warp == 3 || warp >= 6;
-    const int lgroup = warp >= 8 ? 1 : 0;
+    const int lgroup = warp >= 6 ? 1 : 0, side = warp & 1;
     static_assert(G_STAGES % 2 == 0, "the loss groups alternate over the stages");
     if (loss_on && loss_warp) {
-      // Residual dots of this CTA's 128 columns, stage by stage, from the shared-memory tile the MMAs are reading.
-      // A lane owns one record of the stage and one 64-column chunk of it (warp w: records 16 w .. 16 w + 15; lanes
-      // 0-15 chunk 0, lanes 16-31 chunk 1): eight 16-byte loads and 64 FMAs against weights held in registers, no
-      // shuffles inside the record (a first version that spread a record over 16 lanes was latency bound: 3 260 cycles
-      // per stage against the 512 the MMAs take).
-      const int lw = warp < 4 ? warp - 2 : warp < 8 ? warp - 4 : warp - 8, ch = static_cast<int>(r) >> 4, kr = lw * (G_BK / 4) + (static_cast<int>(r) & 15);
+      // Side A: the CTA's accumulator-row columns [m0, m0 + 128), this pair is holder tj of that block; side B (off the
+      // diagonal only): columns [b0, b0 + 128), holder ti.  Holder h of T takes the h-th T-th of a stage's records.
+      // A lane owns one 64-column chunk (lanes 0-15 chunk 0, 16-31 chunk 1) and every 16th of those records: eight
+      // 16-byte loads and 64 FMAs per record against weights held in registers.
+      const bool active = side == 0 || !diag;
+      const int cbase = side == 0 ? m0 : b0, holder = side == 0 ? tj : ti;
+      const int ch = static_cast<int>(r) >> 4, slot = static_cast<int>(r) & 15;
       float w64[64];
 #pragma unroll
       for (int j = 0; j < 64; ++j) {
-        const int col = m0 + ch * 64 + j;
-        w64[j] = col < n ? __ldg(loss.wt + col) : 0.f;
+        const int col = cbase + ch * 64 + j;
+        w64[j] = (active && col < n) ? __ldg(loss.wt + col) : 0.f;
       }
-      const int cd = loss.d - m0;                  // the bias / valid column, if this CTA holds it
-      const bool has_valid = cd >= 0 && cd < 128 && (cd >> 6) == ch;
+      const int cd = loss.d - cbase;               // the bias / valid column, if this side holds it
+      const bool has_valid = active && cd >= 0 && cd < 128 && (cd >> 6) == ch;
       const int uv = (cd & 63) >> 3, jv = cd & 7;
       unsigned int nvalid = 0;
       int stage = lgroup;
       uint32_t phase = 0;
-      const uint32_t row_off = static_cast<uint32_t>(ch * (G_BK * 128) + kr * 128), sw = static_cast<uint32_t>(kr & 7);
+      const uint32_t side_off = static_cast<uint32_t>(side * G_HALF_BYTES + ch * (G_BK * 128));
 #ifdef OMLDM_GRAM_TIMING
       long long t_wait = 0, t_work = 0;
 #endif
@@ -365,52 +369,70 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
 #ifdef OMLDM_GRAM_TIMING
         const long long t0 = clock64();
 #endif
-        if (r == 0) {                               // one lane polls
-          if (rank == 0) mbar_wait(&full_bar[stage], phase);
-          else mbar_wait(&ready_bar[stage], phase);      // (an acquire at cluster scope here cost ~700 cycles per stage)
-        }
-        __syncwarp();
+        if (active) {
+          if (r == 0) {                             // one lane polls
+            if (rank == 0) mbar_wait(&full_bar[stage], phase);
+            else mbar_wait(&ready_bar[stage], phase);      // (an acquire at cluster scope here cost ~700 cycles per stage)
+          }
+          __syncwarp();
 #ifdef OMLDM_GRAM_TIMING
-        const long long t1 = clock64();
-        t_wait += t1 - t0;
-        if (warp == 2 && r == 0) GRAM_TRACE(3, kb);
+          const long long t1 = clock64();
+          t_wait += t1 - t0;
+          if (warp == 2 && r == 0) GRAM_TRACE(3, kb);
 #endif
-        const uint8_t* rowp = smem + stage * G_STAGE_BYTES + row_off;
-        uint4 raw[8];
+          const uint32_t base = smem_u32(smem) + static_cast<uint32_t>(stage * G_STAGE_BYTES) + side_off;
+          // holder h takes the records [h * share, (h + 1) * share) of the stage: consecutive records keep the 16-byte
+          // loads of a half warp on different banks (every T-th record put them all on two: 917 cycles per stage)
+          const int share = (G_BK + T - 1) / T, iters = (share + 15) / 16;   // the same count in every lane (shuffle below)
+          for (int it = 0; it < iters; ++it) {
+            const int in_share = slot + 16 * it, kr_raw = holder * share + in_share;
+            const bool live = in_share < share && kr_raw < G_BK;
+            const int kr = live ? kr_raw : 0;
+            const uint32_t rowp = base + static_cast<uint32_t>(kr) * 128u;
+            const uint32_t sw = static_cast<uint32_t>(kr & 7);
+            uint4 raw[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) raw[u] = *reinterpret_cast<const uint4*>(rowp + ((static_cast<uint32_t>(u) ^ sw) << 4));
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            for (int u = 0; u < 8; ++u) raw[u] = lds_v4(rowp + ((static_cast<uint32_t>(u) ^ sw) << 4));
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const __half2* hp = reinterpret_cast<const __half2*>(&raw[u]);
-          const float2 f0 = __half22float2(hp[0]), f1 = __half22float2(hp[1]), f2 = __half22float2(hp[2]),
-                       f3 = __half22float2(hp[3]);
-          a0 = fmaf(f0.x, w64[8 * u], a0);
-          a1 = fmaf(f0.y, w64[8 * u + 1], a1);
-          a2 = fmaf(f1.x, w64[8 * u + 2], a2);
-          a3 = fmaf(f1.y, w64[8 * u + 3], a3);
-          a0 = fmaf(f2.x, w64[8 * u + 4], a0);
-          a1 = fmaf(f2.y, w64[8 * u + 5], a1);
-          a2 = fmaf(f3.x, w64[8 * u + 6], a2);
-          a3 = fmaf(f3.y, w64[8 * u + 7], a3);
-        }
-        if (has_valid) {                            // bias half != +-0: the record is not an empty row
-          uint32_t wv = 0;
+            for (int u = 0; u < 8; ++u) {
+              const __half2* hp = reinterpret_cast<const __half2*>(&raw[u]);
+              const float2 f0 = __half22float2(hp[0]), f1 = __half22float2(hp[1]), f2 = __half22float2(hp[2]),
+                           f3 = __half22float2(hp[3]);
+              a0 = fmaf(f0.x, w64[8 * u], a0);
+              a1 = fmaf(f0.y, w64[8 * u + 1], a1);
+              a2 = fmaf(f1.x, w64[8 * u + 2], a2);
+              a3 = fmaf(f1.y, w64[8 * u + 3], a3);
+              a0 = fmaf(f2.x, w64[8 * u + 4], a0);
+              a1 = fmaf(f2.y, w64[8 * u + 5], a1);
+              a2 = fmaf(f3.x, w64[8 * u + 6], a2);
+              a3 = fmaf(f3.y, w64[8 * u + 7], a3);
+            }
+            if (has_valid && live) {                // bias half != +-0: the record is not an empty row
+              uint32_t wv = 0;
 #pragma unroll
-          for (int u = 0; u < 8; ++u)
-            if (u == uv) wv = jv < 2 ? raw[u].x : jv < 4 ? raw[u].y : jv < 6 ? raw[u].z : raw[u].w;
-          nvalid += (((jv & 1) ? wv >> 16 : wv) & 0x7fffu) ? 1u : 0u;
-        }
-        float acc = (a0 + a1) + (a2 + a3);
-        acc += __shfl_xor_sync(0xffffffffu, acc, 16);                      // the record's other chunk
-        const int kg = k_begin + kb * G_BK + kr;
-        if (ch == 0 && kg < k_end) atomicAdd(loss.dots + kg, acc);
-        __syncwarp();
-        if (r == 0) mbar_arrive(&empty_bar[stage]);                        // this warp is done with the stage
+              for (int u = 0; u < 8; ++u)
+                if (u == uv) wv = jv < 2 ? raw[u].x : jv < 4 ? raw[u].y : jv < 6 ? raw[u].z : raw[u].w;
+              nvalid += (((jv & 1) ? wv >> 16 : wv) & 0x7fffu) ? 1u : 0u;
+            }
+            // the two chunks of a record sit in lanes l and l ^ 16, which run this loop in lock step (same kr)
+            float acc = (a0 + a1) + (a2 + a3);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+            if (it + 1 == iters) {
+              // Release the stage BEFORE the last adds go out: the arrive is a release, and a release waits for the
+              // thread's outstanding global reds (an L2 round trip: 690 instead of ~200 cycles of work per stage).
+              // The shared-memory reads of the stage are complete - their values have been used.
+              __syncwarp();
+              if (r == 0) mbar_arrive(&empty_bar[stage]);
+            }
+            const int kg = k_begin + kb * G_BK + kr;
+            if (live && ch == 0 && kg < k_end) atomicAdd(loss.dots + kg, acc);
+          }
 #ifdef OMLDM_GRAM_TIMING
-        t_work += clock64() - t1;
-        if (warp == 2 && r == 0) GRAM_TRACE(4, kb);
+          t_work += clock64() - t1;
+          if (warp == 2 && r == 0) GRAM_TRACE(4, kb);
 #endif
+        }
         stage += 2;
         if (stage >= G_STAGES) { stage -= G_STAGES; phase ^= 1; }
       }
@@ -423,11 +445,11 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       nvalid = __reduce_add_sync(0xffffffffu, nvalid);
       if (r == 0 && nvalid) atomicAdd(loss.words + blockIdx.y, nvalid);
       __threadfence();                              // this warp's adds before the CTA's arrival below
-      named_bar_arrive(2, 288);                     // warp 0 collects the eight loss warps
+      named_bar_arrive(2, 160);                     // warp 0 collects the four loss warps
     }
-    if (loss_on) named_bar_sync(3, 320);            // warps 2..11: the epilogue below reuses the stage memory - not before
+    if (loss_on) named_bar_sync(3, 192);            // warps 2..7: the epilogue below reuses the stage memory - not before
                                                     // the slowest loss warp has read its last stage
-    if (warp >= 4 && warp < 8) {
+    if (warp >= 4) {
     __syncwarp();
     mbar_wait(accum_bar, 0);
     if (warp == 4) GRAM_STAMP(3);
@@ -440,10 +462,10 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
       tmem_ld_wait();
       uint8_t* slot = smem + (q * 8 + c) * 4096;
+      const uint32_t srow = smem_u32(slot) + r * 128;          // shared-space stores (the pointer form compiled to generic ST.E.128)
 #pragma unroll
       for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<float4*>(slot + r * 128 + ((j ^ (r & 7)) << 4)) =
-            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        sts_v4(srow + ((j ^ (r & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       fence_proxy_async();
       __syncwarp();
       if (r == 0) {
@@ -622,13 +644,11 @@ extern "C" int omldm_gram_f16_loss(const void* Z, int ld, int K, int n, float* C
   dim3 grid(2 * tiles, gy);
   const int smem_bytes = G_SMEM + (push.enabled == 2 ? G_LEAD_BYTES : 0);
   if (loss.enabled && gy > 128) return set_error_msg("gram_f16: more than 128 batch slices with the loss inside");
-  // without the loss inside, warps 8..11 have no role: 256 threads, so that two blocks of the separate loss pass still
-  // fit beside a CTA (71 x 256 + 2 x 80 x 256 registers)
   if (loss.enabled)
     gram_f16_kernel<true><<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
                                                                                             k_per_split, T, scratch);
   else
-    gram_f16_kernel<false><<<grid, 256, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
+    gram_f16_kernel<false><<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
                                                                                        k_per_split, T, scratch);
   return check_launch("gram_f16_kernel");
 }
