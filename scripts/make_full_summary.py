@@ -1,7 +1,9 @@
 """Summarise the `ncu --set full` capture of scripts/prof_full.sh: one row per kernel launch of one timed window of
 each bench configuration -> profiles/r2/full_set_rows.csv (selected raw metrics) and full_set_summary.md (one row per
 kernel and configuration with the roofline fractions against MEASURED_PEAKS.json).
-usage: python scripts/make_full_summary.py gpurun_out/prof/full_all_raw.csv"""
+usage: python scripts/make_full_summary.py gpurun_out/prof/full_all_raw.csv
+       python scripts/make_full_summary.py gpurun_out/prof/every_kernel_raw.csv every_kernel
+           (capture of scripts/prof_every_kernel.sh: one row per kernel function at the tests' shapes, no configs)"""
 import csv
 import json
 import os
@@ -46,21 +48,23 @@ def to_us(v, unit):
 
 def main():
     path = sys.argv[1]
+    stem = sys.argv[2] if len(sys.argv) > 2 else "full_set"
+    per_config = stem == "full_set"
     rows = list(csv.reader(open(path)))
     H, U, data = rows[0], rows[1], rows[2:]
     ix = {h: i for i, h in enumerate(H)}
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     hbm = float(peaks["hbm_gbs"])
     names = [short(r[ix["Kernel Name"]]) for r in data]
-    cfgs = [config_of(n) for n in names]
-    for i in range(len(data)):                       # rows without a configuration-specific name
+    cfgs = [config_of(n) if per_config else "-" for n in names]
+    for i in range(len(data) if per_config else 0):  # rows without a configuration-specific name
         if cfgs[i] is None:
             order = list(range(i + 1, len(data))) if any(s in names[i] for s in STARTERS) else list(range(i - 1, -1, -1))
             for j in order:
                 if config_of(names[j]):
                     cfgs[i] = config_of(names[j])
                     break
-    out_csv = os.path.join(ROOT, "profiles", "r2", "full_set_rows.csv")
+    out_csv = os.path.join(ROOT, "profiles", "r2", stem + "_rows.csv")
     with open(out_csv, "w", newline="") as f:
         w = csv.writer(f)
         w.writerow(["id", "config", "kernel"] + [c + " [" + U[ix[c]] + "]" for c in COLS if c in ix])
@@ -84,8 +88,17 @@ def main():
                      f"{g('launch__registers_per_thread')} | {dyn:.1f} + {sta:.1f} | {rd / 1e6:.1f} + {wr / 1e6:.1f} | {gbs:.0f} | "
                      f"{gbs / hbm:.2f} | {float(g('sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active') or 0):.1f} | "
                      f"{float(g('sm__throughput.avg.pct_of_peak_sustained_elapsed') or 0):.1f} |")
-    out_md = os.path.join(ROOT, "profiles", "r2", "full_set_summary.md")
+    out_md = os.path.join(ROOT, "profiles", "r2", stem + "_summary.md")
     with open(out_md, "w") as f:
+        if not per_config:
+            f.write("# `ncu --set full` row for every kernel function of the library (tests' shapes), 1 B200\n\n"
+                    "Capture: `scripts/prof_every_kernel.sh` - the GPU tests under `ncu --set full --clock-control none "
+                    "--kernel-name-base demangled --kernel-id ::regex:omldm:2` (second invocation of every kernel whose name "
+                    "contains `omldm::`; protocol kernels run with emulated ranks inside one cooperative launch).  The shapes are "
+                    "small: read registers, shared memory, grid and pipe mix here, and the bench-shape times in "
+                    "`full_set_summary.md`.\n\n" + "\n".join(sorted(lines[2:], key=lambda l: l.split('`')[1]) if False else lines) + "\n")
+            print("\n".join(lines))
+            return
         f.write("# `ncu --set full` rows, one timed window (2 steps) of every bench configuration, 1 B200\n\n"
                 "Capture: `scripts/prof_full.sh` (plain run first, then `ncu --set full --clock-control none "
                 "--profile-from-start off` around the window; kernels run serialised with cold caches under ncu, so "
