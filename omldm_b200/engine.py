@@ -305,7 +305,7 @@ class Engine:
         # ---- steady state: this buffer's step is captured and nothing changed since - replay without re-deriving
         # anything (the host side of a step is what bounds small models: ~25 us per step before this path existed)
         fast = self._fast.get(Z.data_ptr()) if not kw else None
-        if fast is not None and fast[0] == (B, ld, nnz, Z.dtype, self._epoch):
+        if fast is not None and self.use_graphs and fast[0] == (B, ld, nnz, Z.dtype, self._epoch):
             g, launches, tickers = fast[1], fast[2], fast[3]
             if isinstance(g, tuple):
                 self._replay_pipelined(g, Z)

@@ -12,7 +12,7 @@ import torch
 
 ROOT = os.path.join(os.path.dirname(__file__), "..")
 SELECTION = ("linear_minibatch or fused_poly or kmeans or standard_scaler or sparse_mcpa or hoeffding or mcpa_coef or "
-             "sq_residual or nn_glue or holdout_swap or stage_rows")
+             "sq_residual or nn_glue or holdout_swap or stage_rows or f16s_row or holdout_exchange or ridge_chol")
 
 pytestmark = pytest.mark.skipif(torch.cuda.is_available(), reason="the emulator is for machines without a GPU")
 
