@@ -49,9 +49,9 @@ namespace omldm {
 constexpr int G_BK = OMLDM_GRAM_BK;               // records per stage
 constexpr int G_STAGES = OMLDM_GRAM_STAGES;
 #ifndef OMLDM_GRAM_THREADS
-#define OMLDM_GRAM_THREADS 256
+#define OMLDM_GRAM_THREADS 384
 #endif
-constexpr int G_THREADS = OMLDM_GRAM_THREADS;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2, 3, 6, 7 loss (two groups), warps 4..7 epilogue, warp 4 relay, warp 5 lead push
+constexpr int G_THREADS = OMLDM_GRAM_THREADS;                    // warp 0 TMA, warp 1 TMEM + MMA, warps 2, 3, 6..11 loss (four groups, only with the loss inside), warps 4..7 epilogue, warp 4 relay, warp 5 lead push
 constexpr int G_HALF_BYTES = 2 * G_BK * 128;      // 128 columns = 2 chunks of 64 halves x 64 records = 16 KB
 constexpr int G_STAGE_BYTES = 2 * G_HALF_BYTES;   // A side + B side
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -88,14 +88,17 @@ struct GramPush {
 // z_r . w and add them into dots[r] (fp32 red at L2; 2 T partials per record).  The last CTA to finish a batch slice
 // squares and sums that slice's dots into stats[0], counts its valid rows into stats[2] and clears them; the last slice
 // writes the learning-curve sample.  No second pass over the batch, no second kernel.
-// Measured (B200, 32 768 x 1003): correct to 1e-9 relative, but 47.6 us per launch against 35.5 us without the loss, and
-// 53.5 against 47.2 us per engine step - a loss warp needs ~700 cycles of work plus ~650 cycles of barrier hand-over per
-// stage it owns (two groups: 1 024 available), so stages are released late and the main loop takes 51 k instead of 38 k
-// cycles.  The separate loss pass beside the kernel therefore stays the default; this path is `lossInGram: true`.
-// Things that were tried on the way (each measured): the loss on the diagonal tiles' CTAs only (48.8 us, those CTAs
-// then pace the kernel); the remote "stage landed" arrive issued by the MMA thread (the mere presence of that branch in
-// its loop: main loop 58 k cycles) or by one relay thread with a release at cluster scope (~1 000 cycles each); every
-// T-th record per holder (16-way bank conflicts); generic instead of shared-space loads.
+// Measured (B200, 32 768 x 1003): correct to 1e-9 relative; 39.3 us per launch against 34.9 us without the loss, and
+// 48.0 against 46.8 us per engine step - a tie with the separate loss pass beside the kernel, which therefore stays the
+// default; this path is `lossInGram: true`.  What is left of the difference is mostly the slice finish at the very end of
+// the kernel (one warp reads and clears 4 681 dots: ~37 dependent-ish L2 round trips); the six loss warps that have no
+// epilogue role could share it.
+// Things that were tried on the way (each measured): the loss on the diagonal tiles' CTAs only (48.8 us per launch, those
+// CTAs then pace the kernel); two groups of loss warps instead of four (47.6 us: a loss warp needs ~700 cycles of work
+// plus ~650 cycles of barrier hand-over per stage use, so with 1 024 cycles available stages were released late and the
+// main loop took 51 k instead of 38 k cycles); the remote "stage landed" arrive issued by the MMA thread (the mere presence
+// of that branch in its loop: main loop 58 k cycles) or by one relay thread with a release at cluster scope (~1 000 cycles
+// each); every T-th record per holder (16-way bank conflicts); generic instead of shared-space loads.
 struct GramLoss {
   const float* wt;           // [w_0 .. w_{d-1}, b, -1, -1]: residual of a record = z . wt
   float* dots;               // K floats, zero between launches
@@ -200,7 +203,7 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     __syncwarp();
     if (loss_on) {
       // ---------------------------------------------------------- loss: close this batch slice if we are its last CTA half
-      named_bar_sync(2, 160);                      // the four loss warps of this CTA have added their dots
+      named_bar_sync(2, 288);                      // the eight loss warps of this CTA have added their dots
       const uint32_t lane = lane_id();
       unsigned int last = 0;
       if (lane == 0) {
@@ -336,11 +339,12 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
     const int q = warp & 3;                        // TMEM lane quadrant this warp may read
     const uint32_t r = lane_id();
     const int row0 = m0 + q * 32;
-    // four loss warps: warps 2 / 3 (A side / B side) take the even stages, warps 6 / 7 the odd ones - a warp needs most
-    // of two stage periods per stage (~370 cycles of it for the barrier hand-over), the MMAs 512 cycles
+    // eight loss warps in four groups of two (A side / B side): warps 2 / 3, 6 / 7, 8 / 9, 10 / 11; group g takes the stage
+    // uses g, g + 4, ... - a warp needs ~1 350 cycles per stage use (700 of work, 650 of barrier hand-over), the MMAs
+    // 512 cycles, so two groups (1 024 cycles each) paced the pipeline and four (2 048) do not
     const bool loss_warp = warp == 2 || warp == 3 || warp >= 6;
-    const int lgroup = warp >= 6 ? 1 : 0, side = warp & 1;
-    static_assert(G_STAGES % 2 == 0, "the loss groups alternate over the stages");
+    const int lgroup = warp < 4 ? 0 : warp < 8 ? 1 : warp < 10 ? 2 : 3, side = warp & 1;
+    constexpr int LGROUPS = 4;
     if (loss_on && loss_warp) {
       // Side A: the CTA's accumulator-row columns [m0, m0 + 128), this pair is holder tj of that block; side B (off the
       // diagonal only): columns [b0, b0 + 128), holder ti.  Holder h of T takes the h-th T-th of a stage's records.
@@ -359,13 +363,15 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       const bool has_valid = active && cd >= 0 && cd < 128 && (cd >> 6) == ch;
       const int uv = (cd & 63) >> 3, jv = cd & 7;
       unsigned int nvalid = 0;
-      int stage = lgroup;
+      int stage = 0;
       uint32_t phase = 0;
       const uint32_t side_off = static_cast<uint32_t>(side * G_HALF_BYTES + ch * (G_BK * 128));
 #ifdef OMLDM_GRAM_TIMING
       long long t_wait = 0, t_work = 0;
 #endif
-      for (int kb = lgroup; kb < num_kb; kb += 2) {
+      for (int kb = lgroup; kb < num_kb; kb += LGROUPS) {
+        stage = kb % G_STAGES;
+        phase = static_cast<uint32_t>(kb / G_STAGES) & 1u;
 #ifdef OMLDM_GRAM_TIMING
         const long long t0 = clock64();
 #endif
@@ -433,8 +439,6 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
           if (warp == 2 && r == 0) GRAM_TRACE(4, kb);
 #endif
         }
-        stage += 2;
-        if (stage >= G_STAGES) { stage -= G_STAGES; phase ^= 1; }
       }
 #ifdef OMLDM_GRAM_TIMING
       if (warp == 2 && r == 0) {
@@ -445,11 +449,11 @@ gram_f16_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__
       nvalid = __reduce_add_sync(0xffffffffu, nvalid);
       if (r == 0 && nvalid) atomicAdd(loss.words + blockIdx.y, nvalid);
       __threadfence();                              // this warp's adds before the CTA's arrival below
-      named_bar_arrive(2, 160);                     // warp 0 collects the four loss warps
+      named_bar_arrive(2, 288);                     // warp 0 collects the eight loss warps
     }
-    if (loss_on) named_bar_sync(3, 192);            // warps 2..7: the epilogue below reuses the stage memory - not before
+    if (loss_on) named_bar_sync(3, 320);            // warps 2..11: the epilogue below reuses the stage memory - not before
                                                     // the slowest loss warp has read its last stage
-    if (warp >= 4) {
+    if (warp >= 4 && warp < 8) {
     __syncwarp();
     mbar_wait(accum_bar, 0);
     if (warp == 4) GRAM_STAMP(3);
@@ -648,7 +652,8 @@ extern "C" int omldm_gram_f16_loss(const void* Z, int ld, int K, int n, float* C
     gram_f16_kernel<true><<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
                                                                                             k_per_split, T, scratch);
   else
-    gram_f16_kernel<false><<<grid, G_THREADS, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
+    // (warps 8..11 exist only with the loss inside: 256 threads keep two blocks of the separate loss pass beside a CTA)
+    gram_f16_kernel<false><<<grid, 256, smem_bytes, static_cast<cudaStream_t>(stream)>>>(tmZ, tmC, push, loss, n, K,
                                                                                        k_per_split, T, scratch);
   return check_launch("gram_f16_kernel");
 }
