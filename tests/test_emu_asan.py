@@ -36,7 +36,10 @@ def _env(kind):
         env.update(OMLDM_EMU_ASAN="1", ASAN_OPTIONS="detect_leaks=0:halt_on_error=1",
                    UBSAN_OPTIONS="print_stacktrace=1:halt_on_error=1")
     else:
-        env.update(OMLDM_EMU_TSAN="1", TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=66")
+        # libtorch's own CPU ops run on libgomp threads, which TSan cannot see into (it reports their TensorIterator
+        # bookkeeping as races); one OpenMP thread keeps the reports to the code under test: the emulated kernels
+        env.update(OMLDM_EMU_TSAN="1", TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=66",
+                   OMP_NUM_THREADS="1", MKL_NUM_THREADS="1")
     return env
 
 
