@@ -331,17 +331,20 @@ def main() -> None:
                     src, dst = topic.storage[0], torch.empty_like(topic.storage[0], device=dev)
                     dst.copy_(src, non_blocking=True)
                     sync_all()
-                    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    n_cp = max(10, int(1.5e9 // topic.slot_bytes))       # ~1.5 GB: long enough to measure bandwidth
-                    c0.record()
-                    for _ in range(n_cp):
-                        dst.copy_(src, non_blocking=True)
-                    c1.record()
-                    dev_sync()
-                    cms = torch.tensor([c0.elapsed_time(c1)], device=dev)
-                    if world > 1:
-                        dist.all_reduce(cms, op=dist.ReduceOp.MAX)
-                    ceiling = n_cp * topic.slot_bytes / (float(cms.item()) / 1e3) / 1e9
+                    n_cp = max(10, int(1.0e9 // topic.slot_bytes))       # ~1 GB per pass: long enough to measure bandwidth
+                    ceiling = 0.0
+                    for _ in range(3):                                   # best of three passes: it is meant to be a ceiling
+                        sync_all()
+                        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        c0.record()
+                        for _ in range(n_cp):
+                            dst.copy_(src, non_blocking=True)
+                        c1.record()
+                        dev_sync()
+                        cms = torch.tensor([c0.elapsed_time(c1)], device=dev)
+                        if world > 1:
+                            dist.all_reduce(cms, op=dist.ReduceOp.MAX)
+                        ceiling = max(ceiling, n_cp * topic.slot_bytes / (float(cms.item()) / 1e3) / 1e9)
                     del dst
                 e_windows = []
                 for _ in range(1 if dry else 5):
@@ -365,7 +368,7 @@ def main() -> None:
                               "h2d_ceiling_gbs_per_gpu": ceiling,
                               "fraction_of_h2d_ceiling": (h2d * args.steps / e_med / 1e9 / ceiling) if ceiling else None,
                               "h2d_ceiling_note": "pinned -> device cudaMemcpyAsync of one slot, all ranks copying at "
-                                                  "once, nothing else running (max over ranks)",
+                                                  "once, nothing else running (max over ranks, best of 3 passes)",
                               "last_loss_sum": float(loss_host[0])}
                 topic.stop()
             except Exception as ex:      # the device-timed line above stays valid; report why e2e is missing
