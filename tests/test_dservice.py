@@ -7,6 +7,7 @@ import os
 import socket
 
 import numpy as np
+import pytest
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
@@ -29,14 +30,19 @@ def _records(n, d, seed):
     return out
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, gpu=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    if gpu:       # one process per GPU, NCCL for the plumbing, the fused peer-memory protocol kernels for the steps
+        import torch
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
     from omldm_b200.dservice import DistributedService
     from omldm_b200.utils.config import JobParameters
     d = 8
     svc = DistributedService(JobParameters(parallelism=world, timeout=250, jobName="dsvc", testSetSize=16), rank, world,
-                             "cpu", batch=128, impl="nccl")
+                             f"cuda:{rank}" if gpu else "cpu", batch=128, impl="fused" if gpu else "nccl")
     log = {}
     # ---- records before any Create: buffered by the engine, nothing is trained
     svc.topic("trainingData").put_many(_records(300, d, 10 + rank))
@@ -85,10 +91,23 @@ def _worker(rank, world, port, q):
 
 
 def test_requests_in_mid_stream_on_two_ranks():
+    _run_two_ranks(gpu=False)
+
+
+@pytest.mark.gpu
+def test_requests_in_mid_stream_on_two_gpus():
+    """The same scenario with one process per GPU: NCCL bootstrap, fused protocol kernels over peer memory."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    _run_two_ranks(gpu=True)
+
+
+def _run_two_ranks(gpu):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, gpu)) for r in range(2)]
     for p in procs:
         p.start()
     res = dict(q.get(timeout=180) for _ in procs)
