@@ -138,6 +138,8 @@ def main() -> None:
     args = ap.parse_args()
 
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:        # under torchrun only rank 0 prints the line
+            return
         print(json.dumps({"impl": "reference", "unavailable":
                           "reference is a Scala/Flink/Kafka Maven job with 3 out-of-tree SNAPSHOT dependencies; "
                           "no JVM/Maven/Kafka in this image and it is not pip-installable (no setup.py/pyproject)"}))
