@@ -23,6 +23,8 @@ def _run(args, nproc=1):
     assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
     lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1, p.stdout[-2000:]            # ONE json line, from rank 0
+    if nproc == 1:       # and nothing else on stdout: whatever libraries print goes to stderr (torchrun adds its own banner)
+        assert p.stdout.strip() == lines[0], p.stdout[-2000:]
     return json.loads(lines[0])
 
 
@@ -54,6 +56,10 @@ def test_bench_reference_arm_and_two_ranks():
                        capture_output=True, text=True, cwd=ROOT, timeout=120)
     ref = json.loads(p.stdout.strip().splitlines()[-1])
     assert p.returncode == 0 and ref["impl"] == "reference" and "unavailable" in ref
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29573", os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                        "--gpus", "2"], capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert p.returncode == 0 and len([l for l in p.stdout.splitlines() if l.startswith("{")]) == 1      # rank 0 only
     out = _run(["--config", "orr", "--batch", "64", "--no-e2e"], nproc=2)       # gloo, world 2: one line, aggregate value
     assert out["n_gpus"] == 2 and out["config"]["global_batch"] == 128 and out["e2e"] is None
     out = _run(["--config", "orr", "--batch", "64", "--no-e2e", "--tc", "syncFusion=scatter"], nproc=2)
